@@ -1,0 +1,168 @@
+/* spydrpick_b200.h -- C-ABI of the B200-native SpydrPick hot path.
+ *
+ * The reference (santeripuranen/SpydrPick @ f6bc110) has no plugin / FFI boundary; the
+ * accelerated path sits behind four C++ template entry points called only from main():
+ *
+ *   apegrunt::cache_sample_weights()    externals/apegrunt/include/apegrunt/Alignment_utility.hpp:186
+ *     -> apegrunt::calculate_weights()  externals/apegrunt/include/apegrunt/Alignment_StateVector_weights.hpp:192
+ *   spydrpick::determine_MI_threshold() include/SpydrPick.hpp:285
+ *   spydrpick::get_MI_network()         include/SpydrPick.hpp:132
+ *   aracne::run_ARACNE()                include/ARACNE.hpp:550
+ *
+ * Each function below names the reference interface it replaces. Conventions:
+ *   - plain pointers and sizes only; no C++ / torch types; no exceptions; no exit().
+ *   - return 0 (SPK_OK) or a negative SPK_E_* code; message via spk_last_error().
+ *   - states are the reference's codes a=0,t=1,c=2,g=3,GAP=4
+ *     (externals/apegrunt/src/StateVector_state_types.cpp:33-44), dense row-major [n][L].
+ *   - one host thread drives a context; calls are blocking unless stated; not re-entrant.
+ *   - there is NO CPU fallback: every entry point fails with SPK_E_CUDA when no sm_100 device
+ *     is usable.
+ */
+#ifndef SPYDRPICK_B200_H
+#define SPYDRPICK_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SPK_OK            0
+#define SPK_E_INVALID    -1   /* bad argument / call order */
+#define SPK_E_CUDA       -2   /* CUDA runtime / driver error, or no usable device */
+#define SPK_E_NOMEM      -3   /* device or host allocation failed */
+#define SPK_E_OVERFLOW   -4   /* candidate / edge buffer too small (raise max_edges) */
+#define SPK_E_PRECISION  -5   /* fp32 filter error exceeded the safety band (raise n_terms / band) */
+
+typedef struct spk_ctx spk_ctx;
+
+/* Edge record == apegrunt::Edge (externals/apegrunt/include/graph/Graph.hpp:113-147):
+ * i < j are filtered-column indices, mi the weight. 16 bytes. */
+typedef struct { uint32_t i, j; double mi; } spk_edge;
+
+/* ---- context ------------------------------------------------------------------------ */
+/* device < 0: use the current CUDA device. */
+int         spk_create(spk_ctx** out, int device, int verbose);
+void        spk_destroy(spk_ctx* ctx);
+const char* spk_last_error(const spk_ctx* ctx);     /* ctx may be NULL: last create error */
+/* Run all work of this context on an externally owned cudaStream_t (e.g. torch's current
+ * stream). NULL restores the context's own stream. */
+int         spk_set_stream(spk_ctx* ctx, void* cuda_stream);
+
+/* ---- alignment upload ---------------------------------------------------------------- */
+/* Replaces the reference's in-memory Alignment as seen by the hot path
+ * (apegrunt/Alignment_interface.hpp:62-207): dense states + loci translation pos[L]
+ * (original positions, apegrunt/Distance.hpp:63-83). Copies to the device and builds the
+ * packed forms (bit planes, column-major bytes, state-presence masks =
+ * apegrunt/Alignment_impl_block_compressed_storage.hpp:1089-1128). pos may be NULL (= 0..L-1).
+ * Weights are reset to 1 (StateVector default weight). */
+int spk_set_alignment(spk_ctx* ctx, const uint8_t* states, uint32_t n, uint32_t L, const uint64_t* pos);
+
+/* ---- K1: sample reweighting ----------------------------------------------------------- */
+/* Replaces apegrunt::calculate_weights (Alignment_StateVector_weights.hpp:192-353) up to the
+ * integer neighbour counts: counts[i] = 1 + #{j != i : similar(i,j)} with
+ * similar = ident(i,j) >= min_identical, min_identical = (size_t)(threshold*(double)L) computed
+ * by the caller as the reference does (:228,251). emulate_lastblock_quirk != 0 reproduces
+ * is_similar_to_impl's double count of the final 32-column block when L % 32 == 0
+ * (StateVector_impl_block_compressed_alignment_storage.hpp:628-659). */
+int spk_neighbour_counts(spk_ctx* ctx, uint64_t min_identical, int emulate_lastblock_quirk,
+                         uint64_t* counts /* [n] host */);
+
+/* Replaces the per-sequence set_weight() done by cache_sample_weights
+ * (Alignment_utility.hpp:186-258) / MI_Parameters' weight snapshot (include/mi_parameters.hpp:53-59). */
+int spk_set_weights(spk_ctx* ctx, const double* w /* [n] host */);
+
+/* ---- K2b: MI for an explicit pair list ------------------------------------------------ */
+/* Replaces MI_solver::single over sampled pairs (include/mi.hpp:183-224,367-372;
+ * include/SpydrPick.hpp:210-255). fp64, the reference's exact formula. */
+int spk_mi_pairs(spk_ctx* ctx, const uint32_t* pi, const uint32_t* pj, uint64_t npairs,
+                 double pseudocount, double* mi /* [npairs] host */);
+
+/* Replaces spydrpick::determine_MI_threshold (include/SpydrPick.hpp:285-343). The reference
+ * seeds std::mt19937 from the clock (:178); here the seed is explicit (seed+iteration). */
+int spk_determine_mi_threshold(spk_ctx* ctx, uint64_t n_values, uint64_t threshold_pairs /*0=auto*/,
+                               uint32_t iterations, double pseudocount, uint64_t seed, double* threshold);
+
+/* ---- K2: all-pairs scan --------------------------------------------------------------- */
+typedef struct {
+    double   threshold;        /* strict: edge saved iff threshold < mi          (include/mi.hpp:430,454) */
+    double   pseudocount;      /* --mi-pseudocount, default 0.5                  (src/SpydrPick_options.cpp:41) */
+    uint64_t ld_threshold;     /* --ld-threshold; colmax uses distance > this    (include/mi.hpp:423,447) */
+    int32_t  linear_genome;    /* 0 = circular (default), 1 = linear             (include/mi.hpp:313-320) */
+    uint64_t circle_size;      /* 0 = L (the reference's choice, apegrunt/Distance.hpp:67-71) */
+    uint64_t max_edges;        /* capacity hint for saved edges; 0 = 2*min(1e7,100*L)+slack */
+    int32_t  sort_desc;        /* 1: edges sorted (weight desc, id asc) = Graph::sort (graph/Graph.hpp:234-242) */
+    int32_t  n_terms;          /* bf16 terms of the weight split in the tensor-core filter: 1..3, 0 = default */
+    double   band;             /* filter safety band delta (candidates: mi32 > threshold - band); 0 = default */
+    int32_t  engine;           /* 0 = tcgen05 filter + fp64 refine (product path); 1 = fp64 exhaustive (diagnostic) */
+    uint32_t part_index;       /* tile-space partition for multi-GPU: this context scans part_index of n_parts */
+    uint32_t n_parts;          /* 0 or 1 = whole upper triangle */
+    int32_t  keep_on_device;   /* 1: do not copy edges to the host (device pointers below stay valid) */
+} spk_scan_params;
+
+typedef struct {
+    const spk_edge* edges;         uint64_t n_edges;     /* host (NULL if keep_on_device) */
+    const spk_edge* edges_wo_gaps; uint64_t n_wo_gaps;   /* MI without gaps for saved edges touching a gap column
+                                                            (include/mi.hpp:465-489, literal semantics) */
+    const double*   colmax;                              /* [L] per-column max MI (include/mi.hpp:245-290), host */
+    const void*     d_edges;                             /* device copies (spk_edge[], spk_edge[], double[L]) */
+    const void*     d_edges_wo_gaps;
+    const void*     d_colmax;
+    uint64_t n_candidates;       /* pairs refined in fp64 */
+    double   max_filter_error;   /* max |mi_fp32 - mi_fp64| over the candidates */
+} spk_scan_result;
+
+/* Replaces spydrpick::get_MI_network up to (not including) the quartile step
+ * (include/SpydrPick.hpp:132-168; MI_solver::operator() include/mi.hpp:377-508).
+ * Result memory is owned by the context and valid until the next scan / destroy. */
+int spk_mi_scan(spk_ctx* ctx, const spk_scan_params* params, spk_scan_result* result);
+
+/* Tukey fences from per-column maxima: maxvaltracker::quartile + get_MI_network
+ * (include/mi.hpp:267-281, include/SpydrPick.hpp:148-152). Host arithmetic. */
+int spk_outlier_thresholds(const double* colmax, uint64_t L, double* outlier, double* extreme);
+
+/* ---- sort + K3: ARACNE ----------------------------------------------------------------- */
+/* Graph::sort (graph/Graph.hpp:234-242): weight desc, then id = (node2<<32)|node1 asc. In place, host array. */
+int spk_sort_edges(spk_ctx* ctx, spk_edge* edges, uint64_t n_edges);
+
+/* Replaces aracne::run_ARACNE (include/ARACNE.hpp:411-550). edges must be sorted as above.
+ * direct_flags[e] = 1 for DIRECT edges (the reference's bool(edge), the ARACNE output column),
+ * 0 for edges with a triangle in which they are the weakest and mid-min >= edge_threshold.
+ * Edges [part_index*E/n_parts, (part_index+1)*E/n_parts) are evaluated (others left untouched);
+ * n_parts <= 1 evaluates all. */
+int spk_aracne(spk_ctx* ctx, const spk_edge* edges, uint64_t n_edges, double edge_threshold,
+               uint32_t part_index, uint32_t n_parts, uint8_t* direct_flags /* [n_edges] host */);
+
+/* Device-resident variants for callers that keep data in HBM (bench, multi-GPU plumbing):
+ * d_edges is a device pointer to n_edges sorted spk_edge records, d_flags device uint8[n_edges]. */
+int spk_sort_edges_device(spk_ctx* ctx, void* d_edges, uint64_t n_edges);
+int spk_aracne_device(spk_ctx* ctx, const void* d_edges, uint64_t n_edges, double edge_threshold,
+                      uint32_t part_index, uint32_t n_parts, void* d_flags);
+
+/* ---- instrumentation -------------------------------------------------------------------- */
+/* Device time (CUDA events on the context's stream) of the stages of the most recent calls, ms. */
+typedef struct {
+    float upload_ms, prep_ms;               /* spk_set_alignment: H2D copy, packing kernels */
+    float hamming_ms;                       /* K1 kernel */
+    float expand_ms, stats_ms;              /* operand expansion, column statistics */
+    float gemm_ms;                          /* K2 tcgen05 filter kernel */
+    float refine_ms;                        /* K2r/K2c fp64 refine kernel */
+    float compact_ms, sort_ms;              /* threshold/colmax compaction, edge sort */
+    float aracne_build_ms, aracne_ms;       /* CSR build, K3 kernel */
+    float pairs_ms;                         /* K2b kernel */
+    uint64_t gemm_tiles, kernel_launches;   /* tiles processed by the last scan; kernels launched since create */
+} spk_timings;
+int spk_get_timings(spk_ctx* ctx, spk_timings* out);
+
+/* Debug/validation hook: raw fp32 joint counts of one 32x64 column tile as produced by the
+ * tcgen05 mainloop (counts[32][64][4][4], index [i][j][a][b]); used by the parity tests to
+ * localise descriptor / layout faults. */
+int spk_debug_tile_counts(spk_ctx* ctx, uint32_t iblock32, uint32_t jblock64, int32_t n_terms, float* counts);
+
+const char* spk_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPYDRPICK_B200_H */

@@ -1,0 +1,212 @@
+"""ctypes binding of include/spydrpick_b200.h (the C-ABI a reference maintainer would bind).
+
+Fails loudly when the CUDA library is missing: there is no CPU fallback in the product path.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libspydrpick_b200.so")
+
+EDGE_DTYPE = np.dtype([("i", np.uint32), ("j", np.uint32), ("mi", np.float64)], align=True)
+assert EDGE_DTYPE.itemsize == 16
+
+SPK_OK, SPK_E_INVALID, SPK_E_CUDA, SPK_E_NOMEM, SPK_E_OVERFLOW, SPK_E_PRECISION = 0, -1, -2, -3, -4, -5
+
+EXPORTS = ["spk_create", "spk_destroy", "spk_last_error", "spk_set_stream", "spk_set_alignment",
+           "spk_neighbour_counts", "spk_set_weights", "spk_mi_pairs", "spk_determine_mi_threshold",
+           "spk_mi_scan", "spk_outlier_thresholds", "spk_sort_edges", "spk_aracne", "spk_sort_edges_device",
+           "spk_aracne_device", "spk_get_timings", "spk_debug_tile_counts", "spk_version"]
+
+
+class ScanParams(C.Structure):
+    _fields_ = [("threshold", C.c_double), ("pseudocount", C.c_double), ("ld_threshold", C.c_uint64),
+                ("linear_genome", C.c_int32), ("circle_size", C.c_uint64), ("max_edges", C.c_uint64),
+                ("sort_desc", C.c_int32), ("n_terms", C.c_int32), ("band", C.c_double), ("engine", C.c_int32),
+                ("part_index", C.c_uint32), ("n_parts", C.c_uint32), ("keep_on_device", C.c_int32)]
+
+
+class ScanResult(C.Structure):
+    _fields_ = [("edges", C.c_void_p), ("n_edges", C.c_uint64), ("edges_wo_gaps", C.c_void_p), ("n_wo_gaps", C.c_uint64),
+                ("colmax", C.POINTER(C.c_double)), ("d_edges", C.c_void_p), ("d_edges_wo_gaps", C.c_void_p),
+                ("d_colmax", C.c_void_p), ("n_candidates", C.c_uint64), ("max_filter_error", C.c_double)]
+
+
+class Timings(C.Structure):
+    _fields_ = [(k, C.c_float) for k in ("upload_ms", "prep_ms", "hamming_ms", "expand_ms", "stats_ms", "gemm_ms",
+                                        "refine_ms", "compact_ms", "sort_ms", "aracne_build_ms", "aracne_ms", "pairs_ms")] + \
+               [("gemm_tiles", C.c_uint64), ("kernel_launches", C.c_uint64)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+class SpkError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("spydrpick_b200 error %d: %s" % (code, msg))
+        self.code = code
+
+
+_lib = None
+
+
+def load():
+    """Loads the CUDA library; raises (never falls back) when it is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError("spydrpick_b200: %s not built (run `python -m spydrpick_b200.build`); "
+                          "there is no CPU fallback" % LIB_PATH)
+    L = C.CDLL(LIB_PATH)
+    L.spk_last_error.restype = C.c_char_p
+    L.spk_last_error.argtypes = [C.c_void_p]
+    L.spk_version.restype = C.c_char_p
+    L.spk_destroy.restype = None
+    L.spk_destroy.argtypes = [C.c_void_p]
+    L.spk_create.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int]
+    L.spk_set_stream.argtypes = [C.c_void_p, C.c_void_p]
+    L.spk_set_alignment.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p]
+    L.spk_neighbour_counts.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_void_p]
+    L.spk_set_weights.argtypes = [C.c_void_p, C.c_void_p]
+    L.spk_mi_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_double, C.c_void_p]
+    L.spk_determine_mi_threshold.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_double, C.c_uint64,
+                                             C.POINTER(C.c_double)]
+    L.spk_mi_scan.argtypes = [C.c_void_p, C.POINTER(ScanParams), C.POINTER(ScanResult)]
+    L.spk_outlier_thresholds.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    L.spk_sort_edges.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
+    L.spk_aracne.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_double, C.c_uint32, C.c_uint32, C.c_void_p]
+    L.spk_sort_edges_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
+    L.spk_aracne_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_double, C.c_uint32, C.c_uint32, C.c_void_p]
+    L.spk_get_timings.argtypes = [C.c_void_p, C.POINTER(Timings)]
+    L.spk_debug_tile_counts.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_int32, C.c_void_p]
+    _lib = L
+    return L
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class Context:
+    """Thin RAII wrapper over spk_ctx."""
+
+    def __init__(self, device=-1, verbose=False):
+        self.lib = load()
+        h = C.c_void_p()
+        rc = self.lib.spk_create(C.byref(h), device, int(verbose))
+        if rc != SPK_OK:
+            raise SpkError(rc, (self.lib.spk_last_error(None) or b"").decode())
+        self.h = h
+        self.n = self.L = 0
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.spk_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _check(self, rc):
+        if rc != SPK_OK:
+            raise SpkError(rc, (self.lib.spk_last_error(self.h) or b"").decode())
+
+    def set_stream(self, cuda_stream_handle):
+        self._check(self.lib.spk_set_stream(self.h, C.c_void_p(cuda_stream_handle)))
+
+    def set_alignment(self, states, pos=None):
+        s = np.ascontiguousarray(states, dtype=np.uint8)
+        assert s.ndim == 2
+        p = None if pos is None else np.ascontiguousarray(pos, dtype=np.uint64)
+        self._check(self.lib.spk_set_alignment(self.h, _ptr(s), s.shape[0], s.shape[1], _ptr(p)))
+        self.n, self.L = s.shape
+
+    def neighbour_counts(self, min_identical, lastblock_quirk=True):
+        out = np.zeros(self.n, dtype=np.uint64)
+        self._check(self.lib.spk_neighbour_counts(self.h, int(min_identical), int(lastblock_quirk), _ptr(out)))
+        return out
+
+    def set_weights(self, w):
+        w = np.ascontiguousarray(w, dtype=np.float64)
+        assert w.shape == (self.n,)
+        self._check(self.lib.spk_set_weights(self.h, _ptr(w)))
+
+    def mi_pairs(self, pi, pj, pseudocount=0.5):
+        pi = np.ascontiguousarray(pi, dtype=np.uint32); pj = np.ascontiguousarray(pj, dtype=np.uint32)
+        out = np.zeros(pi.shape[0], dtype=np.float64)
+        self._check(self.lib.spk_mi_pairs(self.h, _ptr(pi), _ptr(pj), pi.shape[0], pseudocount, _ptr(out)))
+        return out
+
+    def determine_mi_threshold(self, n_values, threshold_pairs=0, iterations=10, pseudocount=0.5, seed=1):
+        thr = C.c_double()
+        self._check(self.lib.spk_determine_mi_threshold(self.h, int(n_values), int(threshold_pairs), int(iterations),
+                                                        pseudocount, int(seed), C.byref(thr)))
+        return float(thr.value)
+
+    def mi_scan(self, threshold, pseudocount=0.5, ld_threshold=0, linear_genome=False, circle_size=0, max_edges=0,
+                sort_desc=True, n_terms=0, band=0.0, engine=0, part_index=0, n_parts=1, keep_on_device=False):
+        p = ScanParams(threshold, pseudocount, ld_threshold, int(linear_genome), circle_size, max_edges, int(sort_desc),
+                       n_terms, band, engine, part_index, n_parts, int(keep_on_device))
+        r = ScanResult()
+        self._check(self.lib.spk_mi_scan(self.h, C.byref(p), C.byref(r)))
+
+        def grab(ptr, cnt):
+            if cnt == 0 or not ptr:
+                return np.zeros(0, dtype=EDGE_DTYPE)
+            buf = (C.c_char * (cnt * 16)).from_address(ptr)
+            return np.frombuffer(buf, dtype=EDGE_DTYPE).copy()
+
+        out = {"n_edges": int(r.n_edges), "n_wo_gaps": int(r.n_wo_gaps), "n_candidates": int(r.n_candidates),
+               "max_filter_error": float(r.max_filter_error),
+               "colmax": np.ctypeslib.as_array(r.colmax, shape=(self.L,)).copy(),
+               "d_edges": r.d_edges, "d_edges_wo_gaps": r.d_edges_wo_gaps, "d_colmax": r.d_colmax}
+        if not keep_on_device:
+            out["edges"] = grab(r.edges, r.n_edges)
+            out["edges_wo_gaps"] = grab(r.edges_wo_gaps, r.n_wo_gaps)
+        return out
+
+    def outlier_thresholds(self, colmax):
+        c = np.ascontiguousarray(colmax, dtype=np.float64)
+        a = C.c_double(); b = C.c_double()
+        self._check(self.lib.spk_outlier_thresholds(_ptr(c), c.shape[0], C.byref(a), C.byref(b)))
+        return float(a.value), float(b.value)
+
+    def sort_edges(self, edges):
+        e = np.ascontiguousarray(edges, dtype=EDGE_DTYPE).copy()
+        self._check(self.lib.spk_sort_edges(self.h, _ptr(e), e.shape[0]))
+        return e
+
+    def aracne(self, edges, edge_threshold=2.220446049250313e-16, part_index=0, n_parts=1):
+        e = np.ascontiguousarray(edges, dtype=EDGE_DTYPE)
+        f = np.zeros(e.shape[0], dtype=np.uint8)
+        self._check(self.lib.spk_aracne(self.h, _ptr(e), e.shape[0], edge_threshold, part_index, n_parts, _ptr(f)))
+        return f
+
+    def sort_edges_device(self, d_edges, n):
+        self._check(self.lib.spk_sort_edges_device(self.h, C.c_void_p(d_edges), n))
+
+    def aracne_device(self, d_edges, n, d_flags, edge_threshold=2.220446049250313e-16, part_index=0, n_parts=1):
+        self._check(self.lib.spk_aracne_device(self.h, C.c_void_p(d_edges), n, edge_threshold, part_index, n_parts,
+                                               C.c_void_p(d_flags)))
+
+    def timings(self):
+        t = Timings()
+        self._check(self.lib.spk_get_timings(self.h, C.byref(t)))
+        return t.as_dict()
+
+    def debug_tile_counts(self, ib, jb, n_terms=2):
+        out = np.zeros((32, 64, 4, 4), dtype=np.float32)
+        self._check(self.lib.spk_debug_tile_counts(self.h, ib, jb, n_terms, _ptr(out)))
+        return out

@@ -1,0 +1,425 @@
+// spk_cabi.cu -- the C-ABI (include/spydrpick_b200.h): context, buffers, stage orchestration.
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
+#include <cstdarg>
+#include <cstring>
+#include <random>
+#include <unordered_set>
+#include "spk_internal.h"
+
+namespace spk {
+
+static thread_local std::string g_create_error;
+
+int fail(Ctx* c, int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
+    if (c) c->err = buf; else g_create_error = buf;
+    if (c && c->verbose) fprintf(stderr, "spydrpick_b200: error %d: %s\n", code, buf);
+    return code;
+}
+int cuda_check(Ctx* c, cudaError_t e, const char* what) {
+    if (e == cudaSuccess) return SPK_OK;
+    return fail(c, SPK_E_CUDA, "%s: %s", what, cudaGetErrorString(e));
+}
+void* scratch(Ctx* c, size_t bytes) {
+    if (bytes <= c->scratch_bytes) return c->d_scratch;
+    cudaStreamSynchronize(c->stream);
+    if (c->d_scratch) cudaFree(c->d_scratch);
+    c->d_scratch = nullptr; c->scratch_bytes = 0;
+    const size_t want = bytes + bytes / 8;
+    if (cudaMalloc(&c->d_scratch, want) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    c->scratch_bytes = want;
+    return c->d_scratch;
+}
+
+template <class P> static void free_dev(P*& p) { if (p) { cudaFree(p); p = nullptr; } }
+
+static void free_alignment(Ctx* c) {
+    free_dev(c->d_states); free_dev(c->d_colmajor); free_dev(c->d_planes); free_dev(c->d_pos); free_dev(c->d_masks);
+    free_dev(c->d_w); free_dev(c->d_marg); free_dev(c->d_colstat); free_dev(c->d_U); free_dev(c->d_V);
+    free_dev(c->d_colmax); free_dev(c->d_colmax32); free_dev(c->d_counts);
+    c->operands_terms = 0; c->operands_cap_terms = 0; c->stats_valid = false;
+}
+static void free_scan(Ctx* c) {
+    free_dev(c->d_cand); free_dev(c->d_edges); free_dev(c->d_wo); free_dev(c->d_refined); free_dev(c->d_refined_wo);
+    c->cand_cap = c->edges_cap = c->wo_cap = c->refined_cap = 0;
+}
+
+template <class P> static int dev_alloc(Ctx* c, P*& p, size_t bytes, const char* what) {
+    free_dev(p);
+    if (cudaMalloc(&p, bytes ? bytes : 16) != cudaSuccess) { cudaGetLastError(); return fail(c, SPK_E_NOMEM, "device allocation failed: %s (%zu bytes)", what, bytes); }
+    return SPK_OK;
+}
+
+__global__ void ordered_to_double_kernel(unsigned long long* v, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { const double d = f64_from_ordered(v[i]); v[i] = (unsigned long long)__double_as_longlong(d); }
+}
+__global__ void fill_u64_kernel(unsigned long long* p, unsigned long long v, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
+}
+
+} // namespace spk
+
+using namespace spk;
+struct spk_ctx : public spk::Ctx {};
+
+extern "C" {
+
+const char* spk_version(void) { return "spydrpick_b200 0.1 (sm_100a)"; }
+
+int spk_create(spk_ctx** out, int device, int verbose) {
+    if (!out) return SPK_E_INVALID;
+    *out = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(nullptr, SPK_E_CUDA, "no CUDA device available (this library has no CPU fallback)");
+    }
+    if (device < 0) { if (cudaGetDevice(&device) != cudaSuccess) return fail(nullptr, SPK_E_CUDA, "cudaGetDevice failed"); }
+    if (device >= ndev) return fail(nullptr, SPK_E_INVALID, "device %d out of range (%d devices)", device, ndev);
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return fail(nullptr, SPK_E_CUDA, "cudaGetDeviceProperties failed");
+    if (prop.major != 10) return fail(nullptr, SPK_E_CUDA, "device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
+    spk_ctx* c = new spk_ctx();
+    c->device = device; c->verbose = verbose; c->sm_count = prop.multiProcessorCount;
+    if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess) {
+        delete c; return fail(nullptr, SPK_E_CUDA, "cannot create stream on device %d", device);
+    }
+    c->stream = c->own_stream;
+    for (auto& e : c->ev) cudaEventCreate(&e);
+    if (cudaMalloc(&c->d_counters, 8 * sizeof(unsigned long long)) != cudaSuccess || cudaMalloc(&c->d_tilemap, 1 << 20) != cudaSuccess) {
+        delete c; return fail(nullptr, SPK_E_NOMEM, "context allocation failed");
+    }
+    *out = c;
+    return SPK_OK;
+}
+
+void spk_destroy(spk_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    free_alignment(c); free_scan(c);
+    free_dev(c->d_scratch); free_dev(c->d_counters);
+    if (c->d_tilemap) { cudaFree(c->d_tilemap); c->d_tilemap = nullptr; }
+    for (auto& e : c->ev) if (e) cudaEventDestroy(e);
+    if (c->own_stream) cudaStreamDestroy(c->own_stream);
+    delete c;
+}
+
+const char* spk_last_error(const spk_ctx* c) { return c ? c->err.c_str() : g_create_error.c_str(); }
+
+int spk_set_stream(spk_ctx* c, void* s) {
+    if (!c) return SPK_E_INVALID;
+    cudaStreamSynchronize(c->stream);
+    c->stream = s ? (cudaStream_t)s : c->own_stream;
+    return SPK_OK;
+}
+
+int spk_set_alignment(spk_ctx* c, const uint8_t* states, uint32_t n, uint32_t L, const uint64_t* pos) {
+    if (!c || !states || n == 0 || L < 2) return c ? fail(c, SPK_E_INVALID, "set_alignment: need states, n >= 1, L >= 2") : SPK_E_INVALID;
+    if (L >= (1u << 29)) return fail(c, SPK_E_INVALID, "L too large");
+    SPK_CUDA(c, cudaSetDevice(c->device));
+    const bool same_shape = (c->n == n && c->L == L && c->d_states);
+    if (!same_shape) {
+        free_alignment(c);
+        c->n = n; c->L = L;
+        c->n_pad = (n + BLOCK_K - 1) / BLOCK_K * BLOCK_K;
+        c->L_pad = (L + TILE_J - 1) / TILE_J * TILE_J;
+        c->W32 = (L + 31) / 32;
+        int r;
+        if ((r = dev_alloc(c, c->d_states, (size_t)n * L, "states"))) return r;
+        if ((r = dev_alloc(c, c->d_colmajor, (size_t)c->L_pad * c->n_pad, "colmajor"))) return r;
+        if ((r = dev_alloc(c, c->d_planes, (size_t)3 * n * c->W32 * 4, "planes"))) return r;
+        if ((r = dev_alloc(c, c->d_pos, (size_t)c->L_pad * 8, "pos"))) return r;
+        if ((r = dev_alloc(c, c->d_masks, (size_t)c->L_pad, "masks"))) return r;
+        if ((r = dev_alloc(c, c->d_w, (size_t)c->n_pad * 8, "weights"))) return r;
+        if ((r = dev_alloc(c, c->d_marg, (size_t)c->L_pad * 5 * 8, "marginals"))) return r;
+        if ((r = dev_alloc(c, c->d_colstat, (size_t)c->L_pad * sizeof(ColStat), "colstat"))) return r;
+        if ((r = dev_alloc(c, c->d_colmax, (size_t)c->L_pad * 8, "colmax"))) return r;
+        if ((r = dev_alloc(c, c->d_colmax32, (size_t)c->L_pad * 4, "colmax32"))) return r;
+        if ((r = dev_alloc(c, c->d_counts, (size_t)n * 8, "counts"))) return r;
+    }
+    c->operands_terms = 0; c->stats_valid = false;
+    SPK_CUDA(c, cudaEventRecord(c->ev[0], c->stream));
+    SPK_CUDA(c, cudaMemcpyAsync(c->d_states, states, (size_t)n * L, cudaMemcpyHostToDevice, c->stream));
+    std::vector<uint64_t> hp(c->L_pad, 0);
+    for (uint32_t k = 0; k < L; ++k) hp[k] = pos ? pos[k] : k;
+    SPK_CUDA(c, cudaMemcpyAsync(c->d_pos, hp.data(), (size_t)c->L_pad * 8, cudaMemcpyHostToDevice, c->stream));
+    std::vector<double> ones(c->n_pad, 0.0);
+    for (uint32_t s = 0; s < n; ++s) ones[s] = 1.0;
+    SPK_CUDA(c, cudaMemcpyAsync(c->d_w, ones.data(), (size_t)c->n_pad * 8, cudaMemcpyHostToDevice, c->stream));
+    c->w_total = (double)n;
+    SPK_CUDA(c, cudaEventRecord(c->ev[1], c->stream));
+    int r = prep_alignment(c); if (r) return r;
+    SPK_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
+    SPK_CUDA(c, cudaEventSynchronize(c->ev[2]));
+    SPK_CUDA(c, cudaEventElapsedTime(&c->tm.upload_ms, c->ev[0], c->ev[1]));
+    SPK_CUDA(c, cudaEventElapsedTime(&c->tm.prep_ms, c->ev[1], c->ev[2]));
+    return SPK_OK;
+}
+
+int spk_neighbour_counts(spk_ctx* c, uint64_t min_identical, int quirk, uint64_t* counts) {
+    if (!c || !counts) return SPK_E_INVALID;
+    if (!c->d_states) return fail(c, SPK_E_INVALID, "neighbour_counts: no alignment set");
+    SPK_CUDA(c, cudaSetDevice(c->device));
+    int r = hamming_neighbour_counts(c, min_identical, quirk); if (r) return r;
+    SPK_CUDA(c, cudaMemcpyAsync(counts, c->d_counts, (size_t)c->n * 8, cudaMemcpyDeviceToHost, c->stream));
+    SPK_CUDA(c, cudaStreamSynchronize(c->stream));
+    return SPK_OK;
+}
+
+int spk_set_weights(spk_ctx* c, const double* w) {
+    if (!c || !w) return SPK_E_INVALID;
+    if (!c->d_states) return fail(c, SPK_E_INVALID, "set_weights: no alignment set");
+    SPK_CUDA(c, cudaSetDevice(c->device));
+    std::vector<double> hw(c->n_pad, 0.0);
+    double tot = 0.0;
+    for (uint32_t s = 0; s < c->n; ++s) { hw[s] = w[s]; tot += w[s]; }
+    SPK_CUDA(c, cudaMemcpyAsync(c->d_w, hw.data(), (size_t)c->n_pad * 8, cudaMemcpyHostToDevice, c->stream));
+    SPK_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->w_total = tot;
+    c->operands_terms = 0; c->stats_valid = false;
+    return SPK_OK;
+}
+
+int spk_mi_pairs(spk_ctx* c, const uint32_t* pi, const uint32_t* pj, uint64_t npairs, double pc, double* mi) {
+    if (!c || (npairs && (!pi || !pj || !mi))) return SPK_E_INVALID;
+    if (!c->d_states) return fail(c, SPK_E_INVALID, "mi_pairs: no alignment set");
+    if (npairs == 0) return SPK_OK;
+    for (uint64_t k = 0; k < npairs; ++k) if (pi[k] >= c->L || pj[k] >= c->L) return fail(c, SPK_E_INVALID, "mi_pairs: column index out of range");
+    SPK_CUDA(c, cudaSetDevice(c->device));
+    const size_t ib = (npairs * 4 + 255) & ~(size_t)255, ob = npairs * 8;
+    uint8_t* base = (uint8_t*)scratch(c, 2 * ib + ob);
+    if (!base) return fail(c, SPK_E_NOMEM, "scratch allocation failed");
+    uint32_t* d_pi = (uint32_t*)base; uint32_t* d_pj = (uint32_t*)(base + ib); double* d_mi = (double*)(base + 2 * ib);
+    SPK_CUDA(c, cudaMemcpyAsync(d_pi, pi, npairs * 4, cudaMemcpyHostToDevice, c->stream));
+    SPK_CUDA(c, cudaMemcpyAsync(d_pj, pj, npairs * 4, cudaMemcpyHostToDevice, c->stream));
+    int r = mi_pairs_exact(c, d_pi, d_pj, npairs, pc, d_mi); if (r) return r;
+    SPK_CUDA(c, cudaMemcpyAsync(mi, d_mi, ob, cudaMemcpyDeviceToHost, c->stream));
+    SPK_CUDA(c, cudaStreamSynchronize(c->stream));
+    return SPK_OK;
+}
+
+// host logic of determine_MI_threshold (include/SpydrPick.hpp:258-343)
+int spk_determine_mi_threshold(spk_ctx* c, uint64_t n_values, uint64_t threshold_pairs, uint32_t iterations,
+                               double pc, uint64_t seed, double* threshold) {
+    if (!c || !threshold || iterations == 0) return SPK_E_INVALID;
+    if (!c->d_states) return fail(c, SPK_E_INVALID, "determine_mi_threshold: no alignment set");
+    const uint64_t L = c->L;
+    const uint64_t possible = L * (L - 1) / 2;
+    const double pct = 1.0 - double(n_values) / double(possible);
+    uint64_t tp = threshold_pairs;
+    if (tp == 0) {                                           // SpydrPick.hpp:263-273
+        tp = 100000;
+        while (double(tp) - pct * double(tp) < 100.0 && tp < 500000) tp += 10000;
+    }
+    if (possible / 10 < tp) tp = possible / 10;              // SpydrPick.hpp:276-279
+    if (tp == 0) return fail(c, SPK_E_INVALID, "alignment too small for threshold estimation");
+    const uint64_t idx = (uint64_t)(pct * double(tp));
+    std::vector<uint32_t> pi(tp), pj(tp);
+    std::vector<double> mi(tp), thresholds;
+    for (uint32_t it = 0; it < iterations; ++it) {
+        std::mt19937 gen((uint32_t)(seed + it));
+        std::uniform_int_distribution<uint64_t> dist(0, L - 1);
+        std::unordered_set<uint64_t> seen; seen.reserve(tp * 2);
+        uint64_t k = 0;
+        while (k < tp) {
+            uint64_t a = dist(gen), b = dist(gen);
+            while (a == b) { a = dist(gen); b = dist(gen); }
+            if (a > b) std::swap(a, b);
+            if (seen.insert((a << 32) | b).second) { pi[k] = (uint32_t)a; pj[k] = (uint32_t)b; ++k; }
+        }
+        int r = spk_mi_pairs(c, pi.data(), pj.data(), tp, pc, mi.data()); if (r) return r;
+        std::nth_element(mi.begin(), mi.begin() + idx, mi.end());
+        thresholds.push_back(mi[idx]);
+    }
+    const size_t med = thresholds.size() / 2 - (thresholds.size() % 2 ? 0 : 1);
+    std::nth_element(thresholds.begin(), thresholds.begin() + med, thresholds.end());
+    *threshold = thresholds[med];
+    return SPK_OK;
+}
+
+int spk_outlier_thresholds(const double* colmax, uint64_t L, double* outlier, double* extreme) {
+    if (!colmax || !outlier || !extreme || L == 0) return SPK_E_INVALID;
+    std::vector<double> v(colmax, colmax + L);
+    std::sort(v.begin(), v.end());
+    const double Q1 = v[L / 4 * 1], Q3 = v[L / 4 * 3];       // mi.hpp:280 (integer division first)
+    *outlier = Q3 + 1.5 * (Q3 - Q1);
+    *extreme = Q3 + 3.0 * (Q3 - Q1);
+    return SPK_OK;
+}
+
+static int ensure_scan_buffers(Ctx* c, uint64_t max_edges, bool exhaustive) {
+    uint64_t want_edges = max_edges;
+    if (want_edges == 0) want_edges = 2 * std::min<uint64_t>(10000000ull, 100ull * c->L) + 65536;
+    const uint64_t possible = (uint64_t)c->L * (c->L - 1) / 2;
+    want_edges = std::min<uint64_t>(want_edges, possible + 1);
+    uint64_t want_cand = want_edges + want_edges / 2 + (uint64_t)c->L * 64 + (1u << 20);
+    want_cand = std::min<uint64_t>(want_cand, possible + 1);
+    if (exhaustive) want_cand = std::max<uint64_t>(std::min<uint64_t>(possible + 1, 1ull << 24), (uint64_t)c->L);
+    int r;
+    if (c->edges_cap < want_edges) {
+        if ((r = dev_alloc(c, c->d_edges, want_edges * sizeof(spk_edge), "edges"))) return r;
+        if ((r = dev_alloc(c, c->d_wo, want_edges * sizeof(spk_edge), "edges_wo_gaps"))) return r;
+        c->edges_cap = c->wo_cap = want_edges;
+    }
+    if (c->cand_cap < want_cand) {
+        if ((r = dev_alloc(c, c->d_cand, want_cand * sizeof(Candidate), "candidates"))) return r;
+        if ((r = dev_alloc(c, c->d_refined, want_cand * sizeof(spk_edge), "refined"))) return r;
+        if ((r = dev_alloc(c, c->d_refined_wo, want_cand * 8, "refined_wo"))) return r;
+        c->cand_cap = c->refined_cap = want_cand;
+    }
+    return SPK_OK;
+}
+
+int spk_mi_scan(spk_ctx* c, const spk_scan_params* pp, spk_scan_result* res) {
+    if (!c || !pp || !res) return SPK_E_INVALID;
+    if (!c->d_states) return fail(c, SPK_E_INVALID, "mi_scan: no alignment set");
+    spk_scan_params p = *pp;
+    memset(res, 0, sizeof *res);
+    SPK_CUDA(c, cudaSetDevice(c->device));
+    if (!(p.pseudocount > 0.0)) return fail(c, SPK_E_INVALID, "mi_scan: pseudocount must be > 0 (0 makes the reference produce NaN via 0*log 0)");
+    const int T = p.n_terms ? p.n_terms : 2;
+    if (T < 1 || T > 3) return fail(c, SPK_E_INVALID, "mi_scan: n_terms must be 1..3");
+    const double band = p.band > 0.0 ? p.band : (T == 1 ? 4e-3 : 2e-4);
+    const uint64_t circle = p.circle_size ? p.circle_size : c->L;
+    if (p.n_parts == 0) p.n_parts = 1;
+    if (p.part_index >= p.n_parts) return fail(c, SPK_E_INVALID, "mi_scan: part_index >= n_parts");
+    int r = ensure_scan_buffers(c, p.max_edges, p.engine == 1); if (r) return r;
+
+    SPK_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 8 * sizeof(unsigned long long), c->stream));
+    fill_u64_kernel<<<(c->L_pad + 255) / 256, 256, 0, c->stream>>>((unsigned long long*)c->d_colmax, f64_ordered(-DBL_MAX), c->L_pad);
+    c->tm.kernel_launches += 1;
+    c->tm.gemm_ms = c->tm.refine_ms = c->tm.compact_ms = c->tm.sort_ms = 0.f; c->tm.gemm_tiles = 0;
+
+    unsigned long long h_counters[8] = {0};
+    if (p.engine == 1) {
+        r = mi_scan_exact(c, p, circle); if (r) return r;
+    } else {
+        r = prep_column_stats(c, p.pseudocount); if (r) return r;
+        r = prep_operands(c, T); if (r) return r;
+        r = mi_gemm_filter(c, p, T, band, circle); if (r) return r;
+        SPK_CUDA(c, cudaMemcpyAsync(h_counters, c->d_counters, sizeof h_counters, cudaMemcpyDeviceToHost, c->stream));
+        SPK_CUDA(c, cudaStreamSynchronize(c->stream));
+        if (h_counters[4]) return fail(c, SPK_E_OVERFLOW, "candidate buffer overflow (%llu candidates > capacity %llu): raise max_edges or the threshold",
+                                       h_counters[0], (unsigned long long)c->cand_cap);
+        const uint64_t ncand = h_counters[0];
+        res->n_candidates = ncand;
+        SPK_CUDA(c, cudaEventRecord(c->ev[4], c->stream));
+        r = mi_refine_candidates(c, ncand, p.pseudocount); if (r) return r;
+        SPK_CUDA(c, cudaEventRecord(c->ev[5], c->stream));
+        r = mi_compact(c, ncand, p, circle); if (r) return r;
+        SPK_CUDA(c, cudaEventRecord(c->ev[6], c->stream));
+        SPK_CUDA(c, cudaEventSynchronize(c->ev[6]));
+        SPK_CUDA(c, cudaEventElapsedTime(&c->tm.refine_ms, c->ev[4], c->ev[5]));
+        SPK_CUDA(c, cudaEventElapsedTime(&c->tm.compact_ms, c->ev[5], c->ev[6]));
+    }
+    ordered_to_double_kernel<<<(c->L_pad + 255) / 256, 256, 0, c->stream>>>((unsigned long long*)c->d_colmax, c->L_pad);
+    c->tm.kernel_launches += 1;
+    SPK_CUDA(c, cudaMemcpyAsync(h_counters, c->d_counters, sizeof h_counters, cudaMemcpyDeviceToHost, c->stream));
+    SPK_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (h_counters[4]) return fail(c, SPK_E_OVERFLOW, "edge buffer overflow (%llu edges > capacity %llu): raise max_edges", h_counters[1],
+                                   (unsigned long long)c->edges_cap);
+    const uint64_t ne = h_counters[1], nw = h_counters[2];
+    res->max_filter_error = h_counters[3] ? f64_from_ordered(h_counters[3]) : 0.0;
+    if (p.engine != 1 && res->max_filter_error > 0.5 * band)
+        return fail(c, SPK_E_PRECISION, "fp32 filter error %.3g exceeds half the safety band %.3g: raise n_terms or band",
+                    res->max_filter_error, band);
+    if (p.sort_desc) { r = sort_edges_device(c, c->d_edges, ne); if (r) return r; }
+    res->n_edges = ne; res->n_wo_gaps = nw;
+    res->d_edges = c->d_edges; res->d_edges_wo_gaps = c->d_wo; res->d_colmax = c->d_colmax;
+    c->h_colmax.resize(c->L);
+    SPK_CUDA(c, cudaMemcpyAsync(c->h_colmax.data(), c->d_colmax, (size_t)c->L * 8, cudaMemcpyDeviceToHost, c->stream));
+    if (!p.keep_on_device) {
+        c->h_edges.resize(ne); c->h_wo.resize(nw);
+        if (ne) SPK_CUDA(c, cudaMemcpyAsync(c->h_edges.data(), c->d_edges, ne * sizeof(spk_edge), cudaMemcpyDeviceToHost, c->stream));
+        if (nw) SPK_CUDA(c, cudaMemcpyAsync(c->h_wo.data(), c->d_wo, nw * sizeof(spk_edge), cudaMemcpyDeviceToHost, c->stream));
+    }
+    SPK_CUDA(c, cudaStreamSynchronize(c->stream));
+    res->colmax = c->h_colmax.data();
+    if (!p.keep_on_device) { res->edges = c->h_edges.data(); res->edges_wo_gaps = c->h_wo.data(); }
+    return SPK_OK;
+}
+
+int spk_sort_edges_device(spk_ctx* c, void* d_edges, uint64_t n) {
+    if (!c || (!d_edges && n)) return SPK_E_INVALID;
+    SPK_CUDA(c, cudaSetDevice(c->device));
+    int r = sort_edges_device(c, (spk_edge*)d_edges, n); if (r) return r;
+    SPK_CUDA(c, cudaStreamSynchronize(c->stream));
+    return SPK_OK;
+}
+
+int spk_sort_edges(spk_ctx* c, spk_edge* edges, uint64_t n) {
+    if (!c || (!edges && n)) return SPK_E_INVALID;
+    if (n < 2) return SPK_OK;
+    SPK_CUDA(c, cudaSetDevice(c->device));
+    spk_edge* d = nullptr;
+    if (cudaMalloc(&d, n * sizeof(spk_edge)) != cudaSuccess) { cudaGetLastError(); return fail(c, SPK_E_NOMEM, "sort: device allocation failed"); }
+    int r = cuda_check(c, cudaMemcpyAsync(d, edges, n * sizeof(spk_edge), cudaMemcpyHostToDevice, c->stream), "H2D edges");
+    if (!r) r = sort_edges_device(c, d, n);
+    if (!r) r = cuda_check(c, cudaMemcpyAsync(edges, d, n * sizeof(spk_edge), cudaMemcpyDeviceToHost, c->stream), "D2H edges");
+    if (!r) r = cuda_check(c, cudaStreamSynchronize(c->stream), "sync");
+    cudaFree(d);
+    return r;
+}
+
+int spk_aracne_device(spk_ctx* c, const void* d_edges, uint64_t n, double eps, uint32_t part, uint32_t nparts, void* d_flags) {
+    if (!c || (n && (!d_edges || !d_flags))) return SPK_E_INVALID;
+    if (nparts == 0) nparts = 1;
+    if (part >= nparts) return fail(c, SPK_E_INVALID, "aracne: part_index >= n_parts");
+    SPK_CUDA(c, cudaSetDevice(c->device));
+    int r = aracne_device(c, (const spk_edge*)d_edges, n, eps, part, nparts, (uint8_t*)d_flags); if (r) return r;
+    SPK_CUDA(c, cudaStreamSynchronize(c->stream));
+    return SPK_OK;
+}
+
+int spk_aracne(spk_ctx* c, const spk_edge* edges, uint64_t n, double eps, uint32_t part, uint32_t nparts, uint8_t* flags) {
+    if (!c || (n && (!edges || !flags))) return SPK_E_INVALID;
+    if (n == 0) return SPK_OK;
+    if (nparts == 0) nparts = 1;
+    if (part >= nparts) return fail(c, SPK_E_INVALID, "aracne: part_index >= n_parts");
+    SPK_CUDA(c, cudaSetDevice(c->device));
+    spk_edge* d = nullptr; uint8_t* f = nullptr;
+    if (cudaMalloc(&d, n * sizeof(spk_edge)) != cudaSuccess || cudaMalloc(&f, n) != cudaSuccess) {
+        cudaGetLastError(); if (d) cudaFree(d);
+        return fail(c, SPK_E_NOMEM, "aracne: device allocation failed");
+    }
+    int r = cuda_check(c, cudaMemcpyAsync(d, edges, n * sizeof(spk_edge), cudaMemcpyHostToDevice, c->stream), "H2D edges");
+    if (!r) r = cuda_check(c, cudaMemcpyAsync(f, flags, n, cudaMemcpyHostToDevice, c->stream), "H2D flags");
+    if (!r) r = aracne_device(c, d, n, eps, part, nparts, f);
+    if (!r) r = cuda_check(c, cudaMemcpyAsync(flags, f, n, cudaMemcpyDeviceToHost, c->stream), "D2H flags");
+    if (!r) r = cuda_check(c, cudaStreamSynchronize(c->stream), "sync");
+    cudaFree(d); cudaFree(f);
+    return r;
+}
+
+int spk_get_timings(spk_ctx* c, spk_timings* out) {
+    if (!c || !out) return SPK_E_INVALID;
+    *out = c->tm;
+    return SPK_OK;
+}
+
+int spk_debug_tile_counts(spk_ctx* c, uint32_t ib, uint32_t jb, int32_t n_terms, float* counts) {
+    if (!c || !counts) return SPK_E_INVALID;
+    if (!c->d_states) return fail(c, SPK_E_INVALID, "debug_tile_counts: no alignment set");
+    const int T = n_terms ? n_terms : 2;
+    if (T < 1 || T > 3) return fail(c, SPK_E_INVALID, "n_terms must be 1..3");
+    if (ib >= (c->L + TILE_I - 1) / TILE_I || jb >= c->L_pad / TILE_J) return fail(c, SPK_E_INVALID, "tile out of range");
+    SPK_CUDA(c, cudaSetDevice(c->device));
+    int r = prep_column_stats(c, 0.5); if (r) return r;
+    r = prep_operands(c, T); if (r) return r;
+    const size_t bytes = (size_t)TILE_I * TILE_J * 16 * sizeof(float);
+    float* d_out = nullptr;
+    if (cudaMalloc(&d_out, bytes) != cudaSuccess) { cudaGetLastError(); return fail(c, SPK_E_NOMEM, "debug buffer"); }
+    cudaMemsetAsync(d_out, 0xff, bytes, c->stream);
+    r = mi_gemm_debug_tile(c, ib, jb, T, d_out);
+    if (!r) r = cuda_check(c, cudaMemcpy(counts, d_out, bytes, cudaMemcpyDeviceToHost), "D2H debug tile");
+    cudaFree(d_out);
+    return r;
+}
+
+} // extern "C"

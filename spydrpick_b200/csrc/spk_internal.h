@@ -1,0 +1,165 @@
+// spk_internal.h -- shared declarations of the CUDA implementation behind include/spydrpick_b200.h
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+#include <vector>
+#include "../../include/spydrpick_b200.h"
+
+namespace spk {
+
+constexpr int NSTATES = 5;
+constexpr int GAP = 4;
+
+// GEMM tile geometry (K2): A tile = 32 i-columns x 4 states = 128 rows (weighted, T terms),
+// B tile = 64 j-columns x 4 states = 256 rows (unweighted one-hot), K block = 64 samples.
+constexpr int TILE_I = 32;
+constexpr int TILE_J = 64;
+constexpr int BLOCK_K = 64;
+constexpr int SUPER_I = 16;          // i-tiles per super-row (L2 panel reuse)
+
+// per-column statistics consumed by the fp32 epilogue (64 bytes)
+struct ColStat {
+    float m[5];        // weighted marginal counts of states a,t,c,g,gap
+    float h[5];        // h[k-1] = sum_{a in P} xlogx((m[a]+pc*k)/(W+pc*|P|*k)), k = |P_other| in 1..5 (natural log)
+    uint32_t mask;     // 5-bit presence mask
+    uint32_t npres;    // popcount(mask)
+    uint32_t pos_lo, pos_hi;   // original position (loci translation)
+    uint32_t pad[2];
+};
+static_assert(sizeof(ColStat) == 64, "ColStat must be 64 bytes");
+
+// candidate emitted by the filter: pair + fp32 MI
+struct Candidate { uint32_t i, j; float mi32; uint32_t pad; };
+
+struct Ctx {
+    int device = 0;
+    int verbose = 0;
+    cudaStream_t own_stream = nullptr;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    int sm_count = 148;
+
+    // alignment
+    uint32_t n = 0, L = 0;
+    uint32_t n_pad = 0;      // samples padded to BLOCK_K
+    uint32_t L_pad = 0;      // columns padded to TILE_J
+    uint32_t W32 = 0;        // 32-bit words per bit plane row = ceil(L/32)
+    uint8_t*  d_states = nullptr;     // [n][L] raw
+    uint8_t*  d_colmajor = nullptr;   // [L_pad][n_pad] column-major bytes (pad samples = 255, pad columns = GAP)
+    uint32_t* d_planes = nullptr;     // [3][n][W32] bit planes
+    uint64_t* d_pos = nullptr;        // [L_pad]
+    uint8_t*  d_masks = nullptr;      // [L_pad]
+    double*   d_w = nullptr;          // [n_pad] (pad = 0)
+    double*   d_marg = nullptr;       // [L_pad][5] fp64 weighted marginals
+    ColStat*  d_colstat = nullptr;    // [L_pad]
+    double    w_total = 0.0;
+    bool      stats_valid = false;    // d_marg / d_colstat match current weights + pseudocount
+    double    stats_pc = -1.0;
+    // one-hot operands
+    __nv_bfloat16* d_U = nullptr;     // [4*L_pad][n_pad] unweighted
+    __nv_bfloat16* d_V = nullptr;     // [T][4*L_pad][n_pad] weighted terms
+    int       operands_terms = 0;     // number of valid terms in d_V (0 = invalid)
+    size_t    operands_cap_terms = 0;
+
+    // scan outputs (device)
+    Candidate* d_cand = nullptr;  uint64_t cand_cap = 0;
+    spk_edge*  d_edges = nullptr; uint64_t edges_cap = 0;
+    spk_edge*  d_wo = nullptr;    uint64_t wo_cap = 0;
+    spk_edge*  d_refined = nullptr; double* d_refined_wo = nullptr; uint64_t refined_cap = 0;
+    double*    d_colmax = nullptr;        // [L_pad] as ordered uint64 during the scan, doubles after
+    float*     d_colmax32 = nullptr;      // [L_pad] running fp32 maxima (ordered-int encoded)
+    unsigned long long* d_counters = nullptr;   // [8] n_cand, n_edges, n_wo, max_err_bits, ...
+    // host mirrors
+    std::vector<spk_edge> h_edges, h_wo;
+    std::vector<double> h_colmax;
+
+    // scratch
+    void* d_scratch = nullptr; size_t scratch_bytes = 0;
+    void* d_tilemap = nullptr;            // CUtensorMap storage is passed by value; super-row prefix table lives here
+    uint64_t* d_counts = nullptr;         // [n] neighbour counts
+
+    spk_timings tm = {};
+    cudaEvent_t ev[8] = {};
+};
+
+int fail(Ctx* c, int code, const char* fmt, ...);
+int cuda_check(Ctx* c, cudaError_t e, const char* what);
+#define SPK_CUDA(c, call) do { int _r = ::spk::cuda_check((c), (call), #call); if (_r) return _r; } while (0)
+
+void* scratch(Ctx* c, size_t bytes);   // grows the context scratch buffer; nullptr on failure
+
+// ---- prep (spk_prep.cu)
+int prep_alignment(Ctx* c);                                   // colmajor, planes, masks from d_states
+int prep_column_stats(Ctx* c, double pseudocount);            // d_marg, d_colstat, w_total
+int prep_operands(Ctx* c, int n_terms);                       // d_U, d_V
+
+// ---- K1 (spk_hamming.cu)
+int hamming_neighbour_counts(Ctx* c, uint64_t min_identical, int quirk);
+
+// ---- exact fp64 MI (spk_mi_exact.cu)
+int mi_pairs_exact(Ctx* c, const uint32_t* d_pi, const uint32_t* d_pj, uint64_t npairs, double pc, double* d_mi);
+// refine candidates -> d_refined (i,j,mi64), d_refined_wo (NaN when no gap column involved)
+int mi_refine_candidates(Ctx* c, uint64_t ncand, double pc);
+// exhaustive diagnostic engine: emits every pair of the partition as a candidate-free exact scan
+int mi_scan_exact(Ctx* c, const spk_scan_params& p, uint64_t circle);
+// threshold + colmax + compaction over refined candidates
+int mi_compact(Ctx* c, uint64_t ncand, const spk_scan_params& p, uint64_t circle);
+
+// ---- K2 (spk_mi_gemm.cu)
+int mi_gemm_filter(Ctx* c, const spk_scan_params& p, int n_terms, double band, uint64_t circle);
+int mi_gemm_debug_tile(Ctx* c, uint32_t ib, uint32_t jb, int n_terms, float* d_out);
+
+// ---- graph (spk_graph.cu)
+int sort_edges_device(Ctx* c, spk_edge* d_edges, uint64_t n);
+int aracne_device(Ctx* c, const spk_edge* d_edges, uint64_t n, double eps, uint32_t part, uint32_t nparts, uint8_t* d_flags);
+
+// ordered-int encodings for atomic max on floating point
+__host__ __device__ inline uint32_t f32_ordered(float f) {
+    uint32_t u;
+#ifdef __CUDA_ARCH__
+    u = __float_as_uint(f);
+#else
+    memcpy(&u, &f, 4);
+#endif
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__host__ __device__ inline float f32_from_ordered(uint32_t u) {
+    u = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
+#ifdef __CUDA_ARCH__
+    return __uint_as_float(u);
+#else
+    float f; memcpy(&f, &u, 4); return f;
+#endif
+}
+__host__ __device__ inline unsigned long long f64_ordered(double d) {
+    unsigned long long u;
+#ifdef __CUDA_ARCH__
+    u = (unsigned long long)__double_as_longlong(d);
+#else
+    memcpy(&u, &d, 8);
+#endif
+    return (u & 0x8000000000000000ull) ? ~u : (u | 0x8000000000000000ull);
+}
+__host__ __device__ inline double f64_from_ordered(unsigned long long u) {
+    u = (u & 0x8000000000000000ull) ? (u & 0x7fffffffffffffffull) : ~u;
+#ifdef __CUDA_ARCH__
+    return __longlong_as_double((long long)u);
+#else
+    double d; memcpy(&d, &u, 8); return d;
+#endif
+}
+
+// distance used for the LD mask of colmax (apegrunt/Distance.hpp:28-37), size_t wrap included
+__host__ __device__ inline unsigned long long genome_distance(unsigned long long p1, unsigned long long p2,
+                                                              int linear, unsigned long long circle) {
+    long long d0 = (long long)p1 - (long long)p2;
+    unsigned long long d = (unsigned long long)(d0 < 0 ? -d0 : d0);
+    if (linear) return d;
+    unsigned long long alt = circle - d;
+    return alt < d ? alt : d;
+}
+
+} // namespace spk

@@ -1,0 +1,256 @@
+// spk_mi_exact.cu -- fp64 exact MI kernels: K2b (pair list), K2r/K2c (refine of filter
+// candidates incl. the literal "MI without gaps" second pass), threshold/colmax compaction and
+// the exhaustive diagnostic engine.
+//
+// Formula: include/mi.hpp:146-181 (normalize_and_get_mi_single) on the 5x5 table
+// buffer[jstate*5+istate] (misc/Crosstable.hpp:62-67). One warp per column pair: lanes stride the
+// samples and accumulate into lane-private shared-memory bins (no atomics, deterministic), then
+// lane l < 25 owns cell l = b*5+a and the entropy terms are evaluated one log per lane.
+#include <cfloat>
+#include "spk_internal.h"
+
+namespace spk {
+
+constexpr int EX_WARPS = 4;
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// weighted crosstable of two column-major byte columns; returns cell value for lane < 25.
+__device__ __forceinline__ double warp_crosstab(const uint8_t* __restrict__ ci, const uint8_t* __restrict__ cj,
+                                                const double* __restrict__ w, uint32_t n_pad, double* bins, uint32_t lane) {
+#pragma unroll
+    for (int k = 0; k < 25; ++k) bins[k * 32 + lane] = 0.0;
+    for (uint32_t s0 = lane * 4; s0 < n_pad; s0 += 128) {
+        const uchar4 xa = *reinterpret_cast<const uchar4*>(ci + s0);
+        const uchar4 xb = *reinterpret_cast<const uchar4*>(cj + s0);
+        const double w0 = w[s0], w1 = w[s0 + 1], w2 = w[s0 + 2], w3 = w[s0 + 3];
+        // pad samples carry state GAP and weight 0 -> add 0 to cell (gap,gap)
+        bins[(xb.x * 5 + xa.x) * 32 + lane] += w0;
+        bins[(xb.y * 5 + xa.y) * 32 + lane] += w1;
+        bins[(xb.z * 5 + xa.z) * 32 + lane] += w2;
+        bins[(xb.w * 5 + xa.w) * 32 + lane] += w3;
+    }
+    __syncwarp();
+    double c = 0.0;
+    if (lane < 25) {
+#pragma unroll 8
+        for (int k = 0; k < 32; ++k) c += bins[lane * 32 + ((k + lane) & 31)];
+    }
+    __syncwarp();
+    return c;
+}
+
+// One pass of normalize_and_get_mi_single over the lane-distributed table (lane l<25: b=l/5,
+// a=l%5). v is updated in place exactly like the reference's buffer (pseudocount added and the
+// rows of present j-states divided by the normalisation constant), so that a second call with
+// the gap bits removed reproduces the reference's MI-without-gaps quirk (mi.hpp:108-135,465-489).
+__device__ __forceinline__ double warp_mi_pass(double& v, uint32_t mask_i, uint32_t mask_j, double pc, uint32_t lane) {
+    const bool valid = lane < 25;
+    const uint32_t a = lane % 5, b = lane / 5;
+    const bool in_i = valid && ((mask_i >> a) & 1u);
+    const bool in_j = valid && ((mask_j >> b) & 1u);
+    if (in_i && in_j) v += pc;
+    const double Z = warp_sum((in_i && in_j) ? v : 0.0);
+    if (in_j) v = v / Z;
+    const double jointH = warp_sum((in_i && in_j) ? v * log(v) : 0.0);
+    // row sums over all five i-states (mi.hpp:173) for rows b in P_j; column sums over rows in P_j
+    double rs = 0.0, cs = 0.0;
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+        const double r = __shfl_sync(0xffffffffu, v, (lane < 5 ? lane * 5 + k : 0));
+        const double q = __shfl_sync(0xffffffffu, v, (lane < 5 ? k * 5 + lane : 0));
+        rs += r;
+        if ((mask_j >> k) & 1u) cs += q;
+    }
+    const bool l5 = lane < 5;
+    const double icondH = warp_sum((l5 && ((mask_j >> lane) & 1u)) ? rs * log(rs) : 0.0);
+    const double jcondH = warp_sum((l5 && ((mask_i >> lane) & 1u)) ? cs * log(cs) : 0.0);
+    return jointH - icondH - jcondH;
+}
+
+// ---- K2b: explicit pair list ---------------------------------------------------------------
+__global__ void __launch_bounds__(EX_WARPS * 32)
+mi_pairs_kernel(const uint8_t* __restrict__ colmajor, const double* __restrict__ w, const uint8_t* __restrict__ masks,
+                const uint32_t* __restrict__ pi, const uint32_t* __restrict__ pj, unsigned long long npairs,
+                uint32_t n_pad, double pc, double* __restrict__ mi) {
+    __shared__ double bins_all[EX_WARPS][25 * 32];
+    const uint32_t lane = threadIdx.x % 32, wid = threadIdx.x / 32;
+    double* bins = bins_all[wid];
+    for (unsigned long long p = (unsigned long long)blockIdx.x * EX_WARPS + wid; p < npairs;
+         p += (unsigned long long)gridDim.x * EX_WARPS) {
+        const uint32_t i = pi[p], j = pj[p];
+        double v = warp_crosstab(colmajor + (size_t)i * n_pad, colmajor + (size_t)j * n_pad, w, n_pad, bins, lane);
+        const double m = warp_mi_pass(v, masks[i], masks[j], pc, lane);
+        if (lane == 0) mi[p] = m;
+    }
+}
+
+// ---- K2r/K2c: refine filter candidates -------------------------------------------------------
+// counters[3] = max |mi32 - mi64| (ordered bits, atomicMax)
+__global__ void __launch_bounds__(EX_WARPS * 32)
+mi_refine_kernel(const uint8_t* __restrict__ colmajor, const double* __restrict__ w, const uint8_t* __restrict__ masks,
+                 const Candidate* __restrict__ cand, unsigned long long ncand, uint32_t n_pad, double pc,
+                 spk_edge* __restrict__ refined, double* __restrict__ refined_wo, unsigned long long* __restrict__ counters) {
+    __shared__ double bins_all[EX_WARPS][25 * 32];
+    const uint32_t lane = threadIdx.x % 32, wid = threadIdx.x / 32;
+    double* bins = bins_all[wid];
+    double maxerr = 0.0;
+    for (unsigned long long p = (unsigned long long)blockIdx.x * EX_WARPS + wid; p < ncand;
+         p += (unsigned long long)gridDim.x * EX_WARPS) {
+        const Candidate cd = cand[p];
+        const uint32_t mi_ = masks[cd.i], mj_ = masks[cd.j];
+        double v = warp_crosstab(colmajor + (size_t)cd.i * n_pad, colmajor + (size_t)cd.j * n_pad, w, n_pad, bins, lane);
+        const double m = warp_mi_pass(v, mi_, mj_, pc, lane);
+        double m2 = __longlong_as_double(0x7ff8000000000000ll);   // NaN = "no gap column involved"
+        if ((mi_ | mj_) & (1u << GAP)) m2 = warp_mi_pass(v, mi_ & ~(1u << GAP), mj_ & ~(1u << GAP), pc, lane);
+        if (lane == 0) {
+            spk_edge e; e.i = cd.i; e.j = cd.j; e.mi = m;
+            refined[p] = e; refined_wo[p] = m2;
+            if (cd.mi32 == cd.mi32) maxerr = fmax(maxerr, fabs((double)cd.mi32 - m));
+        }
+    }
+    if (lane == 0 && maxerr > 0.0) atomicMax(&counters[3], f64_ordered(maxerr));
+}
+
+// ---- threshold / colmax / compaction over refined pairs (mi.hpp:414-461) ----------------------
+// counters[1] = n_edges, counters[2] = n_wo, counters[4] = overflow flag
+__global__ void mi_compact_kernel(const spk_edge* __restrict__ refined, const double* __restrict__ refined_wo,
+                                  unsigned long long ncand, const uint64_t* __restrict__ pos,
+                                  double threshold, unsigned long long ld_threshold, int linear, unsigned long long circle,
+                                  unsigned long long* __restrict__ colmax_ord,
+                                  spk_edge* __restrict__ edges, unsigned long long edges_cap,
+                                  spk_edge* __restrict__ wo, unsigned long long wo_cap,
+                                  unsigned long long* __restrict__ counters) {
+    const unsigned long long p = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t lane = threadIdx.x % 32;
+    bool keep = false, keep_wo = false;
+    spk_edge e; e.i = 0; e.j = 0; e.mi = 0.0; double m2 = 0.0;
+    if (p < ncand) {
+        e = refined[p]; m2 = refined_wo[p];
+        if (genome_distance(pos[e.i], pos[e.j], linear, circle) > ld_threshold) {
+            const unsigned long long o = f64_ordered(e.mi);
+            if (o > colmax_ord[e.i]) atomicMax(&colmax_ord[e.i], o);
+            if (o > colmax_ord[e.j]) atomicMax(&colmax_ord[e.j], o);
+        }
+        keep = threshold < e.mi;                 // strict (mi.hpp:430,454); NaN never kept
+        keep_wo = keep && (m2 == m2);
+    }
+    const uint32_t bal = __ballot_sync(0xffffffffu, keep);
+    if (bal) {
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(&counters[1], (unsigned long long)__popc(bal));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (keep) {
+            const unsigned long long idx = base + __popc(bal & ((1u << lane) - 1u));
+            if (idx < edges_cap) edges[idx] = e; else counters[4] = 1ull;
+        }
+    }
+    const uint32_t bal2 = __ballot_sync(0xffffffffu, keep_wo);
+    if (bal2) {
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(&counters[2], (unsigned long long)__popc(bal2));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (keep_wo) {
+            const unsigned long long idx = base + __popc(bal2 & ((1u << lane) - 1u));
+            spk_edge e2 = e; e2.mi = m2;
+            if (idx < wo_cap) wo[idx] = e2; else counters[4] = 1ull;
+        }
+    }
+}
+
+// ---- exhaustive engine helper: enumerate all pairs (i, j>i) for rows [i0, i1) -----------------
+__global__ void enumerate_pairs_kernel(Candidate* __restrict__ cand, uint32_t i0, uint32_t i1, uint32_t L,
+                                       unsigned long long total) {
+    // pairs laid out row by row; row i has L-1-i entries. Closed-form inverse is avoided: one block per row.
+    for (uint32_t i = i0 + blockIdx.x; i < i1; i += gridDim.x) {
+        // offset of row i within [i0,i1): sum_{r=i0}^{i-1} (L-1-r)
+        const unsigned long long k = (unsigned long long)(i - i0);
+        const unsigned long long off = k * (unsigned long long)(L - 1 - i0) - k * (k - 1) / 2;
+        for (uint32_t j = i + 1 + threadIdx.x; j < L; j += blockDim.x) {
+            Candidate c; c.i = i; c.j = j; c.mi32 = __int_as_float(0x7fc00000); c.pad = 0;
+            const unsigned long long idx = off + (j - i - 1);
+            if (idx < total) cand[idx] = c;
+        }
+    }
+}
+
+// =============================================================================================
+static int refine_grid(Ctx* c, unsigned long long n) {
+    unsigned long long blocks = (n + EX_WARPS - 1) / EX_WARPS;
+    const unsigned long long cap = (unsigned long long)c->sm_count * 16;
+    return (int)(blocks < cap ? (blocks ? blocks : 1) : cap);
+}
+
+int mi_pairs_exact(Ctx* c, const uint32_t* d_pi, const uint32_t* d_pj, uint64_t npairs, double pc, double* d_mi) {
+    if (npairs == 0) return SPK_OK;
+    SPK_CUDA(c, cudaEventRecord(c->ev[0], c->stream));
+    mi_pairs_kernel<<<refine_grid(c, npairs), EX_WARPS * 32, 0, c->stream>>>(c->d_colmajor, c->d_w, c->d_masks, d_pi, d_pj,
+                                                                            npairs, c->n_pad, pc, d_mi);
+    c->tm.kernel_launches += 1;
+    SPK_CUDA(c, cudaEventRecord(c->ev[1], c->stream));
+    SPK_CUDA(c, cudaEventSynchronize(c->ev[1]));
+    SPK_CUDA(c, cudaEventElapsedTime(&c->tm.pairs_ms, c->ev[0], c->ev[1]));
+    SPK_CUDA(c, cudaGetLastError());
+    return SPK_OK;
+}
+
+int mi_refine_candidates(Ctx* c, uint64_t ncand, double pc) {
+    if (ncand == 0) return SPK_OK;
+    mi_refine_kernel<<<refine_grid(c, ncand), EX_WARPS * 32, 0, c->stream>>>(c->d_colmajor, c->d_w, c->d_masks, c->d_cand, ncand,
+                                                                            c->n_pad, pc, c->d_refined, c->d_refined_wo,
+                                                                            c->d_counters);
+    c->tm.kernel_launches += 1;
+    SPK_CUDA(c, cudaGetLastError());
+    return SPK_OK;
+}
+
+int mi_compact(Ctx* c, uint64_t ncand, const spk_scan_params& p, uint64_t circle) {
+    if (ncand == 0) return SPK_OK;
+    mi_compact_kernel<<<(unsigned)((ncand + 255) / 256), 256, 0, c->stream>>>(
+        c->d_refined, c->d_refined_wo, ncand, c->d_pos, p.threshold, p.ld_threshold, p.linear_genome, circle,
+        (unsigned long long*)c->d_colmax, c->d_edges, c->edges_cap, c->d_wo, c->wo_cap, c->d_counters);
+    c->tm.kernel_launches += 1;
+    SPK_CUDA(c, cudaGetLastError());
+    return SPK_OK;
+}
+
+// exhaustive diagnostic engine: every pair of this partition goes through the fp64 kernels.
+int mi_scan_exact(Ctx* c, const spk_scan_params& p, uint64_t circle) {
+    const uint32_t L = c->L;
+    const uint32_t nparts = p.n_parts ? p.n_parts : 1;
+    // rows are dealt to partitions in contiguous chunks of 64 rows, round-robin
+    const uint32_t chunk_rows = 64;
+    float ms_refine = 0.f, ms_compact = 0.f;
+    for (uint32_t r0 = 0, chunk = 0; r0 + 1 < L; r0 += chunk_rows, ++chunk) {
+        if (chunk % nparts != p.part_index) continue;
+        const uint32_t r1 = (r0 + chunk_rows < L - 1) ? r0 + chunk_rows : L - 1;
+        // split so that the chunk fits the candidate buffer
+        uint32_t a = r0;
+        while (a < r1) {
+            uint32_t b = a; unsigned long long cnt = 0;
+            while (b < r1 && cnt + (L - 1 - b) <= c->cand_cap) { cnt += (L - 1 - b); ++b; }
+            if (b == a) return fail(c, SPK_E_OVERFLOW, "candidate buffer smaller than one row of pairs");
+            enumerate_pairs_kernel<<<b - a, 256, 0, c->stream>>>(c->d_cand, a, b, L, cnt);
+            c->tm.kernel_launches += 1;
+            SPK_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
+            int r = mi_refine_candidates(c, cnt, p.pseudocount); if (r) return r;
+            SPK_CUDA(c, cudaEventRecord(c->ev[3], c->stream));
+            r = mi_compact(c, cnt, p, circle); if (r) return r;
+            SPK_CUDA(c, cudaEventRecord(c->ev[4], c->stream));
+            SPK_CUDA(c, cudaEventSynchronize(c->ev[4]));
+            float t1, t2;
+            SPK_CUDA(c, cudaEventElapsedTime(&t1, c->ev[2], c->ev[3]));
+            SPK_CUDA(c, cudaEventElapsedTime(&t2, c->ev[3], c->ev[4]));
+            ms_refine += t1; ms_compact += t2;
+            a = b;
+        }
+    }
+    c->tm.refine_ms = ms_refine; c->tm.compact_ms = ms_compact;
+    return SPK_OK;
+}
+
+} // namespace spk

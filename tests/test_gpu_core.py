@@ -1,0 +1,186 @@
+"""GPU parity tests (through the C-ABI) for K1 (Hamming), the fp64 MI kernels (K2b/K2r/K2c and the
+exhaustive engine), edge sort and K3 (ARACNE), each against the CPU oracle on the same inputs.
+Integer / index / flag results must be bit-exact; fp64 MI within 1e-12 relative (re-association only)."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import oracle.oracle as orc
+from spydrpick_b200 import Context, EDGE_DTYPE
+from spydrpick_b200.synth import generate_alignment
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+KAT = json.load(open(os.path.join(HERE, "golden", "kat.json")))
+EPS = 2.220446049250313e-16
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = Context()
+    yield c
+    c.close()
+
+
+def _edge_set(e):
+    return {(int(a), int(b)) for a, b in zip(e["i"], e["j"])}
+
+
+def _edges(lst):
+    e = np.zeros(len(lst), dtype=EDGE_DTYPE)
+    for k, (i, j, w) in enumerate(lst):
+        e[k] = (i, j, w)
+    return e
+
+
+# ---------------------------------------------------------------- K1
+@pytest.mark.parametrize("n,L", [(50, 96), (130, 257), (64, 64), (200, 1000), (333, 1024), (7, 33)])
+@pytest.mark.parametrize("quirk", [True, False])
+def test_neighbour_counts_bit_exact(ctx, n, L, quirk):
+    s, _, _ = generate_alignment(n, L, seed=100 + n + L, n_planted=0)
+    ctx.set_alignment(s)
+    for frac in (0.9, 0.7, 0.99):
+        thr = int(frac * float(L))
+        got = ctx.neighbour_counts(thr, quirk)
+        exp = orc.neighbour_counts(s, thr, quirk)
+        assert np.array_equal(got, exp), (n, L, frac, quirk)
+
+
+def test_neighbour_rule_pins(ctx):
+    L = 64
+    a = np.zeros(L, dtype=np.uint8); b = np.zeros(L, dtype=np.uint8); b[:10] = 1
+    s = np.stack([a, b])
+    ctx.set_alignment(s)
+    assert list(ctx.neighbour_counts(55, True)) == [2, 2]
+    assert list(ctx.neighbour_counts(55, False)) == [1, 1]
+    assert list(ctx.neighbour_counts(87, True)) == [1, 1]
+    g = np.full((2, 40), 4, dtype=np.uint8)
+    ctx.set_alignment(g)
+    assert list(ctx.neighbour_counts(40, True)) == [2, 2]
+
+
+# ---------------------------------------------------------------- fp64 MI kernels
+@pytest.mark.parametrize("case", KAT["mi"], ids=lambda c: c["name"])
+def test_mi_pairs_known_answers(ctx, case):
+    s = np.stack([np.array(case["col_i"], dtype=np.uint8), np.array(case["col_j"], dtype=np.uint8)], axis=1)
+    ctx.set_alignment(s)
+    ctx.set_weights(np.array(case["w"]))
+    got = ctx.mi_pairs([0], [1], case["pc"])[0]
+    assert got == pytest.approx(case["mi"], rel=1e-12, abs=1e-14)
+
+
+def test_mi_pairs_vs_oracle(ctx):
+    s, _, _ = generate_alignment(300, 500, seed=7)
+    w = orc.weights_from_counts(orc.neighbour_counts(s, int(0.9 * 500)))
+    ctx.set_alignment(s); ctx.set_weights(w)
+    pi, pj = orc.sample_pairs(4000, 499, seed=3)
+    got = ctx.mi_pairs(pi, pj)
+    exp = orc.mi_pairs(s, w, pi, pj)
+    assert np.allclose(got, exp, rtol=1e-11, atol=1e-14)
+    # symmetry
+    got2 = ctx.mi_pairs(pj, pi)
+    assert np.allclose(got, got2, rtol=1e-11, atol=1e-14)
+
+
+@pytest.mark.parametrize("n,L,linear,ld", [(120, 300, False, 0), (77, 130, True, 40), (64, 96, False, 25)])
+def test_exhaustive_scan_vs_oracle(ctx, n, L, linear, ld):
+    s, pos, _ = generate_alignment(n, L, seed=n * L)
+    w = orc.weights_from_counts(orc.neighbour_counts(s, int(0.9 * L)))
+    ctx.set_alignment(s, pos); ctx.set_weights(w)
+    thr = 0.04
+    exp = orc.mi_scan(s, w, pos, threshold=thr, ld_threshold=ld, linear_genome=linear, circle_size=L)
+    got = ctx.mi_scan(thr, ld_threshold=ld, linear_genome=linear, engine=1, sort_desc=True)
+    e_exp = orc.sort_edges(exp["edges"]); e_got = got["edges"]
+    assert len(e_got) == len(e_exp) > 0
+    assert np.array_equal(e_got["i"], e_exp["i"]) and np.array_equal(e_got["j"], e_exp["j"])
+    assert np.allclose(e_got["mi"], e_exp["mi"], rtol=1e-11, atol=1e-14)
+    assert np.allclose(got["colmax"], exp["colmax"], rtol=1e-11, atol=1e-14)
+    wo_exp = {(int(a), int(b)): m for a, b, m in exp["edges_wo_gaps"]}
+    wo_got = {(int(a), int(b)): m for a, b, m in got["edges_wo_gaps"]}
+    assert wo_exp.keys() == wo_got.keys()
+    for k in wo_exp:
+        assert wo_got[k] == pytest.approx(wo_exp[k], rel=1e-10, abs=1e-13)
+    assert ctx.outlier_thresholds(got["colmax"]) == pytest.approx(orc.outlier_thresholds(exp["colmax"]), rel=1e-10)
+
+
+def test_exhaustive_scan_partition_union(ctx):
+    s, pos, _ = generate_alignment(60, 200, seed=5)
+    ctx.set_alignment(s, pos)
+    whole = ctx.mi_scan(0.05, engine=1)
+    parts = [ctx.mi_scan(0.05, engine=1, part_index=k, n_parts=3) for k in range(3)]
+    assert sum(p["n_edges"] for p in parts) == whole["n_edges"]
+    u = set().union(*[_edge_set(p["edges"]) for p in parts])
+    assert u == _edge_set(whole["edges"])
+    cm = np.max(np.stack([p["colmax"] for p in parts]), axis=0)
+    assert np.array_equal(cm, whole["colmax"])
+
+
+def test_threshold_estimator_vs_oracle_logic(ctx):
+    s, _, _ = generate_alignment(150, 400, seed=8)
+    w = orc.weights_from_counts(orc.neighbour_counts(s, int(0.9 * 400)))
+    ctx.set_alignment(s); ctx.set_weights(w)
+    thr = ctx.determine_mi_threshold(4000, iterations=3, seed=5)
+    # the estimate is a quantile of the empirical MI distribution: check against the exact distribution
+    full = orc.mi_scan(s, w, threshold=-1.0)["edges"]["mi"]
+    frac_above = (full > thr).mean()
+    assert 0.5 * 4000 / len(full) < frac_above < 2.0 * 4000 / len(full)
+
+
+# ---------------------------------------------------------------- sort + K3
+def test_sort_edges_bit_exact(ctx):
+    rng = np.random.default_rng(1)
+    e = np.zeros(5000, dtype=EDGE_DTYPE)
+    e["i"] = rng.integers(0, 300, 5000); e["j"] = e["i"] + 1 + rng.integers(0, 300, 5000)
+    e["mi"] = np.round(rng.random(5000), 2)            # many ties -> id tie-break exercised
+    got = ctx.sort_edges(e); exp = orc.sort_edges(e)
+    assert got.tobytes() == exp.tobytes()
+    k = _edges(KAT["sort"]["edges"])
+    assert [[int(a), int(b), float(c)] for a, b, c in ctx.sort_edges(k)] == KAT["sort"]["sorted"]
+
+
+@pytest.mark.parametrize("case", KAT["aracne"], ids=lambda c: c["name"])
+def test_aracne_known_answers(ctx, case):
+    assert list(ctx.aracne(_edges(case["edges"]), EPS)) == case["direct"]
+
+
+@pytest.mark.parametrize("trial", range(4))
+def test_aracne_vs_oracle_random(ctx, trial):
+    rng = np.random.default_rng(30 + trial)
+    nn = [40, 200, 600, 1500][trial]
+    m = [300, 6000, 30000, 100000][trial]
+    a = rng.integers(0, nn, m); b = rng.integers(0, nn, m)
+    keep = a != b
+    lo = np.minimum(a, b)[keep]; hi = np.maximum(a, b)[keep]
+    uniq = np.unique(lo.astype(np.uint64) << 32 | hi.astype(np.uint64))
+    e = np.zeros(len(uniq), dtype=EDGE_DTYPE)
+    e["i"] = (uniq >> 32).astype(np.uint32); e["j"] = (uniq & 0xffffffff).astype(np.uint32)
+    e["mi"] = np.round(rng.random(len(uniq)), 3 if trial % 2 else 12)
+    e = orc.sort_edges(e)
+    for thr in (EPS, 0.0, 0.05):
+        exp = orc.aracne_closed(e, thr)
+        assert np.array_equal(ctx.aracne(e, thr), exp)
+    if trial < 3:
+        assert np.array_equal(orc.aracne_blocked(e, EPS, 16384), orc.aracne_closed(e, EPS))
+    # edge-range partition (multi-GPU sharding of K3)
+    f = np.zeros(len(e), dtype=np.uint8)
+    for k in range(3):
+        fk = ctx.aracne(e, EPS, part_index=k, n_parts=3)
+        lo_, hi_ = len(e) * k // 3, len(e) * (k + 1) // 3
+        f[lo_:hi_] = fk[lo_:hi_]
+    assert np.array_equal(f, orc.aracne_closed(e, EPS))
+
+
+def test_error_behaviour(ctx):
+    from spydrpick_b200 import SpkError
+    c2 = Context()
+    with pytest.raises(SpkError):
+        c2.neighbour_counts(10)                      # no alignment
+    s, _, _ = generate_alignment(20, 40, seed=2, n_planted=0)
+    c2.set_alignment(s)
+    with pytest.raises(SpkError):
+        c2.mi_pairs([0], [40])                       # column out of range
+    with pytest.raises(SpkError):
+        c2.mi_scan(0.1, pseudocount=0.0)
+    c2.close()

@@ -1,0 +1,120 @@
+"""GPU parity tests for K2: the tcgen05 one-hot GEMM + fused epilogue (filter) followed by the fp64
+refine, against the CPU oracle. Named *_z* so that it runs after the simpler kernels.
+
+Tolerance (BASELINE.json north_star): MI within 1e-5 relative; saved-edge set identical except pairs
+whose MI lies within the tolerance band of the threshold. Because every saved edge is recomputed
+in fp64 with the reference's formula, the observed differences are ~1e-13 and the edge sets equal."""
+import numpy as np
+import pytest
+
+import oracle.oracle as orc
+from spydrpick_b200 import Context
+from spydrpick_b200.synth import generate_alignment
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = Context()
+    yield c
+    c.close()
+
+
+def _expected_counts(s, w, ib, jb):
+    n, L = s.shape
+    out = np.zeros((32, 64, 4, 4), dtype=np.float64)
+    for il in range(32):
+        i = ib * 32 + il
+        if i >= L:
+            continue
+        for jl in range(64):
+            j = jb * 64 + jl
+            if j >= L:
+                continue
+            for a in range(4):
+                ma = (s[:, i] == a)
+                for b in range(4):
+                    out[il, jl, a, b] = w[ma & (s[:, j] == b)].sum()
+    return out
+
+
+@pytest.mark.parametrize("T", [1, 2, 3])
+def test_tcgen05_tile_counts(ctx, T):
+    """Raw TMEM accumulators of one tile vs directly summed weighted joint counts."""
+    s, _, _ = generate_alignment(200, 150, seed=42, n_planted=0)
+    w = orc.weights_from_counts(orc.neighbour_counts(s, int(0.9 * 150)))
+    ctx.set_alignment(s); ctx.set_weights(w)
+    for ib, jb in [(0, 0), (1, 1), (4, 2)]:
+        got = ctx.debug_tile_counts(ib, jb, T).astype(np.float64)
+        exp = _expected_counts(s, w, ib, jb)
+        tol = {1: 4e-3, 2: 3e-5, 3: 2e-6}[T] * max(1.0, exp.max())
+        assert np.isfinite(got).all()
+        assert np.abs(got - exp).max() <= tol, (T, ib, jb, np.abs(got - exp).max())
+    # unweighted: integer counts must be exact in fp32
+    ctx.set_weights(np.ones(200))
+    got = ctx.debug_tile_counts(0, 1, T)
+    assert np.array_equal(got.astype(np.float64), _expected_counts(s, np.ones(200), 0, 1))
+
+
+@pytest.mark.parametrize("n,L,linear,ld,T", [(200, 500, False, 0, 2), (130, 333, True, 30, 3), (257, 700, False, 100, 1),
+                                              (64, 64, False, 0, 2), (90, 1100, False, 0, 2)])
+def test_scan_tcgen05_vs_oracle(ctx, n, L, linear, ld, T):
+    s, pos, _ = generate_alignment(n, L, seed=n + L)
+    w = orc.weights_from_counts(orc.neighbour_counts(s, int(0.9 * L)))
+    ctx.set_alignment(s, pos); ctx.set_weights(w)
+    thr = 0.05
+    exp = orc.mi_scan(s, w, pos, threshold=thr, ld_threshold=ld, linear_genome=linear, circle_size=L)
+    got = ctx.mi_scan(thr, ld_threshold=ld, linear_genome=linear, n_terms=T, sort_desc=True)
+    e_exp = orc.sort_edges(exp["edges"]); e_got = got["edges"]
+    assert got["n_candidates"] >= len(e_exp)
+    assert len(e_got) == len(e_exp) > 0
+    assert np.array_equal(e_got["i"], e_exp["i"]) and np.array_equal(e_got["j"], e_exp["j"])
+    assert np.allclose(e_got["mi"], e_exp["mi"], rtol=1e-5, atol=0)         # north-star tolerance
+    assert np.allclose(e_got["mi"], e_exp["mi"], rtol=1e-10, atol=1e-13)    # what fp64 refine actually gives
+    assert np.allclose(got["colmax"], exp["colmax"], rtol=1e-10, atol=1e-13)
+    wo_exp = {(int(a), int(b)): m for a, b, m in exp["edges_wo_gaps"]}
+    wo_got = {(int(a), int(b)): m for a, b, m in got["edges_wo_gaps"]}
+    assert wo_exp.keys() == wo_got.keys()
+    for k in wo_exp:
+        assert wo_got[k] == pytest.approx(wo_exp[k], rel=1e-9, abs=1e-12)
+    assert got["max_filter_error"] < {1: 2e-3, 2: 1e-4, 3: 1e-4}[T]
+
+
+def test_scan_partition_union_and_engines_agree(ctx):
+    s, pos, _ = generate_alignment(150, 900, seed=77)
+    w = orc.weights_from_counts(orc.neighbour_counts(s, int(0.9 * 900)))
+    ctx.set_alignment(s, pos); ctx.set_weights(w)
+    whole = ctx.mi_scan(0.06)
+    exact = ctx.mi_scan(0.06, engine=1)
+    assert whole["edges"].tobytes() == exact["edges"].tobytes()
+    assert np.array_equal(whole["colmax"], exact["colmax"])
+    parts = [ctx.mi_scan(0.06, part_index=k, n_parts=4) for k in range(4)]
+    assert sum(p["n_edges"] for p in parts) == whole["n_edges"]
+    merged = np.concatenate([p["edges"] for p in parts])
+    assert ctx.sort_edges(merged).tobytes() == whole["edges"].tobytes()
+    assert np.array_equal(np.max(np.stack([p["colmax"] for p in parts]), axis=0), whole["colmax"])
+
+
+def test_full_pipeline_outputs_match_oracle():
+    """weights -> scan -> sort -> ARACNE -> text files, byte-identical to the oracle's."""
+    from spydrpick_b200 import host
+    s, pos, gsize = generate_alignment(200, 800, seed=20260101)
+    opt = host.Options(mi_threshold=0.05)
+    ali = host.Alignment(s, pos, n_original_positions=gsize)
+    net = host.run_pipeline(ali, opt)
+    counts = orc.neighbour_counts(s, int(0.9 * 800), True)
+    assert np.array_equal(ali.neighbour_counts, counts)
+    w = orc.weights_from_counts(counts)
+    r = orc.mi_scan(s, w, pos, threshold=0.05, circle_size=800)
+    e = orc.sort_edges(r["edges"])
+    flags = orc.aracne_blocked(e, host.DBL_EPSILON, 16384)
+    assert np.array_equal(net.network["i"], e["i"]) and np.array_equal(net.network["j"], e["j"])
+    assert np.array_equal(net.flags, flags)
+    outlier, extreme = orc.outlier_thresholds(r["colmax"])
+    assert net.outlier_threshold == pytest.approx(outlier, rel=1e-10)
+    exp_txt = orc.format_edges(e, flags, pos, 1, False, gsize)
+    assert host.format_edges(net, ali, opt) == exp_txt
+    exp_out = orc.format_outliers(e, flags, r["edges_wo_gaps"], pos, outlier, extreme, 1, False, gsize, 0)
+    assert host.format_outliers(net, ali, opt) == exp_out
+    ali.ctx.close()
