@@ -1,0 +1,351 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the hot path: weighted all-pairs MI scan + ARACNE.
+
+Workload (BASELINE.json configs[1]): synthetic bacterial-like alignment, 3,000 sequences x 100,000
+filtered SNP columns. One STEP = one pass of the hot path: K1 neighbour counts -> weights -> K2 scan
+(tcgen05 filter + fp64 refine + compaction) -> edge sort -> K3 ARACNE. `value` = column pairs per
+second with the alignment already resident in HBM; `e2e` = the same step through the host-buffer
+C-ABI (alignment H2D and edges / flags D2H inside the timed region).
+
+  python bench.py --gpus N --steps K --warmup W            (N>1: launched by torch.distributed.run)
+  python bench.py --impl reference ...                      (CPU port of the reference, bounded sample)
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "weighted_mi_scan_gpairs_per_s"
+UNIT = "Gpairs/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--n", type=int, default=3000)
+    ap.add_argument("--L", type=int, default=100000)
+    ap.add_argument("--seed", type=int, default=20260102)
+    ap.add_argument("--n-terms", type=int, default=0)
+    ap.add_argument("--mi-values", type=int, default=0, help="saved pairs target (0 = min(1e7, 100*L))")
+    ap.add_argument("--cpu-sample-seconds", type=float, default=15.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"bf16_tflops": d.get("bf16_tflops_sustained", d.get("bf16_tflops", 1400.0)), "hbm_gbs": d.get("hbm_gbs", 6650.0),
+                "source": "measured (MEASURED_PEAKS.json, sustained bf16)"}
+    return {"bf16_tflops": 1400.0, "hbm_gbs": 6650.0, "source": "fallback (B200_PROFILING.md)"}
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons during the timed region."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index=0):
+        self.index = index; self.samples = []; self.stop = False; self.t = None
+
+    def _run(self):
+        while not self.stop:
+            try:
+                out = subprocess.check_output(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                               "--format=csv,noheader,nounits"], timeout=5).decode().strip()
+                self.samples.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def __enter__(self):
+        self.t = threading.Thread(target=self._run, daemon=True); self.t.start(); return self
+
+    def __exit__(self, *a):
+        self.stop = True; self.t.join(timeout=6)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unavailable"]}
+        sm = sorted(float(s[0]) for s in self.samples if s[0].replace(".", "").isdigit())
+        mx = [float(s[1]) for s in self.samples if s[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [nm for k, nm in enumerate(names) if any(len(s) > 2 + k and s[2 + k].lower().startswith("active") for s in self.samples)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons}
+
+
+def make_workload(args):
+    from spydrpick_b200.synth import generate_alignment
+    return generate_alignment(args.n, args.L, seed=args.seed)
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU baseline: the oracle port of the reference, all host threads, bounded sample of the workload
+# ------------------------------------------------------------------------------------------------
+def cpu_baseline(states, pos, weights, threshold, seconds):
+    import oracle.oracle as orc
+    n, L = states.shape
+    cores = orc.hardware_threads()
+    # calibrate on a small column subset, then size the sample for ~`seconds` of work
+    Lc = min(L, 400)
+    t0 = time.time(); orc.mi_scan(states[:, :Lc], weights, pos[:Lc], threshold=threshold, circle_size=Lc); dt = time.time() - t0
+    rate = (Lc * (Lc - 1) / 2) / max(dt, 1e-6)
+    Ls = int(min(L, max(Lc, (2 * seconds * rate) ** 0.5)))
+    t0 = time.time()
+    r = orc.mi_scan(states[:, :Ls], weights, pos[:Ls], threshold=threshold, circle_size=Ls)
+    e = orc.sort_edges(r["edges"]); orc.aracne_closed(e)
+    dt = time.time() - t0
+    pairs = Ls * (Ls - 1) / 2
+    return {"value": pairs / dt / 1e9, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": "first %d of %d columns (all %d samples): %d pairs, scan+sort+ARACNE in %.1f s" % (Ls, L, n, pairs, dt)}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path (oracle port: the reference binary needs Boost + TBB,
+    absent here), all host threads, bounded sample per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import oracle.oracle as orc
+    states, pos, _ = make_workload(args)
+    n, L = states.shape
+    Ls = min(L, 1500)          # bounded sample: ~1.1M pairs per step
+    sub = np.ascontiguousarray(states[:, :Ls])
+    thr = 0.05
+    times = []
+    for it in range(args.warmup + args.steps):
+        t0 = time.time()
+        counts = orc.neighbour_counts(sub, int(0.9 * Ls), True)
+        w = orc.weights_from_counts(counts)
+        r = orc.mi_scan(sub, w, pos[:Ls], threshold=thr, circle_size=Ls)
+        e = orc.sort_edges(r["edges"]); orc.aracne_closed(e)
+        if it >= args.warmup:
+            times.append(time.time() - t0)
+    pairs = Ls * (Ls - 1) / 2
+    ms = 1e3 * sum(times) / len(times)
+    v = pairs / (ms / 1e3) / 1e9
+    sample = "first %d of %d columns, all %d samples (%d pairs per step)" % (Ls, L, n, pairs)
+    print(json.dumps({"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+                      "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                      "dtype": "f64", "data": "synthetic",
+                      "config": {"workload": "3000x100000 synthetic SNP alignment, MI scan + ARACNE (CPU port on a bounded sample)",
+                                 "n": n, "L": L, "sample": sample},
+                      "cpu_baseline": {"value": v, "unit": UNIT, "cores": orc.hardware_threads(), "kind": "port", "sample": sample},
+                      "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+class _DevView:
+    """Wraps a raw device pointer so torch can view it (__cuda_array_interface__)."""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (int(nbytes),), "typestr": "|u1", "data": (int(ptr), False), "version": 2}
+
+
+def dev_bytes(torch, ptr, nbytes, device):
+    if nbytes == 0:
+        return torch.empty(0, dtype=torch.uint8, device=device)
+    return torch.as_tensor(_DevView(ptr, nbytes), device=device)
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from spydrpick_b200 import Context
+    world = int(os.environ.get("WORLD_SIZE", "1")); rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the B200 path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+
+    # ---- workload: rank 0 generates, alignment broadcast ONCE over NCCL (outside the timed region)
+    n, L = args.n, args.L
+    if rank == 0:
+        states, pos, gsize = make_workload(args)
+    if world > 1:
+        st = torch.from_numpy(states).to(device) if rank == 0 else torch.empty((n, L), dtype=torch.uint8, device=device)
+        ps = torch.from_numpy(pos.astype(np.int64)).to(device) if rank == 0 else torch.empty(L, dtype=torch.int64, device=device)
+        dist.broadcast(st, 0); dist.broadcast(ps, 0)
+        states = st.cpu().numpy(); pos = ps.cpu().numpy().astype(np.uint64)
+        del st, ps
+    pairs_total = L * (L - 1) // 2
+    mi_values = args.mi_values or min(10_000_000, 100 * L)
+
+    ctx = Context(device=local_rank)
+    stream = torch.cuda.current_stream(device)
+    ctx.set_stream(stream.cuda_stream)
+    ctx.set_alignment(states, pos)
+    min_ident = int(0.9 * float(L))
+    counts = ctx.neighbour_counts(min_ident, True)
+    weights = 1.0 / counts.astype(np.float64)
+    ctx.set_weights(weights)
+    # pinned save threshold from one K2b estimate (untimed; the reference's estimate is clock-seeded)
+    t0 = time.time()
+    threshold = ctx.determine_mi_threshold(mi_values, iterations=10, seed=args.seed)
+    t_threshold = time.time() - t0
+    if world > 1:
+        tt = torch.tensor([threshold], dtype=torch.float64, device=device); dist.broadcast(tt, 0); threshold = float(tt.item())
+    max_edges = int(mi_values * 2.5) + 65536
+    EPS = 2.220446049250313e-16
+
+    def merge_across_ranks(r):
+        """Edge allgather over NCCL/NVLink before ARACNE (+ colmax allreduce-max). Returns (edge tensor, n_edges)."""
+        ne = r["n_edges"]
+        if world == 1:
+            return None, r["d_edges"], ne
+        cnt = torch.tensor([ne], dtype=torch.int64, device=device)
+        allc = [torch.zeros(1, dtype=torch.int64, device=device) for _ in range(world)]
+        dist.all_gather(allc, cnt)
+        allc = [int(c.item()) for c in allc]
+        mx = max(allc)
+        mine = torch.zeros(mx * 16, dtype=torch.uint8, device=device)
+        if ne:
+            mine[:ne * 16].copy_(dev_bytes(torch, r["d_edges"], ne * 16, device))
+        gathered = torch.empty(world * mx * 16, dtype=torch.uint8, device=device)
+        dist.all_gather_into_tensor(gathered, mine)
+        merged = torch.cat([gathered[k * mx * 16: k * mx * 16 + allc[k] * 16] for k in range(world)])
+        cm = dev_bytes(torch, r["d_colmax"], L * 8, device).view(torch.float64)
+        dist.all_reduce(cm, op=dist.ReduceOp.MAX)
+        return merged, merged.data_ptr(), sum(allc)
+
+    def step_device():
+        """alignment resident in HBM; results stay in HBM."""
+        c = ctx.neighbour_counts(min_ident, True)
+        ctx.set_weights(1.0 / c.astype(np.float64))
+        r = ctx.mi_scan(threshold, max_edges=max_edges, sort_desc=(world == 1), n_terms=args.n_terms,
+                        part_index=rank, n_parts=world, keep_on_device=True)
+        keep, d_edges, ne = merge_across_ranks(r)
+        if world > 1:
+            ctx.sort_edges_device(d_edges, ne)
+        flags = torch.zeros(max(ne, 1), dtype=torch.uint8, device=device)
+        ctx.aracne_device(d_edges, ne, flags.data_ptr(), EPS, part_index=rank, n_parts=world)
+        if world > 1:
+            # flag shards -> every rank (edge-range partition of K3)
+            bounds = [ne * k // world for k in range(world + 1)]
+            mx = max(bounds[k + 1] - bounds[k] for k in range(world))
+            mine = torch.zeros(mx, dtype=torch.uint8, device=device)
+            mine[:bounds[rank + 1] - bounds[rank]].copy_(flags[bounds[rank]:bounds[rank + 1]])
+            allf = torch.empty(world * mx, dtype=torch.uint8, device=device)
+            dist.all_gather_into_tensor(allf, mine)
+        return r, ne, int(flags[:ne].sum().item()) if world == 1 else 0
+
+    def step_e2e():
+        """host buffers through the C-ABI: H2D of the alignment, D2H of edges + flags inside the step."""
+        ctx.set_alignment(states, pos)
+        c = ctx.neighbour_counts(min_ident, True)
+        ctx.set_weights(1.0 / c.astype(np.float64))
+        r = ctx.mi_scan(threshold, max_edges=max_edges, sort_desc=(world == 1), n_terms=args.n_terms,
+                        part_index=rank, n_parts=world, keep_on_device=False)
+        edges = r["edges"]
+        if world > 1:
+            gathered = [None] * world
+            dist.all_gather_object(gathered, edges.tobytes())
+            from spydrpick_b200 import EDGE_DTYPE
+            edges = ctx.sort_edges(np.concatenate([np.frombuffer(b, dtype=EDGE_DTYPE) for b in gathered]))
+        flags = ctx.aracne(edges, EPS, part_index=rank, n_parts=world)
+        h2d = states.nbytes + pos.nbytes + 8 * n + (edges.nbytes + len(flags) if len(edges) else 0)
+        d2h = edges.nbytes + r["edges_wo_gaps"].nbytes + 8 * L + 8 * n + len(flags)
+        return h2d, d2h
+
+    def timed(fn, steps, warmup, with_clocks=False):
+        for _ in range(warmup):
+            out = fn()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+        sampler = ClockSampler(local_rank) if with_clocks else None
+        if sampler:
+            sampler.__enter__()
+        lt0 = ctx.timings()["kernel_launches"]
+        e0.record(stream)
+        for _ in range(steps):
+            out = fn()
+        e1.record(stream)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        if sampler:
+            sampler.__exit__()
+        ms = e0.elapsed_time(e1) / steps
+        launches = (ctx.timings()["kernel_launches"] - lt0) // max(steps, 1)
+        if world > 1:
+            t = torch.tensor([ms], dtype=torch.float64, device=device); dist.all_reduce(t, op=dist.ReduceOp.MAX); ms = float(t.item())
+        return ms, out, launches, (sampler.summary() if sampler else None)
+
+    ms, (r, ne, ndirect), launches, clocks = timed(step_device, args.steps, args.warmup, with_clocks=True)
+    tm = ctx.timings()
+    value = pairs_total / (ms / 1e3) / 1e9
+
+    # roofline of the dominant kernel (K2 tcgen05 GEMM): algorithmic flops = 2*16*n per pair
+    pk = peaks()
+    tiles = tm["gemm_tiles"]
+    pairs_launch = tiles * 32 * 64                       # pairs one launch (this rank) covers, incl. masked diagonal halves
+    flops = 2.0 * 16.0 * n * pairs_launch
+    achieved = flops / (tm["gemm_ms"] / 1e3) / 1e12 if tm["gemm_ms"] > 0 else 0.0
+    roofline = {"bound": "tensor", "achieved": achieved, "peak": pk["bf16_tflops"], "unit": "TFLOP/s",
+                "frac": achieved / pk["bf16_tflops"], "traffic": None, "kernel": "mi_gemm_kernel", "kernel_ms": tm["gemm_ms"],
+                "peak_source": pk["source"],
+                "note": "algorithmic 32*n flop/pair; executed tensor flops are n_terms x that (bf16 weight split)"}
+
+    e2e = None
+    if not args.no_e2e:
+        ems, (h2d, d2h), _, _ = timed(step_e2e, max(1, min(args.steps, 2)), 1)
+        e2e = {"value": pairs_total / (ems / 1e3) / 1e9, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+               "ms_per_step": ems}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu = cpu_baseline(states, pos, weights, threshold, args.cpu_sample_seconds)
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bf16",
+                "data": "synthetic",
+                "config": {"workload": "%dx%d synthetic SNP alignment: K1 reweighting + weighted MI scan + sort + ARACNE" % (n, L),
+                           "n": n, "L": L, "pairs": pairs_total, "saved_edges": int(ne), "mi_threshold": threshold,
+                           "n_terms": args.n_terms or 2, "l2_policy": "inputs (>=2.4 GB one-hot operands) larger than L2",
+                           "threshold_estimate_s": t_threshold, "parallelism": "tile-space partition x%d + NCCL edge allgather" % world},
+                "clocks": clocks, "gpu_launches": int(launches),
+                "stages_ms": {k: tm[k] for k in ("hamming_ms", "stats_ms", "expand_ms", "gemm_ms", "refine_ms", "compact_ms",
+                                                 "sort_ms", "aracne_build_ms", "aracne_ms")},
+                "candidates": r["n_candidates"], "max_filter_error": r["max_filter_error"],
+                "roofline": roofline}
+        if e2e:
+            line["e2e"] = e2e
+        if cpu:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line))
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

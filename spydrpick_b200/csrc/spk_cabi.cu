@@ -285,7 +285,7 @@ int spk_mi_scan(spk_ctx* c, const spk_scan_params* pp, spk_scan_result* res) {
     if (!(p.pseudocount > 0.0)) return fail(c, SPK_E_INVALID, "mi_scan: pseudocount must be > 0 (0 makes the reference produce NaN via 0*log 0)");
     const int T = p.n_terms ? p.n_terms : 2;
     if (T < 1 || T > 3) return fail(c, SPK_E_INVALID, "mi_scan: n_terms must be 1..3");
-    const double band = p.band > 0.0 ? p.band : (T == 1 ? 4e-3 : 2e-4);
+    const double band = p.band > 0.0 ? p.band : (T == 1 ? 1e-2 : 2e-4);
     const uint64_t circle = p.circle_size ? p.circle_size : c->L;
     if (p.n_parts == 0) p.n_parts = 1;
     if (p.part_index >= p.n_parts) return fail(c, SPK_E_INVALID, "mi_scan: part_index >= n_parts");

@@ -53,7 +53,7 @@ struct GemmParams {
     uint32_t rows_per_term;            // 4*L_pad (row offset between weight terms in V)
     uint32_t part, n_parts;
     unsigned long long n_local_slots;
-    float w_total, pc, thr_lo, band;
+    float w_total, pc, thr_lo, thr_hi, band;
     unsigned long long ld_threshold, circle; int linear;
     float* debug_out;                  // non-null: single tile (debug_ib, debug_jb), raw counts dump
     uint32_t debug_ib, debug_jb;
@@ -196,7 +196,8 @@ mi_gemm_kernel(const __grid_constant__ CUtensorMap map_v, const __grid_constant_
     ColStat* sI = (ColStat*)aux;                                  // [32]
     ColStat* sJ = sI + TILE_I;                                    // [64]
     uint32_t* s_cmj = (uint32_t*)(sJ + TILE_J);                   // [64] running colmax of the tile's j columns
-    uint64_t* full_bar = (uint64_t*)(s_cmj + TILE_J);
+    float* s_mi = (float*)(s_cmj + TILE_J);                       // [16][128] fp32 MI of the tile (pass 1 -> pass 2)
+    uint64_t* full_bar = (uint64_t*)(s_mi + 16 * 128);
     uint64_t* empty_bar = full_bar + NSTAGES;
     uint64_t* tfull_bar = empty_bar + NSTAGES;                    // [2]
     uint64_t* tempty_bar = tfull_bar + 2;                         // [2]
@@ -301,6 +302,7 @@ mi_gemm_kernel(const __grid_constant__ CUtensorMap map_v, const __grid_constant_
             const unsigned long long pos_i = ((unsigned long long)sI[i_local].pos_hi << 32) | sI[i_local].pos_lo;
             float cm_i = f32_from_ordered(p.colmax32[gi]);
             float cm_i_new = cm_i;
+            uint32_t ldmask = 0;
 
             mbar_wait(&tfull_bar[buf], acc_phase);
             tcgen05_fence_after();
@@ -341,46 +343,60 @@ mi_gemm_kernel(const __grid_constant__ CUtensorMap map_v, const __grid_constant_
                 const ColStat& cj = sJ[j_local];
                 const uint32_t mask_j = cj.mask, np_j = cj.npres;
                 const bool valid = (gi < gj) && (gj < p.L) && np_i && np_j;
-                float mi32 = 0.f;
+                float mi32 = __int_as_float(0x7fc00000);                   // NaN marks "no pair here"
                 if (valid) {
                     float m_j[4] = {cj.m[0], cj.m[1], cj.m[2], cj.m[3]};
                     const float invZ = __frcp_rn(p.w_total + p.pc * (float)(np_i * np_j));
                     mi32 = pair_mi32(v, m_i, mask_i, sI[i_local].h[np_j - 1], m_j, mask_j, cj.h[np_i - 1], p.pc, invZ);
-                }
-                bool emit = valid && (mi32 > p.thr_lo);
-                if (valid) {
                     const unsigned long long pos_j = ((unsigned long long)cj.pos_hi << 32) | cj.pos_lo;
                     if (genome_distance(pos_i, pos_j, p.linear, p.circle) > p.ld_threshold) {
-                        const float cm_j = f32_from_ordered(s_cmj[j_local]);
-                        emit = emit || (mi32 >= cm_i_new - p.band) || (mi32 >= cm_j - p.band);
+                        ldmask |= 1u << c;
                         cm_i_new = fmaxf(cm_i_new, mi32);
-                        if (mi32 > cm_j) atomicMax(&s_cmj[j_local], f32_ordered(mi32));
+                        if (mi32 > f32_from_ordered(s_cmj[j_local])) atomicMax(&s_cmj[j_local], f32_ordered(mi32));
                     }
                 }
-                const uint32_t bal = __ballot_sync(0xffffffffu, emit);
-                if (bal) {
-                    unsigned long long base = 0;
-                    if (lane == 0) base = atomicAdd(&p.counters[0], (unsigned long long)__popc(bal));
-                    base = __shfl_sync(0xffffffffu, base, 0);
-                    if (emit) {
-                        const unsigned long long idx = base + __popc(bal & ((1u << lane) - 1u));
-                        if (idx < p.cand_cap) { Candidate cd; cd.i = gi; cd.j = gj; cd.mi32 = mi32; cd.pad = 0; p.cand[idx] = cd; }
-                        else p.counters[4] = 1ull;
-                    }
-                }
+                s_mi[c * 128 + et] = mi32;
             }
             // accumulator drained: hand the TMEM buffer back to the MMA warp
             tcgen05_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&tempty_bar[buf]);
-            // publish running maxima
             if (!p.debug_out) {
+                // tile-level maxima of this thread's i column (4 lanes of the quad cover different j)
                 cm_i_new = fmaxf(cm_i_new, __shfl_xor_sync(0xffffffffu, cm_i_new, 1));
                 cm_i_new = fmaxf(cm_i_new, __shfl_xor_sync(0xffffffffu, cm_i_new, 2));
                 if (q4 == 0 && cm_i_new > cm_i) atomicMax(&p.colmax32[gi], f32_ordered(cm_i_new));
             }
-            asm volatile("bar.sync 1, 128;" ::: "memory");
-            if (!p.debug_out && et < TILE_J) atomicMax(&p.colmax32[jb * TILE_J + et], s_cmj[et]);
+            asm volatile("bar.sync 1, 128;" ::: "memory");                 // s_cmj now holds the tile-level j maxima
+            if (!p.debug_out) {
+                if (et < TILE_J) atomicMax(&p.colmax32[jb * TILE_J + et], s_cmj[et]);
+                // pass 2: candidate emission. A pair is a candidate if its fp32 MI is within `band` of the save
+                // threshold, or (LD-admissible) within `band` of the running maximum of one of its columns while
+                // that maximum has not yet cleared thr+band (columns above it are covered by the threshold rule).
+                const bool i_open = !(cm_i_new > p.thr_hi);
+#pragma unroll 1
+                for (uint32_t c = 0; c < 16; ++c) {
+                    const float mi32 = s_mi[c * 128 + et];
+                    const uint32_t j_local = c * 4 + q4;
+                    bool emit = mi32 > p.thr_lo;                           // false for NaN
+                    if ((ldmask >> c) & 1u) {
+                        const float cm_j = f32_from_ordered(s_cmj[j_local]);
+                        emit = emit || (i_open && mi32 >= cm_i_new - p.band) || (!(cm_j > p.thr_hi) && mi32 >= cm_j - p.band);
+                    }
+                    const uint32_t bal = __ballot_sync(0xffffffffu, emit);
+                    if (bal) {
+                        unsigned long long base = 0;
+                        if (lane == 0) base = atomicAdd(&p.counters[0], (unsigned long long)__popc(bal));
+                        base = __shfl_sync(0xffffffffu, base, 0);
+                        if (emit) {
+                            const unsigned long long idx = base + __popc(bal & ((1u << lane) - 1u));
+                            if (idx < p.cand_cap) { Candidate cd; cd.i = gi; cd.j = jb * TILE_J + j_local; cd.mi32 = mi32; cd.pad = 0; p.cand[idx] = cd; }
+                            else p.counters[4] = 1ull;
+                        }
+                    }
+                }
+            }
+            asm volatile("bar.sync 1, 128;" ::: "memory");                 // sI/sJ/s_cmj/s_mi free for the next tile
             ++it;
         }
     }
@@ -434,7 +450,7 @@ __global__ void fill_u32_kernel(uint32_t* p, uint32_t v, size_t n) {
 template <int T, int NSTAGES>
 static int launch_gemm(Ctx* c, const CUtensorMap& mv, const CUtensorMap& mu, const GemmParams& gp, unsigned grid) {
     constexpr size_t STAGE_BYTES = B_TILE_BYTES + T * A_TILE_BYTES;
-    const size_t smem = (size_t)NSTAGES * STAGE_BYTES + (TILE_I + TILE_J) * sizeof(ColStat) + TILE_J * 4 +
+    const size_t smem = (size_t)NSTAGES * STAGE_BYTES + (TILE_I + TILE_J) * sizeof(ColStat) + TILE_J * 4 + 16 * 128 * 4 +
                         (2 * NSTAGES + 4) * 8 + 16 + 1024;
     auto kfn = mi_gemm_kernel<T, NSTAGES>;
     SPK_CUDA(c, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -484,7 +500,7 @@ int mi_gemm_filter(Ctx* c, const spk_scan_params& p, int T, double band, uint64_
     gp.sr_prefix = d_prefix; gp.n_sr = n_sr; gp.n_i = n_i; gp.n_j = n_j;
     gp.part = p.part_index; gp.n_parts = nparts; gp.n_local_slots = local_chunks * SUPER_I;
     gp.w_total = (float)c->w_total; gp.pc = (float)p.pseudocount;
-    gp.band = (float)band; gp.thr_lo = (float)(p.threshold - band);
+    gp.band = (float)band; gp.thr_lo = (float)(p.threshold - band); gp.thr_hi = (float)(p.threshold + band);
     gp.ld_threshold = p.ld_threshold; gp.circle = circle; gp.linear = p.linear_genome;
     gp.debug_out = nullptr;
     SPK_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
