@@ -207,24 +207,15 @@ def run_b200(args):
     EPS = 2.220446049250313e-16
 
     def merge_across_ranks(r):
-        """Edge allgather over NCCL/NVLink before ARACNE (+ colmax allreduce-max). Returns (edge tensor, n_edges)."""
+        """Edge allgather over NCCL/NVLink before ARACNE (+ colmax allreduce-max). Returns (keepalive, ptr, n_edges)."""
+        from spydrpick_b200 import dist as sdist
         ne = r["n_edges"]
         if world == 1:
             return None, r["d_edges"], ne
-        cnt = torch.tensor([ne], dtype=torch.int64, device=device)
-        allc = [torch.zeros(1, dtype=torch.int64, device=device) for _ in range(world)]
-        dist.all_gather(allc, cnt)
-        allc = [int(c.item()) for c in allc]
-        mx = max(allc)
-        mine = torch.zeros(mx * 16, dtype=torch.uint8, device=device)
-        if ne:
-            mine[:ne * 16].copy_(dev_bytes(torch, r["d_edges"], ne * 16, device))
-        gathered = torch.empty(world * mx * 16, dtype=torch.uint8, device=device)
-        dist.all_gather_into_tensor(gathered, mine)
-        merged = torch.cat([gathered[k * mx * 16: k * mx * 16 + allc[k] * 16] for k in range(world)])
-        cm = dev_bytes(torch, r["d_colmax"], L * 8, device).view(torch.float64)
-        dist.all_reduce(cm, op=dist.ReduceOp.MAX)
-        return merged, merged.data_ptr(), sum(allc)
+        mine = dev_bytes(torch, r["d_edges"], ne * 16, device)
+        merged, total, _ = sdist.allgather_edges(mine, ne)
+        sdist.allreduce_colmax(dev_bytes(torch, r["d_colmax"], L * 8, device).view(torch.float64))
+        return merged, merged.data_ptr(), total
 
     def step_device():
         """alignment resident in HBM; results stay in HBM."""
@@ -238,14 +229,9 @@ def run_b200(args):
         flags = torch.zeros(max(ne, 1), dtype=torch.uint8, device=device)
         ctx.aracne_device(d_edges, ne, flags.data_ptr(), EPS, part_index=rank, n_parts=world)
         if world > 1:
-            # flag shards -> every rank (edge-range partition of K3)
-            bounds = [ne * k // world for k in range(world + 1)]
-            mx = max(bounds[k + 1] - bounds[k] for k in range(world))
-            mine = torch.zeros(mx, dtype=torch.uint8, device=device)
-            mine[:bounds[rank + 1] - bounds[rank]].copy_(flags[bounds[rank]:bounds[rank + 1]])
-            allf = torch.empty(world * mx, dtype=torch.uint8, device=device)
-            dist.all_gather_into_tensor(allf, mine)
-        return r, ne, int(flags[:ne].sum().item()) if world == 1 else 0
+            from spydrpick_b200 import dist as sdist
+            flags = sdist.allgather_flag_shards(flags, ne)       # edge-range partition of K3 -> every rank
+        return r, ne, int(flags[:ne].sum().item())
 
     def step_e2e():
         """host buffers through the C-ABI: H2D of the alignment, D2H of edges + flags inside the step."""

@@ -1,0 +1,52 @@
+"""Multi-GPU plumbing for the sharded hot path (torch.distributed; NCCL on GPUs, gloo in CPU tests).
+
+The scan shards the upper-triangle tile space (`part_index = rank`); the one exchange step before ARACNE
+is an all-gather of the per-rank edge lists plus a max-reduction of colmax. ARACNE shards
+the sorted edge range; its flag shards are all-gathered. Tensors are uint8 views of spk_edge[] (16 B).
+"""
+import torch
+import torch.distributed as dist
+
+EDGE_BYTES = 16
+
+
+def allgather_edges(mine: torch.Tensor, n_edges: int, group=None):
+    """mine: 1-D uint8 tensor whose first n_edges*16 bytes are this rank's edges.
+    Returns (merged uint8 tensor [total*16], total, per-rank counts) -- identical on every rank (rank order)."""
+    world = dist.get_world_size(group)
+    dev = mine.device
+    cnt = torch.tensor([n_edges], dtype=torch.int64, device=dev)
+    allc = [torch.zeros(1, dtype=torch.int64, device=dev) for _ in range(world)]
+    dist.all_gather(allc, cnt, group=group)
+    counts = [int(c.item()) for c in allc]
+    mx = max(max(counts), 1)
+    pad = torch.zeros(mx * EDGE_BYTES, dtype=torch.uint8, device=dev)
+    if n_edges:
+        pad[:n_edges * EDGE_BYTES].copy_(mine[:n_edges * EDGE_BYTES])
+    parts = [torch.empty_like(pad) for _ in range(world)]
+    dist.all_gather(parts, pad, group=group)
+    merged = torch.cat([parts[k][:counts[k] * EDGE_BYTES] for k in range(world)])
+    return merged, sum(counts), counts
+
+
+def allreduce_colmax(colmax: torch.Tensor, group=None):
+    """In-place element-wise max over ranks of the float64 per-column maxima (MI_solver::join, mi.hpp:355-361)."""
+    dist.all_reduce(colmax, op=dist.ReduceOp.MAX, group=group)
+    return colmax
+
+
+def shard_bounds(n_edges: int, world: int):
+    """Edge-range partition used by spk_aracne(part_index, n_parts)."""
+    return [n_edges * k // world for k in range(world + 1)]
+
+
+def allgather_flag_shards(flags: torch.Tensor, n_edges: int, group=None):
+    """flags: uint8 [>= n_edges] with this rank's shard filled in. Returns the full flag vector on every rank."""
+    world = dist.get_world_size(group); rank = dist.get_rank(group)
+    b = shard_bounds(n_edges, world)
+    mx = max(max(b[k + 1] - b[k] for k in range(world)), 1)
+    mine = torch.zeros(mx, dtype=torch.uint8, device=flags.device)
+    mine[:b[rank + 1] - b[rank]].copy_(flags[b[rank]:b[rank + 1]])
+    parts = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(parts, mine, group=group)
+    return torch.cat([parts[k][:b[k + 1] - b[k]] for k in range(world)])
