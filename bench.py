@@ -37,6 +37,7 @@ def parse_args():
     ap.add_argument("--L", type=int, default=100000)
     ap.add_argument("--seed", type=int, default=20260102)
     ap.add_argument("--n-terms", type=int, default=0)
+    ap.add_argument("--engine", type=int, default=0, help="0/3 = int8 compact one-hot GEMM (default), 2 = dense bf16 GEMM")
     ap.add_argument("--mi-values", type=int, default=0, help="saved pairs target (0 = min(1e7, 100*L))")
     ap.add_argument("--cpu-sample-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -221,7 +222,7 @@ def run_b200(args):
         """alignment resident in HBM; results stay in HBM."""
         c = ctx.neighbour_counts(min_ident, True)
         ctx.set_weights(1.0 / c.astype(np.float64))
-        r = ctx.mi_scan(threshold, max_edges=max_edges, sort_desc=(world == 1), n_terms=args.n_terms,
+        r = ctx.mi_scan(threshold, max_edges=max_edges, sort_desc=(world == 1), n_terms=args.n_terms, engine=args.engine,
                         part_index=rank, n_parts=world, keep_on_device=True)
         keep, d_edges, ne = merge_across_ranks(r)
         if world > 1:
@@ -238,7 +239,7 @@ def run_b200(args):
         ctx.set_alignment(states, pos)
         c = ctx.neighbour_counts(min_ident, True)
         ctx.set_weights(1.0 / c.astype(np.float64))
-        r = ctx.mi_scan(threshold, max_edges=max_edges, sort_desc=(world == 1), n_terms=args.n_terms,
+        r = ctx.mi_scan(threshold, max_edges=max_edges, sort_desc=(world == 1), n_terms=args.n_terms, engine=args.engine,
                         part_index=rank, n_parts=world, keep_on_device=False)
         edges = r["edges"]
         if world > 1:
@@ -284,13 +285,23 @@ def run_b200(args):
     # roofline of the dominant kernel (K2 tcgen05 GEMM): algorithmic flops = 2*16*n per pair
     pk = peaks()
     tiles = tm["gemm_tiles"]
-    pairs_launch = tiles * 32 * 64                       # pairs one launch (this rank) covers, incl. masked diagonal halves
+    pairs_launch = tm["gemm_pairs"]                      # pairs one launch (this rank) covers, incl. padding / masked diagonal halves
     flops = 2.0 * 16.0 * n * pairs_launch
     achieved = flops / (tm["gemm_ms"] / 1e3) / 1e12 if tm["gemm_ms"] > 0 else 0.0
+    i8 = args.engine in (0, 3)
+    n_pad = (n + 127) // 128 * 128
+    executed = 2.0 * 128 * 256 * n_pad * tiles * (1 if i8 else (args.n_terms or 2))   # tensor ops actually issued
+    executed_tops = executed / (tm["gemm_ms"] / 1e3) / 1e12 if tm["gemm_ms"] > 0 else 0.0
     roofline = {"bound": "tensor", "achieved": achieved, "peak": pk["bf16_tflops"], "unit": "TFLOP/s",
-                "frac": achieved / pk["bf16_tflops"], "traffic": None, "kernel": "mi_gemm_kernel", "kernel_ms": tm["gemm_ms"],
+                "frac": achieved / pk["bf16_tflops"], "traffic": None,
+                "kernel": "mi_i8_kernel" if i8 else "mi_gemm_kernel", "kernel_ms": tm["gemm_ms"],
                 "peak_source": pk["source"],
-                "note": "algorithmic 32*n flop/pair; executed tensor flops are n_terms x that (bf16 weight split)"}
+                "executed_tops": executed_tops,
+                "executed_frac_of_pipe_peak": executed_tops / (pk["bf16_tflops"] * (2.0 if i8 else 1.0)),
+                "note": ("algorithmic 32*n flop/pair vs the measured bf16 peak; the int8 compact engine issues FEWER tensor ops "
+                         "than that (only the one-hot rows a column needs, u8 x u8 -> s32 at 2x the bf16 rate), so frac may "
+                         "exceed 1; executed_frac_of_pipe_peak = issued int8 ops / (2 x measured bf16 peak)") if i8 else
+                        "algorithmic 32*n flop/pair; executed tensor flops are n_terms x that (bf16 weight split)"}
 
     e2e = None
     if not args.no_e2e:
@@ -304,11 +315,13 @@ def run_b200(args):
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bf16",
+                "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "u8 x u8 -> s32 tensor filter + f64 refine" if i8 else "bf16 tensor filter + f64 refine",
                 "data": "synthetic",
                 "config": {"workload": "%dx%d synthetic SNP alignment: K1 reweighting + weighted MI scan + sort + ARACNE" % (n, L),
                            "n": n, "L": L, "pairs": pairs_total, "saved_edges": int(ne), "mi_threshold": threshold,
-                           "n_terms": args.n_terms or 2, "l2_policy": "inputs (>=2.4 GB one-hot operands) larger than L2",
+                           "engine": "int8 compact one-hot" if i8 else "dense bf16 one-hot, n_terms=%d" % (args.n_terms or 2),
+                           "l2_policy": "inputs (>1.5 GB one-hot operands) larger than L2",
                            "threshold_estimate_s": t_threshold, "parallelism": "tile-space partition x%d + NCCL edge allgather" % world},
                 "clocks": clocks, "gpu_launches": int(launches),
                 "stages_ms": {k: tm[k] for k in ("hamming_ms", "stats_ms", "expand_ms", "gemm_ms", "refine_ms", "compact_ms",

@@ -93,9 +93,11 @@ typedef struct {
     uint64_t circle_size;      /* 0 = L (the reference's choice, apegrunt/Distance.hpp:67-71) */
     uint64_t max_edges;        /* capacity hint for saved edges; 0 = 2*min(1e7,100*L)+slack */
     int32_t  sort_desc;        /* 1: edges sorted (weight desc, id asc) = Graph::sort (graph/Graph.hpp:234-242) */
-    int32_t  n_terms;          /* bf16 terms of the weight split in the tensor-core filter: 1..3, 0 = default */
+    int32_t  n_terms;          /* engine 2 only: bf16 terms of the weight split, 1..3, 0 = default (2) */
     double   band;             /* filter safety band delta (candidates: mi32 > threshold - band); 0 = default */
-    int32_t  engine;           /* 0 = tcgen05 filter + fp64 refine (product path); 1 = fp64 exhaustive (diagnostic) */
+    int32_t  engine;           /* tensor-core filter + fp64 refine: 0 = default (= 3), 3 = int8 compact one-hot GEMM
+                                  (tcgen05 kind::i8, exact s32 counts, 16-bit weights), 2 = dense 4-state bf16 GEMM with
+                                  hi/lo weight split; 1 = fp64 exhaustive (diagnostic, no tensor cores) */
     uint32_t part_index;       /* tile-space partition for multi-GPU: this context scans part_index of n_parts */
     uint32_t n_parts;          /* 0 or 1 = whole upper triangle */
     int32_t  keep_on_device;   /* 1: do not copy edges to the host (device pointers below stay valid) */
@@ -152,6 +154,7 @@ typedef struct {
     float aracne_build_ms, aracne_ms;       /* CSR build, K3 kernel */
     float pairs_ms;                         /* K2b kernel */
     uint64_t gemm_tiles, kernel_launches;   /* tiles processed by the last scan; kernels launched since create */
+    uint64_t gemm_pairs;                    /* column pairs covered by those tiles (incl. padding / masked diagonal halves) */
 } spk_timings;
 int spk_get_timings(spk_ctx* ctx, spk_timings* out);
 
@@ -159,6 +162,16 @@ int spk_get_timings(spk_ctx* ctx, spk_timings* out);
  * tcgen05 mainloop (counts[32][64][4][4], index [i][j][a][b]); used by the parity tests to
  * localise descriptor / layout faults. */
 int spk_debug_tile_counts(spk_ctx* ctx, uint32_t iblock32, uint32_t jblock64, int32_t n_terms, float* counts);
+
+/* int8 compact engine introspection (tests): tiles per class {1,2,4 rows}, first permuted column of each
+ * class, the permutation (original column per permuted column, 0xffffffff = padding), per-column info
+ * (k | kept state codes, 3 bits each from bit 4 | dropped state << 16), quantised 16-bit weights and the
+ * weight per quantisation step. perm / info / q / delta may be NULL. */
+int spk_debug_i8_layout(spk_ctx* ctx, uint32_t* ntiles3, uint32_t* col_start3, uint32_t* perm, uint32_t* info,
+                        uint64_t perm_cap, uint32_t* q /* [n] */, double* delta);
+/* Raw s32 joint counts (quantised-weight units) of the tile pair (ti <= tj) as produced by the kind::i8
+ * mainloop: tables[(128/KI)][(128/KJ)][KI][KJ], KI/KJ = rows per column of the two tiles' classes. */
+int spk_debug_i8_tile(spk_ctx* ctx, uint32_t ti, uint32_t tj, uint32_t* tables /* [16384] */);
 
 const char* spk_version(void);
 

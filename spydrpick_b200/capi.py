@@ -18,7 +18,8 @@ SPK_OK, SPK_E_INVALID, SPK_E_CUDA, SPK_E_NOMEM, SPK_E_OVERFLOW, SPK_E_PRECISION 
 EXPORTS = ["spk_create", "spk_destroy", "spk_last_error", "spk_set_stream", "spk_set_alignment",
            "spk_neighbour_counts", "spk_set_weights", "spk_mi_pairs", "spk_determine_mi_threshold",
            "spk_mi_scan", "spk_outlier_thresholds", "spk_sort_edges", "spk_aracne", "spk_sort_edges_device",
-           "spk_aracne_device", "spk_get_timings", "spk_debug_tile_counts", "spk_version"]
+           "spk_aracne_device", "spk_get_timings", "spk_debug_tile_counts", "spk_debug_i8_layout", "spk_debug_i8_tile",
+           "spk_version"]
 
 
 class ScanParams(C.Structure):
@@ -37,7 +38,7 @@ class ScanResult(C.Structure):
 class Timings(C.Structure):
     _fields_ = [(k, C.c_float) for k in ("upload_ms", "prep_ms", "hamming_ms", "expand_ms", "stats_ms", "gemm_ms",
                                         "refine_ms", "compact_ms", "sort_ms", "aracne_build_ms", "aracne_ms", "pairs_ms")] + \
-               [("gemm_tiles", C.c_uint64), ("kernel_launches", C.c_uint64)]
+               [("gemm_tiles", C.c_uint64), ("kernel_launches", C.c_uint64), ("gemm_pairs", C.c_uint64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -82,6 +83,9 @@ def load():
     L.spk_aracne_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_double, C.c_uint32, C.c_uint32, C.c_void_p]
     L.spk_get_timings.argtypes = [C.c_void_p, C.POINTER(Timings)]
     L.spk_debug_tile_counts.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_int32, C.c_void_p]
+    L.spk_debug_i8_layout.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p,
+                                      C.POINTER(C.c_double)]
+    L.spk_debug_i8_tile.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p]
     _lib = L
     return L
 
@@ -209,4 +213,24 @@ class Context:
     def debug_tile_counts(self, ib, jb, n_terms=2):
         out = np.zeros((32, 64, 4, 4), dtype=np.float32)
         self._check(self.lib.spk_debug_tile_counts(self.h, ib, jb, n_terms, _ptr(out)))
+        return out
+
+    def debug_i8_layout(self, with_weights=False):
+        """int8 compact engine layout: dict(ntiles[3], col_start[3], perm, info[, q, delta])."""
+        nt = np.zeros(3, dtype=np.uint32); cs = np.zeros(3, dtype=np.uint32)
+        self._check(self.lib.spk_debug_i8_layout(self.h, _ptr(nt), _ptr(cs), None, None, 0, None, None))
+        lperm = int(nt[0]) * 128 + int(nt[1]) * 64 + int(nt[2]) * 32
+        perm = np.zeros(lperm, dtype=np.uint32); info = np.zeros(lperm, dtype=np.uint32)
+        q = np.zeros(self.n, dtype=np.uint32) if with_weights else None
+        delta = C.c_double()
+        self._check(self.lib.spk_debug_i8_layout(self.h, _ptr(nt), _ptr(cs), _ptr(perm), _ptr(info), lperm, _ptr(q),
+                                                 C.byref(delta)))
+        out = {"ntiles": nt, "col_start": cs, "perm": perm, "info": info, "delta": float(delta.value)}
+        if with_weights:
+            out["q"] = q
+        return out
+
+    def debug_i8_tile(self, ti, tj):
+        out = np.zeros(16384, dtype=np.uint32)
+        self._check(self.lib.spk_debug_i8_tile(self.h, ti, tj, _ptr(out)))
         return out

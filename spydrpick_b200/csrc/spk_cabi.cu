@@ -40,6 +40,7 @@ static void free_alignment(Ctx* c) {
     free_dev(c->d_states); free_dev(c->d_colmajor); free_dev(c->d_planes); free_dev(c->d_pos); free_dev(c->d_masks);
     free_dev(c->d_w); free_dev(c->d_marg); free_dev(c->d_colstat); free_dev(c->d_U); free_dev(c->d_V);
     free_dev(c->d_colmax); free_dev(c->d_colmax32); free_dev(c->d_counts);
+    i8_free(c);
     c->operands_terms = 0; c->operands_cap_terms = 0; c->stats_valid = false;
 }
 static void free_scan(Ctx* c) {
@@ -127,7 +128,7 @@ int spk_set_alignment(spk_ctx* c, const uint8_t* states, uint32_t n, uint32_t L,
     if (!same_shape) {
         free_alignment(c);
         c->n = n; c->L = L;
-        c->n_pad = (n + BLOCK_K - 1) / BLOCK_K * BLOCK_K;
+        c->n_pad = (n + 127) / 128 * 128;                    // K blocks: 64 samples (bf16 engine), 128 (int8 engine)
         c->L_pad = (L + TILE_J - 1) / TILE_J * TILE_J;
         c->W32 = (L + 31) / 32;
         int r;
@@ -153,10 +154,12 @@ int spk_set_alignment(spk_ctx* c, const uint8_t* states, uint32_t n, uint32_t L,
     for (uint32_t s = 0; s < n; ++s) ones[s] = 1.0;
     SPK_CUDA(c, cudaMemcpyAsync(c->d_w, ones.data(), (size_t)c->n_pad * 8, cudaMemcpyHostToDevice, c->stream));
     c->w_total = (double)n;
+    c->h_w.assign(n, 1.0);
     SPK_CUDA(c, cudaEventRecord(c->ev[1], c->stream));
     int r = prep_alignment(c); if (r) return r;
     SPK_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
     SPK_CUDA(c, cudaEventSynchronize(c->ev[2]));
+    r = i8_build_layout(c); if (r) return r;
     SPK_CUDA(c, cudaEventElapsedTime(&c->tm.upload_ms, c->ev[0], c->ev[1]));
     SPK_CUDA(c, cudaEventElapsedTime(&c->tm.prep_ms, c->ev[1], c->ev[2]));
     return SPK_OK;
@@ -182,6 +185,8 @@ int spk_set_weights(spk_ctx* c, const double* w) {
     SPK_CUDA(c, cudaMemcpyAsync(c->d_w, hw.data(), (size_t)c->n_pad * 8, cudaMemcpyHostToDevice, c->stream));
     SPK_CUDA(c, cudaStreamSynchronize(c->stream));
     c->w_total = tot;
+    c->h_w.assign(w, w + c->n);
+    c->i8_weights_valid = false;
     c->operands_terms = 0; c->stats_valid = false;
     return SPK_OK;
 }
@@ -285,7 +290,9 @@ int spk_mi_scan(spk_ctx* c, const spk_scan_params* pp, spk_scan_result* res) {
     if (!(p.pseudocount > 0.0)) return fail(c, SPK_E_INVALID, "mi_scan: pseudocount must be > 0 (0 makes the reference produce NaN via 0*log 0)");
     const int T = p.n_terms ? p.n_terms : 2;
     if (T < 1 || T > 3) return fail(c, SPK_E_INVALID, "mi_scan: n_terms must be 1..3");
-    const double band = p.band > 0.0 ? p.band : (T == 1 ? 1e-2 : 2e-4);
+    if (p.engine < 0 || p.engine > 3) return fail(c, SPK_E_INVALID, "mi_scan: engine must be 0..3");
+    const bool use_i8 = (p.engine == 0 || p.engine == 3);
+    const double band = p.band > 0.0 ? p.band : (use_i8 ? 2e-4 : (T == 1 ? 1e-2 : 2e-4));
     const uint64_t circle = p.circle_size ? p.circle_size : c->L;
     if (p.n_parts == 0) p.n_parts = 1;
     if (p.part_index >= p.n_parts) return fail(c, SPK_E_INVALID, "mi_scan: part_index >= n_parts");
@@ -300,9 +307,13 @@ int spk_mi_scan(spk_ctx* c, const spk_scan_params* pp, spk_scan_result* res) {
     if (p.engine == 1) {
         r = mi_scan_exact(c, p, circle); if (r) return r;
     } else {
-        r = prep_column_stats(c, p.pseudocount); if (r) return r;
-        r = prep_operands(c, T); if (r) return r;
-        r = mi_gemm_filter(c, p, T, band, circle); if (r) return r;
+        if (use_i8) {
+            r = mi_i8_filter(c, p, band, circle); if (r) return r;
+        } else {
+            r = prep_column_stats(c, p.pseudocount); if (r) return r;
+            r = prep_operands(c, T); if (r) return r;
+            r = mi_gemm_filter(c, p, T, band, circle); if (r) return r;
+        }
         SPK_CUDA(c, cudaMemcpyAsync(h_counters, c->d_counters, sizeof h_counters, cudaMemcpyDeviceToHost, c->stream));
         SPK_CUDA(c, cudaStreamSynchronize(c->stream));
         if (h_counters[4]) return fail(c, SPK_E_OVERFLOW, "candidate buffer overflow (%llu candidates > capacity %llu): raise max_edges or the threshold",
@@ -327,7 +338,7 @@ int spk_mi_scan(spk_ctx* c, const spk_scan_params* pp, spk_scan_result* res) {
     const uint64_t ne = h_counters[1], nw = h_counters[2];
     res->max_filter_error = h_counters[3] ? f64_from_ordered(h_counters[3]) : 0.0;
     if (p.engine != 1 && res->max_filter_error > 0.5 * band)
-        return fail(c, SPK_E_PRECISION, "fp32 filter error %.3g exceeds half the safety band %.3g: raise n_terms or band",
+        return fail(c, SPK_E_PRECISION, "fp32 filter error %.3g exceeds half the safety band %.3g: raise band (or n_terms with engine 2)",
                     res->max_filter_error, band);
     if (p.sort_desc) { r = sort_edges_device(c, c->d_edges, ne); if (r) return r; }
     res->n_edges = ne; res->n_wo_gaps = nw;
@@ -418,6 +429,39 @@ int spk_debug_tile_counts(spk_ctx* c, uint32_t ib, uint32_t jb, int32_t n_terms,
     cudaMemsetAsync(d_out, 0xff, bytes, c->stream);
     r = mi_gemm_debug_tile(c, ib, jb, T, d_out);
     if (!r) r = cuda_check(c, cudaMemcpy(counts, d_out, bytes, cudaMemcpyDeviceToHost), "D2H debug tile");
+    cudaFree(d_out);
+    return r;
+}
+
+int spk_debug_i8_layout(spk_ctx* c, uint32_t* ntiles3, uint32_t* col_start3, uint32_t* perm, uint32_t* info, uint64_t perm_cap,
+                        uint32_t* q, double* delta) {
+    if (!c || !ntiles3 || !col_start3) return SPK_E_INVALID;
+    if (!c->d_states || c->i8.NT == 0) return fail(c, SPK_E_INVALID, "debug_i8_layout: no alignment set");
+    SPK_CUDA(c, cudaSetDevice(c->device));
+    for (int g = 0; g < 3; ++g) { ntiles3[g] = c->i8.ntiles[g]; col_start3[g] = c->i8.col_start[g]; }
+    if (perm || info) {
+        if (perm_cap < c->i8.Lperm) return fail(c, SPK_E_INVALID, "debug_i8_layout: perm_cap < %u", c->i8.Lperm);
+        if (perm) SPK_CUDA(c, cudaMemcpy(perm, c->d_i8_perm, (size_t)c->i8.Lperm * 4, cudaMemcpyDeviceToHost));
+        if (info) SPK_CUDA(c, cudaMemcpy(info, c->d_i8_info, (size_t)c->i8.Lperm * 4, cudaMemcpyDeviceToHost));
+    }
+    if (q) {
+        if (!c->i8_weights_valid) return fail(c, SPK_E_INVALID, "debug_i8_layout: weights not quantised yet (run a scan or debug tile first)");
+        SPK_CUDA(c, cudaMemcpy(q, c->d_q, (size_t)c->n * 4, cudaMemcpyDeviceToHost));
+    }
+    if (delta) *delta = c->i8_delta;
+    return SPK_OK;
+}
+
+int spk_debug_i8_tile(spk_ctx* c, uint32_t ti, uint32_t tj, uint32_t* tables /* [16384] */) {
+    if (!c || !tables) return SPK_E_INVALID;
+    if (!c->d_states) return fail(c, SPK_E_INVALID, "debug_i8_tile: no alignment set");
+    SPK_CUDA(c, cudaSetDevice(c->device));
+    uint32_t* d_out = nullptr;
+    const size_t bytes = 16384 * sizeof(uint32_t);
+    if (cudaMalloc(&d_out, bytes) != cudaSuccess) { cudaGetLastError(); return fail(c, SPK_E_NOMEM, "debug buffer"); }
+    cudaMemsetAsync(d_out, 0xff, bytes, c->stream);
+    int r = mi_i8_debug_tile(c, ti, tj, 0.5, d_out);
+    if (!r) r = cuda_check(c, cudaMemcpy(tables, d_out, bytes, cudaMemcpyDeviceToHost), "D2H debug tile");
     cudaFree(d_out);
     return r;
 }

@@ -34,6 +34,29 @@ static_assert(sizeof(ColStat) == 64, "ColStat must be 64 bytes");
 // candidate emitted by the filter: pair + fp32 MI
 struct Candidate { uint32_t i, j; float mi32; uint32_t pad; };
 
+// ---- int8 compact engine (spk_mi_i8.cu) -----------------------------------------------------
+// Columns are classed by k = (#present states - 1) one-hot rows they need (the highest-coded present
+// state -- the gap when there is one -- is recovered from the marginals): class 0: k<=1 (1 row),
+// class 1: k==2 (2 rows), class 2: k in {3,4} (4 rows). Columns are permuted so that classes are
+// contiguous and every class segment is padded to whole 128-row tiles.
+constexpr uint32_t I8_INVALID = 0xffffffffu;
+struct ColRec8 {          // 80 bytes, per permuted column
+    uint32_t mq[4];       // integer (quantised-weight) marginals of the kept states, kept order; 0 beyond k
+    uint32_t mqd;         // integer marginal of the dropped (recovered) state
+    uint32_t smq;         // sum of mq[]
+    uint32_t k;           // kept rows actually used (0..4); #present states = k+1
+    uint32_t orig;        // original (filtered-alignment) column index, I8_INVALID for padding
+    uint32_t pos_lo, pos_hi;
+    float h[5];           // h[m-1]    = sum_{a present} xlogx((mq_a + pcq*m)/(Wq + pcq*(k+1)*m)), natural log
+    float invz[5];        // invz[m-1] = 1/(Wq + pcq*(k+1)*m)        (m = #present states of the partner column)
+};
+static_assert(sizeof(ColRec8) == 80, "ColRec8 must be 80 bytes");
+struct I8Layout {
+    uint32_t ncols[3] = {0, 0, 0}, ncols_pad[3] = {0, 0, 0}, ntiles[3] = {0, 0, 0};
+    uint32_t col_start[3] = {0, 0, 0}, tile_start[3] = {0, 0, 0};
+    uint32_t NT = 0, Lperm = 0;
+};
+
 struct Ctx {
     int device = 0;
     int verbose = 0;
@@ -63,6 +86,22 @@ struct Ctx {
     __nv_bfloat16* d_V = nullptr;     // [T][4*L_pad][n_pad] weighted terms
     int       operands_terms = 0;     // number of valid terms in d_V (0 = invalid)
     size_t    operands_cap_terms = 0;
+
+    // int8 compact engine
+    I8Layout  i8;
+    std::vector<uint8_t> h_masks;         // host copy of d_masks (layout construction)
+    std::vector<double>  h_w;             // host copy of the weights (quantisation)
+    uint32_t* d_i8_perm = nullptr;        // [Lperm] original column per permuted column (I8_INVALID = padding)
+    uint32_t* d_i8_info = nullptr;        // [Lperm] k | kept state codes (3 bits each from bit 4) | dropped state << 16
+    ColRec8*  d_i8_rec = nullptr;         // [Lperm]
+    uint8_t*  d_A8 = nullptr;             // [128*NT][n_pad] one-hot u8 (M operand)
+    uint8_t*  d_B8 = nullptr;             // [256*NT][n_pad] one-hot * weight byte (hi, lo) u8 (N operand)
+    uint32_t* d_q = nullptr;              // [n_pad] 16-bit quantised weights
+    uint32_t* d_i8_colmax32 = nullptr;    // [Lperm] running fp32 maxima, permuted index (ordered-uint)
+    double    i8_delta = 0.0;             // weight represented by one quantisation step
+    unsigned long long i8_wq_total = 0;   // sum of quantised weights
+    bool      i8_weights_valid = false, i8_operands_valid = false;
+    double    i8_rec_pc = -1.0;           // pseudocount the ColRec8 tables were built for (<0: invalid)
 
     // scan outputs (device)
     Candidate* d_cand = nullptr;  uint64_t cand_cap = 0;
@@ -111,6 +150,12 @@ int mi_compact(Ctx* c, uint64_t ncand, const spk_scan_params& p, uint64_t circle
 // ---- K2 (spk_mi_gemm.cu)
 int mi_gemm_filter(Ctx* c, const spk_scan_params& p, int n_terms, double band, uint64_t circle);
 int mi_gemm_debug_tile(Ctx* c, uint32_t ib, uint32_t jb, int n_terms, float* d_out);
+
+// ---- K2, int8 compact engine (spk_mi_i8.cu)
+int i8_build_layout(Ctx* c);                                   // after prep_alignment: classes, permutation
+void i8_free(Ctx* c);
+int mi_i8_filter(Ctx* c, const spk_scan_params& p, double band, uint64_t circle);
+int mi_i8_debug_tile(Ctx* c, uint32_t ti, uint32_t tj, double pc, uint32_t* d_out);
 
 // ---- graph (spk_graph.cu)
 int sort_edges_device(Ctx* c, spk_edge* d_edges, uint64_t n);

@@ -1,0 +1,749 @@
+// spk_mi_i8.cu -- K2, int8 "compact one-hot" engine: all-pairs weighted joint counts as a tcgen05
+// kind::i8 GEMM (u8 x u8 -> s32, exact) over only the one-hot rows a column actually needs, with a
+// fused fp32 MI / threshold / colmax-candidate / ballot-compaction epilogue.
+//
+// Replaces the same reference loops as spk_mi_gemm.cu
+//   Weighted_crosstable_2Dblock::operator()   externals/apegrunt/include/misc/Crosstable.hpp:362-427
+//   mutual_information_block_kernel::block     include/mi.hpp:108-181
+//   MI_solver::operator() store loop           include/mi.hpp:414-461
+// and is, like it, a FILTER in front of the fp64 refine (spk_mi_exact.cu).
+//
+// Two ideas on top of the dense bf16 formulation:
+//  (1) Row compaction. A column with np present states needs only k = np-1 one-hot rows: the joint
+//      table restricted to present states has (np_i x np_j) cells whose row / column sums are the
+//      column marginals, so one row and one column (the highest-coded present state: the gap when the
+//      column has gaps) are recovered by subtraction. SNP alignments are overwhelmingly biallelic
+//      (k = 1 or 2), so the GEMM shrinks ~(4/1.8)^2 against the fixed 4-row layout. Columns are
+//      permuted into classes of 1, 2 and 4 rows; an output tile is always 128 x 128 ROWS = (128/KI) x
+//      (128/KJ) columns, KI <= KJ.
+//  (2) Exact integer accumulation. Sample weights are quantised to 16 bits (w ~ q * delta,
+//      q = 256*hi + lo); the N operand carries the two weight bytes as separate rows, the M operand is
+//      the plain one-hot, and tcgen05.mma.kind::i8 accumulates in s32 -- at twice the bf16 rate and
+//      without accumulation rounding. Marginals are integer sums of the same q, so the recovered
+//      cells are exact for the quantised problem; the only filter error left is the weight
+//      quantisation (<= delta/2 per sample) and the fp32 entropy arithmetic.
+//
+// GEMM (per tile):  A (M=128) rows = (i column, kept state a)          u8 one-hot
+//                   B (N=256) rows = (j column, weight byte t, state b) u8 one-hot * {hi, lo}
+//                   D[row][col] s32 in TMEM; N_ab = 256*D[.., t=0, b] + D[.., t=1, b].
+//
+// Kernel anatomy (persistent, 1 CTA/SM, 320 threads):
+//   warp 0     TMA producer   cp.async.bulk.tensor 2D (128B swizzle), 4-stage ring of 48 KB (128 samples)
+//   warp 1     MMA issuer     tcgen05.mma.cta_group::1.kind::i8 M128 N256 K32, commit -> mbarriers; owns TMEM
+//   warps 2-9  epilogue       two warps per TMEM lane quadrant (each 128 of the 256 columns):
+//                             tcgen05.ld 32x32b, hi/lo combine, KI-lane transpose, MI, candidates
+// TMEM: 2 accumulator buffers x 256 columns, epilogue of tile t overlaps the mainloop of tile t+1.
+#include <cuda.h>
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include "spk_internal.h"
+#include "spk_tcgen05.cuh"
+
+namespace spk {
+
+constexpr int I8_THREADS = 320;
+constexpr int I8_EPI_THREADS = 256;
+constexpr uint32_t I8_BK = 128;                         // samples (= bytes) per stage row
+constexpr uint32_t I8_A_BYTES = 128 * I8_BK;            // 16 KB
+constexpr uint32_t I8_B_BYTES = 256 * I8_BK;            // 32 KB
+constexpr uint32_t I8_STAGE_BYTES = I8_A_BYTES + I8_B_BYTES;
+constexpr int I8_NSTAGES = 4;
+constexpr uint32_t I8_SUPER = 16;                       // i-tiles per super-row (B panel reuse through L2)
+constexpr uint32_t I8_IDESC =                           // cute::UMMA::InstrDescriptor
+    (2u << 4) |                  // c_format = S32
+    (0u << 7) | (0u << 10) |     // a_format = b_format = UINT8
+    (0u << 15) | (0u << 16) |    // A, B K-major
+    ((256u >> 3) << 17) |        // N = 256
+    ((128u >> 4) << 24);         // M = 128
+
+struct I8Params {
+    const ColRec8* rec;
+    Candidate* cand; unsigned long long cand_cap;
+    unsigned long long* counters;          // [0] n_cand, [4] overflow flag
+    uint32_t* colmax32;                    // [Lperm] running fp32 maxima (ordered-uint), permuted index
+    const unsigned long long* sr_prefix;   // [n_sr+1] chunk prefix per super-row
+    uint32_t n_sr, NT;
+    uint32_t tile_start[3], col_start[3];
+    uint32_t num_kb;                       // K blocks of 128 samples
+    uint32_t part, n_parts;
+    unsigned long long n_local_slots;
+    float pcq;                             // pseudocount in quantised-weight units
+    float thr_lo, thr_hi, band;
+    unsigned long long ld_threshold, circle; int linear;
+    uint32_t* debug_out; uint32_t debug_ti, debug_tj;
+};
+
+struct __align__(16) JRec { uint32_t mq[4]; uint32_t smq, k, orig, pad; };
+struct I8EpiSmem {
+    JRec jrec[128];
+    unsigned long long jpos[128];
+    float jh[5 * 129];
+    float ih[5 * 128];
+    float iinvz[5 * 128];
+    uint32_t cmj[128];
+};
+
+// local slot -> (ti, tj); SUPER consecutive slots share the B (j) panel
+__device__ __forceinline__ bool i8_slot_to_tile(const I8Params& p, unsigned long long ls, uint32_t& ti, uint32_t& tj) {
+    if (p.debug_out) { ti = p.debug_ti; tj = p.debug_tj; return ls == 0; }
+    const unsigned long long q = (ls / I8_SUPER) * p.n_parts + p.part;
+    const uint32_t w = (uint32_t)(ls % I8_SUPER);
+    if (q >= p.sr_prefix[p.n_sr]) return false;
+    uint32_t lo = 0, hi = p.n_sr;
+    while (hi - lo > 1) { const uint32_t mid = (lo + hi) >> 1; if (p.sr_prefix[mid] <= q) lo = mid; else hi = mid; }
+    ti = lo * I8_SUPER + w;
+    tj = lo * I8_SUPER + (uint32_t)(q - p.sr_prefix[lo]);
+    return ti < p.NT && tj < p.NT && ti <= tj;
+}
+__device__ __forceinline__ uint32_t i8_tile_class(const I8Params& p, uint32_t t) {
+    return (t >= p.tile_start[2]) ? 2u : (t >= p.tile_start[1]) ? 1u : 0u;
+}
+
+template <int W> __device__ __forceinline__ void i8_tmem_ld(uint32_t taddr, uint32_t* r);
+template <> __device__ __forceinline__ void i8_tmem_ld<16>(uint32_t taddr, uint32_t* r) { tmem_ld16_u32(taddr, r); tmem_ld_wait(); }
+template <> __device__ __forceinline__ void i8_tmem_ld<32>(uint32_t taddr, uint32_t* r) {
+    tmem_ld16_u32(taddr, r); tmem_ld16_u32(taddr + 16u, r + 16); tmem_ld_wait();
+}
+
+// colmax bookkeeping for pairs whose column maxima have not yet cleared thr+band (rare: the first
+// tiles that touch a column). Warp-collective: lanes with equal lane%KI share the j column.
+template <int KI>
+__device__ __noinline__ bool i8_open_columns_path(const I8Params& p, I8EpiSmem& sm, float mi32, bool valid,
+                                                  unsigned long long pos_i, uint32_t j_local, uint32_t gcol_j,
+                                                  float* cm_i, uint32_t lane) {
+    bool emit = false;
+    const unsigned long long pos_j = sm.jpos[j_local];
+    const bool ld_ok = valid && genome_distance(pos_i, pos_j, p.linear, p.circle) > p.ld_threshold;
+    if (ld_ok) {
+        const float c = fmaxf(*cm_i, mi32);
+        *cm_i = c;
+        if (!(c > p.thr_hi) && mi32 >= c - p.band) emit = true;
+    }
+    float gm = ld_ok ? mi32 : -INFINITY;
+#pragma unroll
+    for (int o = KI; o < 32; o <<= 1) gm = fmaxf(gm, __shfl_xor_sync(0xffffffffu, gm, o));
+    const float cur = f32_from_ordered(sm.cmj[j_local]);
+    const float nm = fmaxf(cur, gm);
+    if (gm > cur && lane < (uint32_t)KI) {
+        atomicMax(&sm.cmj[j_local], f32_ordered(gm));
+        atomicMax(&p.colmax32[gcol_j], f32_ordered(gm));
+    }
+    if (ld_ok && !(nm > p.thr_hi) && mi32 >= nm - p.band) emit = true;
+    return emit;
+}
+
+// ---------------------------------------------------------------------------------------------
+// epilogue of one tile for the class pair (KI rows per i column, KJ rows per j column), KI <= KJ
+// ---------------------------------------------------------------------------------------------
+template <int KI, int KJ>
+__device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmem& sm, uint32_t tmem_acc, uint32_t q, uint32_t half,
+                                                 uint32_t lane, bool diag, uint32_t ci0, uint32_t cj0, bool any_j_open) {
+    constexpr int LOADW = (KI == 4) ? 32 : 16;         // TMEM columns per load
+    constexpr int NJ = LOADW / (2 * KJ);               // j columns per load
+    constexpr int PPL = NJ / KI;                       // pairs per lane per load
+    constexpr int WJ = 128 / KJ;
+    static_assert(PPL >= 1, "tile geometry");
+    const uint32_t row = q * 32u + lane;
+    const uint32_t i_local = row / KI, g = lane % KI;
+    const uint32_t pi = ci0 + i_local;
+    // per-lane constants of the i column
+    const ColRec8* ri = p.rec + pi;
+    uint32_t mi_[KI];
+#pragma unroll
+    for (int a = 0; a < KI; ++a) mi_[a] = __ldg(&ri->mq[a]);
+    const uint32_t mi_d = __ldg(&ri->mqd), ki = __ldg(&ri->k), orig_i = __ldg(&ri->orig);
+    const unsigned long long pos_i = ((unsigned long long)__ldg(&ri->pos_hi) << 32) | __ldg(&ri->pos_lo);
+    const bool vi = orig_i != I8_INVALID;
+    const float cm_i0 = f32_from_ordered(p.colmax32[pi]);
+    float cm_i = cm_i0;
+    const bool i_open = vi && !(cm_i0 > p.thr_hi);
+    const bool slow = any_j_open || __any_sync(0xffffffffu, i_open);
+    const float ln2 = 0.69314718055994530942f;
+
+#pragma unroll 1
+    for (uint32_t ld = 0; ld < 128u / LOADW; ++ld) {
+        const uint32_t col0 = half * 128u + ld * LOADW;
+        uint32_t r[LOADW];
+        i8_tmem_ld<LOADW>(tmem_acc + ((q * 32u) << 16) + col0, r);
+        uint32_t v[NJ * KJ];
+#pragma unroll
+        for (int jj = 0; jj < NJ; ++jj)
+#pragma unroll
+            for (int b = 0; b < KJ; ++b) v[jj * KJ + b] = (r[jj * 2 * KJ + b] << 8) + r[jj * 2 * KJ + KJ + b];
+        // transpose inside the KI-lane group: afterwards v[(s*KI + a)*KJ + b] = N[a][b] of j = s*KI + g
+        if (KI == 2) {
+#pragma unroll
+            for (int s = 0; s < NJ / 2; ++s)
+#pragma unroll
+                for (int b = 0; b < KJ; ++b) {
+                    const int s0 = (2 * s) * KJ + b, s1 = (2 * s + 1) * KJ + b;
+                    const uint32_t send = g ? v[s0] : v[s1];
+                    const uint32_t recv = __shfl_xor_sync(0xffffffffu, send, 1);
+                    if (g) v[s0] = recv; else v[s1] = recv;
+                }
+        } else if (KI == 4) {
+            const bool b0 = lane & 1u, b1 = lane & 2u;
+#pragma unroll
+            for (int s = 0; s < NJ / 4; ++s) {
+#pragma unroll
+                for (int pr = 0; pr < 2; ++pr)
+#pragma unroll
+                    for (int b = 0; b < KJ; ++b) {
+                        const int s0 = (4 * s + 2 * pr) * KJ + b, s1 = (4 * s + 2 * pr + 1) * KJ + b;
+                        const uint32_t send = b0 ? v[s0] : v[s1];
+                        const uint32_t recv = __shfl_xor_sync(0xffffffffu, send, 1);
+                        if (b0) v[s0] = recv; else v[s1] = recv;
+                    }
+#pragma unroll
+                for (int pr = 0; pr < 2; ++pr)
+#pragma unroll
+                    for (int b = 0; b < KJ; ++b) {
+                        const int s0 = (4 * s + pr) * KJ + b, s1 = (4 * s + pr + 2) * KJ + b;
+                        const uint32_t send = b1 ? v[s0] : v[s1];
+                        const uint32_t recv = __shfl_xor_sync(0xffffffffu, send, 2);
+                        if (b1) v[s0] = recv; else v[s1] = recv;
+                    }
+            }
+        }
+#pragma unroll
+        for (int s = 0; s < PPL; ++s) {
+            const uint32_t j_local = col0 / (2 * KJ) + s * KI + g;
+            if (p.debug_out) {
+#pragma unroll
+                for (int a = 0; a < KI; ++a)
+#pragma unroll
+                    for (int b = 0; b < KJ; ++b)
+                        p.debug_out[(((size_t)i_local * WJ + j_local) * KI + a) * KJ + b] = v[(s * KI + a) * KJ + b];
+                continue;
+            }
+            const JRec jr = sm.jrec[j_local];
+            const uint32_t kj = jr.k;
+            const float invZ = sm.iinvz[kj * 128u + i_local];
+            const float hsum = sm.ih[kj * 128u + i_local] + sm.jh[ki * 129u + j_local];
+            const float pcZ = p.pcq * invZ;
+            auto xlg = [&](uint32_t nq) { const float pr = fmaf((float)nq, invZ, pcZ); return pr * __log2f(pr); };
+            uint32_t colsum[KJ];
+#pragma unroll
+            for (int b = 0; b < KJ; ++b) colsum[b] = 0;
+            uint32_t tot = 0;
+            float S = 0.f;
+#pragma unroll
+            for (int a = 0; a < KI; ++a) {
+                const bool rv = (KI == 2) ? true : (KI == 1 ? (ki >= 1u) : (a < 3 || ki == 4u));
+                uint32_t rs = 0;
+                float racc = 0.f;
+#pragma unroll
+                for (int b = 0; b < KJ; ++b) {
+                    const bool cv = (KJ == 2) ? true : (KJ == 1 ? (kj >= 1u) : (b < 3 || kj == 4u));
+                    const uint32_t nab = v[(s * KI + a) * KJ + b];
+                    rs += nab; colsum[b] += nab;
+                    const float t = xlg(nab);
+                    racc += cv ? t : 0.f;
+                }
+                racc += xlg(mi_[a] - rs);                                // cell (a, dropped_j)
+                S += rv ? racc : 0.f;
+                tot += rs;
+            }
+#pragma unroll
+            for (int b = 0; b < KJ; ++b) {
+                const bool cv = (KJ == 2) ? true : (KJ == 1 ? (kj >= 1u) : (b < 3 || kj == 4u));
+                const float t = xlg(jr.mq[b] - colsum[b]);               // cell (dropped_i, b)
+                S += cv ? t : 0.f;
+            }
+            S += xlg(mi_d - jr.smq + tot);                               // cell (dropped_i, dropped_j)
+            const uint32_t pj = cj0 + j_local;
+            const bool valid = vi && (jr.orig != I8_INVALID) && (!diag || pi < pj);
+            const float mi32 = valid ? fmaf(S, ln2, -hsum) : __int_as_float(0x7fc00000);
+            bool emit = mi32 > p.thr_lo;                                   // false for NaN
+            if (slow) emit = i8_open_columns_path<KI>(p, sm, mi32, valid, pos_i, j_local, pj, &cm_i, lane) || emit;
+            const uint32_t bal = __ballot_sync(0xffffffffu, emit);
+            if (bal) {
+                unsigned long long base = 0;
+                if (lane == 0) base = atomicAdd(&p.counters[0], (unsigned long long)__popc(bal));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (emit) {
+                    const unsigned long long idx = base + __popc(bal & ((1u << lane) - 1u));
+                    if (idx < p.cand_cap) {
+                        Candidate cd;
+                        cd.i = min(orig_i, jr.orig); cd.j = max(orig_i, jr.orig); cd.mi32 = mi32; cd.pad = 0;
+                        p.cand[idx] = cd;
+                    } else p.counters[4] = 1ull;
+                }
+            }
+        }
+    }
+    if (slow && !p.debug_out) {
+#pragma unroll
+        for (int o = 1; o < KI; o <<= 1) cm_i = fmaxf(cm_i, __shfl_xor_sync(0xffffffffu, cm_i, o));
+        if (g == 0 && vi && cm_i > cm_i0) atomicMax(&p.colmax32[pi], f32_ordered(cm_i));
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(I8_THREADS, 1)
+mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const I8Params p) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* tiles = smem;
+    I8EpiSmem& sm = *(I8EpiSmem*)(smem + (size_t)I8_NSTAGES * I8_STAGE_BYTES);
+    uint64_t* full_bar = (uint64_t*)(smem + (size_t)I8_NSTAGES * I8_STAGE_BYTES + ((sizeof(I8EpiSmem) + 15) & ~(size_t)15));
+    uint64_t* empty_bar = full_bar + I8_NSTAGES;
+    uint64_t* tfull_bar = empty_bar + I8_NSTAGES;        // [2]
+    uint64_t* tempty_bar = tfull_bar + 2;                // [2]
+    uint32_t* tmem_slot = (uint32_t*)(tempty_bar + 2);
+
+    const uint32_t warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < I8_NSTAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], I8_EPI_THREADS / 32); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512u) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tcgen05_fence_before();
+    __syncthreads();
+    tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            uint32_t stage = 0, phase = 0;
+            for (unsigned long long ls = blockIdx.x; ls < p.n_local_slots; ls += gridDim.x) {
+                uint32_t ti, tj;
+                if (!i8_slot_to_tile(p, ls, ti, tj)) continue;
+                for (uint32_t kb = 0; kb < p.num_kb; ++kb) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1u);
+                    uint8_t* st = tiles + (size_t)stage * I8_STAGE_BYTES;
+                    mbar_expect_tx(&full_bar[stage], I8_STAGE_BYTES);
+                    tma_load_2d(&map_b, &full_bar[stage], st, (int32_t)(kb * I8_BK), (int32_t)(tj * 256u));
+                    tma_load_2d(&map_a, &full_bar[stage], st + I8_B_BYTES, (int32_t)(kb * I8_BK), (int32_t)(ti * 128u));
+                    if (++stage == I8_NSTAGES) { stage = 0; phase ^= 1u; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            uint32_t stage = 0, phase = 0, it = 0;
+            for (unsigned long long ls = blockIdx.x; ls < p.n_local_slots; ls += gridDim.x) {
+                uint32_t ti, tj;
+                if (!i8_slot_to_tile(p, ls, ti, tj)) continue;
+                const uint32_t buf = it & 1u, acc_phase = (it >> 1) & 1u;
+                mbar_wait(&tempty_bar[buf], acc_phase ^ 1u);
+                tcgen05_fence_after();
+                const uint32_t d_tmem = tmem_base + buf * 256u;
+                for (uint32_t kb = 0; kb < p.num_kb; ++kb) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tcgen05_fence_after();
+                    const uint32_t sb = smem_u32(tiles + (size_t)stage * I8_STAGE_BYTES);
+                    const uint32_t sa = sb + I8_B_BYTES;
+#pragma unroll
+                    for (uint32_t k = 0; k < I8_BK / 32; ++k)
+                        umma_i8(d_tmem, umma_smem_desc(sa + k * 32), umma_smem_desc(sb + k * 32), I8_IDESC, (kb | k) ? 1u : 0u);
+                    umma_commit(&empty_bar[stage]);
+                    if (++stage == I8_NSTAGES) { stage = 0; phase ^= 1u; }
+                }
+                umma_commit(&tfull_bar[buf]);
+                ++it;
+            }
+        }
+    } else {
+        // ===================== epilogue (8 warps, 256 threads) =====================
+        const uint32_t q = warp & 3u;                            // TMEM lane quadrant this warp may access
+        const uint32_t half = (warp - 2) >> 2;                   // which 128 of the 256 accumulator columns
+        const uint32_t et = threadIdx.x - 64;                    // 0..255
+        uint32_t it = 0;
+        for (unsigned long long ls = blockIdx.x; ls < p.n_local_slots; ls += gridDim.x) {
+            uint32_t ti, tj;
+            if (!i8_slot_to_tile(p, ls, ti, tj)) continue;
+            const uint32_t buf = it & 1u, acc_phase = (it >> 1) & 1u;
+            const uint32_t ci = i8_tile_class(p, ti), cj = i8_tile_class(p, tj);
+            const uint32_t WI = 128u >> ci, WJ = 128u >> cj;
+            const uint32_t ci0 = p.col_start[ci] + (ti - p.tile_start[ci]) * WI;
+            const uint32_t cj0 = p.col_start[cj] + (tj - p.tile_start[cj]) * WJ;
+            // stage the tile's column records (readers of the previous tile are past the trailing barrier)
+            uint32_t my_open = 0;
+            if (et < WJ) {
+                const ColRec8 rc = p.rec[cj0 + et];
+                JRec jr;
+                jr.mq[0] = rc.mq[0]; jr.mq[1] = rc.mq[1]; jr.mq[2] = rc.mq[2]; jr.mq[3] = rc.mq[3];
+                jr.smq = rc.smq; jr.k = rc.k; jr.orig = rc.orig; jr.pad = 0;
+                sm.jrec[et] = jr;
+                sm.jpos[et] = ((unsigned long long)rc.pos_hi << 32) | rc.pos_lo;
+#pragma unroll
+                for (int m = 0; m < 5; ++m) sm.jh[m * 129 + et] = rc.h[m];
+                const uint32_t cm = p.colmax32[cj0 + et];
+                sm.cmj[et] = cm;
+                my_open = (rc.orig != I8_INVALID && !(f32_from_ordered(cm) > p.thr_hi)) ? 1u : 0u;
+            } else if (et >= 128 && et - 128 < WI) {
+                const uint32_t e = et - 128;
+                const ColRec8* rc = p.rec + ci0 + e;
+#pragma unroll
+                for (int m = 0; m < 5; ++m) { sm.ih[m * 128 + e] = rc->h[m]; sm.iinvz[m * 128 + e] = rc->invz[m]; }
+            }
+            uint32_t any_open;
+            asm volatile(
+                "{\n\t.reg .pred p, q;\n\t"
+                "setp.ne.u32 p, %1, 0;\n\t"
+                "bar.red.or.pred q, 1, 256, p;\n\t"
+                "selp.u32 %0, 1, 0, q;\n\t}"
+                : "=r"(any_open) : "r"(my_open) : "memory");
+
+            mbar_wait(&tfull_bar[buf], acc_phase);
+            tcgen05_fence_after();
+            const uint32_t tmem_acc = tmem_base + buf * 256u;
+            const bool diag = (ti == tj);
+            switch (ci * 3u + cj) {
+                case 0: i8_epilogue_tile<1, 1>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0, any_open != 0); break;
+                case 1: i8_epilogue_tile<1, 2>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0, any_open != 0); break;
+                case 2: i8_epilogue_tile<1, 4>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0, any_open != 0); break;
+                case 4: i8_epilogue_tile<2, 2>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0, any_open != 0); break;
+                case 5: i8_epilogue_tile<2, 4>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0, any_open != 0); break;
+                default: i8_epilogue_tile<4, 4>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0, any_open != 0); break;
+            }
+            // accumulator drained: hand the TMEM buffer back to the MMA warp
+            tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty_bar[buf]);
+            asm volatile("bar.sync 1, 256;" ::: "memory");                 // staging arrays free for the next tile
+            ++it;
+        }
+    }
+
+    tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tcgen05_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+    }
+}
+
+// =============================================================================================
+// preparation kernels: integer marginals + epilogue tables, operand expansion
+// =============================================================================================
+// one warp per permuted column
+__global__ void i8_colrec_kernel(const uint8_t* __restrict__ colmajor, const uint32_t* __restrict__ qw,
+                                 const uint32_t* __restrict__ perm, const uint32_t* __restrict__ info,
+                                 const uint64_t* __restrict__ pos, ColRec8* __restrict__ rec,
+                                 uint32_t Lperm, uint32_t n, uint32_t n_pad, double wq_total, double pcq) {
+    const uint32_t pc = blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32;
+    const uint32_t lane = threadIdx.x % 32;
+    if (pc >= Lperm) return;
+    const uint32_t orig = perm[pc];
+    uint32_t m[NSTATES] = {0, 0, 0, 0, 0};
+    if (orig != I8_INVALID) {
+        const uint8_t* col = colmajor + (size_t)orig * n_pad;
+        for (uint32_t s = lane; s < n; s += 32) {
+            const uint32_t x = col[s], w = qw[s];
+#pragma unroll
+            for (int a = 0; a < NSTATES; ++a) m[a] += (x == (uint32_t)a) ? w : 0u;
+        }
+#pragma unroll
+        for (int a = 0; a < NSTATES; ++a)
+            for (int o = 16; o; o >>= 1) m[a] += __shfl_xor_sync(0xffffffffu, m[a], o);
+    }
+    if (lane == 0) {
+        ColRec8 r; memset(&r, 0, sizeof r);
+        r.orig = orig;
+        uint32_t k = 0;
+        double pm[NSTATES]; int npres = 0;                       // marginals of the present states
+        if (orig != I8_INVALID) {
+            const uint32_t inf = info[pc];
+            k = inf & 15u;
+            for (uint32_t a = 0; a < k; ++a) { const uint32_t code = (inf >> (4 + 3 * a)) & 7u; r.mq[a] = m[code]; r.smq += m[code]; pm[npres++] = (double)m[code]; }
+            const uint32_t drop = (inf >> 16) & 7u;
+            r.mqd = m[drop]; pm[npres++] = (double)m[drop];
+            const uint64_t ps = pos[orig];
+            r.pos_lo = (uint32_t)ps; r.pos_hi = (uint32_t)(ps >> 32);
+        }
+        r.k = k;
+        for (int mm = 1; mm <= NSTATES; ++mm) {
+            const double Z = wq_total + pcq * (double)(k + 1) * (double)mm;
+            double h = 0.0;
+            for (int a = 0; a < npres; ++a) { const double pr = (pm[a] + pcq * (double)mm) / Z; h += pr * log(pr); }
+            r.h[mm - 1] = (float)h;
+            r.invz[mm - 1] = (float)(1.0 / Z);
+        }
+        rec[pc] = r;
+    }
+}
+
+// one warp per permuted column; each lane converts 16 consecutive samples per iteration
+__global__ void i8_expand_kernel(const uint8_t* __restrict__ colmajor, const uint8_t* __restrict__ qhi, const uint8_t* __restrict__ qlo,
+                                 const uint32_t* __restrict__ perm, const uint32_t* __restrict__ info,
+                                 uint8_t* __restrict__ A8, uint8_t* __restrict__ B8, uint32_t Lperm, uint32_t n, uint32_t n_pad,
+                                 uint32_t cs1, uint32_t cs2, uint32_t ts1, uint32_t ts2) {
+    const uint32_t pc = blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32;
+    if (pc >= Lperm) return;
+    const uint32_t orig = perm[pc];
+    if (orig == I8_INVALID) return;                              // rows stay zero
+    const uint32_t lane = threadIdx.x % 32;
+    const uint32_t cls = (pc >= cs2) ? 2u : (pc >= cs1) ? 1u : 0u;
+    const uint32_t kp = 1u << cls;
+    const uint32_t cstart = cls == 2 ? cs2 : cls == 1 ? cs1 : 0u;
+    const uint32_t tstart = cls == 2 ? ts2 : cls == 1 ? ts1 : 0u;
+    const uint32_t lc = pc - cstart;
+    const size_t rowA = (size_t)128 * tstart + (size_t)lc * kp;
+    const size_t rowB = (size_t)256 * tstart + (size_t)lc * 2 * kp;
+    const uint32_t inf = info[pc];
+    const uint32_t k = inf & 15u;
+    const uint8_t* col = colmajor + (size_t)orig * n_pad;
+    for (uint32_t s0 = lane * 16; s0 < n_pad; s0 += 512) {
+        const uint4 raw = *reinterpret_cast<const uint4*>(col + s0);
+        const uint4 rh = *reinterpret_cast<const uint4*>(qhi + s0);
+        const uint4 rl = *reinterpret_cast<const uint4*>(qlo + s0);
+        uint8_t x[16], wh[16], wl[16];
+        memcpy(x, &raw, 16); memcpy(wh, &rh, 16); memcpy(wl, &rl, 16);
+        for (uint32_t a = 0; a < k; ++a) {
+            const uint32_t code = (inf >> (4 + 3 * a)) & 7u;
+            __align__(16) uint8_t oa[16], oh[16], ol[16];
+#pragma unroll
+            for (int t = 0; t < 16; ++t) {
+                const bool hit = (x[t] == code) && (s0 + t < n);
+                oa[t] = hit ? 1 : 0; oh[t] = hit ? wh[t] : 0; ol[t] = hit ? wl[t] : 0;
+            }
+            *reinterpret_cast<uint4*>(A8 + (rowA + a) * n_pad + s0) = *reinterpret_cast<const uint4*>(oa);
+            *reinterpret_cast<uint4*>(B8 + (rowB + a) * n_pad + s0) = *reinterpret_cast<const uint4*>(oh);
+            *reinterpret_cast<uint4*>(B8 + (rowB + kp + a) * n_pad + s0) = *reinterpret_cast<const uint4*>(ol);
+        }
+    }
+}
+
+__global__ void i8_fill_u32_kernel(uint32_t* p, uint32_t v, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
+}
+
+// =============================================================================================
+// host side
+// =============================================================================================
+template <class P> static void i8_free_dev(P*& p) { if (p) { cudaFree(p); p = nullptr; } }
+
+void i8_free(Ctx* c) {
+    i8_free_dev(c->d_i8_perm); i8_free_dev(c->d_i8_info); i8_free_dev(c->d_i8_rec); i8_free_dev(c->d_A8); i8_free_dev(c->d_B8);
+    i8_free_dev(c->d_q); i8_free_dev(c->d_i8_colmax32);
+    c->i8 = I8Layout();
+    c->i8_weights_valid = c->i8_operands_valid = false; c->i8_rec_pc = -1.0;
+}
+
+// classes + permutation from the presence masks (host; O(L))
+int i8_build_layout(Ctx* c) {
+    const uint32_t L = c->L;
+    c->h_masks.resize(L);
+    SPK_CUDA(c, cudaMemcpyAsync(c->h_masks.data(), c->d_masks, L, cudaMemcpyDeviceToHost, c->stream));
+    SPK_CUDA(c, cudaStreamSynchronize(c->stream));
+    I8Layout lay;
+    std::vector<uint8_t> cls(L);
+    for (uint32_t col = 0; col < L; ++col) {
+        const int np = __builtin_popcount(c->h_masks[col] & 31u);
+        const int k = np > 0 ? np - 1 : 0;
+        cls[col] = (uint8_t)(k <= 1 ? 0 : (k == 2 ? 1 : 2));
+        lay.ncols[cls[col]]++;
+    }
+    uint32_t cstart = 0, tstart = 0;
+    for (int g = 0; g < 3; ++g) {
+        const uint32_t width = 128u >> g;
+        lay.ncols_pad[g] = (lay.ncols[g] + width - 1) / width * width;
+        lay.ntiles[g] = lay.ncols_pad[g] / width;
+        lay.col_start[g] = cstart; lay.tile_start[g] = tstart;
+        cstart += lay.ncols_pad[g]; tstart += lay.ntiles[g];
+    }
+    lay.Lperm = cstart; lay.NT = tstart;
+    std::vector<uint32_t> perm(lay.Lperm, I8_INVALID), info(lay.Lperm, 0u);
+    uint32_t fill[3] = {lay.col_start[0], lay.col_start[1], lay.col_start[2]};
+    for (uint32_t col = 0; col < L; ++col) {
+        const uint32_t pc = fill[cls[col]]++;
+        perm[pc] = col;
+        const uint32_t mask = c->h_masks[col] & 31u;
+        int drop = 4; while (drop > 0 && !((mask >> drop) & 1u)) --drop;          // highest-coded present state
+        uint32_t inf = 0, k = 0;
+        for (int a = 0; a < drop; ++a) if ((mask >> a) & 1u) { inf |= (uint32_t)a << (4 + 3 * k); ++k; }
+        info[pc] = inf | k | ((uint32_t)drop << 16);
+    }
+    i8_free(c);
+    c->i8 = lay;
+    if (cudaMalloc(&c->d_i8_perm, (size_t)lay.Lperm * 4) != cudaSuccess || cudaMalloc(&c->d_i8_info, (size_t)lay.Lperm * 4) != cudaSuccess ||
+        cudaMalloc(&c->d_i8_rec, (size_t)lay.Lperm * sizeof(ColRec8)) != cudaSuccess ||
+        cudaMalloc(&c->d_i8_colmax32, (size_t)lay.Lperm * 4) != cudaSuccess ||
+        cudaMalloc(&c->d_q, (size_t)c->n_pad * 6) != cudaSuccess) {
+        cudaGetLastError();
+        return fail(c, SPK_E_NOMEM, "int8 engine: layout allocation failed");
+    }
+    SPK_CUDA(c, cudaMemcpyAsync(c->d_i8_perm, perm.data(), (size_t)lay.Lperm * 4, cudaMemcpyHostToDevice, c->stream));
+    SPK_CUDA(c, cudaMemcpyAsync(c->d_i8_info, info.data(), (size_t)lay.Lperm * 4, cudaMemcpyHostToDevice, c->stream));
+    SPK_CUDA(c, cudaStreamSynchronize(c->stream));
+    return SPK_OK;
+}
+
+// 16-bit weight quantisation (host; O(n)), operands, column records
+static int i8_prepare(Ctx* c, double pc) {
+    const uint32_t n = c->n, n_pad = c->n_pad;
+    if (n > 65536u) return fail(c, SPK_E_INVALID, "int8 engine supports at most 65536 samples (s32 accumulators); use engine 2");
+    if (c->i8.NT == 0) return fail(c, SPK_E_INVALID, "int8 engine: no layout (set_alignment first)");
+    uint8_t* d_qhi = (uint8_t*)(c->d_q + n_pad); uint8_t* d_qlo = d_qhi + n_pad;
+    if (!c->i8_weights_valid) {
+        if (c->h_w.size() != n) return fail(c, SPK_E_INVALID, "int8 engine: weights not set");
+        double wmax = 0.0;
+        for (uint32_t s = 0; s < n; ++s) {
+            if (!(c->h_w[s] >= 0.0) || !std::isfinite(c->h_w[s])) return fail(c, SPK_E_INVALID, "int8 engine: weights must be finite and >= 0");
+            wmax = std::max(wmax, c->h_w[s]);
+        }
+        if (!(wmax > 0.0)) return fail(c, SPK_E_INVALID, "int8 engine: all weights are zero");
+        std::vector<uint32_t> q(n_pad, 0u); std::vector<uint8_t> qb(2 * (size_t)n_pad, 0);
+        unsigned long long tot = 0;
+        for (uint32_t s = 0; s < n; ++s) {
+            const uint32_t v = (uint32_t)std::llround(c->h_w[s] / wmax * 65535.0);
+            q[s] = v; qb[s] = (uint8_t)(v >> 8); qb[n_pad + s] = (uint8_t)(v & 255u); tot += v;
+        }
+        c->i8_delta = wmax / 65535.0; c->i8_wq_total = tot;
+        SPK_CUDA(c, cudaMemcpyAsync(c->d_q, q.data(), (size_t)n_pad * 4, cudaMemcpyHostToDevice, c->stream));
+        SPK_CUDA(c, cudaMemcpyAsync(d_qhi, qb.data(), (size_t)n_pad * 2, cudaMemcpyHostToDevice, c->stream));
+        SPK_CUDA(c, cudaStreamSynchronize(c->stream));
+        c->i8_weights_valid = true; c->i8_operands_valid = false; c->i8_rec_pc = -1.0;
+    }
+    SPK_CUDA(c, cudaEventRecord(c->ev[0], c->stream));
+    if (!c->i8_operands_valid) {
+        const size_t rowsA = (size_t)128 * c->i8.NT;
+        if (!c->d_A8) {
+            if (cudaMalloc(&c->d_A8, rowsA * n_pad) != cudaSuccess || cudaMalloc(&c->d_B8, 2 * rowsA * n_pad) != cudaSuccess) {
+                cudaGetLastError(); i8_free_dev(c->d_A8);
+                return fail(c, SPK_E_NOMEM, "int8 engine: cannot allocate operands (%zu bytes)", 3 * rowsA * n_pad);
+            }
+        }
+        SPK_CUDA(c, cudaMemsetAsync(c->d_A8, 0, rowsA * n_pad, c->stream));
+        SPK_CUDA(c, cudaMemsetAsync(c->d_B8, 0, 2 * rowsA * n_pad, c->stream));
+        i8_expand_kernel<<<(c->i8.Lperm + 7) / 8, 256, 0, c->stream>>>(c->d_colmajor, d_qhi, d_qlo, c->d_i8_perm, c->d_i8_info, c->d_A8, c->d_B8,
+                                                                      c->i8.Lperm, n, n_pad, c->i8.col_start[1], c->i8.col_start[2],
+                                                                      c->i8.tile_start[1], c->i8.tile_start[2]);
+        c->tm.kernel_launches += 1;
+        SPK_CUDA(c, cudaGetLastError());
+        c->i8_operands_valid = true;
+    }
+    SPK_CUDA(c, cudaEventRecord(c->ev[1], c->stream));
+    if (c->i8_rec_pc != pc) {
+        i8_colrec_kernel<<<(c->i8.Lperm + 7) / 8, 256, 0, c->stream>>>(c->d_colmajor, c->d_q, c->d_i8_perm, c->d_i8_info, c->d_pos, c->d_i8_rec,
+                                                                      c->i8.Lperm, n, n_pad, (double)c->i8_wq_total, pc / c->i8_delta);
+        c->tm.kernel_launches += 1;
+        SPK_CUDA(c, cudaGetLastError());
+        c->i8_rec_pc = pc;
+    }
+    SPK_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
+    SPK_CUDA(c, cudaEventSynchronize(c->ev[2]));
+    SPK_CUDA(c, cudaEventElapsedTime(&c->tm.expand_ms, c->ev[0], c->ev[1]));
+    SPK_CUDA(c, cudaEventElapsedTime(&c->tm.stats_ms, c->ev[1], c->ev[2]));
+    return SPK_OK;
+}
+
+typedef CUresult (*PFN_encodeTiled8)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                     const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                     CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// 2D u8 tensor [rows][n_pad] (samples contiguous), box = 128 samples x box_rows, 128B swizzle
+static int i8_make_map(Ctx* c, CUtensorMap* map, void* base, uint64_t rows, uint64_t k_bytes, uint32_t box_rows) {
+    static PFN_encodeTiled8 enc = nullptr;
+    if (!enc) {
+        void* ptr = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess && qres == cudaDriverEntryPointSuccess)
+            enc = (PFN_encodeTiled8)ptr;
+    }
+    if (!enc) return fail(c, SPK_E_CUDA, "cuTensorMapEncodeTiled entry point not available");
+    cuuint64_t gdim[2] = {k_bytes, rows};
+    cuuint64_t gstride[1] = {k_bytes};
+    cuuint32_t box[2] = {I8_BK, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, base, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(c, SPK_E_CUDA, "cuTensorMapEncodeTiled (u8) failed (%d)", (int)r);
+    return SPK_OK;
+}
+
+static size_t i8_smem_bytes() {
+    return (size_t)I8_NSTAGES * I8_STAGE_BYTES + ((sizeof(I8EpiSmem) + 15) & ~(size_t)15) + (2 * I8_NSTAGES + 4) * 8 + 16 + 1024;
+}
+
+static int i8_launch(Ctx* c, I8Params& gp) {
+    CUtensorMap ma, mb;
+    int r = i8_make_map(c, &ma, c->d_A8, (uint64_t)128 * c->i8.NT, c->n_pad, 128); if (r) return r;
+    r = i8_make_map(c, &mb, c->d_B8, (uint64_t)256 * c->i8.NT, c->n_pad, 256); if (r) return r;
+    gp.rec = c->d_i8_rec;
+    gp.num_kb = c->n_pad / I8_BK;
+    gp.NT = c->i8.NT;
+    for (int g = 0; g < 3; ++g) { gp.tile_start[g] = c->i8.tile_start[g]; gp.col_start[g] = c->i8.col_start[g]; }
+    gp.colmax32 = c->d_i8_colmax32;
+    gp.counters = c->d_counters;
+    const unsigned long long slots = gp.debug_out ? 1ull : gp.n_local_slots;
+    const unsigned grid = (unsigned)(slots < (unsigned long long)c->sm_count ? (slots ? slots : 1) : (unsigned long long)c->sm_count);
+    const size_t smem = i8_smem_bytes();
+    SPK_CUDA(c, cudaFuncSetAttribute(mi_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    mi_i8_kernel<<<grid, I8_THREADS, smem, c->stream>>>(ma, mb, gp);
+    c->tm.kernel_launches += 1;
+    SPK_CUDA(c, cudaGetLastError());
+    return SPK_OK;
+}
+
+int mi_i8_filter(Ctx* c, const spk_scan_params& p, double band, uint64_t circle) {
+    int r = i8_prepare(c, p.pseudocount); if (r) return r;
+    I8Params gp; memset(&gp, 0, sizeof gp);
+    const uint32_t NT = c->i8.NT;
+    const uint32_t n_sr = (NT + I8_SUPER - 1) / I8_SUPER;
+    std::vector<unsigned long long> prefix(n_sr + 1, 0);
+    for (uint32_t sr = 0; sr < n_sr; ++sr) prefix[sr + 1] = prefix[sr] + (NT - sr * I8_SUPER);
+    if ((size_t)(n_sr + 1) * 8 > (1u << 20)) return fail(c, SPK_E_INVALID, "int8 engine: too many column tiles");
+    const uint32_t nparts = p.n_parts ? p.n_parts : 1;
+    if (p.part_index >= nparts) return fail(c, SPK_E_INVALID, "part_index >= n_parts");
+    const unsigned long long total_chunks = prefix[n_sr];
+    const unsigned long long local_chunks = total_chunks > p.part_index ? (total_chunks - p.part_index + nparts - 1) / nparts : 0;
+    unsigned long long* d_prefix = (unsigned long long*)c->d_tilemap;
+    SPK_CUDA(c, cudaMemcpyAsync(d_prefix, prefix.data(), (n_sr + 1) * 8, cudaMemcpyHostToDevice, c->stream));
+    i8_fill_u32_kernel<<<(c->i8.Lperm + 255) / 256, 256, 0, c->stream>>>(c->d_i8_colmax32, f32_ordered(-INFINITY), c->i8.Lperm);
+    c->tm.kernel_launches += 1;
+    gp.cand = c->d_cand; gp.cand_cap = c->cand_cap;
+    gp.sr_prefix = d_prefix; gp.n_sr = n_sr;
+    gp.part = p.part_index; gp.n_parts = nparts; gp.n_local_slots = local_chunks * I8_SUPER;
+    gp.pcq = (float)(p.pseudocount / c->i8_delta);
+    gp.band = (float)band; gp.thr_lo = (float)(p.threshold - band); gp.thr_hi = (float)(p.threshold + band);
+    gp.ld_threshold = p.ld_threshold; gp.circle = circle; gp.linear = p.linear_genome;
+    gp.debug_out = nullptr;
+    SPK_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
+    r = i8_launch(c, gp); if (r) return r;
+    SPK_CUDA(c, cudaEventRecord(c->ev[3], c->stream));
+    SPK_CUDA(c, cudaEventSynchronize(c->ev[3]));
+    SPK_CUDA(c, cudaEventElapsedTime(&c->tm.gemm_ms, c->ev[2], c->ev[3]));
+    unsigned long long tiles = 0, pairs = 0;
+    auto width = [&](uint32_t t) { return t >= c->i8.tile_start[2] ? 32u : (t >= c->i8.tile_start[1] ? 64u : 128u); };
+    for (unsigned long long lq = 0; lq < local_chunks; ++lq) {
+        const unsigned long long q = lq * nparts + p.part_index;
+        const uint32_t sr = (uint32_t)(std::upper_bound(prefix.begin(), prefix.end(), q) - prefix.begin()) - 1;
+        const uint32_t tj = sr * I8_SUPER + (uint32_t)(q - prefix[sr]);
+        for (uint32_t w = 0; w < I8_SUPER; ++w) {
+            const uint32_t ti = sr * I8_SUPER + w;
+            if (ti < NT && tj < NT && ti <= tj) { ++tiles; pairs += (unsigned long long)width(ti) * width(tj); }
+        }
+    }
+    c->tm.gemm_tiles = tiles; c->tm.gemm_pairs = pairs;
+    return SPK_OK;
+}
+
+// raw integer tables of one tile pair: out[(128/KI)][(128/KJ)][KI][KJ] (<= 16384 words)
+int mi_i8_debug_tile(Ctx* c, uint32_t ti, uint32_t tj, double pc, uint32_t* d_out) {
+    int r = i8_prepare(c, pc); if (r) return r;
+    if (ti > tj || tj >= c->i8.NT) return fail(c, SPK_E_INVALID, "int8 debug tile: need ti <= tj < NT");
+    I8Params gp; memset(&gp, 0, sizeof gp);
+    gp.sr_prefix = (const unsigned long long*)c->d_tilemap;
+    gp.n_parts = 1; gp.n_local_slots = 1;
+    gp.pcq = (float)(pc / c->i8_delta);
+    gp.debug_out = d_out; gp.debug_ti = ti; gp.debug_tj = tj;
+    r = i8_launch(c, gp); if (r) return r;
+    SPK_CUDA(c, cudaStreamSynchronize(c->stream));
+    return SPK_OK;
+}
+
+} // namespace spk

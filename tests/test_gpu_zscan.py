@@ -83,7 +83,7 @@ def test_scan_tcgen05_vs_oracle(ctx, n, L, linear, ld, T):
     ctx.set_alignment(s, pos); ctx.set_weights(w)
     thr = 0.05
     exp = orc.mi_scan(s, w, pos, threshold=thr, ld_threshold=ld, linear_genome=linear, circle_size=L)
-    got = ctx.mi_scan(thr, ld_threshold=ld, linear_genome=linear, n_terms=T, sort_desc=True)
+    got = ctx.mi_scan(thr, ld_threshold=ld, linear_genome=linear, n_terms=T, engine=2, sort_desc=True)
     e_exp = orc.sort_edges(exp["edges"]); e_got = got["edges"]
     assert got["n_candidates"] >= len(e_exp)
     assert len(e_got) == len(e_exp) > 0

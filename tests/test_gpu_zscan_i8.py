@@ -1,0 +1,168 @@
+"""GPU parity tests for the int8 compact one-hot engine (spk_mi_i8.cu, engine 3 = default): raw s32
+TMEM accumulators against exactly summed integer joint counts (bit-exact), and the full scan
+(filter + fp64 refine) against the CPU oracle under the north-star tolerance."""
+import numpy as np
+import pytest
+
+import oracle.oracle as orc
+from spydrpick_b200 import Context
+from spydrpick_b200.synth import generate_alignment
+from test_gpu_zscan import assert_edges_match
+
+pytestmark = pytest.mark.gpu
+INVALID = 0xFFFFFFFF
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = Context()
+    yield c
+    c.close()
+
+
+def _mixed_alignment(n, L, seed):
+    """columns of every class: monomorphic, biallelic, +gap, tri-, four-allelic, all five states."""
+    rng = np.random.default_rng(seed)
+    s = np.zeros((n, L), dtype=np.uint8)
+    for c in range(L):
+        kind = c % 7
+        states = [[0], [1, 3], [0, 2, 4], [0, 1, 2], [0, 1, 2, 3], [0, 1, 2, 3, 4], [2, 4]][kind]
+        p = rng.dirichlet(np.ones(len(states)) * 2.0)
+        col = rng.choice(states, size=n, p=p)
+        for k, st in enumerate(states):          # make sure every listed state is present
+            col[(c + k) % n] = st
+        s[:, c] = col
+    return s
+
+
+def _tile_cols(lay, t):
+    nt, cs = lay["ntiles"], lay["col_start"]
+    ts = [0, int(nt[0]), int(nt[0]) + int(nt[1])]
+    g = 2 if t >= ts[2] else (1 if t >= ts[1] else 0)
+    w = 128 >> g
+    c0 = int(cs[g]) + (t - ts[g]) * w
+    return g, 1 << g, w, c0
+
+
+def _expected_tables(s, q, lay, ti, tj):
+    gi, KI, WI, ci0 = _tile_cols(lay, ti)
+    gj, KJ, WJ, cj0 = _tile_cols(lay, tj)
+    out = np.zeros((WI, WJ, KI, KJ), dtype=np.uint64)
+    q = q.astype(np.uint64)
+    for il in range(WI):
+        oi = int(lay["perm"][ci0 + il])
+        if oi == INVALID:
+            continue
+        inf_i = int(lay["info"][ci0 + il])
+        for jl in range(WJ):
+            oj = int(lay["perm"][cj0 + jl])
+            if oj == INVALID:
+                continue
+            inf_j = int(lay["info"][cj0 + jl])
+            for a in range(inf_i & 15):
+                ma = s[:, oi] == ((inf_i >> (4 + 3 * a)) & 7)
+                for b in range(inf_j & 15):
+                    mb = s[:, oj] == ((inf_j >> (4 + 3 * b)) & 7)
+                    out[il, jl, a, b] = q[ma & mb].sum()
+    return out, (WI, WJ, KI, KJ)
+
+
+def test_i8_layout_classes(ctx):
+    s = _mixed_alignment(60, 300, 1)
+    ctx.set_alignment(s)
+    lay = ctx.debug_i8_layout()
+    perm, info = lay["perm"], lay["info"]
+    real = perm[perm != INVALID]
+    assert sorted(real.tolist()) == list(range(300))            # a permutation of the columns
+    for pc, o in enumerate(perm):
+        if o == INVALID:
+            continue
+        present = sorted(set(s[:, o].tolist()))
+        k = int(info[pc]) & 15
+        kept = [(int(info[pc]) >> (4 + 3 * a)) & 7 for a in range(k)]
+        assert kept == present[:-1] and ((int(info[pc]) >> 16) & 7) == present[-1]
+        g = 2 if pc >= lay["col_start"][2] else (1 if pc >= lay["col_start"][1] else 0)
+        assert g == (0 if k <= 1 else (1 if k == 2 else 2))
+
+
+@pytest.mark.parametrize("weighted", [False, True])
+def test_i8_tile_counts_bit_exact(ctx, weighted):
+    n, L = 300, 700
+    s = _mixed_alignment(n, L, 5)
+    ctx.set_alignment(s)
+    if weighted:
+        w = orc.weights_from_counts(orc.neighbour_counts(s, int(0.5 * L)))
+        w = w * np.linspace(0.3, 1.0, n)                        # spread the weights
+        ctx.set_weights(w)
+    lay0 = ctx.debug_i8_layout()
+    nt = lay0["ntiles"]
+    NT = int(nt.sum())
+    ts = [0, int(nt[0]), int(nt[0]) + int(nt[1])]
+    assert all(int(x) >= 1 for x in nt)
+    pairs = [(ts[0], ts[0]), (ts[0], ts[1]), (ts[0], ts[2]), (ts[1], ts[1]), (ts[1], ts[2]), (ts[2], ts[2]),
+             (ts[1] - 1, NT - 1), (ts[2] - 1, ts[2]), (NT - 1, NT - 1)]
+    first = ctx.debug_i8_tile(0, 0)                              # also quantises the weights
+    lay = ctx.debug_i8_layout(with_weights=True)
+    q = lay["q"]
+    if not weighted:
+        assert (q == 65535).all()
+    else:
+        wq = q.astype(np.float64) * lay["delta"]
+        assert np.abs(wq - w).max() <= 0.5 * lay["delta"] * (1 + 1e-9)
+    for ti, tj in pairs:
+        got = ctx.debug_i8_tile(ti, tj) if (ti, tj) != (0, 0) else first
+        exp, shape = _expected_tables(s, q, lay, ti, tj)
+        g = got[: exp.size].reshape(shape).astype(np.uint64)
+        # padding columns produce zero rows in the GEMM
+        assert np.array_equal(g, exp), (ti, tj, shape, int(np.abs(g.astype(np.int64) - exp.astype(np.int64)).max()))
+
+
+@pytest.mark.parametrize("n,L,linear,ld", [(200, 500, False, 0), (130, 333, True, 30), (257, 700, False, 100),
+                                            (64, 64, False, 0), (90, 1100, False, 0), (300, 2100, False, 0)])
+def test_scan_i8_vs_oracle(ctx, n, L, linear, ld):
+    s, pos, _ = generate_alignment(n, L, seed=n + L)
+    w = orc.weights_from_counts(orc.neighbour_counts(s, int(0.9 * L)))
+    ctx.set_alignment(s, pos); ctx.set_weights(w)
+    thr = 0.05
+    exp = orc.mi_scan(s, w, pos, threshold=thr, ld_threshold=ld, linear_genome=linear, circle_size=L)
+    got = ctx.mi_scan(thr, ld_threshold=ld, linear_genome=linear, engine=3, sort_desc=True, max_edges=L * L // 2)
+    e_exp = orc.sort_edges(exp["edges"]); e_got = got["edges"]
+    assert got["n_candidates"] >= len(e_exp)
+    assert len(e_got) == len(e_exp) > 0
+    assert_edges_match(e_got, e_exp, rtol=1e-5, atol=0)            # north-star tolerance
+    assert_edges_match(e_got, e_exp, rtol=1e-10, atol=1e-13)       # what the fp64 refine actually gives
+    assert np.allclose(got["colmax"], exp["colmax"], rtol=1e-10, atol=1e-13)
+    assert got["max_filter_error"] < 5e-5
+
+
+def test_scan_i8_mixed_classes_and_monomorphic(ctx):
+    """every class pair incl. monomorphic columns (k = 0) and all-five-state columns, uneven weights."""
+    n, L = 150, 900
+    s = _mixed_alignment(n, L, 9)
+    pos = np.arange(L, dtype=np.uint64) * 7
+    w = np.linspace(0.05, 1.0, n)
+    ctx.set_alignment(s, pos); ctx.set_weights(w)
+    thr = 0.02
+    exp = orc.mi_scan(s, w, pos, threshold=thr, ld_threshold=50, circle_size=L)
+    got = ctx.mi_scan(thr, ld_threshold=50, engine=3)
+    exact = ctx.mi_scan(thr, ld_threshold=50, engine=1)
+    assert got["edges"].tobytes() == exact["edges"].tobytes()
+    assert np.array_equal(got["colmax"], exact["colmax"])
+    assert_edges_match(got["edges"], orc.sort_edges(exp["edges"]), rtol=1e-10, atol=1e-13)
+    assert np.allclose(got["colmax"], exp["colmax"], rtol=1e-10, atol=1e-13)
+    assert got["max_filter_error"] < 5e-5
+
+
+def test_scan_i8_partitions_and_engines_agree(ctx):
+    s, pos, _ = generate_alignment(150, 2500, seed=78)
+    w = orc.weights_from_counts(orc.neighbour_counts(s, int(0.9 * 2500)))
+    ctx.set_alignment(s, pos); ctx.set_weights(w)
+    whole = ctx.mi_scan(0.06, engine=3)
+    dense = ctx.mi_scan(0.06, engine=2)
+    assert whole["edges"].tobytes() == dense["edges"].tobytes()
+    assert np.array_equal(whole["colmax"], dense["colmax"])
+    parts = [ctx.mi_scan(0.06, part_index=k, n_parts=3, engine=3) for k in range(3)]
+    assert sum(p["n_edges"] for p in parts) == whole["n_edges"]
+    merged = np.concatenate([p["edges"] for p in parts])
+    assert ctx.sort_edges(merged).tobytes() == whole["edges"].tobytes()
+    assert np.array_equal(np.max(np.stack([p["colmax"] for p in parts]), axis=0), whole["colmax"])
