@@ -292,18 +292,23 @@ int spk_mi_scan(spk_ctx* c, const spk_scan_params* pp, spk_scan_result* res) {
     if (T < 1 || T > 3) return fail(c, SPK_E_INVALID, "mi_scan: n_terms must be 1..3");
     if (p.engine < 0 || p.engine > 3) return fail(c, SPK_E_INVALID, "mi_scan: engine must be 0..3");
     const bool use_i8 = (p.engine == 0 || p.engine == 3);
-    const double band = p.band > 0.0 ? p.band : (use_i8 ? 2e-4 : (T == 1 ? 1e-2 : 2e-4));
+    // default band: measured filter errors are ~5e-6 (int8 engine), 4e-5 (bf16 T=2), 4e-3 (T=1); when the band is left to
+    // the library and a run's measured error exceeds band/2 the scan is repeated with a wider band (never silently accepted).
+    double band = p.band > 0.0 ? p.band : (use_i8 ? 4e-5 : (T == 1 ? 1e-2 : 2e-4));
+    const bool band_auto = !(p.band > 0.0);
     const uint64_t circle = p.circle_size ? p.circle_size : c->L;
     if (p.n_parts == 0) p.n_parts = 1;
     if (p.part_index >= p.n_parts) return fail(c, SPK_E_INVALID, "mi_scan: part_index >= n_parts");
     int r = ensure_scan_buffers(c, p.max_edges, p.engine == 1); if (r) return r;
 
+    unsigned long long h_counters[8] = {0};
+    uint64_t ne = 0, nw = 0;
+    for (int attempt = 0;; ++attempt) {
     SPK_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 8 * sizeof(unsigned long long), c->stream));
     fill_u64_kernel<<<(c->L_pad + 255) / 256, 256, 0, c->stream>>>((unsigned long long*)c->d_colmax, f64_ordered(-DBL_MAX), c->L_pad);
     c->tm.kernel_launches += 1;
     c->tm.gemm_ms = c->tm.refine_ms = c->tm.compact_ms = c->tm.sort_ms = 0.f; c->tm.gemm_tiles = 0;
 
-    unsigned long long h_counters[8] = {0};
     if (p.engine == 1) {
         r = mi_scan_exact(c, p, circle); if (r) return r;
     } else {
@@ -335,11 +340,21 @@ int spk_mi_scan(spk_ctx* c, const spk_scan_params* pp, spk_scan_result* res) {
     SPK_CUDA(c, cudaStreamSynchronize(c->stream));
     if (h_counters[4]) return fail(c, SPK_E_OVERFLOW, "edge buffer overflow (%llu edges > capacity %llu): raise max_edges", h_counters[1],
                                    (unsigned long long)c->edges_cap);
-    const uint64_t ne = h_counters[1], nw = h_counters[2];
+    ne = h_counters[1]; nw = h_counters[2];
     res->max_filter_error = h_counters[3] ? f64_from_ordered(h_counters[3]) : 0.0;
-    if (p.engine != 1 && res->max_filter_error > 0.5 * band)
+    if (p.engine != 1 && res->max_filter_error > 0.5 * band) {
+        if (band_auto && attempt < 3) {
+            const double wider = std::max(4.0 * res->max_filter_error, 4.0 * band);
+            if (c->verbose) fprintf(stderr, "spydrpick_b200: filter error %.3g > band/2 (band %.3g): rescanning with band %.3g\n",
+                                    res->max_filter_error, band, wider);
+            band = wider;
+            continue;
+        }
         return fail(c, SPK_E_PRECISION, "fp32 filter error %.3g exceeds half the safety band %.3g: raise band (or n_terms with engine 2)",
                     res->max_filter_error, band);
+    }
+    break;
+    }
     if (p.sort_desc) { r = sort_edges_device(c, c->d_edges, ne); if (r) return r; }
     res->n_edges = ne; res->n_wo_gaps = nw;
     res->d_edges = c->d_edges; res->d_edges_wo_gaps = c->d_wo; res->d_colmax = c->d_colmax;

@@ -57,8 +57,7 @@ def generate_alignment(n, L, seed=20260102, n_lineages=None, ld_copy_prob=0.6, n
         flip = rng.random((n, c1 - c0), dtype=np.float32) < flip_p
         fresh = draw(cols, n)
         x = np.where(flip, fresh, x)
-        x = perm[cols][np.arange(c1 - c0)[None, :], x]
-        states[:, c0:c1] = x
+        states[:, c0:c1] = x                                        # allele INDICES (0 = major) until relabelled below
 
     # short-range LD: column c copies the sample pattern of its run head with prob ld_copy_prob (5% noise)
     copy = rng.random(L) < ld_copy_prob
@@ -69,7 +68,9 @@ def generate_alignment(n, L, seed=20260102, n_lineages=None, ld_copy_prob=0.6, n
     for k0 in range(0, len(cc), chunk):
         idx = cc[k0:k0 + chunk]
         keep_own = rng.random((n, len(idx)), dtype=np.float32) < 0.02
-        states[:, idx] = np.where(keep_own, states[:, idx], states[:, head[idx]])
+        # copy the allele-index pattern (not the labels), folded into the copying column's own allele count
+        src = np.minimum(states[:, head[idx]], (ncls[idx] - 1)[None, :].astype(np.uint8))
+        states[:, idx] = np.where(keep_own, states[:, idx], src)
 
     # planted long-range couplings
     n_planted = min(n_planted, L // 50)
@@ -79,12 +80,14 @@ def generate_alignment(n, L, seed=20260102, n_lineages=None, ld_copy_prob=0.6, n
         relabel = np.argsort(rng.random((n_planted, 4)), axis=1).astype(np.uint8)
         noise = rng.random((n, n_planted), dtype=np.float32) < 0.10
         src = states[:, a]
-        mapped = relabel[np.arange(n_planted)[None, :], src]
+        mapped = relabel[np.arange(n_planted)[None, :], src] % ncls[b][None, :].astype(np.uint8)
         states[:, b] = np.where(noise, states[:, b], mapped)
 
-    # gaps last (so copied columns keep their own gap rates)
+    # allele indices -> nucleotide labels (per-column permutation), then gaps last (so copied columns keep
+    # their own gap rates)
     for c0 in range(0, L, chunk):
         c1 = min(L, c0 + chunk)
+        states[:, c0:c1] = perm[c0:c1][np.arange(c1 - c0)[None, :], states[:, c0:c1]]
         g = rng.random((n, c1 - c0), dtype=np.float32) < gap_rate[c0:c1][None, :].astype(np.float32)
         blk = states[:, c0:c1]
         blk[g] = 4
