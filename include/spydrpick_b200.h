@@ -50,6 +50,11 @@ const char* spk_last_error(const spk_ctx* ctx);     /* ctx may be NULL: last cre
  * stream). NULL restores the context's own stream. */
 int         spk_set_stream(spk_ctx* ctx, void* cuda_stream);
 
+/* Page-locked host memory for the caller's large buffers (the alignment): spk_set_alignment copies from
+ * pinned memory at full PCIe rate; pageable memory works too (the driver stages it), only slower. */
+int  spk_host_alloc(size_t bytes, void** out);
+void spk_host_free(void* p);
+
 /* ---- alignment upload ---------------------------------------------------------------- */
 /* Replaces the reference's in-memory Alignment as seen by the hot path
  * (apegrunt/Alignment_interface.hpp:62-207): dense states + loci translation pos[L]
@@ -129,6 +134,8 @@ int spk_outlier_thresholds(const double* colmax, uint64_t L, double* outlier, do
 int spk_sort_edges(spk_ctx* ctx, spk_edge* edges, uint64_t n_edges);
 
 /* Replaces aracne::run_ARACNE (include/ARACNE.hpp:411-550). edges must be sorted as above.
+ * When `edges` is the pointer spk_mi_scan returned (sort_desc = 1, list unchanged) the device copy of the
+ * scan is reused and nothing is uploaded.
  * direct_flags[e] = 1 for DIRECT edges (the reference's bool(edge), the ARACNE output column),
  * 0 for edges with a triangle in which they are the weakest and mid-min >= edge_threshold.
  * Edges [part_index*E/n_parts, (part_index+1)*E/n_parts) are evaluated (others left untouched);

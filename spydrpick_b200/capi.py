@@ -15,7 +15,8 @@ assert EDGE_DTYPE.itemsize == 16
 
 SPK_OK, SPK_E_INVALID, SPK_E_CUDA, SPK_E_NOMEM, SPK_E_OVERFLOW, SPK_E_PRECISION = 0, -1, -2, -3, -4, -5
 
-EXPORTS = ["spk_create", "spk_destroy", "spk_last_error", "spk_set_stream", "spk_set_alignment",
+EXPORTS = ["spk_create", "spk_destroy", "spk_last_error", "spk_set_stream", "spk_host_alloc", "spk_host_free",
+           "spk_set_alignment",
            "spk_neighbour_counts", "spk_set_weights", "spk_mi_pairs", "spk_determine_mi_threshold",
            "spk_mi_scan", "spk_outlier_thresholds", "spk_sort_edges", "spk_aracne", "spk_sort_edges_device",
            "spk_aracne_device", "spk_get_timings", "spk_debug_tile_counts", "spk_debug_i8_layout", "spk_debug_i8_tile",
@@ -83,6 +84,9 @@ def load():
     L.spk_aracne_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_double, C.c_uint32, C.c_uint32, C.c_void_p]
     L.spk_get_timings.argtypes = [C.c_void_p, C.POINTER(Timings)]
     L.spk_debug_tile_counts.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_int32, C.c_void_p]
+    L.spk_host_alloc.argtypes = [C.c_size_t, C.POINTER(C.c_void_p)]
+    L.spk_host_free.restype = None
+    L.spk_host_free.argtypes = [C.c_void_p]
     L.spk_debug_i8_layout.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p,
                                       C.POINTER(C.c_double)]
     L.spk_debug_i8_tile.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p]
@@ -92,6 +96,37 @@ def load():
 
 def _ptr(a):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class _PinnedOwner:
+    def __init__(self, lib, ptr):
+        self.lib, self.ptr = lib, ptr
+
+    def __del__(self):
+        try:
+            self.lib.spk_host_free(self.ptr)
+        except Exception:
+            pass
+
+
+def pinned_empty(shape, dtype=np.uint8):
+    """numpy array backed by page-locked host memory (spk_host_alloc); freed with the array."""
+    lib = load()
+    dt = np.dtype(dtype)
+    nbytes = int(np.prod(shape)) * dt.itemsize
+    p = C.c_void_p()
+    rc = lib.spk_host_alloc(max(nbytes, 16), C.byref(p))
+    if rc != SPK_OK:
+        raise SpkError(rc, "pinned host allocation of %d bytes failed" % nbytes)
+    buf = (C.c_char * max(nbytes, 16)).from_address(p.value)
+    buf._spk_owner = _PinnedOwner(lib, p)
+    return np.frombuffer(buf, dtype=dt, count=int(np.prod(shape))).reshape(shape)
+
+
+def pinned_copy(a):
+    out = pinned_empty(a.shape, a.dtype)
+    np.copyto(out, a)
+    return out
 
 
 class Context:
@@ -160,7 +195,10 @@ class Context:
         return float(thr.value)
 
     def mi_scan(self, threshold, pseudocount=0.5, ld_threshold=0, linear_genome=False, circle_size=0, max_edges=0,
-                sort_desc=True, n_terms=0, band=0.0, engine=0, part_index=0, n_parts=1, keep_on_device=False):
+                sort_desc=True, n_terms=0, band=0.0, engine=0, part_index=0, n_parts=1, keep_on_device=False,
+                copy=True):
+        """copy=False returns zero-copy views of the library-owned pinned result buffers (valid until the next
+        scan on this context); passing such an `edges` view to aracne() reuses the device copy."""
         p = ScanParams(threshold, pseudocount, ld_threshold, int(linear_genome), circle_size, max_edges, int(sort_desc),
                        n_terms, band, engine, part_index, n_parts, int(keep_on_device))
         r = ScanResult()
@@ -170,7 +208,8 @@ class Context:
             if cnt == 0 or not ptr:
                 return np.zeros(0, dtype=EDGE_DTYPE)
             buf = (C.c_char * (cnt * 16)).from_address(ptr)
-            return np.frombuffer(buf, dtype=EDGE_DTYPE).copy()
+            v = np.frombuffer(buf, dtype=EDGE_DTYPE)
+            return v.copy() if copy else v
 
         out = {"n_edges": int(r.n_edges), "n_wo_gaps": int(r.n_wo_gaps), "n_candidates": int(r.n_candidates),
                "max_filter_error": float(r.max_filter_error),

@@ -105,6 +105,8 @@ void spk_destroy(spk_ctx* c) {
     cudaStreamSynchronize(c->stream);
     free_alignment(c); free_scan(c);
     free_dev(c->d_scratch); free_dev(c->d_counters);
+    if (c->hp_edges) cudaFreeHost(c->hp_edges);
+    if (c->hp_wo) cudaFreeHost(c->hp_wo);
     if (c->d_tilemap) { cudaFree(c->d_tilemap); c->d_tilemap = nullptr; }
     for (auto& e : c->ev) if (e) cudaEventDestroy(e);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -144,7 +146,7 @@ int spk_set_alignment(spk_ctx* c, const uint8_t* states, uint32_t n, uint32_t L,
         if ((r = dev_alloc(c, c->d_colmax32, (size_t)c->L_pad * 4, "colmax32"))) return r;
         if ((r = dev_alloc(c, c->d_counts, (size_t)n * 8, "counts"))) return r;
     }
-    c->operands_terms = 0; c->stats_valid = false;
+    c->operands_terms = 0; c->stats_valid = false; c->host_edges_n = 0;
     SPK_CUDA(c, cudaEventRecord(c->ev[0], c->stream));
     SPK_CUDA(c, cudaMemcpyAsync(c->d_states, states, (size_t)n * L, cudaMemcpyHostToDevice, c->stream));
     std::vector<uint64_t> hp(c->L_pad, 0);
@@ -360,14 +362,27 @@ int spk_mi_scan(spk_ctx* c, const spk_scan_params* pp, spk_scan_result* res) {
     res->d_edges = c->d_edges; res->d_edges_wo_gaps = c->d_wo; res->d_colmax = c->d_colmax;
     c->h_colmax.resize(c->L);
     SPK_CUDA(c, cudaMemcpyAsync(c->h_colmax.data(), c->d_colmax, (size_t)c->L * 8, cudaMemcpyDeviceToHost, c->stream));
+    c->host_edges_n = 0;
     if (!p.keep_on_device) {
-        c->h_edges.resize(ne); c->h_wo.resize(nw);
-        if (ne) SPK_CUDA(c, cudaMemcpyAsync(c->h_edges.data(), c->d_edges, ne * sizeof(spk_edge), cudaMemcpyDeviceToHost, c->stream));
-        if (nw) SPK_CUDA(c, cudaMemcpyAsync(c->h_wo.data(), c->d_wo, nw * sizeof(spk_edge), cudaMemcpyDeviceToHost, c->stream));
+        // pinned mirrors: D2H at full PCIe rate, no page-fault pass over a fresh std::vector
+        auto grow = [&](spk_edge*& buf, uint64_t& cap, uint64_t want) -> int {
+            if (want <= cap) return SPK_OK;
+            if (buf) { cudaFreeHost(buf); buf = nullptr; cap = 0; }
+            const uint64_t newcap = want + want / 4 + 1024;
+            if (cudaHostAlloc((void**)&buf, newcap * sizeof(spk_edge), cudaHostAllocDefault) != cudaSuccess) {
+                cudaGetLastError(); return fail(c, SPK_E_NOMEM, "pinned host allocation failed (%llu edges)", (unsigned long long)newcap);
+            }
+            cap = newcap; return SPK_OK;
+        };
+        if ((r = grow(c->hp_edges, c->hp_edges_cap, ne))) return r;
+        if ((r = grow(c->hp_wo, c->hp_wo_cap, nw))) return r;
+        if (ne) SPK_CUDA(c, cudaMemcpyAsync(c->hp_edges, c->d_edges, ne * sizeof(spk_edge), cudaMemcpyDeviceToHost, c->stream));
+        if (nw) SPK_CUDA(c, cudaMemcpyAsync(c->hp_wo, c->d_wo, nw * sizeof(spk_edge), cudaMemcpyDeviceToHost, c->stream));
+        if (p.sort_desc) c->host_edges_n = ne;
     }
     SPK_CUDA(c, cudaStreamSynchronize(c->stream));
     res->colmax = c->h_colmax.data();
-    if (!p.keep_on_device) { res->edges = c->h_edges.data(); res->edges_wo_gaps = c->h_wo.data(); }
+    if (!p.keep_on_device) { res->edges = c->hp_edges; res->edges_wo_gaps = c->hp_wo; }
     return SPK_OK;
 }
 
@@ -409,6 +424,18 @@ int spk_aracne(spk_ctx* c, const spk_edge* edges, uint64_t n, double eps, uint32
     if (nparts == 0) nparts = 1;
     if (part >= nparts) return fail(c, SPK_E_INVALID, "aracne: part_index >= n_parts");
     SPK_CUDA(c, cudaSetDevice(c->device));
+    if (edges == c->hp_edges && n == c->host_edges_n && c->d_edges) {
+        // the caller hands back the sorted edge list of the last scan unchanged (the reference's
+        // run_ARACNE(network) right after get_MI_network): the device copy is still valid, skip the upload.
+        uint8_t* f0 = nullptr;                                   // (aracne_device owns the context scratch buffer)
+        if (cudaMalloc(&f0, n) != cudaSuccess) { cudaGetLastError(); return fail(c, SPK_E_NOMEM, "aracne: device allocation failed"); }
+        int r0 = cuda_check(c, cudaMemcpyAsync(f0, flags, n, cudaMemcpyHostToDevice, c->stream), "H2D flags");
+        if (!r0) r0 = aracne_device(c, c->d_edges, n, eps, part, nparts, f0);
+        if (!r0) r0 = cuda_check(c, cudaMemcpyAsync(flags, f0, n, cudaMemcpyDeviceToHost, c->stream), "D2H flags");
+        if (!r0) r0 = cuda_check(c, cudaStreamSynchronize(c->stream), "sync");
+        cudaFree(f0);
+        return r0;
+    }
     spk_edge* d = nullptr; uint8_t* f = nullptr;
     if (cudaMalloc(&d, n * sizeof(spk_edge)) != cudaSuccess || cudaMalloc(&f, n) != cudaSuccess) {
         cudaGetLastError(); if (d) cudaFree(d);
@@ -480,5 +507,13 @@ int spk_debug_i8_tile(spk_ctx* c, uint32_t ti, uint32_t tj, uint32_t* tables /* 
     cudaFree(d_out);
     return r;
 }
+
+int spk_host_alloc(size_t bytes, void** out) {
+    if (!out) return SPK_E_INVALID;
+    *out = nullptr;
+    if (cudaHostAlloc(out, bytes ? bytes : 16, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return SPK_E_NOMEM; }
+    return SPK_OK;
+}
+void spk_host_free(void* p) { if (p) cudaFreeHost(p); }
 
 } // extern "C"

@@ -102,6 +102,7 @@ struct Ctx {
     unsigned long long i8_wq_total = 0;   // sum of quantised weights
     bool      i8_weights_valid = false, i8_operands_valid = false;
     double    i8_rec_pc = -1.0;           // pseudocount the ColRec8 tables were built for (<0: invalid)
+    uint32_t  i8_cap_Lperm = 0, i8_cap_NT = 0, i8_cap_npad = 0;   // capacities of the buffers above (grow-only per shape)
 
     // scan outputs (device)
     Candidate* d_cand = nullptr;  uint64_t cand_cap = 0;
@@ -112,7 +113,9 @@ struct Ctx {
     float*     d_colmax32 = nullptr;      // [L_pad] running fp32 maxima (ordered-int encoded)
     unsigned long long* d_counters = nullptr;   // [8] n_cand, n_edges, n_wo, max_err_bits, ...
     // host mirrors
-    std::vector<spk_edge> h_edges, h_wo;
+    spk_edge* hp_edges = nullptr; uint64_t hp_edges_cap = 0;    // pinned (cudaHostAlloc) result mirrors, grow-only
+    spk_edge* hp_wo = nullptr;    uint64_t hp_wo_cap = 0;
+    uint64_t  host_edges_n = 0;        // # edges of the last scan mirrored in hp_edges while d_edges still holds them (0 = stale)
     std::vector<double> h_colmax;
 
     // scratch

@@ -126,7 +126,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
 mi_gemm_kernel(const __grid_constant__ CUtensorMap map_v, const __grid_constant__ CUtensorMap map_u, const GemmParams p) {
     constexpr uint32_t STAGE_BYTES = B_TILE_BYTES + T * A_TILE_BYTES;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
-    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    // align inside the shared window with pointer arithmetic on the __shared__ symbol (keeps LDS/STS addressing)
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     uint8_t* tiles = smem;                                       // NSTAGES * STAGE_BYTES
     uint8_t* aux = smem + (size_t)NSTAGES * STAGE_BYTES;
     ColStat* sI = (ColStat*)aux;                                  // [32]

@@ -74,7 +74,7 @@ struct I8Params {
     uint32_t* debug_out; uint32_t debug_ti, debug_tj;
 };
 
-struct __align__(16) JRec { uint32_t mq[4]; uint32_t smq, k, orig, pad; };
+struct __align__(16) JRec { uint32_t mq[4]; uint32_t smq, k, orig; float cm_lo; };   // cm_lo: running max - band, +inf when closed
 struct I8EpiSmem {
     JRec jrec[128];
     unsigned long long jpos[128];
@@ -106,31 +106,35 @@ template <> __device__ __forceinline__ void i8_tmem_ld<32>(uint32_t taddr, uint3
     tmem_ld16_u32(taddr, r); tmem_ld16_u32(taddr + 16u, r + 16); tmem_ld_wait();
 }
 
-// colmax bookkeeping for pairs whose column maxima have not yet cleared thr+band (rare: the first
-// tiles that touch a column). Warp-collective: lanes with equal lane%KI share the j column.
-template <int KI>
-__device__ __noinline__ bool i8_open_columns_path(const I8Params& p, I8EpiSmem& sm, float mi32, bool valid,
-                                                  unsigned long long pos_i, uint32_t j_local, uint32_t gcol_j,
-                                                  float* cm_i, uint32_t lane) {
-    bool emit = false;
+// colmax bookkeeping, entered only by lanes whose pair is within `band` of the running maximum of one of
+// its two columns while that maximum has not yet cleared thr+band (rare after the first tiles of a column:
+// closed columns carry +inf in cm_lo). Lanes that arrive together and share the j column reduce their
+// maximum with match/redux so a burst emits ~one candidate per warp, not one per lane.
+struct I8OpenRes { float cm_i, cm_i_lo; uint32_t emit; };
+__device__ __noinline__ I8OpenRes i8_open_columns_path(const I8Params& p, I8EpiSmem& sm, float mi32, unsigned long long pos_i,
+                                                       uint32_t j_local, uint32_t gcol_j, float cm_i, float cm_i_lo) {
+    I8OpenRes res; res.cm_i = cm_i; res.cm_i_lo = cm_i_lo; res.emit = 0u;
     const unsigned long long pos_j = sm.jpos[j_local];
-    const bool ld_ok = valid && genome_distance(pos_i, pos_j, p.linear, p.circle) > p.ld_threshold;
-    if (ld_ok) {
-        const float c = fmaxf(*cm_i, mi32);
-        *cm_i = c;
-        if (!(c > p.thr_hi) && mi32 >= c - p.band) emit = true;
+    if (!(genome_distance(pos_i, pos_j, p.linear, p.circle) > p.ld_threshold)) return res;
+    bool emit = false;
+    if (mi32 >= cm_i_lo) {                                         // i side: lane-local running maximum
+        const float c = fmaxf(cm_i, mi32);
+        res.cm_i = c;
+        if (c > p.thr_hi) res.cm_i_lo = INFINITY; else { res.cm_i_lo = c - p.band; emit = true; }
     }
-    float gm = ld_ok ? mi32 : -INFINITY;
-#pragma unroll
-    for (int o = KI; o < 32; o <<= 1) gm = fmaxf(gm, __shfl_xor_sync(0xffffffffu, gm, o));
-    const float cur = f32_from_ordered(sm.cmj[j_local]);
-    const float nm = fmaxf(cur, gm);
-    if (gm > cur && lane < (uint32_t)KI) {
-        atomicMax(&sm.cmj[j_local], f32_ordered(gm));
-        atomicMax(&p.colmax32[gcol_j], f32_ordered(gm));
+    const uint32_t peers = __match_any_sync(__activemask(), j_local);
+    const uint32_t mine = f32_ordered(mi32);
+    const uint32_t gmax = __reduce_max_sync(peers, mine);
+    const uint32_t cur = sm.cmj[j_local];
+    const float nm = f32_from_ordered(gmax > cur ? gmax : cur);
+    if (gmax > cur && (peers & ((1u << (threadIdx.x & 31u)) - 1u)) == 0u) {       // leader of the peer group
+        atomicMax(&sm.cmj[j_local], gmax);
+        atomicMax(&p.colmax32[gcol_j], gmax);
+        sm.jrec[j_local].cm_lo = (nm > p.thr_hi) ? INFINITY : nm - p.band;        // benign race: any stale value is a lower bound
     }
-    if (ld_ok && !(nm > p.thr_hi) && mi32 >= nm - p.band) emit = true;
-    return emit;
+    if (!(nm > p.thr_hi) && mi32 >= nm - p.band) emit = true;
+    res.emit = emit ? 1u : 0u;
+    return res;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -138,7 +142,7 @@ __device__ __noinline__ bool i8_open_columns_path(const I8Params& p, I8EpiSmem& 
 // ---------------------------------------------------------------------------------------------
 template <int KI, int KJ>
 __device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmem& sm, uint32_t tmem_acc, uint32_t q, uint32_t half,
-                                                 uint32_t lane, bool diag, uint32_t ci0, uint32_t cj0, bool any_j_open) {
+                                                 uint32_t lane, bool diag, uint32_t ci0, uint32_t cj0) {
     constexpr int LOADW = (KI == 4) ? 32 : 16;         // TMEM columns per load
     constexpr int NJ = LOADW / (2 * KJ);               // j columns per load
     constexpr int PPL = NJ / KI;                       // pairs per lane per load
@@ -157,8 +161,7 @@ __device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmem& s
     const bool vi = orig_i != I8_INVALID;
     const float cm_i0 = f32_from_ordered(p.colmax32[pi]);
     float cm_i = cm_i0;
-    const bool i_open = vi && !(cm_i0 > p.thr_hi);
-    const bool slow = any_j_open || __any_sync(0xffffffffu, i_open);
+    float cm_i_lo = (vi && !(cm_i0 > p.thr_hi)) ? cm_i0 - p.band : INFINITY;      // +inf: column closed (covered by the threshold rule)
     const float ln2 = 0.69314718055994530942f;
 
 #pragma unroll 1
@@ -222,7 +225,12 @@ __device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmem& s
             const float invZ = sm.iinvz[kj * 128u + i_local];
             const float hsum = sm.ih[kj * 128u + i_local] + sm.jh[ki * 129u + j_local];
             const float pcZ = p.pcq * invZ;
-            auto xlg = [&](uint32_t nq) { const float pr = fmaf((float)nq, invZ, pcZ); return pr * __log2f(pr); };
+            // p >= pc/Z is far above the denormal range: plain MUFU.LG2 (ftz) without the denormal rescue sequence
+            auto xlg = [&](uint32_t nq) {
+                const float pr = fmaf((float)nq, invZ, pcZ);
+                float l; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(l) : "f"(pr));
+                return pr * l;
+            };
             uint32_t colsum[KJ];
 #pragma unroll
             for (int b = 0; b < KJ; ++b) colsum[b] = 0;
@@ -256,7 +264,10 @@ __device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmem& s
             const bool valid = vi && (jr.orig != I8_INVALID) && (!diag || pi < pj);
             const float mi32 = valid ? fmaf(S, ln2, -hsum) : __int_as_float(0x7fc00000);
             bool emit = mi32 > p.thr_lo;                                   // false for NaN
-            if (slow) emit = i8_open_columns_path<KI>(p, sm, mi32, valid, pos_i, j_local, pj, &cm_i, lane) || emit;
+            if (mi32 >= fminf(cm_i_lo, jr.cm_lo)) {                        // false for NaN (invalid pair)
+                const I8OpenRes orr = i8_open_columns_path(p, sm, mi32, pos_i, j_local, pj, cm_i, cm_i_lo);
+                cm_i = orr.cm_i; cm_i_lo = orr.cm_i_lo; emit = emit || (orr.emit != 0u);
+            }
             const uint32_t bal = __ballot_sync(0xffffffffu, emit);
             if (bal) {
                 unsigned long long base = 0;
@@ -273,18 +284,15 @@ __device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmem& s
             }
         }
     }
-    if (slow && !p.debug_out) {
-#pragma unroll
-        for (int o = 1; o < KI; o <<= 1) cm_i = fmaxf(cm_i, __shfl_xor_sync(0xffffffffu, cm_i, o));
-        if (g == 0 && vi && cm_i > cm_i0) atomicMax(&p.colmax32[pi], f32_ordered(cm_i));
-    }
+    if (!p.debug_out && vi && cm_i > cm_i0) atomicMax(&p.colmax32[pi], f32_ordered(cm_i));
 }
 
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(I8_THREADS, 1)
 mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const I8Params p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
-    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    // align inside the shared window with pointer arithmetic on the __shared__ symbol (keeps LDS/STS addressing)
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     uint8_t* tiles = smem;
     I8EpiSmem& sm = *(I8EpiSmem*)(smem + (size_t)I8_NSTAGES * I8_STAGE_BYTES);
     uint64_t* full_bar = (uint64_t*)(smem + (size_t)I8_NSTAGES * I8_STAGE_BYTES + ((sizeof(I8EpiSmem) + 15) & ~(size_t)15));
@@ -369,44 +377,37 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
             const uint32_t ci0 = p.col_start[ci] + (ti - p.tile_start[ci]) * WI;
             const uint32_t cj0 = p.col_start[cj] + (tj - p.tile_start[cj]) * WJ;
             // stage the tile's column records (readers of the previous tile are past the trailing barrier)
-            uint32_t my_open = 0;
             if (et < WJ) {
                 const ColRec8 rc = p.rec[cj0 + et];
                 JRec jr;
                 jr.mq[0] = rc.mq[0]; jr.mq[1] = rc.mq[1]; jr.mq[2] = rc.mq[2]; jr.mq[3] = rc.mq[3];
-                jr.smq = rc.smq; jr.k = rc.k; jr.orig = rc.orig; jr.pad = 0;
+                jr.smq = rc.smq; jr.k = rc.k; jr.orig = rc.orig;
+                const uint32_t cm = p.colmax32[cj0 + et];
+                const float cmf = f32_from_ordered(cm);
+                jr.cm_lo = (rc.orig != I8_INVALID && !(cmf > p.thr_hi)) ? cmf - p.band : INFINITY;
                 sm.jrec[et] = jr;
                 sm.jpos[et] = ((unsigned long long)rc.pos_hi << 32) | rc.pos_lo;
 #pragma unroll
                 for (int m = 0; m < 5; ++m) sm.jh[m * 129 + et] = rc.h[m];
-                const uint32_t cm = p.colmax32[cj0 + et];
                 sm.cmj[et] = cm;
-                my_open = (rc.orig != I8_INVALID && !(f32_from_ordered(cm) > p.thr_hi)) ? 1u : 0u;
             } else if (et >= 128 && et - 128 < WI) {
                 const uint32_t e = et - 128;
                 const ColRec8* rc = p.rec + ci0 + e;
 #pragma unroll
                 for (int m = 0; m < 5; ++m) { sm.ih[m * 128 + e] = rc->h[m]; sm.iinvz[m * 128 + e] = rc->invz[m]; }
             }
-            uint32_t any_open;
-            asm volatile(
-                "{\n\t.reg .pred p, q;\n\t"
-                "setp.ne.u32 p, %1, 0;\n\t"
-                "bar.red.or.pred q, 1, 256, p;\n\t"
-                "selp.u32 %0, 1, 0, q;\n\t}"
-                : "=r"(any_open) : "r"(my_open) : "memory");
-
+            asm volatile("bar.sync 1, 256;" ::: "memory");
             mbar_wait(&tfull_bar[buf], acc_phase);
             tcgen05_fence_after();
             const uint32_t tmem_acc = tmem_base + buf * 256u;
             const bool diag = (ti == tj);
             switch (ci * 3u + cj) {
-                case 0: i8_epilogue_tile<1, 1>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0, any_open != 0); break;
-                case 1: i8_epilogue_tile<1, 2>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0, any_open != 0); break;
-                case 2: i8_epilogue_tile<1, 4>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0, any_open != 0); break;
-                case 4: i8_epilogue_tile<2, 2>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0, any_open != 0); break;
-                case 5: i8_epilogue_tile<2, 4>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0, any_open != 0); break;
-                default: i8_epilogue_tile<4, 4>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0, any_open != 0); break;
+                case 0: i8_epilogue_tile<1, 1>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0); break;
+                case 1: i8_epilogue_tile<1, 2>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0); break;
+                case 2: i8_epilogue_tile<1, 4>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0); break;
+                case 4: i8_epilogue_tile<2, 2>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0); break;
+                case 5: i8_epilogue_tile<2, 4>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0); break;
+                default: i8_epilogue_tile<4, 4>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0); break;
             }
             // accumulator drained: hand the TMEM buffer back to the MMA warp
             tcgen05_fence_before();
@@ -531,6 +532,7 @@ void i8_free(Ctx* c) {
     i8_free_dev(c->d_q); i8_free_dev(c->d_i8_colmax32);
     c->i8 = I8Layout();
     c->i8_weights_valid = c->i8_operands_valid = false; c->i8_rec_pc = -1.0;
+    c->i8_cap_Lperm = c->i8_cap_NT = c->i8_cap_npad = 0;
 }
 
 // classes + permutation from the presence masks (host; O(L))
@@ -567,14 +569,20 @@ int i8_build_layout(Ctx* c) {
         for (int a = 0; a < drop; ++a) if ((mask >> a) & 1u) { inf |= (uint32_t)a << (4 + 3 * k); ++k; }
         info[pc] = inf | k | ((uint32_t)drop << 16);
     }
-    i8_free(c);
+    // re-uploads of the same shape keep their device buffers (cudaFree/cudaMalloc of GBs costs tens of ms)
+    if (lay.Lperm > c->i8_cap_Lperm || lay.NT > c->i8_cap_NT || c->n_pad != c->i8_cap_npad) i8_free(c);
     c->i8 = lay;
-    if (cudaMalloc(&c->d_i8_perm, (size_t)lay.Lperm * 4) != cudaSuccess || cudaMalloc(&c->d_i8_info, (size_t)lay.Lperm * 4) != cudaSuccess ||
-        cudaMalloc(&c->d_i8_rec, (size_t)lay.Lperm * sizeof(ColRec8)) != cudaSuccess ||
-        cudaMalloc(&c->d_i8_colmax32, (size_t)lay.Lperm * 4) != cudaSuccess ||
+    c->i8_weights_valid = c->i8_operands_valid = false; c->i8_rec_pc = -1.0;
+    if (c->i8_cap_Lperm == 0) {
+    c->i8_cap_Lperm = lay.Lperm + 1024; c->i8_cap_NT = lay.NT + 8; c->i8_cap_npad = c->n_pad;
+    const uint32_t capL = c->i8_cap_Lperm;
+    if (cudaMalloc(&c->d_i8_perm, (size_t)capL * 4) != cudaSuccess || cudaMalloc(&c->d_i8_info, (size_t)capL * 4) != cudaSuccess ||
+        cudaMalloc(&c->d_i8_rec, (size_t)capL * sizeof(ColRec8)) != cudaSuccess ||
+        cudaMalloc(&c->d_i8_colmax32, (size_t)capL * 4) != cudaSuccess ||
         cudaMalloc(&c->d_q, (size_t)c->n_pad * 6) != cudaSuccess) {
         cudaGetLastError();
         return fail(c, SPK_E_NOMEM, "int8 engine: layout allocation failed");
+    }
     }
     SPK_CUDA(c, cudaMemcpyAsync(c->d_i8_perm, perm.data(), (size_t)lay.Lperm * 4, cudaMemcpyHostToDevice, c->stream));
     SPK_CUDA(c, cudaMemcpyAsync(c->d_i8_info, info.data(), (size_t)lay.Lperm * 4, cudaMemcpyHostToDevice, c->stream));
@@ -612,7 +620,8 @@ static int i8_prepare(Ctx* c, double pc) {
     if (!c->i8_operands_valid) {
         const size_t rowsA = (size_t)128 * c->i8.NT;
         if (!c->d_A8) {
-            if (cudaMalloc(&c->d_A8, rowsA * n_pad) != cudaSuccess || cudaMalloc(&c->d_B8, 2 * rowsA * n_pad) != cudaSuccess) {
+            const size_t capA = (size_t)128 * c->i8_cap_NT;
+            if (cudaMalloc(&c->d_A8, capA * n_pad) != cudaSuccess || cudaMalloc(&c->d_B8, 2 * capA * n_pad) != cudaSuccess) {
                 cudaGetLastError(); i8_free_dev(c->d_A8);
                 return fail(c, SPK_E_NOMEM, "int8 engine: cannot allocate operands (%zu bytes)", 3 * rowsA * n_pad);
             }

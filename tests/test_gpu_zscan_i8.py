@@ -166,3 +166,23 @@ def test_scan_i8_partitions_and_engines_agree(ctx):
     merged = np.concatenate([p["edges"] for p in parts])
     assert ctx.sort_edges(merged).tobytes() == whole["edges"].tobytes()
     assert np.array_equal(np.max(np.stack([p["colmax"] for p in parts]), axis=0), whole["colmax"])
+
+
+def test_pinned_buffers_and_aracne_device_reuse(ctx):
+    """zero-copy result views + spk_aracne on the scan's own edge pointer (device copy reused) == the copying path."""
+    from spydrpick_b200.capi import pinned_copy
+    s, pos, _ = generate_alignment(120, 1500, seed=5)
+    sp = pinned_copy(s)
+    assert np.array_equal(sp, s)
+    ctx.set_alignment(sp, pos)
+    ctx.set_weights(orc.weights_from_counts(orc.neighbour_counts(s, int(0.9 * 1500))))
+    r = ctx.mi_scan(0.05, copy=False)
+    view = r["edges"]
+    copy = view.copy()
+    f_view = ctx.aracne(view)                # pointer == library buffer -> no upload
+    f_copy = ctx.aracne(copy)                # generic path
+    assert np.array_equal(f_view, f_copy)
+    assert np.array_equal(f_view, orc.aracne_closed(copy, 2.220446049250313e-16))
+    # after a new alignment the old pointer must not be trusted
+    ctx.set_alignment(sp, pos)
+    assert np.array_equal(ctx.aracne(copy), f_copy)
