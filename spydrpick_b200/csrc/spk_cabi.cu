@@ -40,7 +40,7 @@ static void free_alignment(Ctx* c) {
     free_dev(c->d_states); free_dev(c->d_colmajor); free_dev(c->d_planes); free_dev(c->d_pos); free_dev(c->d_masks);
     free_dev(c->d_w); free_dev(c->d_marg); free_dev(c->d_colstat); free_dev(c->d_U); free_dev(c->d_V);
     free_dev(c->d_colmax); free_dev(c->d_colmax32); free_dev(c->d_counts);
-    i8_free(c);
+    i8_free(c); mi_exact_free(c);
     c->operands_terms = 0; c->operands_cap_terms = 0; c->stats_valid = false;
 }
 static void free_scan(Ctx* c) {
@@ -146,7 +146,7 @@ int spk_set_alignment(spk_ctx* c, const uint8_t* states, uint32_t n, uint32_t L,
         if ((r = dev_alloc(c, c->d_colmax32, (size_t)c->L_pad * 4, "colmax32"))) return r;
         if ((r = dev_alloc(c, c->d_counts, (size_t)n * 8, "counts"))) return r;
     }
-    c->operands_terms = 0; c->stats_valid = false; c->host_edges_n = 0;
+    c->operands_terms = 0; c->stats_valid = false; c->host_edges_n = 0; c->g_state = 0;
     SPK_CUDA(c, cudaEventRecord(c->ev[0], c->stream));
     SPK_CUDA(c, cudaMemcpyAsync(c->d_states, states, (size_t)n * L, cudaMemcpyHostToDevice, c->stream));
     std::vector<uint64_t> hp(c->L_pad, 0);
@@ -188,7 +188,7 @@ int spk_set_weights(spk_ctx* c, const double* w) {
     SPK_CUDA(c, cudaStreamSynchronize(c->stream));
     c->w_total = tot;
     c->h_w.assign(w, w + c->n);
-    c->i8_weights_valid = false;
+    c->i8_weights_valid = false; c->g_state = 0;
     c->operands_terms = 0; c->stats_valid = false;
     return SPK_OK;
 }

@@ -123,6 +123,16 @@ struct Ctx {
     void* d_tilemap = nullptr;            // CUtensorMap storage is passed by value; super-row prefix table lives here
     uint64_t* d_counts = nullptr;         // [n] neighbour counts
 
+    // weight-grouped bit planes for the fp64 kernels (spk_mi_exact.cu): samples are ordered by distinct weight
+    // value, every group padded to whole 32-bit words, so N_ab = sum_w gval[w] * popc(Bi_a[w] & Bj_b[w]).
+    uint32_t* d_gbits = nullptr;          // [L_pad][5][g_NW] one bit plane per (column, state)
+    double*   d_gval = nullptr;           // [g_NW] weight of the samples of word w (0 for padding words)
+    double*   d_gmarg = nullptr;          // [L_pad][5] fp64 weighted marginals summed the same way
+    int32_t*  d_gslot = nullptr;          // [g_NW*32] sample index per bit slot, -1 = padding
+    uint32_t  g_NW = 0;                   // words per plane (multiple of 32)
+    size_t    g_cap_words = 0;            // capacity of d_gbits in words
+    int       g_state = 0;                // 0 = not built, 1 = built, 2 = weights not groupable (byte kernel is used)
+
     spk_timings tm = {};
     cudaEvent_t ev[8] = {};
 };
@@ -149,6 +159,7 @@ int mi_refine_candidates(Ctx* c, uint64_t ncand, double pc);
 int mi_scan_exact(Ctx* c, const spk_scan_params& p, uint64_t circle);
 // threshold + colmax + compaction over refined candidates
 int mi_compact(Ctx* c, uint64_t ncand, const spk_scan_params& p, uint64_t circle);
+void mi_exact_free(Ctx* c);                                   // releases the weight-grouped bit planes
 
 // ---- K2 (spk_mi_gemm.cu)
 int mi_gemm_filter(Ctx* c, const spk_scan_params& p, int n_terms, double band, uint64_t circle);

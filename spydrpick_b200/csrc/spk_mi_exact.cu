@@ -7,6 +7,8 @@
 // samples and accumulate into lane-private shared-memory bins (no atomics, deterministic), then
 // lane l < 25 owns cell l = b*5+a and the entropy terms are evaluated one log per lane.
 #include <cfloat>
+#include <algorithm>
+#include <vector>
 #include "spk_internal.h"
 
 namespace spk {
@@ -72,18 +74,150 @@ __device__ __forceinline__ double warp_mi_pass(double& v, uint32_t mask_i, uint3
     return jointH - icondH - jcondH;
 }
 
+// =============================================================================================
+// Weight-grouped popcount crosstable. Sample weights take few distinct values (w = 1/#neighbours, or all
+// 1): ordering the samples by weight value and padding each group to whole words turns the weighted
+// joint count into  N_ab = sum_w gval[w] * popc(Bi_a[w] & Bj_b[w])  -- ~30x fewer instructions per pair
+// than scattering per-sample weights into 25 bins. Only the kept x kept cells (all present states but the
+// highest-coded one) are accumulated; the remaining row / column / corner follow from the fp64 marginals
+// (summed the same way), exactly as a crosstable's margins do.
+// =============================================================================================
+__global__ void __launch_bounds__(128)
+gbits_build_kernel(const uint8_t* __restrict__ colmajor, const int32_t* __restrict__ gslot, const double* __restrict__ gval,
+                   uint32_t* __restrict__ gbits, double* __restrict__ gmarg, uint32_t L, uint32_t n_pad, uint32_t NW) {
+    __shared__ double red[4][NSTATES];
+    const uint32_t c = blockIdx.x;
+    const uint8_t* col = colmajor + (size_t)c * n_pad;
+    double m[NSTATES] = {0, 0, 0, 0, 0};
+    for (uint32_t w = threadIdx.x; w < NW; w += blockDim.x) {
+        uint32_t pl[NSTATES] = {0, 0, 0, 0, 0};
+        if (c < L) {
+            for (uint32_t b = 0; b < 32; ++b) {
+                const int32_t sidx = gslot[w * 32 + b];
+                if (sidx >= 0) {
+                    const uint32_t x = col[sidx];
+#pragma unroll
+                    for (int a = 0; a < NSTATES; ++a) pl[a] |= (x == (uint32_t)a) ? (1u << b) : 0u;
+                }
+            }
+        }
+        const double v = gval[w];
+#pragma unroll
+        for (int a = 0; a < NSTATES; ++a) {
+            gbits[((size_t)c * NSTATES + a) * NW + w] = pl[a];
+            m[a] += v * (double)__popc(pl[a]);
+        }
+    }
+#pragma unroll
+    for (int a = 0; a < NSTATES; ++a) {
+        m[a] = warp_sum(m[a]);
+        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5][a] = m[a];
+    }
+    __syncthreads();
+    if (threadIdx.x < NSTATES) gmarg[(size_t)c * NSTATES + threadIdx.x] = red[0][threadIdx.x] + red[1][threadIdx.x] + red[2][threadIdx.x] + red[3][threadIdx.x];
+}
+
+template <int KI, int KJ>
+__device__ __forceinline__ void gacc(const uint32_t* __restrict__ Bi, const uint32_t* __restrict__ Bj, const uint32_t* si, const uint32_t* sj,
+                                     const double* __restrict__ gval, uint32_t NW, uint32_t lane, double* acc /*[16]*/) {
+    double t[KI * KJ];
+#pragma unroll
+    for (int k = 0; k < KI * KJ; ++k) t[k] = 0.0;
+    for (uint32_t w = lane; w < NW; w += 32) {
+        const double v = gval[w];
+        uint32_t xi[KI], xj[KJ];
+#pragma unroll
+        for (int a = 0; a < KI; ++a) xi[a] = Bi[si[a] * NW + w];
+#pragma unroll
+        for (int b = 0; b < KJ; ++b) xj[b] = Bj[sj[b] * NW + w];
+#pragma unroll
+        for (int a = 0; a < KI; ++a)
+#pragma unroll
+            for (int b = 0; b < KJ; ++b) t[a * KJ + b] = fma((double)__popc(xi[a] & xj[b]), v, t[a * KJ + b]);
+    }
+#pragma unroll
+    for (int a = 0; a < KI; ++a)
+#pragma unroll
+        for (int b = 0; b < KJ; ++b) acc[a * 4 + b] = warp_sum(t[a * KJ + b]);
+}
+
+// Returns the cell value for lane < 25 (b = lane/5 j-state, a = lane%5 i-state), like warp_crosstab.
+__device__ __forceinline__ double warp_crosstab_grouped(const uint32_t* __restrict__ gbits, const double* __restrict__ gval,
+                                                        const double* __restrict__ gmarg, uint32_t NW, uint32_t i, uint32_t j,
+                                                        uint32_t mask_i, uint32_t mask_j, uint32_t lane) {
+    // kept states = present states minus the highest-coded present one
+    uint32_t si[4] = {0, 0, 0, 0}, sj[4] = {0, 0, 0, 0};
+    const uint32_t di = 31u - __clz(mask_i | 1u), dj = 31u - __clz(mask_j | 1u);      // dropped (recovered) states
+    uint32_t mk = mask_i & ~(1u << di), ki = 0, kj = 0;
+#pragma unroll
+    for (int a = 0; a < 4; ++a) if (mk) { si[a] = __ffs(mk) - 1; mk &= mk - 1; ++ki; }
+    mk = mask_j & ~(1u << dj);
+#pragma unroll
+    for (int b = 0; b < 4; ++b) if (mk) { sj[b] = __ffs(mk) - 1; mk &= mk - 1; ++kj; }
+    const uint32_t* Bi = gbits + (size_t)i * NSTATES * NW;
+    const uint32_t* Bj = gbits + (size_t)j * NSTATES * NW;
+    double acc[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) acc[k] = 0.0;
+    switch (ki * 5 + kj) {
+#define SPK_GCASE(A, B) case (A) * 5 + (B): gacc<A, B>(Bi, Bj, si, sj, gval, NW, lane, acc); break;
+        SPK_GCASE(1, 1) SPK_GCASE(1, 2) SPK_GCASE(1, 3) SPK_GCASE(1, 4)
+        SPK_GCASE(2, 1) SPK_GCASE(2, 2) SPK_GCASE(2, 3) SPK_GCASE(2, 4)
+        SPK_GCASE(3, 1) SPK_GCASE(3, 2) SPK_GCASE(3, 3) SPK_GCASE(3, 4)
+        SPK_GCASE(4, 1) SPK_GCASE(4, 2) SPK_GCASE(4, 3) SPK_GCASE(4, 4)
+#undef SPK_GCASE
+        default: break;                                              // a monomorphic column: margins only
+    }
+    // assemble this lane's cell of the 5x5 table
+    const uint32_t a = lane % 5, b = lane / 5;
+    double v = 0.0;
+    if (lane < 25 && ((mask_i >> a) & 1u) && ((mask_j >> b) & 1u)) {
+        int ia = -1, jb = -1;                                        // kept index, -1 = dropped state
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { if ((uint32_t)k < ki && si[k] == a) ia = k; if ((uint32_t)k < kj && sj[k] == b) jb = k; }
+        const double* mi_ = gmarg + (size_t)i * NSTATES;
+        const double* mj_ = gmarg + (size_t)j * NSTATES;
+        double rowsum = 0.0, colsum = 0.0, tot = 0.0, mjk = 0.0;    // over kept x kept cells
+#pragma unroll
+        for (int x = 0; x < 4; ++x)
+#pragma unroll
+            for (int y = 0; y < 4; ++y) {
+                const double cxy = acc[x * 4 + y];
+                if (x == ia) rowsum += cxy;
+                if (y == jb) colsum += cxy;
+                tot += cxy;
+            }
+#pragma unroll
+        for (int y = 0; y < 4; ++y) if ((uint32_t)y < kj) mjk += mj_[sj[y]];
+        if (ia >= 0 && jb >= 0) {
+            double cell = 0.0;
+#pragma unroll
+            for (int x = 0; x < 4; ++x)
+#pragma unroll
+                for (int y = 0; y < 4; ++y) if (x == ia && y == jb) cell = acc[x * 4 + y];
+            v = cell;
+        } else if (ia >= 0) v = mi_[a] - rowsum;                     // (kept a, dropped j-state)
+        else if (jb >= 0) v = mj_[b] - colsum;                       // (dropped i-state, kept b)
+        else v = mi_[di] - (mjk - tot);                              // corner
+        v = fmax(v, 0.0);
+    }
+    return v;
+}
+
 // ---- K2b: explicit pair list ---------------------------------------------------------------
 __global__ void __launch_bounds__(EX_WARPS * 32)
 mi_pairs_kernel(const uint8_t* __restrict__ colmajor, const double* __restrict__ w, const uint8_t* __restrict__ masks,
                 const uint32_t* __restrict__ pi, const uint32_t* __restrict__ pj, unsigned long long npairs,
-                uint32_t n_pad, double pc, double* __restrict__ mi) {
+                uint32_t n_pad, double pc, double* __restrict__ mi,
+                const uint32_t* __restrict__ gbits, const double* __restrict__ gval, const double* __restrict__ gmarg, uint32_t NW) {
     __shared__ double bins_all[EX_WARPS][25 * 32];
     const uint32_t lane = threadIdx.x % 32, wid = threadIdx.x / 32;
     double* bins = bins_all[wid];
     for (unsigned long long p = (unsigned long long)blockIdx.x * EX_WARPS + wid; p < npairs;
          p += (unsigned long long)gridDim.x * EX_WARPS) {
         const uint32_t i = pi[p], j = pj[p];
-        double v = warp_crosstab(colmajor + (size_t)i * n_pad, colmajor + (size_t)j * n_pad, w, n_pad, bins, lane);
+        double v = gbits ? warp_crosstab_grouped(gbits, gval, gmarg, NW, i, j, masks[i], masks[j], lane)
+                         : warp_crosstab(colmajor + (size_t)i * n_pad, colmajor + (size_t)j * n_pad, w, n_pad, bins, lane);
         const double m = warp_mi_pass(v, masks[i], masks[j], pc, lane);
         if (lane == 0) mi[p] = m;
     }
@@ -94,7 +228,8 @@ mi_pairs_kernel(const uint8_t* __restrict__ colmajor, const double* __restrict__
 __global__ void __launch_bounds__(EX_WARPS * 32)
 mi_refine_kernel(const uint8_t* __restrict__ colmajor, const double* __restrict__ w, const uint8_t* __restrict__ masks,
                  const Candidate* __restrict__ cand, unsigned long long ncand, uint32_t n_pad, double pc,
-                 spk_edge* __restrict__ refined, double* __restrict__ refined_wo, unsigned long long* __restrict__ counters) {
+                 spk_edge* __restrict__ refined, double* __restrict__ refined_wo, unsigned long long* __restrict__ counters,
+                 const uint32_t* __restrict__ gbits, const double* __restrict__ gval, const double* __restrict__ gmarg, uint32_t NW) {
     __shared__ double bins_all[EX_WARPS][25 * 32];
     const uint32_t lane = threadIdx.x % 32, wid = threadIdx.x / 32;
     double* bins = bins_all[wid];
@@ -103,7 +238,8 @@ mi_refine_kernel(const uint8_t* __restrict__ colmajor, const double* __restrict_
          p += (unsigned long long)gridDim.x * EX_WARPS) {
         const Candidate cd = cand[p];
         const uint32_t mi_ = masks[cd.i], mj_ = masks[cd.j];
-        double v = warp_crosstab(colmajor + (size_t)cd.i * n_pad, colmajor + (size_t)cd.j * n_pad, w, n_pad, bins, lane);
+        double v = gbits ? warp_crosstab_grouped(gbits, gval, gmarg, NW, cd.i, cd.j, mi_, mj_, lane)
+                         : warp_crosstab(colmajor + (size_t)cd.i * n_pad, colmajor + (size_t)cd.j * n_pad, w, n_pad, bins, lane);
         const double m = warp_mi_pass(v, mi_, mj_, pc, lane);
         double m2 = __longlong_as_double(0x7ff8000000000000ll);   // NaN = "no gap column involved"
         if ((mi_ | mj_) & (1u << GAP)) m2 = warp_mi_pass(v, mi_ & ~(1u << GAP), mj_ & ~(1u << GAP), pc, lane);
@@ -179,6 +315,61 @@ __global__ void enumerate_pairs_kernel(Candidate* __restrict__ cand, uint32_t i0
 }
 
 // =============================================================================================
+// host: group the samples by distinct weight value and build the bit planes (once per weights/alignment)
+void mi_exact_free(Ctx* c) {
+    if (c->d_gbits) { cudaFree(c->d_gbits); c->d_gbits = nullptr; }
+    if (c->d_gval) { cudaFree(c->d_gval); c->d_gval = nullptr; }
+    if (c->d_gmarg) { cudaFree(c->d_gmarg); c->d_gmarg = nullptr; }
+    if (c->d_gslot) { cudaFree(c->d_gslot); c->d_gslot = nullptr; }
+    c->g_cap_words = 0; c->g_NW = 0; c->g_state = 0;
+}
+
+static int ensure_grouped(Ctx* c) {
+    if (c->g_state != 0) return SPK_OK;
+    const uint32_t n = c->n;
+    if (c->h_w.size() != n) { c->g_state = 2; return SPK_OK; }
+    // order samples by weight value (bit pattern), stable
+    std::vector<uint32_t> order(n);
+    for (uint32_t s = 0; s < n; ++s) order[s] = s;
+    std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return c->h_w[a] < c->h_w[b]; });
+    std::vector<int32_t> slot; std::vector<double> val;
+    slot.reserve((size_t)n + 4096);
+    for (uint32_t k = 0; k < n;) {
+        uint32_t e = k;
+        while (e < n && c->h_w[order[e]] == c->h_w[order[k]]) ++e;
+        for (uint32_t t = k; t < e; ++t) slot.push_back((int32_t)order[t]);
+        while (slot.size() % 32) slot.push_back(-1);
+        while (val.size() < slot.size() / 32) val.push_back(c->h_w[order[k]]);
+        k = e;
+        if (slot.size() / 32 > 2 * (size_t)((n + 31) / 32) + 64) { c->g_state = 2; return SPK_OK; }   // too many distinct weights
+    }
+    while ((slot.size() / 32) % 32) { for (int t = 0; t < 32; ++t) slot.push_back(-1); val.push_back(0.0); }
+    const uint32_t NW = (uint32_t)(slot.size() / 32);
+    const size_t words = (size_t)c->L_pad * NSTATES * NW;
+    if (words > c->g_cap_words || !c->d_gbits) {
+        mi_exact_free(c);
+        if (cudaMalloc(&c->d_gbits, words * 4) != cudaSuccess || cudaMalloc(&c->d_gmarg, (size_t)c->L_pad * NSTATES * 8) != cudaSuccess) {
+            cudaGetLastError(); mi_exact_free(c);
+            c->g_state = 2;                                          // not enough memory: the byte kernel still works
+            return SPK_OK;
+        }
+        c->g_cap_words = words;
+    }
+    if (c->d_gval) { cudaFree(c->d_gval); c->d_gval = nullptr; }
+    if (c->d_gslot) { cudaFree(c->d_gslot); c->d_gslot = nullptr; }
+    if (cudaMalloc(&c->d_gval, (size_t)NW * 8) != cudaSuccess || cudaMalloc(&c->d_gslot, (size_t)NW * 32 * 4) != cudaSuccess) {
+        cudaGetLastError(); return fail(c, SPK_E_NOMEM, "grouped bit planes: allocation failed");
+    }
+    SPK_CUDA(c, cudaMemcpyAsync(c->d_gval, val.data(), (size_t)NW * 8, cudaMemcpyHostToDevice, c->stream));
+    SPK_CUDA(c, cudaMemcpyAsync(c->d_gslot, slot.data(), (size_t)NW * 32 * 4, cudaMemcpyHostToDevice, c->stream));
+    gbits_build_kernel<<<c->L_pad, 128, 0, c->stream>>>(c->d_colmajor, c->d_gslot, c->d_gval, c->d_gbits, c->d_gmarg, c->L, c->n_pad, NW);
+    c->tm.kernel_launches += 1;
+    SPK_CUDA(c, cudaGetLastError());
+    SPK_CUDA(c, cudaStreamSynchronize(c->stream));                   // slot / val are host temporaries
+    c->g_NW = NW; c->g_state = 1;
+    return SPK_OK;
+}
+
 static int refine_grid(Ctx* c, unsigned long long n) {
     unsigned long long blocks = (n + EX_WARPS - 1) / EX_WARPS;
     const unsigned long long cap = (unsigned long long)c->sm_count * 16;
@@ -188,8 +379,11 @@ static int refine_grid(Ctx* c, unsigned long long n) {
 int mi_pairs_exact(Ctx* c, const uint32_t* d_pi, const uint32_t* d_pj, uint64_t npairs, double pc, double* d_mi) {
     if (npairs == 0) return SPK_OK;
     SPK_CUDA(c, cudaEventRecord(c->ev[0], c->stream));
+    { int rg = ensure_grouped(c); if (rg) return rg; }
+    const bool grouped = (c->g_state == 1);
     mi_pairs_kernel<<<refine_grid(c, npairs), EX_WARPS * 32, 0, c->stream>>>(c->d_colmajor, c->d_w, c->d_masks, d_pi, d_pj,
-                                                                            npairs, c->n_pad, pc, d_mi);
+                                                                            npairs, c->n_pad, pc, d_mi,
+                                                                            grouped ? c->d_gbits : nullptr, c->d_gval, c->d_gmarg, c->g_NW);
     c->tm.kernel_launches += 1;
     SPK_CUDA(c, cudaEventRecord(c->ev[1], c->stream));
     SPK_CUDA(c, cudaEventSynchronize(c->ev[1]));
@@ -200,9 +394,12 @@ int mi_pairs_exact(Ctx* c, const uint32_t* d_pi, const uint32_t* d_pj, uint64_t 
 
 int mi_refine_candidates(Ctx* c, uint64_t ncand, double pc) {
     if (ncand == 0) return SPK_OK;
+    { int rg = ensure_grouped(c); if (rg) return rg; }
+    const bool grouped = (c->g_state == 1);
     mi_refine_kernel<<<refine_grid(c, ncand), EX_WARPS * 32, 0, c->stream>>>(c->d_colmajor, c->d_w, c->d_masks, c->d_cand, ncand,
                                                                             c->n_pad, pc, c->d_refined, c->d_refined_wo,
-                                                                            c->d_counters);
+                                                                            c->d_counters,
+                                                                            grouped ? c->d_gbits : nullptr, c->d_gval, c->d_gmarg, c->g_NW);
     c->tm.kernel_launches += 1;
     SPK_CUDA(c, cudaGetLastError());
     return SPK_OK;
