@@ -44,7 +44,7 @@ static void free_alignment(Ctx* c) {
     c->operands_terms = 0; c->operands_cap_terms = 0; c->stats_valid = false;
 }
 static void free_scan(Ctx* c) {
-    free_dev(c->d_cand); free_dev(c->d_edges); free_dev(c->d_wo); free_dev(c->d_refined); free_dev(c->d_refined_wo);
+    free_dev(c->d_cand); free_dev(c->d_cand2); c->cand2_cap = 0; free_dev(c->d_edges); free_dev(c->d_wo); free_dev(c->d_refined); free_dev(c->d_refined_wo);
     c->cand_cap = c->edges_cap = c->wo_cap = c->refined_cap = 0;
 }
 
@@ -328,7 +328,7 @@ int spk_mi_scan(spk_ctx* c, const spk_scan_params* pp, spk_scan_result* res) {
         const uint64_t ncand = h_counters[0];
         res->n_candidates = ncand;
         SPK_CUDA(c, cudaEventRecord(c->ev[4], c->stream));
-        r = mi_refine_candidates(c, ncand, p.pseudocount); if (r) return r;
+        r = mi_refine_candidates(c, ncand, p.pseudocount, p.threshold); if (r) return r;
         SPK_CUDA(c, cudaEventRecord(c->ev[5], c->stream));
         r = mi_compact(c, ncand, p, circle); if (r) return r;
         SPK_CUDA(c, cudaEventRecord(c->ev[6], c->stream));

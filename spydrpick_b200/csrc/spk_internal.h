@@ -106,6 +106,7 @@ struct Ctx {
 
     // scan outputs (device)
     Candidate* d_cand = nullptr;  uint64_t cand_cap = 0;
+    Candidate* d_cand2 = nullptr; uint64_t cand2_cap = 0;     // class-sorted copy for the fp64 refine
     spk_edge*  d_edges = nullptr; uint64_t edges_cap = 0;
     spk_edge*  d_wo = nullptr;    uint64_t wo_cap = 0;
     spk_edge*  d_refined = nullptr; double* d_refined_wo = nullptr; uint64_t refined_cap = 0;
@@ -129,6 +130,8 @@ struct Ctx {
     double*   d_gval = nullptr;           // [g_NW] weight of the samples of word w (0 for padding words)
     double*   d_gmarg = nullptr;          // [L_pad][5] fp64 weighted marginals summed the same way
     int32_t*  d_gslot = nullptr;          // [g_NW*32] sample index per bit slot, -1 = padding
+    double*   d_gH = nullptr;             // [L_pad][5] marginal entropy sum_a p_a ln p_a for partner #states 1..5
+    double    g_pc = -1.0;                // pseudocount d_gH was built for
     uint32_t  g_NW = 0;                   // words per plane (multiple of 32)
     size_t    g_cap_words = 0;            // capacity of d_gbits in words
     int       g_state = 0;                // 0 = not built, 1 = built, 2 = weights not groupable (byte kernel is used)
@@ -154,7 +157,7 @@ int hamming_neighbour_counts(Ctx* c, uint64_t min_identical, int quirk);
 // ---- exact fp64 MI (spk_mi_exact.cu)
 int mi_pairs_exact(Ctx* c, const uint32_t* d_pi, const uint32_t* d_pj, uint64_t npairs, double pc, double* d_mi);
 // refine candidates -> d_refined (i,j,mi64), d_refined_wo (NaN when no gap column involved)
-int mi_refine_candidates(Ctx* c, uint64_t ncand, double pc);
+int mi_refine_candidates(Ctx* c, uint64_t ncand, double pc, double wo_threshold);   // MI-without-gaps only when mi > wo_threshold
 // exhaustive diagnostic engine: emits every pair of the partition as a candidate-free exact scan
 int mi_scan_exact(Ctx* c, const spk_scan_params& p, uint64_t circle);
 // threshold + colmax + compaction over refined candidates

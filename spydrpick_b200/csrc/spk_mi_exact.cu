@@ -159,12 +159,15 @@ __device__ __forceinline__ double warp_crosstab_grouped(const uint32_t* __restri
     double acc[16];
 #pragma unroll
     for (int k = 0; k < 16; ++k) acc[k] = 0.0;
-    switch (ki * 5 + kj) {
+    // classes of 1, 2 or 4 accumulated rows; a 3-row column borrows the (all-zero) plane of an absent state
+    if (ki == 3) si[3] = __ffs(~mask_i & 31u) - 1;
+    if (kj == 3) sj[3] = __ffs(~mask_j & 31u) - 1;
+    const uint32_t ci = ki == 3 ? 4u : ki, cj = kj == 3 ? 4u : kj;
+    switch (ci * 5 + cj) {
 #define SPK_GCASE(A, B) case (A) * 5 + (B): gacc<A, B>(Bi, Bj, si, sj, gval, NW, lane, acc); break;
-        SPK_GCASE(1, 1) SPK_GCASE(1, 2) SPK_GCASE(1, 3) SPK_GCASE(1, 4)
-        SPK_GCASE(2, 1) SPK_GCASE(2, 2) SPK_GCASE(2, 3) SPK_GCASE(2, 4)
-        SPK_GCASE(3, 1) SPK_GCASE(3, 2) SPK_GCASE(3, 3) SPK_GCASE(3, 4)
-        SPK_GCASE(4, 1) SPK_GCASE(4, 2) SPK_GCASE(4, 3) SPK_GCASE(4, 4)
+        SPK_GCASE(1, 1) SPK_GCASE(1, 2) SPK_GCASE(1, 4)
+        SPK_GCASE(2, 1) SPK_GCASE(2, 2) SPK_GCASE(2, 4)
+        SPK_GCASE(4, 1) SPK_GCASE(4, 2) SPK_GCASE(4, 4)
 #undef SPK_GCASE
         default: break;                                              // a monomorphic column: margins only
     }
@@ -202,6 +205,335 @@ __device__ __forceinline__ double warp_crosstab_grouped(const uint32_t* __restri
         v = fmax(v, 0.0);
     }
     return v;
+}
+
+// marginal-entropy tables for the grouped path: gH[c][m-1] = sum_{a in P_c} p_a ln p_a with
+// p_a = (marg_a + pc*m) / (W + pc*|P_c|*m), m = #present states of the partner column. These are the row /
+// column sums of the normalised joint table (mi.hpp:173-178) in closed form.
+__global__ void gh_tables_kernel(const double* __restrict__ gmarg, const uint8_t* __restrict__ masks, double* __restrict__ gH,
+                                 uint32_t L_pad, double w_total, double pc) {
+    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= L_pad) return;
+    const uint32_t mask = masks[c] & 31u;
+    const int np = __popc(mask);
+    for (int m = 1; m <= NSTATES; ++m) {
+        const double Z = w_total + pc * (double)np * (double)m;
+        double h = 0.0;
+        for (int a = 0; a < NSTATES; ++a) if ((mask >> a) & 1u) { const double pr = (gmarg[(size_t)c * NSTATES + a] + pc * (double)m) / Z; h += pr * log(pr); }
+        gH[(size_t)c * NSTATES + (m - 1)] = h;
+    }
+}
+
+// MI of one pair on the grouped path. Pass 1 needs one log per lane and one reduction (marginal terms come from
+// gH); the normalised table is left in v exactly as the reference leaves its buffer, so that the literal
+// "MI without gaps" second pass (mi.hpp:108-135,465-489) can run on it when the caller needs it.
+__device__ __forceinline__ double grouped_mi_pass1(double& v, uint32_t mask_i, uint32_t mask_j, double w_total, double pc,
+                                                   const double* __restrict__ gH, uint32_t i, uint32_t j, uint32_t lane) {
+    const uint32_t a = lane % 5, b = lane / 5;
+    const bool in_ij = lane < 25 && ((mask_i >> a) & 1u) && ((mask_j >> b) & 1u);
+    const int np_i = __popc(mask_i), np_j = __popc(mask_j);
+    const double Z = w_total + pc * (double)(np_i * np_j);
+    double t = 0.0;
+    if (in_ij) { v = (v + pc) / Z; t = v * log(v); } else v = 0.0;
+    const double jointH = warp_sum(t);
+    return jointH - gH[(size_t)i * NSTATES + (np_j - 1)] - gH[(size_t)j * NSTATES + (np_i - 1)];
+}
+
+__global__ void __launch_bounds__(EX_WARPS * 32, 4)
+mi_pairs_grouped_kernel(const uint8_t* __restrict__ masks, const uint32_t* __restrict__ pi, const uint32_t* __restrict__ pj,
+                        unsigned long long npairs, double pc, double w_total, double* __restrict__ mi,
+                        const uint32_t* __restrict__ gbits, const double* __restrict__ gval, const double* __restrict__ gmarg,
+                        const double* __restrict__ gH, uint32_t NW) {
+    const uint32_t lane = threadIdx.x % 32, wid = threadIdx.x / 32;
+    for (unsigned long long p = (unsigned long long)blockIdx.x * EX_WARPS + wid; p < npairs;
+         p += (unsigned long long)gridDim.x * EX_WARPS) {
+        const uint32_t i = pi[p], j = pj[p];
+        const uint32_t mi_ = masks[i], mj_ = masks[j];
+        double v = warp_crosstab_grouped(gbits, gval, gmarg, NW, i, j, mi_, mj_, lane);
+        const double m = grouped_mi_pass1(v, mi_, mj_, w_total, pc, gH, i, j, lane);
+        if (lane == 0) mi[p] = m;
+    }
+}
+
+__global__ void __launch_bounds__(EX_WARPS * 32, 4)
+mi_refine_grouped_kernel(const uint8_t* __restrict__ masks, const Candidate* __restrict__ cand, unsigned long long ncand,
+                         double pc, double w_total, double wo_threshold,
+                         spk_edge* __restrict__ refined, double* __restrict__ refined_wo, unsigned long long* __restrict__ counters,
+                         const uint32_t* __restrict__ gbits, const double* __restrict__ gval, const double* __restrict__ gmarg,
+                         const double* __restrict__ gH, uint32_t NW) {
+    const uint32_t lane = threadIdx.x % 32, wid = threadIdx.x / 32;
+    double maxerr = 0.0;
+    for (unsigned long long p = (unsigned long long)blockIdx.x * EX_WARPS + wid; p < ncand;
+         p += (unsigned long long)gridDim.x * EX_WARPS) {
+        const Candidate cd = cand[p];
+        const uint32_t mi_ = masks[cd.i], mj_ = masks[cd.j];
+        double v = warp_crosstab_grouped(gbits, gval, gmarg, NW, cd.i, cd.j, mi_, mj_, lane);
+        const double m = grouped_mi_pass1(v, mi_, mj_, w_total, pc, gH, cd.i, cd.j, lane);
+        double m2 = __longlong_as_double(0x7ff8000000000000ll);   // NaN = "no gap column involved" / not needed
+        // the gap-free value is only reported for SAVED edges (mi.hpp:465): skip the second pass otherwise
+        if (((mi_ | mj_) & (1u << GAP)) && m > wo_threshold) m2 = warp_mi_pass(v, mi_ & ~(1u << GAP), mj_ & ~(1u << GAP), pc, lane);
+        if (lane == 0) {
+            spk_edge e; e.i = cd.i; e.j = cd.j; e.mi = m;
+            refined[p] = e; refined_wo[p] = m2;
+            if (cd.mi32 == cd.mi32) maxerr = fmax(maxerr, fabs((double)cd.mi32 - m));
+        }
+    }
+    if (lane == 0 && maxerr > 0.0) atomicMax(&counters[3], f64_ordered(maxerr));
+}
+
+// =============================================================================================
+// Thread-per-pair evaluation on the grouped bit planes. A warp-per-pair layout leaves most lanes idle in the
+// entropy step (a biallelic pair has 9 cells) and spends its time in shuffle reductions; here every thread owns
+// one pair: popcount-accumulates its KI x KJ kept cells over the plane words (16-byte loads), completes the
+// table from the fp64 margins and evaluates the reference's formula sequentially. Candidates arrive grouped by
+// K2 tile, so the threads of a warp mostly share the class pair (little divergence) and one of the two columns
+// (broadcast loads).
+// =============================================================================================
+template <int KI, int KJ>
+__device__ __forceinline__ void pair_eval(const uint32_t* __restrict__ gbits, const double* __restrict__ gval,
+                                       const double* __restrict__ gmarg, const double* __restrict__ gH, uint32_t NW,
+                                       uint32_t i, uint32_t j, uint32_t mask_i, uint32_t mask_j, double w_total, double pc,
+                                       double wo_threshold, double* out_m, double* out_m2) {
+    const uint32_t di = 31u - __clz(mask_i | 1u), dj = 31u - __clz(mask_j | 1u);      // recovered states (gap if present)
+    const uint32_t zi = __ffs(~mask_i & 31u) - 1, zj = __ffs(~mask_j & 31u) - 1;      // an absent state: all-zero plane
+    uint32_t si[KI], sj[KJ];
+    uint32_t mk = mask_i & ~(1u << di), ki = 0, kj = 0;
+#pragma unroll
+    for (int a = 0; a < KI; ++a) { if (mk) { si[a] = __ffs(mk) - 1; mk &= mk - 1; ++ki; } else si[a] = zi; }
+    mk = mask_j & ~(1u << dj);
+#pragma unroll
+    for (int b = 0; b < KJ; ++b) { if (mk) { sj[b] = __ffs(mk) - 1; mk &= mk - 1; ++kj; } else sj[b] = zj; }
+    const uint4* Bi[KI]; const uint4* Bj[KJ];
+#pragma unroll
+    for (int a = 0; a < KI; ++a) Bi[a] = reinterpret_cast<const uint4*>(gbits + ((size_t)i * NSTATES + si[a]) * NW);
+#pragma unroll
+    for (int b = 0; b < KJ; ++b) Bj[b] = reinterpret_cast<const uint4*>(gbits + ((size_t)j * NSTATES + sj[b]) * NW);
+    double acc[KI][KJ];
+#pragma unroll
+    for (int a = 0; a < KI; ++a)
+#pragma unroll
+        for (int b = 0; b < KJ; ++b) acc[a][b] = 0.0;
+    const double2* gv2 = reinterpret_cast<const double2*>(gval);
+    for (uint32_t w4 = 0; w4 < NW / 4; ++w4) {
+        const double2 v01 = gv2[2 * w4], v23 = gv2[2 * w4 + 1];
+        uint4 xi[KI], xj[KJ];
+#pragma unroll
+        for (int a = 0; a < KI; ++a) xi[a] = __ldg(Bi[a] + w4);
+#pragma unroll
+        for (int b = 0; b < KJ; ++b) xj[b] = __ldg(Bj[b] + w4);
+#pragma unroll
+        for (int a = 0; a < KI; ++a)
+#pragma unroll
+            for (int b = 0; b < KJ; ++b) {
+                double t = acc[a][b];
+                t = fma((double)__popc(xi[a].x & xj[b].x), v01.x, t);
+                t = fma((double)__popc(xi[a].y & xj[b].y), v01.y, t);
+                t = fma((double)__popc(xi[a].z & xj[b].z), v23.x, t);
+                t = fma((double)__popc(xi[a].w & xj[b].w), v23.y, t);
+                acc[a][b] = t;
+            }
+    }
+    // full table over (kept rows + recovered row) x (kept cols + recovered col); index KI / KJ = recovered state
+    double N[KI + 1][KJ + 1];
+    double colsum[KJ];
+#pragma unroll
+    for (int b = 0; b < KJ; ++b) colsum[b] = 0.0;
+    double dsum = 0.0;
+#pragma unroll
+    for (int a = 0; a < KI; ++a) {
+        double rs = 0.0;
+#pragma unroll
+        for (int b = 0; b < KJ; ++b) { N[a][b] = acc[a][b]; rs += acc[a][b]; colsum[b] += acc[a][b]; }
+        const double ma = ((uint32_t)a < ki) ? gmarg[(size_t)i * NSTATES + si[a]] : 0.0;
+        N[a][KJ] = fmax(ma - rs, 0.0);
+    }
+#pragma unroll
+    for (int b = 0; b < KJ; ++b) {
+        const double mb = ((uint32_t)b < kj) ? gmarg[(size_t)j * NSTATES + sj[b]] : 0.0;
+        N[KI][b] = fmax(mb - colsum[b], 0.0);
+        dsum += N[KI][b];
+    }
+    N[KI][KJ] = fmax(gmarg[(size_t)i * NSTATES + di] - dsum, 0.0);
+    // ---- pass 1 (mi.hpp:146-181): p = (N + pc)/Z over present x present cells
+    const int np_i = (int)ki + 1, np_j = (int)kj + 1;
+    const double Z = w_total + pc * (double)(np_i * np_j);
+    double jointH = 0.0;
+#pragma unroll
+    for (int a = 0; a <= KI; ++a)
+#pragma unroll
+        for (int b = 0; b <= KJ; ++b) {
+            const bool valid = (a == KI || (uint32_t)a < ki) && (b == KJ || (uint32_t)b < kj);
+            const double pr = (N[a][b] + pc) / Z;
+            N[a][b] = valid ? pr : 0.0;
+            jointH += valid ? pr * log(pr) : 0.0;
+        }
+    const double m = jointH - gH[(size_t)i * NSTATES + (np_j - 1)] - gH[(size_t)j * NSTATES + (np_i - 1)];
+    *out_m = m;
+    double m2 = __longlong_as_double(0x7ff8000000000000ll);          // NaN = no gap column involved / not needed
+    const bool gi = (mask_i >> GAP) & 1u, gj = (mask_j >> GAP) & 1u;
+    if ((gi || gj) && m > wo_threshold) {
+        // ---- pass 2, literal (mi.hpp:108-135,465-489): the already normalised table, gap states removed from
+        // the masks, pseudocount added and normalised again; row sums still run over all five i-states.
+        double Z2 = 0.0;
+#pragma unroll
+        for (int a = 0; a <= KI; ++a)
+#pragma unroll
+            for (int b = 0; b <= KJ; ++b) {
+                const bool in2 = ((a == KI) ? !gi : ((uint32_t)a < ki)) && ((b == KJ) ? !gj : ((uint32_t)b < kj));
+                if (in2) { N[a][b] += pc; Z2 += N[a][b]; }
+            }
+        double jH = 0.0, cH = 0.0;
+        double rs2[KJ + 1];
+#pragma unroll
+        for (int b = 0; b <= KJ; ++b) rs2[b] = 0.0;
+#pragma unroll
+        for (int a = 0; a <= KI; ++a) {
+            const bool ain = (a == KI) ? !gi : ((uint32_t)a < ki);
+            double cs = 0.0;
+#pragma unroll
+            for (int b = 0; b <= KJ; ++b) {
+                const bool bin = (b == KJ) ? !gj : ((uint32_t)b < kj);
+                if (bin) {
+                    const double q = N[a][b] / Z2;               // every i-state of a present j row is divided (mi.hpp:165)
+                    rs2[b] += q;                                  // row sum over ALL i-states, the gap_i cell included
+                    if (ain) { jH += q * log(q); cs += q; }
+                }
+            }
+            if (ain) cH += cs * log(cs);
+        }
+        double rH = 0.0;
+#pragma unroll
+        for (int b = 0; b <= KJ; ++b) {
+            const bool bin = (b == KJ) ? !gj : ((uint32_t)b < kj);
+            if (bin) rH += rs2[b] * log(rs2[b]);
+        }
+        m2 = jH - rH - cH;
+    }
+    *out_m2 = m2;
+}
+
+template <int KI, int KJ>
+__device__ __noinline__ void pair_eval_nl(const uint32_t* __restrict__ gbits, const double* __restrict__ gval,
+                                          const double* __restrict__ gmarg, const double* __restrict__ gH, uint32_t NW,
+                                          uint32_t i, uint32_t j, uint32_t mask_i, uint32_t mask_j, double w_total, double pc,
+                                          double wo_threshold, double* out_m, double* out_m2) {
+    pair_eval<KI, KJ>(gbits, gval, gmarg, gH, NW, i, j, mask_i, mask_j, w_total, pc, wo_threshold, out_m, out_m2);
+}
+
+__device__ __forceinline__ void pair_eval_dispatch(const uint32_t* __restrict__ gbits, const double* __restrict__ gval,
+                                                   const double* __restrict__ gmarg, const double* __restrict__ gH, uint32_t NW,
+                                                   uint32_t i, uint32_t j, uint32_t mask_i, uint32_t mask_j, double w_total, double pc,
+                                                   double wo_threshold, double* m, double* m2) {
+    const int ki = __popc(mask_i) - 1, kj = __popc(mask_j) - 1;
+    const int ci = ki <= 1 ? 1 : (ki == 2 ? 2 : 4), cj = kj <= 1 ? 1 : (kj == 2 ? 2 : 4);
+    switch (ci * 8 + cj) {
+#define SPK_PCASE(A, B) case (A) * 8 + (B): pair_eval_nl<A, B>(gbits, gval, gmarg, gH, NW, i, j, mask_i, mask_j, w_total, pc, wo_threshold, m, m2); break;
+        SPK_PCASE(1, 1) SPK_PCASE(1, 2) SPK_PCASE(1, 4)
+        SPK_PCASE(2, 1) SPK_PCASE(2, 2) SPK_PCASE(2, 4)
+        SPK_PCASE(4, 1) SPK_PCASE(4, 2) SPK_PCASE(4, 4)
+#undef SPK_PCASE
+        default: break;
+    }
+}
+
+__global__ void __launch_bounds__(128)
+mi_pairs_thread_kernel(const uint8_t* __restrict__ masks, const uint32_t* __restrict__ pi, const uint32_t* __restrict__ pj,
+                       unsigned long long npairs, double pc, double w_total, double* __restrict__ mi,
+                       const uint32_t* __restrict__ gbits, const double* __restrict__ gval, const double* __restrict__ gmarg,
+                       const double* __restrict__ gH, uint32_t NW) {
+    const unsigned long long p = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= npairs) return;
+    const uint32_t i = pi[p], j = pj[p];
+    double m = 0.0, m2 = 0.0;
+    pair_eval_dispatch(gbits, gval, gmarg, gH, NW, i, j, masks[i], masks[j], w_total, pc, INFINITY, &m, &m2);
+    mi[p] = m;
+}
+
+__global__ void __launch_bounds__(128)
+mi_refine_thread_kernel(const uint8_t* __restrict__ masks, const Candidate* __restrict__ cand, unsigned long long ncand,
+                        double pc, double w_total, double wo_threshold,
+                        spk_edge* __restrict__ refined, double* __restrict__ refined_wo, unsigned long long* __restrict__ counters,
+                        const uint32_t* __restrict__ gbits, const double* __restrict__ gval, const double* __restrict__ gmarg,
+                        const double* __restrict__ gH, uint32_t NW) {
+    const unsigned long long p = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    double err = 0.0;
+    if (p < ncand) {
+        const Candidate cd = cand[p];
+        double m = 0.0, m2 = 0.0;
+        pair_eval_dispatch(gbits, gval, gmarg, gH, NW, cd.i, cd.j, masks[cd.i], masks[cd.j], w_total, pc, wo_threshold, &m, &m2);
+        spk_edge e; e.i = cd.i; e.j = cd.j; e.mi = m;
+        refined[p] = e; refined_wo[p] = m2;
+        if (cd.mi32 == cd.mi32) err = fabs((double)cd.mi32 - m);
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) err = fmax(err, __shfl_xor_sync(0xffffffffu, err, o));
+    if ((threadIdx.x & 31) == 0 && err > 0.0) atomicMax(&counters[3], f64_ordered(err));
+}
+
+// ---- class-sorted refine: candidates are bucketed by the (rows_i, rows_j) class pair so that every launch runs
+// ONE instantiation with converged warps (the 9-way divergent dispatch thrashes the instruction cache).
+__device__ __forceinline__ uint32_t pair_class(uint32_t mask_i, uint32_t mask_j) {
+    const int ki = __popc(mask_i) - 1, kj = __popc(mask_j) - 1;
+    return (uint32_t)((ki <= 1 ? 0 : (ki == 2 ? 1 : 2)) * 3 + (kj <= 1 ? 0 : (kj == 2 ? 1 : 2)));
+}
+__global__ void __launch_bounds__(256)
+classify_count_kernel(const Candidate* __restrict__ cand, unsigned long long ncand, const uint8_t* __restrict__ masks,
+                      unsigned long long* __restrict__ counts /*[9]*/) {
+    __shared__ unsigned int h[9];
+    if (threadIdx.x < 9) h[threadIdx.x] = 0;
+    __syncthreads();
+    for (unsigned long long p = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; p < ncand; p += (unsigned long long)gridDim.x * blockDim.x) {
+        const Candidate cd = cand[p];
+        atomicAdd(&h[pair_class(masks[cd.i], masks[cd.j])], 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x < 9 && h[threadIdx.x]) atomicAdd(&counts[threadIdx.x], (unsigned long long)h[threadIdx.x]);
+}
+__global__ void __launch_bounds__(256)
+classify_scatter_kernel(const Candidate* __restrict__ cand, unsigned long long ncand, const uint8_t* __restrict__ masks,
+                        unsigned long long* __restrict__ cursors /*[9], preset to the class offsets*/, Candidate* __restrict__ out) {
+    __shared__ unsigned int h[9];
+    __shared__ unsigned long long base[9];
+    const unsigned long long chunk = (unsigned long long)blockDim.x * 8;
+    for (unsigned long long c0 = (unsigned long long)blockIdx.x * chunk; c0 < ncand; c0 += (unsigned long long)gridDim.x * chunk) {
+        if (threadIdx.x < 9) h[threadIdx.x] = 0;
+        __syncthreads();
+        Candidate cd[8]; uint32_t cls[8], loc[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const unsigned long long p = c0 + (unsigned long long)k * blockDim.x + threadIdx.x;
+            cls[k] = 9;
+            if (p < ncand) { cd[k] = cand[p]; cls[k] = pair_class(masks[cd[k].i], masks[cd[k].j]); loc[k] = atomicAdd(&h[cls[k]], 1u); }
+        }
+        __syncthreads();
+        if (threadIdx.x < 9) base[threadIdx.x] = h[threadIdx.x] ? atomicAdd(&cursors[threadIdx.x], (unsigned long long)h[threadIdx.x]) : 0ull;
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < 8; ++k) if (cls[k] < 9) out[base[cls[k]] + loc[k]] = cd[k];
+        __syncthreads();
+    }
+}
+
+template <int KI, int KJ>
+__global__ void __launch_bounds__(128)
+mi_refine_class_kernel(const uint8_t* __restrict__ masks, const Candidate* __restrict__ cand, unsigned long long ncand,
+                       double pc, double w_total, double wo_threshold,
+                       spk_edge* __restrict__ refined, double* __restrict__ refined_wo, unsigned long long* __restrict__ counters,
+                       const uint32_t* __restrict__ gbits, const double* __restrict__ gval, const double* __restrict__ gmarg,
+                       const double* __restrict__ gH, uint32_t NW) {
+    const unsigned long long p = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    double err = 0.0;
+    if (p < ncand) {
+        const Candidate cd = cand[p];
+        double m = 0.0, m2 = 0.0;
+        pair_eval<KI, KJ>(gbits, gval, gmarg, gH, NW, cd.i, cd.j, masks[cd.i], masks[cd.j], w_total, pc, wo_threshold, &m, &m2);
+        spk_edge e; e.i = cd.i; e.j = cd.j; e.mi = m;
+        refined[p] = e; refined_wo[p] = m2;
+        if (cd.mi32 == cd.mi32) err = fabs((double)cd.mi32 - m);
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) err = fmax(err, __shfl_xor_sync(0xffffffffu, err, o));
+    if ((threadIdx.x & 31) == 0 && err > 0.0) atomicMax(&counters[3], f64_ordered(err));
 }
 
 // ---- K2b: explicit pair list ---------------------------------------------------------------
@@ -321,11 +653,24 @@ void mi_exact_free(Ctx* c) {
     if (c->d_gval) { cudaFree(c->d_gval); c->d_gval = nullptr; }
     if (c->d_gmarg) { cudaFree(c->d_gmarg); c->d_gmarg = nullptr; }
     if (c->d_gslot) { cudaFree(c->d_gslot); c->d_gslot = nullptr; }
-    c->g_cap_words = 0; c->g_NW = 0; c->g_state = 0;
+    if (c->d_gH) { cudaFree(c->d_gH); c->d_gH = nullptr; }
+    c->g_cap_words = 0; c->g_NW = 0; c->g_state = 0; c->g_pc = -1.0;
 }
 
-static int ensure_grouped(Ctx* c) {
-    if (c->g_state != 0) return SPK_OK;
+static int ensure_gh(Ctx* c, double pc) {
+    if (c->g_state != 1 || c->g_pc == pc) return SPK_OK;
+    if (!c->d_gH && cudaMalloc(&c->d_gH, (size_t)c->L_pad * NSTATES * 8) != cudaSuccess) {
+        cudaGetLastError(); return fail(c, SPK_E_NOMEM, "grouped bit planes: allocation failed");
+    }
+    gh_tables_kernel<<<(c->L_pad + 127) / 128, 128, 0, c->stream>>>(c->d_gmarg, c->d_masks, c->d_gH, c->L_pad, c->w_total, pc);
+    c->tm.kernel_launches += 1;
+    SPK_CUDA(c, cudaGetLastError());
+    c->g_pc = pc;
+    return SPK_OK;
+}
+
+static int ensure_grouped(Ctx* c, double pc) {
+    if (c->g_state != 0) return ensure_gh(c, pc);
     const uint32_t n = c->n;
     if (c->h_w.size() != n) { c->g_state = 2; return SPK_OK; }
     // order samples by weight value (bit pattern), stable
@@ -366,8 +711,8 @@ static int ensure_grouped(Ctx* c) {
     c->tm.kernel_launches += 1;
     SPK_CUDA(c, cudaGetLastError());
     SPK_CUDA(c, cudaStreamSynchronize(c->stream));                   // slot / val are host temporaries
-    c->g_NW = NW; c->g_state = 1;
-    return SPK_OK;
+    c->g_NW = NW; c->g_state = 1; c->g_pc = -1.0;
+    return ensure_gh(c, pc);
 }
 
 static int refine_grid(Ctx* c, unsigned long long n) {
@@ -379,11 +724,13 @@ static int refine_grid(Ctx* c, unsigned long long n) {
 int mi_pairs_exact(Ctx* c, const uint32_t* d_pi, const uint32_t* d_pj, uint64_t npairs, double pc, double* d_mi) {
     if (npairs == 0) return SPK_OK;
     SPK_CUDA(c, cudaEventRecord(c->ev[0], c->stream));
-    { int rg = ensure_grouped(c); if (rg) return rg; }
-    const bool grouped = (c->g_state == 1);
-    mi_pairs_kernel<<<refine_grid(c, npairs), EX_WARPS * 32, 0, c->stream>>>(c->d_colmajor, c->d_w, c->d_masks, d_pi, d_pj,
-                                                                            npairs, c->n_pad, pc, d_mi,
-                                                                            grouped ? c->d_gbits : nullptr, c->d_gval, c->d_gmarg, c->g_NW);
+    { int rg = ensure_grouped(c, pc); if (rg) return rg; }
+    if (c->g_state == 1)
+        mi_pairs_thread_kernel<<<(unsigned)((npairs + 127) / 128), 128, 0, c->stream>>>(c->d_masks, d_pi, d_pj, npairs, pc, c->w_total, d_mi,
+                                                                                       c->d_gbits, c->d_gval, c->d_gmarg, c->d_gH, c->g_NW);
+    else
+        mi_pairs_kernel<<<refine_grid(c, npairs), EX_WARPS * 32, 0, c->stream>>>(c->d_colmajor, c->d_w, c->d_masks, d_pi, d_pj,
+                                                                                npairs, c->n_pad, pc, d_mi, nullptr, nullptr, nullptr, 0);
     c->tm.kernel_launches += 1;
     SPK_CUDA(c, cudaEventRecord(c->ev[1], c->stream));
     SPK_CUDA(c, cudaEventSynchronize(c->ev[1]));
@@ -392,14 +739,47 @@ int mi_pairs_exact(Ctx* c, const uint32_t* d_pi, const uint32_t* d_pj, uint64_t 
     return SPK_OK;
 }
 
-int mi_refine_candidates(Ctx* c, uint64_t ncand, double pc) {
+int mi_refine_candidates(Ctx* c, uint64_t ncand, double pc, double wo_threshold) {
     if (ncand == 0) return SPK_OK;
-    { int rg = ensure_grouped(c); if (rg) return rg; }
-    const bool grouped = (c->g_state == 1);
-    mi_refine_kernel<<<refine_grid(c, ncand), EX_WARPS * 32, 0, c->stream>>>(c->d_colmajor, c->d_w, c->d_masks, c->d_cand, ncand,
-                                                                            c->n_pad, pc, c->d_refined, c->d_refined_wo,
-                                                                            c->d_counters,
-                                                                            grouped ? c->d_gbits : nullptr, c->d_gval, c->d_gmarg, c->g_NW);
+    { int rg = ensure_grouped(c, pc); if (rg) return rg; }
+    if (c->g_state == 1) {
+        // bucket by class pair (counting sort), then one converged launch per class
+        unsigned long long* d_cnt = (unsigned long long*)scratch(c, 32 * sizeof(unsigned long long));
+        if (!d_cnt) return fail(c, SPK_E_NOMEM, "scratch allocation failed");
+        if (c->cand2_cap < c->cand_cap) {
+            if (c->d_cand2) { cudaFree(c->d_cand2); c->d_cand2 = nullptr; c->cand2_cap = 0; }
+            if (cudaMalloc(&c->d_cand2, c->cand_cap * sizeof(Candidate)) != cudaSuccess) { cudaGetLastError(); return fail(c, SPK_E_NOMEM, "candidate sort buffer"); }
+            c->cand2_cap = c->cand_cap;
+        }
+        SPK_CUDA(c, cudaMemsetAsync(d_cnt, 0, 32 * sizeof(unsigned long long), c->stream));
+        const unsigned cgrid = (unsigned)std::min<unsigned long long>((ncand + 2047) / 2048, (unsigned long long)c->sm_count * 8);
+        classify_count_kernel<<<cgrid, 256, 0, c->stream>>>(c->d_cand, ncand, c->d_masks, d_cnt);
+        unsigned long long h_cnt[9], h_off[10];
+        SPK_CUDA(c, cudaMemcpyAsync(h_cnt, d_cnt, sizeof h_cnt, cudaMemcpyDeviceToHost, c->stream));
+        SPK_CUDA(c, cudaStreamSynchronize(c->stream));
+        h_off[0] = 0; for (int q = 0; q < 9; ++q) h_off[q + 1] = h_off[q] + h_cnt[q];
+        SPK_CUDA(c, cudaMemcpyAsync(d_cnt + 16, h_off, 9 * sizeof(unsigned long long), cudaMemcpyHostToDevice, c->stream));
+        classify_scatter_kernel<<<cgrid, 256, 0, c->stream>>>(c->d_cand, ncand, c->d_masks, d_cnt + 16, c->d_cand2);
+        c->tm.kernel_launches += 2;
+        for (int q = 0; q < 9; ++q) {
+            const unsigned long long n_q = h_cnt[q], o_q = h_off[q];
+            if (!n_q) continue;
+            const unsigned g = (unsigned)((n_q + 127) / 128);
+#define SPK_RCASE(Q, A, B) case Q: mi_refine_class_kernel<A, B><<<g, 128, 0, c->stream>>>(c->d_masks, c->d_cand2 + o_q, n_q, pc, c->w_total, wo_threshold, \
+                c->d_refined + o_q, c->d_refined_wo + o_q, c->d_counters, c->d_gbits, c->d_gval, c->d_gmarg, c->d_gH, c->g_NW); break;
+            switch (q) {
+                SPK_RCASE(0, 1, 1) SPK_RCASE(1, 1, 2) SPK_RCASE(2, 1, 4)
+                SPK_RCASE(3, 2, 1) SPK_RCASE(4, 2, 2) SPK_RCASE(5, 2, 4)
+                SPK_RCASE(6, 4, 1) SPK_RCASE(7, 4, 2) SPK_RCASE(8, 4, 4)
+            }
+#undef SPK_RCASE
+            c->tm.kernel_launches += 1;
+        }
+    }
+    else
+        mi_refine_kernel<<<refine_grid(c, ncand), EX_WARPS * 32, 0, c->stream>>>(c->d_colmajor, c->d_w, c->d_masks, c->d_cand, ncand,
+                                                                                c->n_pad, pc, c->d_refined, c->d_refined_wo,
+                                                                                c->d_counters, nullptr, nullptr, nullptr, 0);
     c->tm.kernel_launches += 1;
     SPK_CUDA(c, cudaGetLastError());
     return SPK_OK;
@@ -434,7 +814,7 @@ int mi_scan_exact(Ctx* c, const spk_scan_params& p, uint64_t circle) {
             enumerate_pairs_kernel<<<b - a, 256, 0, c->stream>>>(c->d_cand, a, b, L, cnt);
             c->tm.kernel_launches += 1;
             SPK_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
-            int r = mi_refine_candidates(c, cnt, p.pseudocount); if (r) return r;
+            int r = mi_refine_candidates(c, cnt, p.pseudocount, p.threshold); if (r) return r;
             SPK_CUDA(c, cudaEventRecord(c->ev[3], c->stream));
             r = mi_compact(c, cnt, p, circle); if (r) return r;
             SPK_CUDA(c, cudaEventRecord(c->ev[4], c->stream));
