@@ -175,6 +175,8 @@ def run_b200(args):
     torch.cuda.set_device(local_rank)
     device = torch.device("cuda", local_rank)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"            # keep stdout to the single JSON line
         dist.init_process_group("nccl", device_id=device)
 
     # ---- workload: rank 0 generates, alignment broadcast ONCE over NCCL (outside the timed region)
@@ -238,31 +240,48 @@ def run_b200(args):
     states_pin = pinned_copy(states)                  # the caller's alignment lives in page-locked host memory
     pos_pin = pinned_copy(pos)
 
+    host_edges = host_flags = None
+
     def step_e2e():
         """host buffers through the C-ABI: H2D of the alignment (pinned), D2H of edges + flags inside the step."""
         tw = [time.perf_counter()]
         ctx.set_alignment(states_pin, pos_pin); tw.append(time.perf_counter())
         c = ctx.neighbour_counts(min_ident, True)
         ctx.set_weights(1.0 / c.astype(np.float64)); tw.append(time.perf_counter())
-        r = ctx.mi_scan(threshold, max_edges=max_edges, sort_desc=(world == 1), n_terms=args.n_terms, engine=args.engine,
-                        part_index=rank, n_parts=world, keep_on_device=False, copy=False); tw.append(time.perf_counter())
-        edges = r["edges"]                            # view of the library's pinned result buffer
-        h2d_edges = 0
-        if world > 1:
-            gathered = [None] * world
-            dist.all_gather_object(gathered, edges.tobytes())
-            from spydrpick_b200 import EDGE_DTYPE
-            edges = ctx.sort_edges(np.concatenate([np.frombuffer(b, dtype=EDGE_DTYPE) for b in gathered]))
-            h2d_edges = 2 * edges.nbytes
-        flags = ctx.aracne(edges, EPS, part_index=rank, n_parts=world)
-        ndirect = int(flags.sum())                    # the step's result is read on the host
+        if world == 1:
+            r = ctx.mi_scan(threshold, max_edges=max_edges, sort_desc=True, n_terms=args.n_terms, engine=args.engine,
+                            keep_on_device=False, copy=False); tw.append(time.perf_counter())
+            edges = r["edges"]                        # view of the library's pinned result buffer
+            flags = ctx.aracne(edges, EPS)            # same pointer -> device copy reused, only the flags travel
+            ndirect = int(flags.sum())                # the step's result is read on the host
+            h2d = states.nbytes + pos.nbytes + 8 * n + len(flags)
+            d2h = edges.nbytes + r["edges_wo_gaps"].nbytes + 8 * L + 8 * n + len(flags)
+        else:
+            # N > 1: the partial edge lists never visit the host -- NCCL allgather over NVLink, device sort + K3, then ONE
+            # D2H of the merged list and the flags into pinned host buffers (what a caller of the multi-GPU path receives)
+            r = ctx.mi_scan(threshold, max_edges=max_edges, sort_desc=False, n_terms=args.n_terms, engine=args.engine,
+                            part_index=rank, n_parts=world, keep_on_device=True); tw.append(time.perf_counter())
+            keep, d_edges, ne = merge_across_ranks(r)
+            ctx.sort_edges_device(d_edges, ne)
+            dflags = torch.zeros(max(ne, 1), dtype=torch.uint8, device=device)
+            ctx.aracne_device(d_edges, ne, dflags.data_ptr(), EPS, part_index=rank, n_parts=world)
+            from spydrpick_b200 import dist as sdist
+            dflags = sdist.allgather_flag_shards(dflags, ne)
+            nonlocal host_edges, host_flags
+            if host_edges is None or host_edges.numel() < ne * 16:
+                host_edges = torch.empty(int(ne * 16 * 1.25) + 4096, dtype=torch.uint8).pin_memory()
+                host_flags = torch.empty(int(ne * 1.25) + 4096, dtype=torch.uint8).pin_memory()
+            host_edges[:ne * 16].copy_(dev_bytes(torch, d_edges, ne * 16, device), non_blocking=True)
+            host_flags[:ne].copy_(dflags[:ne], non_blocking=True)
+            torch.cuda.synchronize()
+            ndirect = int(host_flags[:ne].numpy().sum())
+            h2d = states.nbytes + pos.nbytes + 8 * n
+            d2h = ne * 16 + ne + 8 * L + 8 * n
         tw.append(time.perf_counter())
         if os.environ.get("SPK_BENCH_E2E_BREAKDOWN"):
             tmx = ctx.timings()
             sys.stderr.write("e2e wall ms: set_alignment %.1f (upload %.1f prep %.1f) | counts+weights %.1f | scan %.1f | aracne %.1f\n" % (
                 1e3 * (tw[1] - tw[0]), tmx["upload_ms"], tmx["prep_ms"], 1e3 * (tw[2] - tw[1]), 1e3 * (tw[3] - tw[2]), 1e3 * (tw[4] - tw[3])))
-        h2d = states.nbytes + pos.nbytes + 8 * n + len(flags) + h2d_edges
-        d2h = edges.nbytes + r["edges_wo_gaps"].nbytes + 8 * L + 8 * n + len(flags)
         return h2d, d2h
 
     def timed(fn, steps, warmup, with_clocks=False):
@@ -318,7 +337,7 @@ def run_b200(args):
 
     e2e = None
     if not args.no_e2e:
-        ems, (h2d, d2h), _, _ = timed(step_e2e, max(1, min(args.steps, 2)), 1)
+        ems, (h2d, d2h), _, _ = timed(step_e2e, max(1, min(args.steps, 3)), 2)
         e2e = {"value": pairs_total / (ems / 1e3) / 1e9, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                "ms_per_step": ems}
 
