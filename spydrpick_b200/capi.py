@@ -8,7 +8,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libspydrpick_b200.so")
+LIB_PATH = os.environ.get("SPYDRPICK_B200_LIB") or os.path.join(_HERE, "libspydrpick_b200.so")
 
 EDGE_DTYPE = np.dtype([("i", np.uint32), ("j", np.uint32), ("mi", np.float64)], align=True)
 assert EDGE_DTYPE.itemsize == 16

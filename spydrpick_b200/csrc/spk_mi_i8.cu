@@ -27,10 +27,10 @@
 //                   B (N=256) rows = (j column, weight byte t, state b) u8 one-hot * {hi, lo}
 //                   D[row][col] s32 in TMEM; N_ab = 256*D[.., t=0, b] + D[.., t=1, b].
 //
-// Kernel anatomy (persistent, 1 CTA/SM, 320 threads):
+// Kernel anatomy (persistent, 1 CTA/SM, 576 threads):
 //   warp 0     TMA producer   cp.async.bulk.tensor 2D (128B swizzle), 4-stage ring of 48 KB (128 samples)
 //   warp 1     MMA issuer     tcgen05.mma.cta_group::1.kind::i8 M128 N256 K32, commit -> mbarriers; owns TMEM
-//   warps 2-9  epilogue       two warps per TMEM lane quadrant (each 128 of the 256 columns):
+//   warps 2-17 epilogue       four warps per TMEM lane quadrant (each 64 of the 256 columns):
 //                             tcgen05.ld 32x32b, hi/lo combine, KI-lane transpose, MI, candidates
 // TMEM: 2 accumulator buffers x 256 columns, epilogue of tile t overlaps the mainloop of tile t+1.
 #include <cuda.h>
@@ -42,8 +42,16 @@
 
 namespace spk {
 
-constexpr int I8_THREADS = 320;
-constexpr int I8_EPI_THREADS = 256;
+#ifndef SPK_I8_EPI_WARPS
+#define SPK_I8_EPI_WARPS 16           // epilogue warps: 8 (two per TMEM lane quadrant) or 16 (four per quadrant)
+#endif
+#ifndef SPK_I8_TWO_PHASE
+#define SPK_I8_TWO_PHASE 0           // 1: MI of all pairs of a load first (branch-free), emission tests afterwards
+#endif
+constexpr int I8_EPI_WARPS = SPK_I8_EPI_WARPS;
+constexpr int I8_EPI_THREADS = I8_EPI_WARPS * 32;
+constexpr int I8_THREADS = 64 + I8_EPI_THREADS;
+constexpr uint32_t I8_COLS_PER_WARP = 1024u / I8_EPI_WARPS;   // accumulator columns each epilogue warp drains (128 or 64)
 constexpr uint32_t I8_BK = 128;                         // samples (= bytes) per stage row
 constexpr uint32_t I8_A_BYTES = 128 * I8_BK;            // 16 KB
 constexpr uint32_t I8_B_BYTES = 256 * I8_BK;            // 32 KB
@@ -143,7 +151,11 @@ __device__ __noinline__ I8OpenRes i8_open_columns_path(const I8Params& p, I8EpiS
 template <int KI, int KJ>
 __device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmem& sm, uint32_t tmem_acc, uint32_t q, uint32_t half,
                                                  uint32_t lane, bool diag, uint32_t ci0, uint32_t cj0) {
-    constexpr int LOADW = (KI == 4) ? 32 : 16;         // TMEM columns per load
+#if SPK_I8_TWO_PHASE
+    constexpr int LOADW = (KI == 1 && KJ == 1) ? 16 : 32;   // TMEM columns per load (>= 2 independent pairs per lane where possible)
+#else
+    constexpr int LOADW = (KI == 4) ? 32 : 16;
+#endif
     constexpr int NJ = LOADW / (2 * KJ);               // j columns per load
     constexpr int PPL = NJ / KI;                       // pairs per lane per load
     constexpr int WJ = 128 / KJ;
@@ -165,8 +177,8 @@ __device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmem& s
     const float ln2 = 0.69314718055994530942f;
 
 #pragma unroll 1
-    for (uint32_t ld = 0; ld < 128u / LOADW; ++ld) {
-        const uint32_t col0 = half * 128u + ld * LOADW;
+    for (uint32_t ld = 0; ld < I8_COLS_PER_WARP / LOADW; ++ld) {
+        const uint32_t col0 = half * I8_COLS_PER_WARP + ld * LOADW;
         uint32_t r[LOADW];
         i8_tmem_ld<LOADW>(tmem_acc + ((q * 32u) << 16) + col0, r);
         uint32_t v[NJ * KJ];
@@ -210,8 +222,12 @@ __device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmem& s
             }
         }
 #pragma unroll
+        // phase 1: branch-free MI of the PPL pairs of this load (independent chains -> MUFU / LDS latencies overlap)
+        float mi_arr[PPL];
+#pragma unroll
         for (int s = 0; s < PPL; ++s) {
             const uint32_t j_local = col0 / (2 * KJ) + s * KI + g;
+            mi_arr[s] = __int_as_float(0x7fc00000);
             if (p.debug_out) {
 #pragma unroll
                 for (int a = 0; a < KI; ++a)
@@ -260,11 +276,21 @@ __device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmem& s
                 S += cv ? t : 0.f;
             }
             S += xlg(mi_d - jr.smq + tot);                               // cell (dropped_i, dropped_j)
+            const bool valid = vi && (jr.orig != I8_INVALID) && (!diag || pi < cj0 + j_local);
+            mi_arr[s] = valid ? fmaf(S, ln2, -hsum) : __int_as_float(0x7fc00000);
+#if SPK_I8_TWO_PHASE
+        }
+        if (p.debug_out) continue;
+        // phase 2: threshold / open-column tests and candidate emission
+#pragma unroll
+        for (int s = 0; s < PPL; ++s) {
+            const uint32_t j_local = col0 / (2 * KJ) + s * KI + g;
+#endif
             const uint32_t pj = cj0 + j_local;
-            const bool valid = vi && (jr.orig != I8_INVALID) && (!diag || pi < pj);
-            const float mi32 = valid ? fmaf(S, ln2, -hsum) : __int_as_float(0x7fc00000);
+            const float mi32 = mi_arr[s];
+            const float cm_lo_j = sm.jrec[j_local].cm_lo;
             bool emit = mi32 > p.thr_lo;                                   // false for NaN
-            if (mi32 >= fminf(cm_i_lo, jr.cm_lo)) {                        // false for NaN (invalid pair)
+            if (mi32 >= fminf(cm_i_lo, cm_lo_j)) {                         // false for NaN (invalid pair)
                 const I8OpenRes orr = i8_open_columns_path(p, sm, mi32, pos_i, j_local, pj, cm_i, cm_i_lo);
                 cm_i = orr.cm_i; cm_i_lo = orr.cm_i_lo; emit = emit || (orr.emit != 0u);
             }
@@ -277,7 +303,8 @@ __device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmem& s
                     const unsigned long long idx = base + __popc(bal & ((1u << lane) - 1u));
                     if (idx < p.cand_cap) {
                         Candidate cd;
-                        cd.i = min(orig_i, jr.orig); cd.j = max(orig_i, jr.orig); cd.mi32 = mi32; cd.pad = 0;
+                        const uint32_t orig_j = sm.jrec[j_local].orig;
+                        cd.i = min(orig_i, orig_j); cd.j = max(orig_i, orig_j); cd.mi32 = mi32; cd.pad = 0;
                         p.cand[idx] = cd;
                     } else p.counters[4] = 1ull;
                 }
@@ -365,7 +392,7 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
     } else {
         // ===================== epilogue (8 warps, 256 threads) =====================
         const uint32_t q = warp & 3u;                            // TMEM lane quadrant this warp may access
-        const uint32_t half = (warp - 2) >> 2;                   // which 128 of the 256 accumulator columns
+        const uint32_t half = (warp - 2) >> 2;                   // which slice of the 256 accumulator columns
         const uint32_t et = threadIdx.x - 64;                    // 0..255
         uint32_t it = 0;
         for (unsigned long long ls = blockIdx.x; ls < p.n_local_slots; ls += gridDim.x) {
@@ -396,7 +423,7 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
 #pragma unroll
                 for (int m = 0; m < 5; ++m) { sm.ih[m * 128 + e] = rc->h[m]; sm.iinvz[m * 128 + e] = rc->invz[m]; }
             }
-            asm volatile("bar.sync 1, 256;" ::: "memory");
+            asm volatile("bar.sync 1, %0;" ::"n"(I8_EPI_THREADS) : "memory");
             mbar_wait(&tfull_bar[buf], acc_phase);
             tcgen05_fence_after();
             const uint32_t tmem_acc = tmem_base + buf * 256u;
@@ -413,7 +440,7 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
             tcgen05_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&tempty_bar[buf]);
-            asm volatile("bar.sync 1, 256;" ::: "memory");                 // staging arrays free for the next tile
+            asm volatile("bar.sync 1, %0;" ::"n"(I8_EPI_THREADS) : "memory");   // staging arrays free for the next tile
             ++it;
         }
     }
