@@ -27,11 +27,12 @@
 //                   B (N=256) rows = (j column, weight byte t, state b) u8 one-hot * {hi, lo}
 //                   D[row][col] s32 in TMEM; N_ab = 256*D[.., t=0, b] + D[.., t=1, b].
 //
-// Kernel anatomy (persistent, 1 CTA/SM, 576 threads):
+// Kernel anatomy (persistent, 1 CTA/SM, 608 threads):
 //   warp 0     TMA producer   cp.async.bulk.tensor 2D (128B swizzle), 4-stage ring of 48 KB (128 samples)
 //   warp 1     MMA issuer     tcgen05.mma.cta_group::1.kind::i8 M128 N256 K32, commit -> mbarriers; owns TMEM
-//   warps 2-17 epilogue       four warps per TMEM lane quadrant (each 64 of the 256 columns):
+//   warps 2-17 epilogue       four warps per TMEM lane quadrant (each 64 of the 256 columns), free-running:
 //                             tcgen05.ld 32x32b, hi/lo combine, KI-lane transpose, MI, candidates
+//   warp 18    record stager  copies the next tile's column records into the other smem buffer (mbarrier handoff)
 // TMEM: 2 accumulator buffers x 256 columns, epilogue of tile t overlaps the mainloop of tile t+1.
 #include <cuda.h>
 #include <algorithm>
@@ -50,14 +51,18 @@ namespace spk {
 #endif
 constexpr int I8_EPI_WARPS = SPK_I8_EPI_WARPS;
 constexpr int I8_EPI_THREADS = I8_EPI_WARPS * 32;
-constexpr int I8_THREADS = 64 + I8_EPI_THREADS;
+constexpr int I8_THREADS = 64 + I8_EPI_THREADS + 32;        // + TMA warp, MMA warp, record-staging warp
+constexpr int I8_QDEPTH = 4;                             // dynamic tile scheduler ring depth
 constexpr uint32_t I8_COLS_PER_WARP = 1024u / I8_EPI_WARPS;   // accumulator columns each epilogue warp drains (128 or 64)
 constexpr uint32_t I8_BK = 128;                         // samples (= bytes) per stage row
 constexpr uint32_t I8_A_BYTES = 128 * I8_BK;            // 16 KB
 constexpr uint32_t I8_B_BYTES = 256 * I8_BK;            // 32 KB
 constexpr uint32_t I8_STAGE_BYTES = I8_A_BYTES + I8_B_BYTES;
 constexpr int I8_NSTAGES = 4;
-constexpr uint32_t I8_SUPER = 16;                       // i-tiles per super-row (B panel reuse through L2)
+#ifndef SPK_I8_SUPER
+#define SPK_I8_SUPER 16
+#endif
+constexpr uint32_t I8_SUPER = SPK_I8_SUPER;             // i-tiles per super-row: their A panels (SUPER x 128 rows x n_pad B) stay L2-resident while B panels stream
 constexpr uint32_t I8_IDESC =                           // cute::UMMA::InstrDescriptor
     (2u << 4) |                  // c_format = S32
     (0u << 7) | (0u << 10) |     // a_format = b_format = UINT8
@@ -68,7 +73,7 @@ constexpr uint32_t I8_IDESC =                           // cute::UMMA::InstrDesc
 struct I8Params {
     const ColRec8* rec;
     Candidate* cand; unsigned long long cand_cap;
-    unsigned long long* counters;          // [0] n_cand, [4] overflow flag
+    unsigned long long* counters;          // [0] n_cand, [4] overflow flag, [5] dynamic tile scheduler cursor
     uint32_t* colmax32;                    // [Lperm] running fp32 maxima (ordered-uint), permuted index
     const unsigned long long* sr_prefix;   // [n_sr+1] chunk prefix per super-row
     uint32_t n_sr, NT;
@@ -321,18 +326,28 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
     // align inside the shared window with pointer arithmetic on the __shared__ symbol (keeps LDS/STS addressing)
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     uint8_t* tiles = smem;
-    I8EpiSmem& sm = *(I8EpiSmem*)(smem + (size_t)I8_NSTAGES * I8_STAGE_BYTES);
-    uint64_t* full_bar = (uint64_t*)(smem + (size_t)I8_NSTAGES * I8_STAGE_BYTES + ((sizeof(I8EpiSmem) + 15) & ~(size_t)15));
+    constexpr size_t SM_STRIDE = (sizeof(I8EpiSmem) + 15) & ~(size_t)15;
+    uint8_t* sm_base = smem + (size_t)I8_NSTAGES * I8_STAGE_BYTES;              // two record buffers (tile t, tile t+1)
+    uint64_t* full_bar = (uint64_t*)(sm_base + 2 * SM_STRIDE);
     uint64_t* empty_bar = full_bar + I8_NSTAGES;
     uint64_t* tfull_bar = empty_bar + I8_NSTAGES;        // [2]
     uint64_t* tempty_bar = tfull_bar + 2;                // [2]
-    uint32_t* tmem_slot = (uint32_t*)(tempty_bar + 2);
+    uint64_t* sfull_bar = tempty_bar + 2;                // [2] column records of a tile staged
+    uint64_t* sempty_bar = sfull_bar + 2;                // [2] ... and released by all epilogue warps
+    uint64_t* qfull_bar = sempty_bar + 2;                // [I8_QDEPTH] tile scheduler ring: entry published
+    uint64_t* qempty_bar = qfull_bar + I8_QDEPTH;        // [I8_QDEPTH] ... and read by every consumer role
+    uint2* q_tile = (uint2*)(qempty_bar + I8_QDEPTH);    // [I8_QDEPTH] (ti, tj); ti = I8_INVALID ends the stream
+    uint32_t* tmem_slot = (uint32_t*)(q_tile + I8_QDEPTH);
 
     const uint32_t warp = threadIdx.x / 32, lane = threadIdx.x % 32;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < I8_NSTAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-        for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], I8_EPI_THREADS / 32); }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], I8_EPI_WARPS);
+            mbar_init(&sfull_bar[b], 1); mbar_init(&sempty_bar[b], I8_EPI_WARPS);
+        }
+        for (int r = 0; r < I8_QDEPTH; ++r) { mbar_init(&qfull_bar[r], 1); mbar_init(&qempty_bar[r], I8_EPI_WARPS + 2); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
@@ -347,12 +362,30 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp == 0) {
-        // ===================== TMA producer =====================
+        // ===================== TMA producer + dynamic tile scheduler =====================
+        // Tiles are handed out from ONE global cursor in slot order, so the 148 CTAs always work inside a window of
+        // ~148 consecutive slots (a few B panels + one super-row of A panels): the operand working set stays in L2
+        // however unevenly the per-class epilogues run. (A static round-robin lets CTAs drift apart until B panels are
+        // evicted between their users: measured 630 GB of DRAM reads for 1.7 GB of operands.)
         if (lane == 0) {
-            uint32_t stage = 0, phase = 0;
-            for (unsigned long long ls = blockIdx.x; ls < p.n_local_slots; ls += gridDim.x) {
-                uint32_t ti, tj;
-                if (!i8_slot_to_tile(p, ls, ti, tj)) continue;
+            uint32_t stage = 0, phase = 0, r = 0, rph = 0;
+            bool debug_done = false;
+            while (true) {
+                uint32_t ti = I8_INVALID, tj = 0;
+                if (p.debug_out) { if (!debug_done) { ti = p.debug_ti; tj = p.debug_tj; debug_done = true; } }
+                else {
+                    while (true) {
+                        const unsigned long long ls = atomicAdd(&p.counters[5], 1ull);
+                        if (ls >= p.n_local_slots) { ti = I8_INVALID; break; }
+                        if (i8_slot_to_tile(p, ls, ti, tj)) break;
+                        ti = I8_INVALID;
+                    }
+                }
+                mbar_wait(&qempty_bar[r], rph ^ 1u);
+                q_tile[r] = make_uint2(ti, tj);
+                mbar_arrive(&qfull_bar[r]);
+                if (++r == I8_QDEPTH) { r = 0; rph ^= 1u; }
+                if (ti == I8_INVALID) break;
                 for (uint32_t kb = 0; kb < p.num_kb; ++kb) {
                     mbar_wait(&empty_bar[stage], phase ^ 1u);
                     uint8_t* st = tiles + (size_t)stage * I8_STAGE_BYTES;
@@ -366,10 +399,13 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
         if (lane == 0) {
-            uint32_t stage = 0, phase = 0, it = 0;
-            for (unsigned long long ls = blockIdx.x; ls < p.n_local_slots; ls += gridDim.x) {
-                uint32_t ti, tj;
-                if (!i8_slot_to_tile(p, ls, ti, tj)) continue;
+            uint32_t stage = 0, phase = 0, it = 0, r = 0, rph = 0;
+            while (true) {
+                mbar_wait(&qfull_bar[r], rph);
+                const uint32_t ti = q_tile[r].x;
+                mbar_arrive(&qempty_bar[r]);
+                if (++r == I8_QDEPTH) { r = 0; rph ^= 1u; }
+                if (ti == I8_INVALID) break;
                 const uint32_t buf = it & 1u, acc_phase = (it >> 1) & 1u;
                 mbar_wait(&tempty_bar[buf], acc_phase ^ 1u);
                 tcgen05_fence_after();
@@ -389,41 +425,69 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
                 ++it;
             }
         }
-    } else {
-        // ===================== epilogue (8 warps, 256 threads) =====================
-        const uint32_t q = warp & 3u;                            // TMEM lane quadrant this warp may access
-        const uint32_t half = (warp - 2) >> 2;                   // which slice of the 256 accumulator columns
-        const uint32_t et = threadIdx.x - 64;                    // 0..255
-        uint32_t it = 0;
-        for (unsigned long long ls = blockIdx.x; ls < p.n_local_slots; ls += gridDim.x) {
-            uint32_t ti, tj;
-            if (!i8_slot_to_tile(p, ls, ti, tj)) continue;
-            const uint32_t buf = it & 1u, acc_phase = (it >> 1) & 1u;
+    } else if (warp == 2 + I8_EPI_WARPS) {
+        // ===================== record stager: runs one tile ahead of the epilogue =====================
+        // Copies the column records of the next tile from global memory into the other smem buffer, so the
+        // epilogue warps never expose that latency and need no CTA-wide barrier between tiles.
+        uint32_t it = 0, r = 0, rph = 0;
+        while (true) {
+            mbar_wait(&qfull_bar[r], rph);
+            const uint2 qt = q_tile[r];
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&qempty_bar[r]);
+            if (++r == I8_QDEPTH) { r = 0; rph ^= 1u; }
+            const uint32_t ti = qt.x, tj = qt.y;
+            if (ti == I8_INVALID) break;
+            const uint32_t buf = it & 1u, ph = (it >> 1) & 1u;
+            I8EpiSmem& sm = *(I8EpiSmem*)(sm_base + buf * SM_STRIDE);
             const uint32_t ci = i8_tile_class(p, ti), cj = i8_tile_class(p, tj);
             const uint32_t WI = 128u >> ci, WJ = 128u >> cj;
             const uint32_t ci0 = p.col_start[ci] + (ti - p.tile_start[ci]) * WI;
             const uint32_t cj0 = p.col_start[cj] + (tj - p.tile_start[cj]) * WJ;
-            // stage the tile's column records (readers of the previous tile are past the trailing barrier)
-            if (et < WJ) {
-                const ColRec8 rc = p.rec[cj0 + et];
+            mbar_wait(&sempty_bar[buf], ph ^ 1u);
+            for (uint32_t e = lane; e < WJ; e += 32) {
+                const ColRec8 rc = p.rec[cj0 + e];
                 JRec jr;
                 jr.mq[0] = rc.mq[0]; jr.mq[1] = rc.mq[1]; jr.mq[2] = rc.mq[2]; jr.mq[3] = rc.mq[3];
                 jr.smq = rc.smq; jr.k = rc.k; jr.orig = rc.orig;
-                const uint32_t cm = p.colmax32[cj0 + et];
+                const uint32_t cm = p.colmax32[cj0 + e];
                 const float cmf = f32_from_ordered(cm);
                 jr.cm_lo = (rc.orig != I8_INVALID && !(cmf > p.thr_hi)) ? cmf - p.band : INFINITY;
-                sm.jrec[et] = jr;
-                sm.jpos[et] = ((unsigned long long)rc.pos_hi << 32) | rc.pos_lo;
+                sm.jrec[e] = jr;
+                sm.jpos[e] = ((unsigned long long)rc.pos_hi << 32) | rc.pos_lo;
 #pragma unroll
-                for (int m = 0; m < 5; ++m) sm.jh[m * 129 + et] = rc.h[m];
-                sm.cmj[et] = cm;
-            } else if (et >= 128 && et - 128 < WI) {
-                const uint32_t e = et - 128;
+                for (int m = 0; m < 5; ++m) sm.jh[m * 129 + e] = rc.h[m];
+                sm.cmj[e] = cm;
+            }
+            for (uint32_t e = lane; e < WI; e += 32) {
                 const ColRec8* rc = p.rec + ci0 + e;
 #pragma unroll
                 for (int m = 0; m < 5; ++m) { sm.ih[m * 128 + e] = rc->h[m]; sm.iinvz[m * 128 + e] = rc->invz[m]; }
             }
-            asm volatile("bar.sync 1, %0;" ::"n"(I8_EPI_THREADS) : "memory");
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&sfull_bar[buf]);                   // release: the writes above are visible to waiters
+            ++it;
+        }
+    } else {
+        // ===================== epilogue warps: four per TMEM lane quadrant, free-running (no CTA barrier) =====================
+        const uint32_t q = warp & 3u;                            // TMEM lane quadrant this warp may access
+        const uint32_t half = (warp - 2) >> 2;                   // which slice of the 256 accumulator columns
+        uint32_t it = 0, r = 0, rph = 0;
+        while (true) {
+            mbar_wait(&qfull_bar[r], rph);
+            const uint2 qt = q_tile[r];
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&qempty_bar[r]);
+            if (++r == I8_QDEPTH) { r = 0; rph ^= 1u; }
+            const uint32_t ti = qt.x, tj = qt.y;
+            if (ti == I8_INVALID) break;
+            const uint32_t buf = it & 1u, acc_phase = (it >> 1) & 1u;
+            I8EpiSmem& sm = *(I8EpiSmem*)(sm_base + buf * SM_STRIDE);
+            const uint32_t ci = i8_tile_class(p, ti), cj = i8_tile_class(p, tj);
+            const uint32_t WI = 128u >> ci, WJ = 128u >> cj;
+            const uint32_t ci0 = p.col_start[ci] + (ti - p.tile_start[ci]) * WI;
+            const uint32_t cj0 = p.col_start[cj] + (tj - p.tile_start[cj]) * WJ;
+            mbar_wait(&sfull_bar[buf], acc_phase);
             mbar_wait(&tfull_bar[buf], acc_phase);
             tcgen05_fence_after();
             const uint32_t tmem_acc = tmem_base + buf * 256u;
@@ -436,11 +500,10 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
                 case 5: i8_epilogue_tile<2, 4>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0); break;
                 default: i8_epilogue_tile<4, 4>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0); break;
             }
-            // accumulator drained: hand the TMEM buffer back to the MMA warp
+            // accumulator drained and records consumed: hand both buffers back
             tcgen05_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tempty_bar[buf]);
-            asm volatile("bar.sync 1, %0;" ::"n"(I8_EPI_THREADS) : "memory");   // staging arrays free for the next tile
+            if (lane == 0) { mbar_arrive(&tempty_bar[buf]); mbar_arrive(&sempty_bar[buf]); }
             ++it;
         }
     }
@@ -702,7 +765,7 @@ static int i8_make_map(Ctx* c, CUtensorMap* map, void* base, uint64_t rows, uint
 }
 
 static size_t i8_smem_bytes() {
-    return (size_t)I8_NSTAGES * I8_STAGE_BYTES + ((sizeof(I8EpiSmem) + 15) & ~(size_t)15) + (2 * I8_NSTAGES + 4) * 8 + 16 + 1024;
+    return (size_t)I8_NSTAGES * I8_STAGE_BYTES + 2 * ((sizeof(I8EpiSmem) + 15) & ~(size_t)15) + (2 * I8_NSTAGES + 8 + 3 * I8_QDEPTH) * 8 + 16 + 1024;
 }
 
 static int i8_launch(Ctx* c, I8Params& gp) {
