@@ -85,34 +85,25 @@ __device__ __forceinline__ double warp_mi_pass(double& v, uint32_t mask_i, uint3
 __global__ void __launch_bounds__(128)
 gbits_build_kernel(const uint8_t* __restrict__ colmajor, const int32_t* __restrict__ gslot, const double* __restrict__ gval,
                    uint32_t* __restrict__ gbits, double* __restrict__ gmarg, uint32_t L, uint32_t n_pad, uint32_t NW) {
+    // one CTA per column; a warp builds one 32-sample word per iteration: lane b gathers the state of slot 32w+b
+    // (the column's n_pad bytes are L1-resident) and five ballots give the five plane words.
     __shared__ double red[4][NSTATES];
-    const uint32_t c = blockIdx.x;
+    const uint32_t c = blockIdx.x, lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
     const uint8_t* col = colmajor + (size_t)c * n_pad;
     double m[NSTATES] = {0, 0, 0, 0, 0};
-    for (uint32_t w = threadIdx.x; w < NW; w += blockDim.x) {
-        uint32_t pl[NSTATES] = {0, 0, 0, 0, 0};
-        if (c < L) {
-            for (uint32_t b = 0; b < 32; ++b) {
-                const int32_t sidx = gslot[w * 32 + b];
-                if (sidx >= 0) {
-                    const uint32_t x = col[sidx];
-#pragma unroll
-                    for (int a = 0; a < NSTATES; ++a) pl[a] |= (x == (uint32_t)a) ? (1u << b) : 0u;
-                }
-            }
-        }
+    for (uint32_t w = wid; w < NW; w += 4) {
+        const int32_t sidx = gslot[w * 32 + lane];
+        const uint32_t x = (c < L && sidx >= 0) ? (uint32_t)col[sidx] : 255u;
         const double v = gval[w];
 #pragma unroll
         for (int a = 0; a < NSTATES; ++a) {
-            gbits[((size_t)c * NSTATES + a) * NW + w] = pl[a];
-            m[a] += v * (double)__popc(pl[a]);
+            const uint32_t pl = __ballot_sync(0xffffffffu, x == (uint32_t)a);
+            if (lane == (uint32_t)a) { gbits[((size_t)c * NSTATES + a) * NW + w] = pl; m[a] += v * (double)__popc(pl); }
         }
     }
+    // lane a of every warp holds that warp's partial marginal of state a
 #pragma unroll
-    for (int a = 0; a < NSTATES; ++a) {
-        m[a] = warp_sum(m[a]);
-        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5][a] = m[a];
-    }
+    for (int a = 0; a < NSTATES; ++a) if (lane == (uint32_t)a) red[wid][a] = m[a];
     __syncthreads();
     if (threadIdx.x < NSTATES) gmarg[(size_t)c * NSTATES + threadIdx.x] = red[0][threadIdx.x] + red[1][threadIdx.x] + red[2][threadIdx.x] + red[3][threadIdx.x];
 }
