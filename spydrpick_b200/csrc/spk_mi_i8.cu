@@ -27,17 +27,19 @@
 //                   B (N=256) rows = (j column, weight byte t, state b) u8 one-hot * {hi, lo}
 //                   D[row][col] s32 in TMEM; N_ab = 256*D[.., t=0, b] + D[.., t=1, b].
 //
-// Kernel anatomy (persistent, 1 CTA/SM, 608 threads):
+// Kernel anatomy (persistent, 1 CTA/SM, 640 threads):
 //   warp 0     TMA producer   cp.async.bulk.tensor 2D (128B swizzle), 4-stage ring of 48 KB (128 samples)
 //   warp 1     MMA issuer     tcgen05.mma.cta_group::1.kind::i8 M128 N256 K32, commit -> mbarriers; owns TMEM
 //   warps 2-17 epilogue       four warps per TMEM lane quadrant (each 64 of the 256 columns), free-running:
 //                             tcgen05.ld 32x32b, hi/lo combine, KI-lane transpose, MI, candidates
 //   warp 18    record stager  copies the next tile's column records into the other smem buffer (mbarrier handoff)
+//   warp 19    tile scheduler global cursor -> (ti, tj), published through a 4-deep smem ring
 // TMEM: 2 accumulator buffers x 256 columns, epilogue of tile t overlaps the mainloop of tile t+1.
 #include <cuda.h>
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <cstdlib>
 #include "spk_internal.h"
 #include "spk_tcgen05.cuh"
 
@@ -51,7 +53,7 @@ namespace spk {
 #endif
 constexpr int I8_EPI_WARPS = SPK_I8_EPI_WARPS;
 constexpr int I8_EPI_THREADS = I8_EPI_WARPS * 32;
-constexpr int I8_THREADS = 64 + I8_EPI_THREADS + 32;        // + TMA warp, MMA warp, record-staging warp
+constexpr int I8_THREADS = 64 + I8_EPI_THREADS + 64;        // + TMA warp, MMA warp, record-staging warp, tile-scheduler warp
 constexpr int I8_QDEPTH = 4;                             // dynamic tile scheduler ring depth
 constexpr uint32_t I8_COLS_PER_WARP = 1024u / I8_EPI_WARPS;   // accumulator columns each epilogue warp drains (128 or 64)
 constexpr uint32_t I8_BK = 128;                         // samples (= bytes) per stage row
@@ -80,6 +82,7 @@ struct I8Params {
     uint32_t tile_start[3], col_start[3];
     uint32_t num_kb;                       // K blocks of 128 samples
     uint32_t part, n_parts;
+    uint32_t pair;                         // 1: CTA-pair kernel (slot = two vertically adjacent tiles)
     unsigned long long n_local_slots;
     float pcq;                             // pseudocount in quantised-weight units
     float thr_lo, thr_hi, band;
@@ -100,8 +103,9 @@ struct I8EpiSmem {
 // local slot -> (ti, tj); SUPER consecutive slots share the B (j) panel
 __device__ __forceinline__ bool i8_slot_to_tile(const I8Params& p, unsigned long long ls, uint32_t& ti, uint32_t& tj) {
     if (p.debug_out) { ti = p.debug_ti; tj = p.debug_tj; return ls == 0; }
-    const unsigned long long q = (ls / I8_SUPER) * p.n_parts + p.part;
-    const uint32_t w = (uint32_t)(ls % I8_SUPER);
+    const uint32_t spc = p.pair ? I8_SUPER / 2 : I8_SUPER;            // slots per chunk (a CTA pair takes two i-tiles per slot)
+    const unsigned long long q = (ls / spc) * p.n_parts + p.part;
+    const uint32_t w = (uint32_t)(ls % spc) << p.pair;
     if (q >= p.sr_prefix[p.n_sr]) return false;
     uint32_t lo = 0, hi = p.n_sr;
     while (hi - lo > 1) { const uint32_t mid = (lo + hi) >> 1; if (p.sr_prefix[mid] <= q) lo = mid; else hi = mid; }
@@ -320,59 +324,90 @@ __device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmem& s
 }
 
 // ---------------------------------------------------------------------------------------------
+// NCTA = 1: one CTA per tile (tcgen05 cta_group::1, M128 N256). NCTA = 2: a CTA pair (cluster of 2 on one TPC)
+// works on two vertically adjacent tiles (2x, tj), (2x+1, tj) with ONE cta_group::2 MMA stream (M256 N256)
+// issued by the pair's leader: each CTA stages its own A panel and only HALF of the shared B panel, so the
+// L2 -> SM operand traffic per tile falls from 48 KB to 32 KB per 128 samples. (ncu on the 1-CTA kernel:
+// lts2xbar 71 % busy at 69 % tensor-pipe activity -- the L2 feed, not the pipe, was the limiter.)
+template <int NCTA> struct I8Cfg;
+template <> struct I8Cfg<1> { static constexpr uint32_t B_BYTES = 256 * I8_BK, STAGE = I8_A_BYTES + B_BYTES; static constexpr int NSTAGES = 4; };
+template <> struct I8Cfg<2> { static constexpr uint32_t B_BYTES = 128 * I8_BK, STAGE = I8_A_BYTES + B_BYTES; static constexpr int NSTAGES = 6; };
+
+template <int NCTA>
 __global__ void __launch_bounds__(I8_THREADS, 1)
 mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const I8Params p) {
+    using Cfg = I8Cfg<NCTA>;
+    constexpr bool PAIR = (NCTA == 2);
+    constexpr int NST = Cfg::NSTAGES;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     // align inside the shared window with pointer arithmetic on the __shared__ symbol (keeps LDS/STS addressing)
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     uint8_t* tiles = smem;
     constexpr size_t SM_STRIDE = (sizeof(I8EpiSmem) + 15) & ~(size_t)15;
-    uint8_t* sm_base = smem + (size_t)I8_NSTAGES * I8_STAGE_BYTES;              // two record buffers (tile t, tile t+1)
-    uint64_t* full_bar = (uint64_t*)(sm_base + 2 * SM_STRIDE);
-    uint64_t* empty_bar = full_bar + I8_NSTAGES;
-    uint64_t* tfull_bar = empty_bar + I8_NSTAGES;        // [2]
-    uint64_t* tempty_bar = tfull_bar + 2;                // [2]
+    uint8_t* sm_base = smem + (size_t)NST * Cfg::STAGE;                        // two record buffers (tile t, tile t+1)
+    uint64_t* full_bar = (uint64_t*)(sm_base + 2 * SM_STRIDE);                 // pair: only the leader's are used
+    uint64_t* empty_bar = full_bar + NST;
+    uint64_t* tfull_bar = empty_bar + NST;               // [2]
+    uint64_t* tempty_bar = tfull_bar + 2;                // [2] pair: only the leader's, both CTAs' epilogues arrive
     uint64_t* sfull_bar = tempty_bar + 2;                // [2] column records of a tile staged
     uint64_t* sempty_bar = sfull_bar + 2;                // [2] ... and released by all epilogue warps
     uint64_t* qfull_bar = sempty_bar + 2;                // [I8_QDEPTH] tile scheduler ring: entry published
-    uint64_t* qempty_bar = qfull_bar + I8_QDEPTH;        // [I8_QDEPTH] ... and read by every consumer role
+    uint64_t* qempty_bar = qfull_bar + I8_QDEPTH;        // [I8_QDEPTH] ... and read by every consumer role (pair: leader's)
     uint2* q_tile = (uint2*)(qempty_bar + I8_QDEPTH);    // [I8_QDEPTH] (ti, tj); ti = I8_INVALID ends the stream
     uint32_t* tmem_slot = (uint32_t*)(q_tile + I8_QDEPTH);
 
-    const uint32_t warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+    const uint32_t warp = __shfl_sync(0xffffffffu, threadIdx.x / 32, 0), lane = threadIdx.x % 32;     // warp-uniform for the compiler
+    const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
+    const bool leader = (rank == 0u);
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < I8_NSTAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        for (int s = 0; s < NST; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
         for (int b = 0; b < 2; ++b) {
-            mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], I8_EPI_WARPS);
+            mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], NCTA * I8_EPI_WARPS);
             mbar_init(&sfull_bar[b], 1); mbar_init(&sempty_bar[b], I8_EPI_WARPS);
         }
-        for (int r = 0; r < I8_QDEPTH; ++r) { mbar_init(&qfull_bar[r], 1); mbar_init(&qempty_bar[r], I8_EPI_WARPS + 2); }
+        for (int r = 0; r < I8_QDEPTH; ++r) { mbar_init(&qfull_bar[r], 1); mbar_init(&qempty_bar[r], NCTA * (I8_EPI_WARPS + 2) + 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
     }
     if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512u) : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        if constexpr (PAIR) {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512u) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+        } else {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512u) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
     }
     tcgen05_fence_before();
-    __syncthreads();
+    if constexpr (PAIR) cluster_sync_all(); else __syncthreads();
     tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    if (warp == 0) {
-        // ===================== TMA producer + dynamic tile scheduler =====================
+    // queue helpers: entries are written by the leader's scheduler (into both CTAs), released to the leader's barrier
+    auto q_wait = [&](uint32_t r, uint32_t rph) { if constexpr (PAIR) mbar_wait_cluster(&qfull_bar[r], rph); else mbar_wait(&qfull_bar[r], rph); };
+    auto q_release = [&](uint32_t r) { if (PAIR && !leader) mbar_arrive_remote(&qempty_bar[r], 0); else mbar_arrive(&qempty_bar[r]); };
+    // does THIS CTA have a tile to finish for queue entry (t0, tj)? (pair: the odd CTA idles below the diagonal / past the last tile)
+    auto own_valid = [&](uint32_t ti_own, uint32_t tj) {
+        if constexpr (!PAIR) return true;
+        return ti_own < p.NT && ti_own <= tj && (!p.debug_out || ti_own == p.debug_ti);
+    };
+
+    if (warp == 3 + I8_EPI_WARPS) {
+        // ===================== dynamic tile scheduler (leader CTA of a pair; every CTA otherwise) =====================
         // Tiles are handed out from ONE global cursor in slot order, so the 148 CTAs always work inside a window of
         // ~148 consecutive slots (a few B panels + one super-row of A panels): the operand working set stays in L2
         // however unevenly the per-class epilogues run. (A static round-robin lets CTAs drift apart until B panels are
-        // evicted between their users: measured 630 GB of DRAM reads for 1.7 GB of operands.)
-        if (lane == 0) {
-            uint32_t stage = 0, phase = 0, r = 0, rph = 0;
+        // evicted between their users: measured 630 GB of DRAM reads for 1.7 GB of operands.) The cursor round trip and
+        // the slot -> tile search (~2 us of dependent global accesses) run up to I8_QDEPTH tiles ahead in their own warp;
+        // done in the TMA thread they drained the 4-stage operand ring between tiles (tensor pipe 69 % active).
+        if (lane == 0 && leader) {
+            uint32_t r = 0, rph = 0;
             bool debug_done = false;
             while (true) {
                 uint32_t ti = I8_INVALID, tj = 0;
-                if (p.debug_out) { if (!debug_done) { ti = p.debug_ti; tj = p.debug_tj; debug_done = true; } }
+                if (p.debug_out) { if (!debug_done) { ti = PAIR ? (p.debug_ti & ~1u) : p.debug_ti; tj = p.debug_tj; debug_done = true; } }
                 else {
                     while (true) {
                         const unsigned long long ls = atomicAdd(&p.counters[5], 1ull);
@@ -381,47 +416,85 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
                         ti = I8_INVALID;
                     }
                 }
-                mbar_wait(&qempty_bar[r], rph ^ 1u);
+                if constexpr (PAIR) mbar_wait_cluster(&qempty_bar[r], rph ^ 1u); else mbar_wait(&qempty_bar[r], rph ^ 1u);
                 q_tile[r] = make_uint2(ti, tj);
+                if constexpr (PAIR) {
+                    st_remote_u64(&q_tile[r], 1, ((unsigned long long)tj << 32) | ti);
+                    mbar_arrive_remote(&qfull_bar[r], 1);
+                }
                 mbar_arrive(&qfull_bar[r]);
                 if (++r == I8_QDEPTH) { r = 0; rph ^= 1u; }
                 if (ti == I8_INVALID) break;
-                for (uint32_t kb = 0; kb < p.num_kb; ++kb) {
-                    mbar_wait(&empty_bar[stage], phase ^ 1u);
-                    uint8_t* st = tiles + (size_t)stage * I8_STAGE_BYTES;
-                    mbar_expect_tx(&full_bar[stage], I8_STAGE_BYTES);
-                    tma_load_2d(&map_b, &full_bar[stage], st, (int32_t)(kb * I8_BK), (int32_t)(tj * 256u));
-                    tma_load_2d(&map_a, &full_bar[stage], st + I8_B_BYTES, (int32_t)(kb * I8_BK), (int32_t)(ti * 128u));
-                    if (++stage == I8_NSTAGES) { stage = 0; phase ^= 1u; }
+            }
+        }
+    } else if (warp == 0) {
+        // ===================== TMA producer (whole warp converged, one elected lane issues) =====================
+        uint32_t stage = 0, phase = 0, r = 0, rph = 0;
+        while (true) {
+            q_wait(r, rph);
+            const uint2 qt = q_tile[r];
+            __syncwarp();
+            if (elect_one()) q_release(r);
+            if (++r == I8_QDEPTH) { r = 0; rph ^= 1u; }
+            const uint32_t ti = qt.x, tj = qt.y;
+            if (ti == I8_INVALID) break;
+            const int32_t ya = (int32_t)((ti + rank) * 128u);
+            const int32_t yb = (int32_t)(PAIR ? tj * 256u + rank * 128u : tj * 256u);
+            for (uint32_t kb = 0; kb < p.num_kb; ++kb) {
+                mbar_wait(&empty_bar[stage], phase ^ 1u);
+                uint8_t* st = tiles + (size_t)stage * Cfg::STAGE;
+                if (elect_one()) {
+                    if constexpr (PAIR) {
+                        if (leader) mbar_expect_tx(&full_bar[stage], 2u * Cfg::STAGE);       // both CTAs' boxes land on the leader's barrier
+                        tma_load_2d_pair(&map_b, &full_bar[stage], st, (int32_t)(kb * I8_BK), yb);
+                        tma_load_2d_pair(&map_a, &full_bar[stage], st + Cfg::B_BYTES, (int32_t)(kb * I8_BK), ya);
+                    } else {
+                        mbar_expect_tx(&full_bar[stage], Cfg::STAGE);
+                        tma_load_2d(&map_b, &full_bar[stage], st, (int32_t)(kb * I8_BK), yb);
+                        tma_load_2d(&map_a, &full_bar[stage], st + Cfg::B_BYTES, (int32_t)(kb * I8_BK), ya);
+                    }
                 }
+                __syncwarp();
+                if (++stage == NST) { stage = 0; phase ^= 1u; }
             }
         }
     } else if (warp == 1) {
-        // ===================== MMA issuer =====================
-        if (lane == 0) {
+        // ===================== MMA issuer (pair: the leader's warp drives both tensor cores) =====================
+        // The warp stays converged and one elected lane issues: with an `if (lane == 0)` region the compiler wraps
+        // every tcgen05 instruction in a uniform-register waterfall loop (~90 instructions per 128 samples, as
+        // long as the four MMAs themselves take -- the issue thread, not the pipe, was the bottleneck).
+        if (leader) {
+            constexpr uint32_t IDESC = PAIR ? ((I8_IDESC & ~(31u << 24)) | ((256u >> 4) << 24)) : I8_IDESC;
             uint32_t stage = 0, phase = 0, it = 0, r = 0, rph = 0;
             while (true) {
-                mbar_wait(&qfull_bar[r], rph);
+                q_wait(r, rph);
                 const uint32_t ti = q_tile[r].x;
-                mbar_arrive(&qempty_bar[r]);
+                __syncwarp();
+                if (elect_one()) q_release(r);
                 if (++r == I8_QDEPTH) { r = 0; rph ^= 1u; }
                 if (ti == I8_INVALID) break;
                 const uint32_t buf = it & 1u, acc_phase = (it >> 1) & 1u;
-                mbar_wait(&tempty_bar[buf], acc_phase ^ 1u);
+                if constexpr (PAIR) mbar_wait_cluster(&tempty_bar[buf], acc_phase ^ 1u); else mbar_wait(&tempty_bar[buf], acc_phase ^ 1u);
                 tcgen05_fence_after();
                 const uint32_t d_tmem = tmem_base + buf * 256u;
                 for (uint32_t kb = 0; kb < p.num_kb; ++kb) {
                     mbar_wait(&full_bar[stage], phase);
                     tcgen05_fence_after();
-                    const uint32_t sb = smem_u32(tiles + (size_t)stage * I8_STAGE_BYTES);
-                    const uint32_t sa = sb + I8_B_BYTES;
+                    const uint32_t sb = smem_u32(tiles + (size_t)stage * Cfg::STAGE);
+                    const uint64_t db = umma_smem_desc(sb), da = umma_smem_desc(sb + Cfg::B_BYTES);
+                    if (elect_one()) {
 #pragma unroll
-                    for (uint32_t k = 0; k < I8_BK / 32; ++k)
-                        umma_i8(d_tmem, umma_smem_desc(sa + k * 32), umma_smem_desc(sb + k * 32), I8_IDESC, (kb | k) ? 1u : 0u);
-                    umma_commit(&empty_bar[stage]);
-                    if (++stage == I8_NSTAGES) { stage = 0; phase ^= 1u; }
+                        for (uint32_t k = 0; k < I8_BK / 32; ++k) {      // +32 B along K = +2 in the descriptor's 16-byte address field
+                            if constexpr (PAIR) umma_i8_pair(d_tmem, da + 2u * k, db + 2u * k, IDESC, (kb | k) ? 1u : 0u);
+                            else umma_i8(d_tmem, da + 2u * k, db + 2u * k, IDESC, (kb | k) ? 1u : 0u);
+                        }
+                        if constexpr (PAIR) umma_commit_pair(&empty_bar[stage]); else umma_commit(&empty_bar[stage]);
+                    }
+                    __syncwarp();
+                    if (++stage == NST) { stage = 0; phase ^= 1u; }
                 }
-                umma_commit(&tfull_bar[buf]);
+                if (elect_one()) { if constexpr (PAIR) umma_commit_pair(&tfull_bar[buf]); else umma_commit(&tfull_bar[buf]); }
+                __syncwarp();
                 ++it;
             }
         }
@@ -431,13 +504,14 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
         // epilogue warps never expose that latency and need no CTA-wide barrier between tiles.
         uint32_t it = 0, r = 0, rph = 0;
         while (true) {
-            mbar_wait(&qfull_bar[r], rph);
+            q_wait(r, rph);
             const uint2 qt = q_tile[r];
             __syncwarp();
-            if (lane == 0) mbar_arrive(&qempty_bar[r]);
+            if (lane == 0) q_release(r);
             if (++r == I8_QDEPTH) { r = 0; rph ^= 1u; }
-            const uint32_t ti = qt.x, tj = qt.y;
-            if (ti == I8_INVALID) break;
+            if (qt.x == I8_INVALID) break;
+            const uint32_t ti = qt.x + rank, tj = qt.y;
+            if (!own_valid(ti, tj)) continue;
             const uint32_t buf = it & 1u, ph = (it >> 1) & 1u;
             I8EpiSmem& sm = *(I8EpiSmem*)(sm_base + buf * SM_STRIDE);
             const uint32_t ci = i8_tile_class(p, ti), cj = i8_tile_class(p, tj);
@@ -472,47 +546,56 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
         // ===================== epilogue warps: four per TMEM lane quadrant, free-running (no CTA barrier) =====================
         const uint32_t q = warp & 3u;                            // TMEM lane quadrant this warp may access
         const uint32_t half = (warp - 2) >> 2;                   // which slice of the 256 accumulator columns
-        uint32_t it = 0, r = 0, rph = 0;
+        uint32_t it = 0, ait = 0, r = 0, rph = 0;               // it: record buffers (own valid tiles), ait: accumulator buffers (all tiles)
         while (true) {
-            mbar_wait(&qfull_bar[r], rph);
+            q_wait(r, rph);
             const uint2 qt = q_tile[r];
             __syncwarp();
-            if (lane == 0) mbar_arrive(&qempty_bar[r]);
+            if (lane == 0) q_release(r);
             if (++r == I8_QDEPTH) { r = 0; rph ^= 1u; }
-            const uint32_t ti = qt.x, tj = qt.y;
-            if (ti == I8_INVALID) break;
-            const uint32_t buf = it & 1u, acc_phase = (it >> 1) & 1u;
-            I8EpiSmem& sm = *(I8EpiSmem*)(sm_base + buf * SM_STRIDE);
-            const uint32_t ci = i8_tile_class(p, ti), cj = i8_tile_class(p, tj);
-            const uint32_t WI = 128u >> ci, WJ = 128u >> cj;
-            const uint32_t ci0 = p.col_start[ci] + (ti - p.tile_start[ci]) * WI;
-            const uint32_t cj0 = p.col_start[cj] + (tj - p.tile_start[cj]) * WJ;
-            mbar_wait(&sfull_bar[buf], acc_phase);
-            mbar_wait(&tfull_bar[buf], acc_phase);
+            if (qt.x == I8_INVALID) break;
+            const uint32_t ti = qt.x + rank, tj = qt.y;
+            const bool valid = own_valid(ti, tj);
+            const uint32_t abuf = ait & 1u, acc_phase = (ait >> 1) & 1u;
+            const uint32_t buf = it & 1u;
+            if (valid) mbar_wait(&sfull_bar[buf], (it >> 1) & 1u);
+            mbar_wait(&tfull_bar[abuf], acc_phase);
             tcgen05_fence_after();
-            const uint32_t tmem_acc = tmem_base + buf * 256u;
-            const bool diag = (ti == tj);
-            switch (ci * 3u + cj) {
-                case 0: i8_epilogue_tile<1, 1>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0); break;
-                case 1: i8_epilogue_tile<1, 2>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0); break;
-                case 2: i8_epilogue_tile<1, 4>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0); break;
-                case 4: i8_epilogue_tile<2, 2>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0); break;
-                case 5: i8_epilogue_tile<2, 4>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0); break;
-                default: i8_epilogue_tile<4, 4>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0); break;
+            if (valid) {
+                I8EpiSmem& sm = *(I8EpiSmem*)(sm_base + buf * SM_STRIDE);
+                const uint32_t ci = i8_tile_class(p, ti), cj = i8_tile_class(p, tj);
+                const uint32_t WI = 128u >> ci, WJ = 128u >> cj;
+                const uint32_t ci0 = p.col_start[ci] + (ti - p.tile_start[ci]) * WI;
+                const uint32_t cj0 = p.col_start[cj] + (tj - p.tile_start[cj]) * WJ;
+                const uint32_t tmem_acc = tmem_base + abuf * 256u;
+                const bool diag = (ti == tj);
+                switch (ci * 3u + cj) {
+                    case 0: i8_epilogue_tile<1, 1>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0); break;
+                    case 1: i8_epilogue_tile<1, 2>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0); break;
+                    case 2: i8_epilogue_tile<1, 4>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0); break;
+                    case 4: i8_epilogue_tile<2, 2>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0); break;
+                    case 5: i8_epilogue_tile<2, 4>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0); break;
+                    default: i8_epilogue_tile<4, 4>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0); break;
+                }
             }
             // accumulator drained and records consumed: hand both buffers back
             tcgen05_fence_before();
             __syncwarp();
-            if (lane == 0) { mbar_arrive(&tempty_bar[buf]); mbar_arrive(&sempty_bar[buf]); }
-            ++it;
+            if (lane == 0) {
+                if (PAIR && !leader) mbar_arrive_remote(&tempty_bar[abuf], 0); else mbar_arrive(&tempty_bar[abuf]);
+                if (valid) mbar_arrive(&sempty_bar[buf]);
+            }
+            if (valid) ++it;
+            ++ait;
         }
     }
 
     tcgen05_fence_before();
-    __syncthreads();
+    if constexpr (PAIR) cluster_sync_all(); else __syncthreads();
     if (warp == 1) {
         tcgen05_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+        if constexpr (PAIR) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+        else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
     }
 }
 
@@ -764,14 +847,23 @@ static int i8_make_map(Ctx* c, CUtensorMap* map, void* base, uint64_t rows, uint
     return SPK_OK;
 }
 
-static size_t i8_smem_bytes() {
-    return (size_t)I8_NSTAGES * I8_STAGE_BYTES + 2 * ((sizeof(I8EpiSmem) + 15) & ~(size_t)15) + (2 * I8_NSTAGES + 8 + 3 * I8_QDEPTH) * 8 + 16 + 1024;
+template <int NCTA> static size_t i8_smem_bytes() {
+    return (size_t)I8Cfg<NCTA>::NSTAGES * I8Cfg<NCTA>::STAGE + 2 * ((sizeof(I8EpiSmem) + 15) & ~(size_t)15) +
+           (2 * I8Cfg<NCTA>::NSTAGES + 8 + 3 * I8_QDEPTH) * 8 + 16 + 1024;
+}
+
+// SPYDRPICK_B200_I8_PAIR=0 selects the one-CTA-per-tile kernel (A/B comparisons); default: CTA pairs
+static bool i8_use_pair() {
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("SPYDRPICK_B200_I8_PAIR"); v = (e && e[0] == '0') ? 0 : 1; }
+    return v == 1;
 }
 
 static int i8_launch(Ctx* c, I8Params& gp) {
+    const bool pair = gp.pair != 0;
     CUtensorMap ma, mb;
     int r = i8_make_map(c, &ma, c->d_A8, (uint64_t)128 * c->i8.NT, c->n_pad, 128); if (r) return r;
-    r = i8_make_map(c, &mb, c->d_B8, (uint64_t)256 * c->i8.NT, c->n_pad, 256); if (r) return r;
+    r = i8_make_map(c, &mb, c->d_B8, (uint64_t)256 * c->i8.NT, c->n_pad, pair ? 128 : 256); if (r) return r;
     gp.rec = c->d_i8_rec;
     gp.num_kb = c->n_pad / I8_BK;
     gp.NT = c->i8.NT;
@@ -779,10 +871,30 @@ static int i8_launch(Ctx* c, I8Params& gp) {
     gp.colmax32 = c->d_i8_colmax32;
     gp.counters = c->d_counters;
     const unsigned long long slots = gp.debug_out ? 1ull : gp.n_local_slots;
-    const unsigned grid = (unsigned)(slots < (unsigned long long)c->sm_count ? (slots ? slots : 1) : (unsigned long long)c->sm_count);
-    const size_t smem = i8_smem_bytes();
-    SPK_CUDA(c, cudaFuncSetAttribute(mi_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    mi_i8_kernel<<<grid, I8_THREADS, smem, c->stream>>>(ma, mb, gp);
+    if (!pair) {
+        const unsigned grid = (unsigned)(slots < (unsigned long long)c->sm_count ? (slots ? slots : 1) : (unsigned long long)c->sm_count);
+        const size_t smem = i8_smem_bytes<1>();
+        SPK_CUDA(c, cudaFuncSetAttribute(mi_i8_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        mi_i8_kernel<1><<<grid, I8_THREADS, smem, c->stream>>>(ma, mb, gp);
+    } else {
+        const size_t smem = i8_smem_bytes<2>();
+        SPK_CUDA(c, cudaFuncSetAttribute(mi_i8_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        cudaLaunchConfig_t cfg; memset(&cfg, 0, sizeof cfg);
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        cfg.blockDim = dim3(I8_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = c->stream; cfg.attrs = attr; cfg.numAttrs = 1;
+        cfg.gridDim = dim3(2u * (unsigned)(c->sm_count / 2));
+        int max_clusters = 0;
+        if (cudaOccupancyMaxActiveClusters(&max_clusters, mi_i8_kernel<2>, &cfg) != cudaSuccess || max_clusters < 1) {
+            cudaGetLastError();
+            max_clusters = c->sm_count / 2;
+        }
+        unsigned long long pairs = (unsigned long long)max_clusters;
+        if (slots < pairs) pairs = slots ? slots : 1;
+        cfg.gridDim = dim3(2u * (unsigned)pairs);
+        SPK_CUDA(c, cudaLaunchKernelEx(&cfg, mi_i8_kernel<2>, ma, mb, gp));
+    }
     c->tm.kernel_launches += 1;
     SPK_CUDA(c, cudaGetLastError());
     return SPK_OK;
@@ -806,7 +918,8 @@ int mi_i8_filter(Ctx* c, const spk_scan_params& p, double band, uint64_t circle)
     c->tm.kernel_launches += 1;
     gp.cand = c->d_cand; gp.cand_cap = c->cand_cap;
     gp.sr_prefix = d_prefix; gp.n_sr = n_sr;
-    gp.part = p.part_index; gp.n_parts = nparts; gp.n_local_slots = local_chunks * I8_SUPER;
+    gp.pair = i8_use_pair() ? 1u : 0u;
+    gp.part = p.part_index; gp.n_parts = nparts; gp.n_local_slots = local_chunks * (gp.pair ? I8_SUPER / 2 : I8_SUPER);
     gp.pcq = (float)(p.pseudocount / c->i8_delta);
     gp.band = (float)band; gp.thr_lo = (float)(p.threshold - band); gp.thr_hi = (float)(p.threshold + band);
     gp.ld_threshold = p.ld_threshold; gp.circle = circle; gp.linear = p.linear_genome;
@@ -837,6 +950,7 @@ int mi_i8_debug_tile(Ctx* c, uint32_t ti, uint32_t tj, double pc, uint32_t* d_ou
     if (ti > tj || tj >= c->i8.NT) return fail(c, SPK_E_INVALID, "int8 debug tile: need ti <= tj < NT");
     I8Params gp; memset(&gp, 0, sizeof gp);
     gp.sr_prefix = (const unsigned long long*)c->d_tilemap;
+    gp.pair = i8_use_pair() ? 1u : 0u;
     gp.n_parts = 1; gp.n_local_slots = 1;
     gp.pcq = (float)(pc / c->i8_delta);
     gp.debug_out = d_out; gp.debug_ti = ti; gp.debug_tj = tj;
