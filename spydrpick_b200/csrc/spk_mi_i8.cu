@@ -387,7 +387,7 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
 
     // queue helpers: entries are written by the leader's scheduler (into both CTAs), released to the leader's barrier
     auto q_wait = [&](uint32_t r, uint32_t rph) { if constexpr (PAIR) mbar_wait_cluster(&qfull_bar[r], rph); else mbar_wait(&qfull_bar[r], rph); };
-    auto q_release = [&](uint32_t r) { if (PAIR && !leader) mbar_arrive_remote(&qempty_bar[r], 0); else mbar_arrive(&qempty_bar[r]); };
+    auto q_release = [&](uint32_t r) { if (PAIR && !leader) mbar_arrive_remote_nofence(&qempty_bar[r], 0); else mbar_arrive(&qempty_bar[r]); };
     // does THIS CTA have a tile to finish for queue entry (t0, tj)? (pair: the odd CTA idles below the diagonal / past the last tile)
     auto own_valid = [&](uint32_t ti_own, uint32_t tj) {
         if constexpr (!PAIR) return true;
@@ -433,10 +433,9 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
         while (true) {
             q_wait(r, rph);
             const uint2 qt = q_tile[r];
-            __syncwarp();
+            const uint32_t ti = __shfl_sync(0xffffffffu, qt.x, 0), tj = qt.y;      // the shuffle consumes the load before the slot is handed back
             if (elect_one()) q_release(r);
             if (++r == I8_QDEPTH) { r = 0; rph ^= 1u; }
-            const uint32_t ti = qt.x, tj = qt.y;
             if (ti == I8_INVALID) break;
             const int32_t ya = (int32_t)((ti + rank) * 128u);
             const int32_t yb = (int32_t)(PAIR ? tj * 256u + rank * 128u : tj * 256u);
@@ -468,8 +467,7 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
             uint32_t stage = 0, phase = 0, it = 0, r = 0, rph = 0;
             while (true) {
                 q_wait(r, rph);
-                const uint32_t ti = q_tile[r].x;
-                __syncwarp();
+                const uint32_t ti = __shfl_sync(0xffffffffu, q_tile[r].x, 0);
                 if (elect_one()) q_release(r);
                 if (++r == I8_QDEPTH) { r = 0; rph ^= 1u; }
                 if (ti == I8_INVALID) break;
@@ -506,11 +504,11 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
         while (true) {
             q_wait(r, rph);
             const uint2 qt = q_tile[r];
-            __syncwarp();
+            const uint32_t t0 = __shfl_sync(0xffffffffu, qt.x, 0);                 // consumes the load before the slot is handed back
             if (lane == 0) q_release(r);
             if (++r == I8_QDEPTH) { r = 0; rph ^= 1u; }
-            if (qt.x == I8_INVALID) break;
-            const uint32_t ti = qt.x + rank, tj = qt.y;
+            if (t0 == I8_INVALID) break;
+            const uint32_t ti = t0 + rank, tj = qt.y;
             if (!own_valid(ti, tj)) continue;
             const uint32_t buf = it & 1u, ph = (it >> 1) & 1u;
             I8EpiSmem& sm = *(I8EpiSmem*)(sm_base + buf * SM_STRIDE);
@@ -550,11 +548,11 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
         while (true) {
             q_wait(r, rph);
             const uint2 qt = q_tile[r];
-            __syncwarp();
+            const uint32_t t0 = __shfl_sync(0xffffffffu, qt.x, 0);                 // consumes the load before the slot is handed back
             if (lane == 0) q_release(r);
             if (++r == I8_QDEPTH) { r = 0; rph ^= 1u; }
-            if (qt.x == I8_INVALID) break;
-            const uint32_t ti = qt.x + rank, tj = qt.y;
+            if (t0 == I8_INVALID) break;
+            const uint32_t ti = t0 + rank, tj = qt.y;
             const bool valid = own_valid(ti, tj);
             const uint32_t abuf = ait & 1u, acc_phase = (ait >> 1) & 1u;
             const uint32_t buf = it & 1u;
@@ -582,7 +580,7 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
             tcgen05_fence_before();
             __syncwarp();
             if (lane == 0) {
-                if (PAIR && !leader) mbar_arrive_remote(&tempty_bar[abuf], 0); else mbar_arrive(&tempty_bar[abuf]);
+                if (PAIR && !leader) mbar_arrive_remote_nofence(&tempty_bar[abuf], 0); else mbar_arrive(&tempty_bar[abuf]);
                 if (valid) mbar_arrive(&sempty_bar[buf]);
             }
             if (valid) ++it;

@@ -115,6 +115,11 @@ __device__ __forceinline__ uint32_t mapa_u32(const void* p, uint32_t rank) {
 __device__ __forceinline__ void mbar_arrive_remote(uint64_t* bar, uint32_t rank) {
     asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(mapa_u32(bar, rank)) : "memory");
 }
+// same without the cluster-scope release fence (it costs an ERRBAR that waits for every earlier memory operation of the
+// thread): for hand-backs that publish no data -- "I have read the slot" / "I have drained the accumulator"
+__device__ __forceinline__ void mbar_arrive_remote_nofence(uint64_t* bar, uint32_t rank) {
+    asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(mapa_u32(bar, rank)) : "memory");
+}
 __device__ __forceinline__ void st_remote_u64(void* p, uint32_t rank, unsigned long long v) {
     asm volatile("st.shared::cluster.u64 [%0], %1;" ::"r"(mapa_u32(p, rank)), "l"(v) : "memory");
 }
