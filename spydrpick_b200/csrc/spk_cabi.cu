@@ -267,6 +267,7 @@ static int ensure_scan_buffers(Ctx* c, uint64_t max_edges, bool exhaustive) {
     want_edges = std::min<uint64_t>(want_edges, possible + 1);
     uint64_t want_cand = want_edges + want_edges / 2 + (uint64_t)c->L * 64 + (1u << 20);
     want_cand = std::min<uint64_t>(want_cand, possible + 1);
+    want_cand += (uint64_t)c->sm_count * 16 * 2 * 128;        // int8 engine: two partly used emission chunks per epilogue warp
     if (exhaustive) want_cand = std::max<uint64_t>(std::min<uint64_t>(possible + 1, 1ull << 24), (uint64_t)c->L);
     int r;
     if (c->edges_cap < want_edges) {
@@ -325,10 +326,10 @@ int spk_mi_scan(spk_ctx* c, const spk_scan_params* pp, spk_scan_result* res) {
         SPK_CUDA(c, cudaStreamSynchronize(c->stream));
         if (h_counters[4]) return fail(c, SPK_E_OVERFLOW, "candidate buffer overflow (%llu candidates > capacity %llu): raise max_edges or the threshold",
                                        h_counters[0], (unsigned long long)c->cand_cap);
-        const uint64_t ncand = h_counters[0];
-        res->n_candidates = ncand;
+        uint64_t ncand = h_counters[0];                  // int8 engine: reserved slots, a few of them invalid-marked holes
         SPK_CUDA(c, cudaEventRecord(c->ev[4], c->stream));
-        r = mi_refine_candidates(c, ncand, p.pseudocount, p.threshold); if (r) return r;
+        r = mi_refine_candidates(c, ncand, p.pseudocount, p.threshold, &ncand); if (r) return r;
+        res->n_candidates = ncand;
         SPK_CUDA(c, cudaEventRecord(c->ev[5], c->stream));
         r = mi_compact(c, ncand, p, circle); if (r) return r;
         SPK_CUDA(c, cudaEventRecord(c->ev[6], c->stream));

@@ -157,7 +157,7 @@ int hamming_neighbour_counts(Ctx* c, uint64_t min_identical, int quirk);
 // ---- exact fp64 MI (spk_mi_exact.cu)
 int mi_pairs_exact(Ctx* c, const uint32_t* d_pi, const uint32_t* d_pj, uint64_t npairs, double pc, double* d_mi);
 // refine candidates -> d_refined (i,j,mi64), d_refined_wo (NaN when no gap column involved)
-int mi_refine_candidates(Ctx* c, uint64_t ncand, double pc, double wo_threshold);   // MI-without-gaps only when mi > wo_threshold
+int mi_refine_candidates(Ctx* c, uint64_t ncand, double pc, double wo_threshold, uint64_t* n_valid = nullptr);   // MI-without-gaps only when mi > wo_threshold
 // exhaustive diagnostic engine: emits every pair of the partition as a candidate-free exact scan
 int mi_scan_exact(Ctx* c, const spk_scan_params& p, uint64_t circle);
 // threshold + colmax + compaction over refined candidates

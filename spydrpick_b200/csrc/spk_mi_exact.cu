@@ -475,6 +475,7 @@ classify_count_kernel(const Candidate* __restrict__ cand, unsigned long long nca
     __syncthreads();
     for (unsigned long long p = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; p < ncand; p += (unsigned long long)gridDim.x * blockDim.x) {
         const Candidate cd = cand[p];
+        if (cd.i == I8_INVALID) continue;                          // unused slot of an emission chunk (int8 engine)
         atomicAdd(&h[pair_class(masks[cd.i], masks[cd.j])], 1u);
     }
     __syncthreads();
@@ -494,7 +495,10 @@ classify_scatter_kernel(const Candidate* __restrict__ cand, unsigned long long n
         for (int k = 0; k < 8; ++k) {
             const unsigned long long p = c0 + (unsigned long long)k * blockDim.x + threadIdx.x;
             cls[k] = 9;
-            if (p < ncand) { cd[k] = cand[p]; cls[k] = pair_class(masks[cd[k].i], masks[cd[k].j]); loc[k] = atomicAdd(&h[cls[k]], 1u); }
+            if (p < ncand) {
+                cd[k] = cand[p];
+                if (cd[k].i != I8_INVALID) { cls[k] = pair_class(masks[cd[k].i], masks[cd[k].j]); loc[k] = atomicAdd(&h[cls[k]], 1u); }
+            }
         }
         __syncthreads();
         if (threadIdx.x < 9) base[threadIdx.x] = h[threadIdx.x] ? atomicAdd(&cursors[threadIdx.x], (unsigned long long)h[threadIdx.x]) : 0ull;
@@ -560,6 +564,13 @@ mi_refine_kernel(const uint8_t* __restrict__ colmajor, const double* __restrict_
     for (unsigned long long p = (unsigned long long)blockIdx.x * EX_WARPS + wid; p < ncand;
          p += (unsigned long long)gridDim.x * EX_WARPS) {
         const Candidate cd = cand[p];
+        if (cd.i == I8_INVALID) {                                  // unused slot of an emission chunk (int8 engine): never kept
+            if (lane == 0) {
+                spk_edge e; e.i = 0; e.j = 0; e.mi = __longlong_as_double(0x7ff8000000000000ll);
+                refined[p] = e; refined_wo[p] = e.mi;
+            }
+            continue;
+        }
         const uint32_t mi_ = masks[cd.i], mj_ = masks[cd.j];
         double v = gbits ? warp_crosstab_grouped(gbits, gval, gmarg, NW, cd.i, cd.j, mi_, mj_, lane)
                          : warp_crosstab(colmajor + (size_t)cd.i * n_pad, colmajor + (size_t)cd.j * n_pad, w, n_pad, bins, lane);
@@ -730,7 +741,9 @@ int mi_pairs_exact(Ctx* c, const uint32_t* d_pi, const uint32_t* d_pj, uint64_t 
     return SPK_OK;
 }
 
-int mi_refine_candidates(Ctx* c, uint64_t ncand, double pc, double wo_threshold) {
+// *n_valid: entries written to d_refined (the int8 engine leaves invalid-marked holes in the candidate list, dropped here)
+int mi_refine_candidates(Ctx* c, uint64_t ncand, double pc, double wo_threshold, uint64_t* n_valid) {
+    if (n_valid) *n_valid = ncand;
     if (ncand == 0) return SPK_OK;
     { int rg = ensure_grouped(c, pc); if (rg) return rg; }
     if (c->g_state == 1) {
@@ -749,6 +762,7 @@ int mi_refine_candidates(Ctx* c, uint64_t ncand, double pc, double wo_threshold)
         SPK_CUDA(c, cudaMemcpyAsync(h_cnt, d_cnt, sizeof h_cnt, cudaMemcpyDeviceToHost, c->stream));
         SPK_CUDA(c, cudaStreamSynchronize(c->stream));
         h_off[0] = 0; for (int q = 0; q < 9; ++q) h_off[q + 1] = h_off[q] + h_cnt[q];
+        if (n_valid) *n_valid = h_off[9];
         SPK_CUDA(c, cudaMemcpyAsync(d_cnt + 16, h_off, 9 * sizeof(unsigned long long), cudaMemcpyHostToDevice, c->stream));
         classify_scatter_kernel<<<cgrid, 256, 0, c->stream>>>(c->d_cand, ncand, c->d_masks, d_cnt + 16, c->d_cand2);
         c->tm.kernel_launches += 2;

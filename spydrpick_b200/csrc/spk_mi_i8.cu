@@ -83,6 +83,7 @@ struct I8Params {
     uint32_t num_kb;                       // K blocks of 128 samples
     uint32_t part, n_parts;
     uint32_t pair;                         // 1: CTA-pair kernel (slot = two vertically adjacent tiles)
+    const unsigned long long* seed_chunks; // seed pass: the sampled chunk ids (n_local_slots covers exactly these); nullptr = main pass
     unsigned long long n_local_slots;
     float pcq;                             // pseudocount in quantised-weight units
     float thr_lo, thr_hi, band;
@@ -91,20 +92,26 @@ struct I8Params {
 };
 
 struct __align__(16) JRec { uint32_t mq[4]; uint32_t smq, k, orig; float cm_lo; };   // cm_lo: running max - band, +inf when closed
-struct I8EpiSmem {
+struct I8EpiSmem {                 // column records of one tile, staged by the stager warp one tile ahead
     JRec jrec[128];
     unsigned long long jpos[128];
-    float jh[5 * 129];
-    float ih[5 * 128];
-    float iinvz[5 * 128];
+    float jh[5 * 129];              // H_j table by the i column's number of kept rows
+    float ih2[2 * 128];             // H_i / 1/Z of the i columns for the two kept-row counts the j class can have
+    float iinvz2[2 * 128];
     uint32_t cmj[128];
+    uint32_t imq[4 * 128];          // i columns, structure of arrays (lanes read consecutive columns)
+    uint32_t imqd[128], ik[128], iorig[128], icm[128];
+    unsigned long long ipos[128];
 };
+// kept-row counts possible in a j class: class 0 (1 row) {0,1}, class 1 (2 rows) {2}, class 2 (4 rows) {3,4}
+__device__ __forceinline__ uint32_t i8_class_klo(uint32_t c) { return c == 0u ? 0u : (c == 1u ? 2u : 3u); }
+__device__ __forceinline__ uint32_t i8_class_khi(uint32_t c) { return c == 0u ? 1u : (c == 1u ? 2u : 4u); }
 
 // local slot -> (ti, tj); SUPER consecutive slots share the B (j) panel
 __device__ __forceinline__ bool i8_slot_to_tile(const I8Params& p, unsigned long long ls, uint32_t& ti, uint32_t& tj) {
     if (p.debug_out) { ti = p.debug_ti; tj = p.debug_tj; return ls == 0; }
     const uint32_t spc = p.pair ? I8_SUPER / 2 : I8_SUPER;            // slots per chunk (a CTA pair takes two i-tiles per slot)
-    const unsigned long long q = (ls / spc) * p.n_parts + p.part;
+    const unsigned long long q = p.seed_chunks ? p.seed_chunks[ls / spc] : (ls / spc) * p.n_parts + p.part;
     const uint32_t w = (uint32_t)(ls % spc) << p.pair;
     if (q >= p.sr_prefix[p.n_sr]) return false;
     uint32_t lo = 0, hi = p.n_sr;
@@ -128,11 +135,11 @@ template <> __device__ __forceinline__ void i8_tmem_ld<32>(uint32_t taddr, uint3
 // closed columns carry +inf in cm_lo). Lanes that arrive together and share the j column reduce their
 // maximum with match/redux so a burst emits ~one candidate per warp, not one per lane.
 struct I8OpenRes { float cm_i, cm_i_lo; uint32_t emit; };
-__device__ __noinline__ I8OpenRes i8_open_columns_path(const I8Params& p, I8EpiSmem& sm, float mi32, unsigned long long pos_i,
+__device__ __noinline__ I8OpenRes i8_open_columns_path(const I8Params& p, I8EpiSmem& sm, float mi32, uint32_t i_local,
                                                        uint32_t j_local, uint32_t gcol_j, float cm_i, float cm_i_lo) {
     I8OpenRes res; res.cm_i = cm_i; res.cm_i_lo = cm_i_lo; res.emit = 0u;
     const unsigned long long pos_j = sm.jpos[j_local];
-    if (!(genome_distance(pos_i, pos_j, p.linear, p.circle) > p.ld_threshold)) return res;
+    if (!(genome_distance(sm.ipos[i_local], pos_j, p.linear, p.circle) > p.ld_threshold)) return res;
     bool emit = false;
     if (mi32 >= cm_i_lo) {                                         // i side: lane-local running maximum
         const float c = fmaxf(cm_i, mi32);
@@ -155,12 +162,45 @@ __device__ __noinline__ I8OpenRes i8_open_columns_path(const I8Params& p, I8EpiS
 }
 
 // ---------------------------------------------------------------------------------------------
+// candidate emission: every epilogue warp owns a chunk of I8_CH slots of the candidate array (one atomicAdd per
+// chunk, the next chunk is reserved ahead of need), so a warp that finds candidates does not sit out a global
+// atomic round trip (~1 us) per ballot -- measured: tests + emission cost 6 ms of a 55 ms launch that way.
+// Unused slots of a chunk are filled with an invalid marker (i = j = I8_INVALID) which the refine pass drops.
+// ---------------------------------------------------------------------------------------------
+constexpr uint32_t I8_CH = 128;
+struct I8Emit { uint32_t cur, used, next; };      // cur: chunk id (warp-uniform; I8_INVALID = none yet), next: reserved ahead (lane 0 only)
+
+__device__ __forceinline__ uint32_t i8_reserve_chunk(const I8Params& p) {
+    return (uint32_t)(atomicAdd(&p.counters[0], (unsigned long long)I8_CH) / I8_CH);
+}
+__device__ __forceinline__ void i8_fill_invalid(const I8Params& p, uint32_t chunk, uint32_t from, uint32_t lane) {
+    Candidate cd; cd.i = I8_INVALID; cd.j = I8_INVALID; cd.mi32 = 0.f; cd.pad = 0;
+    for (uint32_t k = from + lane; k < I8_CH; k += 32) {
+        const unsigned long long idx = (unsigned long long)chunk * I8_CH + k;
+        if (idx < p.cand_cap) p.cand[idx] = cd;
+    }
+}
+__device__ __noinline__ void i8_emit_switch(const I8Params& p, I8Emit& em, uint32_t lane) {
+    if (em.cur != I8_INVALID) i8_fill_invalid(p, em.cur, em.used, lane);
+    uint32_t nx = em.next;
+    if (lane == 0 && nx == I8_INVALID) nx = i8_reserve_chunk(p);
+    nx = __shfl_sync(0xffffffffu, nx, 0);
+    em.cur = nx; em.used = 0; em.next = I8_INVALID;
+    if ((unsigned long long)(nx + 1u) * I8_CH > p.cand_cap && lane == 0) p.counters[4] = 1ull;
+}
+__device__ __forceinline__ void i8_emit_flush(const I8Params& p, I8Emit& em, uint32_t lane) {
+    if (em.cur != I8_INVALID) i8_fill_invalid(p, em.cur, em.used, lane);
+    const uint32_t nx = __shfl_sync(0xffffffffu, em.next, 0);
+    if (nx != I8_INVALID) i8_fill_invalid(p, nx, 0, lane);
+}
+
+// ---------------------------------------------------------------------------------------------
 // epilogue of one tile for the class pair (KI rows per i column, KJ rows per j column), KI <= KJ
 // ---------------------------------------------------------------------------------------------
 template <int KI, int KJ>
-__device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmem& sm, uint32_t tmem_acc, uint32_t q, uint32_t half,
+__device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmem& sm, I8Emit& em, uint32_t tmem_acc, uint32_t q, uint32_t half,
                                                  uint32_t lane, bool diag, uint32_t ci0, uint32_t cj0) {
-#if SPK_I8_TWO_PHASE
+#if SPK_I8_TWO_PHASE == 1
     constexpr int LOADW = (KI == 1 && KJ == 1) ? 16 : 32;   // TMEM columns per load (>= 2 independent pairs per lane where possible)
 #else
     constexpr int LOADW = (KI == 4) ? 32 : 16;
@@ -172,17 +212,20 @@ __device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmem& s
     const uint32_t row = q * 32u + lane;
     const uint32_t i_local = row / KI, g = lane % KI;
     const uint32_t pi = ci0 + i_local;
-    // per-lane constants of the i column
-    const ColRec8* ri = p.rec + pi;
+    // per-lane constants of the i column (staged in shared memory by the stager warp)
     uint32_t mi_[KI];
 #pragma unroll
-    for (int a = 0; a < KI; ++a) mi_[a] = __ldg(&ri->mq[a]);
-    const uint32_t mi_d = __ldg(&ri->mqd), ki = __ldg(&ri->k), orig_i = __ldg(&ri->orig);
-    const unsigned long long pos_i = ((unsigned long long)__ldg(&ri->pos_hi) << 32) | __ldg(&ri->pos_lo);
-    const bool vi = orig_i != I8_INVALID;
-    const float cm_i0 = f32_from_ordered(p.colmax32[pi]);
+    for (int a = 0; a < KI; ++a) mi_[a] = sm.imq[a * 128 + i_local];
+    // (position and original index stay in shared memory: they are only needed on the rare open-column / emission paths)
+    const uint32_t mi_d = sm.imqd[i_local], ki = sm.ik[i_local];
+    const bool vi = sm.iorig[i_local] != I8_INVALID;
+    const float cm_i0 = f32_from_ordered(sm.icm[i_local]);
     float cm_i = cm_i0;
     float cm_i_lo = (vi && !(cm_i0 > p.thr_hi)) ? cm_i0 - p.band : INFINITY;      // +inf: column closed (covered by the threshold rule)
+    constexpr uint32_t KJ_HI = (KJ == 1) ? 1u : (KJ == 2 ? 2u : 4u);              // j columns of this class keep KJ_HI or (KJ != 2) one row fewer
+    const float invZ_lo = sm.iinvz2[i_local], invZ_hi = sm.iinvz2[128 + i_local];
+    const float ih_lo = sm.ih2[i_local], ih_hi = sm.ih2[128 + i_local];
+    const float* jh_row = sm.jh + ki * 129u;
     const float ln2 = 0.69314718055994530942f;
 
 #pragma unroll 1
@@ -190,6 +233,13 @@ __device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmem& s
         const uint32_t col0 = half * I8_COLS_PER_WARP + ld * LOADW;
         uint32_t r[LOADW];
         i8_tmem_ld<LOADW>(tmem_acc + ((q * 32u) << 16) + col0, r);
+#if defined(SPK_I8_EPI_LEVEL) && SPK_I8_EPI_LEVEL == 1          // experiment: TMEM loads only
+        { uint32_t x = 0;
+#pragma unroll
+          for (int k = 0; k < LOADW; ++k) x ^= r[k];
+          if (x == 0xdeadbeefu) p.counters[6] = x;
+          continue; }
+#endif
         uint32_t v[NJ * KJ];
 #pragma unroll
         for (int jj = 0; jj < NJ; ++jj)
@@ -233,6 +283,7 @@ __device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmem& s
 #pragma unroll
         // phase 1: branch-free MI of the PPL pairs of this load (independent chains -> MUFU / LDS latencies overlap)
         float mi_arr[PPL];
+        bool need = false; (void)need;
 #pragma unroll
         for (int s = 0; s < PPL; ++s) {
             const uint32_t j_local = col0 / (2 * KJ) + s * KI + g;
@@ -247,8 +298,9 @@ __device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmem& s
             }
             const JRec jr = sm.jrec[j_local];
             const uint32_t kj = jr.k;
-            const float invZ = sm.iinvz[kj * 128u + i_local];
-            const float hsum = sm.ih[kj * 128u + i_local] + sm.jh[ki * 129u + j_local];
+            const bool khi = (KJ == 2) || (kj == KJ_HI);
+            const float invZ = khi ? invZ_hi : invZ_lo;
+            const float hsum = (khi ? ih_hi : ih_lo) + jh_row[j_local];
             const float pcZ = p.pcq * invZ;
             // p >= pc/Z is far above the denormal range: plain MUFU.LG2 (ftz) without the denormal rescue sequence
             auto xlg = [&](uint32_t nq) {
@@ -288,8 +340,14 @@ __device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmem& s
             const bool valid = vi && (jr.orig != I8_INVALID) && (!diag || pi < cj0 + j_local);
             mi_arr[s] = valid ? fmaf(S, ln2, -hsum) : __int_as_float(0x7fc00000);
 #if SPK_I8_TWO_PHASE
+#if SPK_I8_TWO_PHASE == 2
+            need = need || (mi_arr[s] >= fminf(fminf(p.thr_lo, cm_i_lo), jr.cm_lo));   // superset of the exact tests below; false for NaN
+#endif
         }
         if (p.debug_out) continue;
+#if SPK_I8_TWO_PHASE == 2
+        if (!__any_sync(0xffffffffu, need)) continue;             // nothing to test or emit in this load (the common case)
+#endif
         // phase 2: threshold / open-column tests and candidate emission
 #pragma unroll
         for (int s = 0; s < PPL; ++s) {
@@ -297,26 +355,52 @@ __device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmem& s
 #endif
             const uint32_t pj = cj0 + j_local;
             const float mi32 = mi_arr[s];
+            if (p.seed_chunks) {
+                // seed pass: no candidates, only the running LD-admissible maxima of both columns
+                const bool adm = (mi32 == mi32) && genome_distance(sm.ipos[i_local], sm.jpos[j_local], p.linear, p.circle) > p.ld_threshold;
+                const float m = adm ? mi32 : -INFINITY;
+                cm_i = fmaxf(cm_i, m);
+                constexpr uint32_t GM = (KI == 1) ? 0xffffffffu : (KI == 2 ? 0x55555555u : 0x11111111u);   // lanes that share this j column
+                const uint32_t o = f32_ordered(m);
+                const uint32_t gmax = __reduce_max_sync(GM << g, o);
+                if (lane == g && gmax > sm.cmj[j_local]) {
+                    if (atomicMax(&sm.cmj[j_local], gmax) < gmax) atomicMax(&p.colmax32[pj], gmax);
+                }
+                continue;
+            }
             const float cm_lo_j = sm.jrec[j_local].cm_lo;
+#if defined(SPK_I8_EPI_LEVEL) && SPK_I8_EPI_LEVEL == 2          // experiment: MI arithmetic without tests / emission
+            if (mi32 == 123.456f) p.counters[6] = 1ull;
+            continue;
+#endif
             bool emit = mi32 > p.thr_lo;                                   // false for NaN
+#if defined(SPK_I8_EPI_LEVEL) && SPK_I8_EPI_LEVEL == 3          // experiment: no open-column path
+            if (mi32 == 123.456f) {
+#else
             if (mi32 >= fminf(cm_i_lo, cm_lo_j)) {                         // false for NaN (invalid pair)
-                const I8OpenRes orr = i8_open_columns_path(p, sm, mi32, pos_i, j_local, pj, cm_i, cm_i_lo);
+#endif
+                const I8OpenRes orr = i8_open_columns_path(p, sm, mi32, i_local, j_local, pj, cm_i, cm_i_lo);
                 cm_i = orr.cm_i; cm_i_lo = orr.cm_i_lo; emit = emit || (orr.emit != 0u);
             }
+#if defined(SPK_I8_EPI_LEVEL) && SPK_I8_EPI_LEVEL == 4          // experiment: no emission
+            if (emit && mi32 == 123.456f) p.counters[6] = 1ull;
+            continue;
+#endif
             const uint32_t bal = __ballot_sync(0xffffffffu, emit);
             if (bal) {
-                unsigned long long base = 0;
-                if (lane == 0) base = atomicAdd(&p.counters[0], (unsigned long long)__popc(bal));
-                base = __shfl_sync(0xffffffffu, base, 0);
+                const uint32_t nb = __popc(bal);
+                if (em.cur == I8_INVALID || em.used + nb > I8_CH) i8_emit_switch(p, em, lane);
                 if (emit) {
-                    const unsigned long long idx = base + __popc(bal & ((1u << lane) - 1u));
+                    const unsigned long long idx = (unsigned long long)em.cur * I8_CH + em.used + __popc(bal & ((1u << lane) - 1u));
                     if (idx < p.cand_cap) {
                         Candidate cd;
-                        const uint32_t orig_j = sm.jrec[j_local].orig;
+                        const uint32_t orig_i = sm.iorig[i_local], orig_j = sm.jrec[j_local].orig;
                         cd.i = min(orig_i, orig_j); cd.j = max(orig_i, orig_j); cd.mi32 = mi32; cd.pad = 0;
                         p.cand[idx] = cd;
-                    } else p.counters[4] = 1ull;
+                    }
                 }
+                em.used += nb;
+                if (lane == 0 && em.next == I8_INVALID && em.used > I8_CH / 2) em.next = i8_reserve_chunk(p);   // result is not needed before the switch
             }
         }
     }
@@ -340,8 +424,11 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
     constexpr bool PAIR = (NCTA == 2);
     constexpr int NST = Cfg::NSTAGES;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
-    // align inside the shared window with pointer arithmetic on the __shared__ symbol (keeps LDS/STS addressing)
-    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    // The dynamic shared segment is the only shared object of this kernel and is declared 1024-aligned, so every
+    // buffer below sits at a compile-time offset from the symbol (LDS/STS with immediate offsets; a run-time
+    // alignment fix-up made the compiler rebuild the shared-window base in front of every access).
+    uint8_t* smem = smem_raw;
+    if (threadIdx.x == 0 && (smem_u32(smem_raw) & 1023u) != 0u) { printf("spk: dynamic shared memory is not 1024-byte aligned\n"); __trap(); }
     uint8_t* tiles = smem;
     constexpr size_t SM_STRIDE = (sizeof(I8EpiSmem) + 15) & ~(size_t)15;
     uint8_t* sm_base = smem + (size_t)NST * Cfg::STAGE;                        // two record buffers (tile t, tile t+1)
@@ -531,10 +618,16 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
                 for (int m = 0; m < 5; ++m) sm.jh[m * 129 + e] = rc.h[m];
                 sm.cmj[e] = cm;
             }
+            const uint32_t klo = i8_class_klo(cj), khi = i8_class_khi(cj);
             for (uint32_t e = lane; e < WI; e += 32) {
                 const ColRec8* rc = p.rec + ci0 + e;
+                sm.ih2[e] = rc->h[klo]; sm.ih2[128 + e] = rc->h[khi];
+                sm.iinvz2[e] = rc->invz[klo]; sm.iinvz2[128 + e] = rc->invz[khi];
 #pragma unroll
-                for (int m = 0; m < 5; ++m) { sm.ih[m * 128 + e] = rc->h[m]; sm.iinvz[m * 128 + e] = rc->invz[m]; }
+                for (int a = 0; a < 4; ++a) sm.imq[a * 128 + e] = rc->mq[a];
+                sm.imqd[e] = rc->mqd; sm.ik[e] = rc->k; sm.iorig[e] = rc->orig;
+                sm.icm[e] = p.colmax32[ci0 + e];                       // may be one tile stale: still a lower bound of the running maximum
+                sm.ipos[e] = ((unsigned long long)rc->pos_hi << 32) | rc->pos_lo;
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&sfull_bar[buf]);                   // release: the writes above are visible to waiters
@@ -545,6 +638,7 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
         const uint32_t q = warp & 3u;                            // TMEM lane quadrant this warp may access
         const uint32_t half = (warp - 2) >> 2;                   // which slice of the 256 accumulator columns
         uint32_t it = 0, ait = 0, r = 0, rph = 0;               // it: record buffers (own valid tiles), ait: accumulator buffers (all tiles)
+        I8Emit em; em.cur = I8_INVALID; em.used = 0; em.next = I8_INVALID;
         while (true) {
             q_wait(r, rph);
             const uint2 qt = q_tile[r];
@@ -559,7 +653,11 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
             if (valid) mbar_wait(&sfull_bar[buf], (it >> 1) & 1u);
             mbar_wait(&tfull_bar[abuf], acc_phase);
             tcgen05_fence_after();
+#ifdef SPK_I8_SKIP_EPI                                   // experiment: mainloop only (results are wrong)
+            if (valid && p.debug_out) {
+#else
             if (valid) {
+#endif
                 I8EpiSmem& sm = *(I8EpiSmem*)(sm_base + buf * SM_STRIDE);
                 const uint32_t ci = i8_tile_class(p, ti), cj = i8_tile_class(p, tj);
                 const uint32_t WI = 128u >> ci, WJ = 128u >> cj;
@@ -568,12 +666,12 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
                 const uint32_t tmem_acc = tmem_base + abuf * 256u;
                 const bool diag = (ti == tj);
                 switch (ci * 3u + cj) {
-                    case 0: i8_epilogue_tile<1, 1>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0); break;
-                    case 1: i8_epilogue_tile<1, 2>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0); break;
-                    case 2: i8_epilogue_tile<1, 4>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0); break;
-                    case 4: i8_epilogue_tile<2, 2>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0); break;
-                    case 5: i8_epilogue_tile<2, 4>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0); break;
-                    default: i8_epilogue_tile<4, 4>(p, sm, tmem_acc, q, half, lane, diag, ci0, cj0); break;
+                    case 0: i8_epilogue_tile<1, 1>(p, sm, em, tmem_acc, q, half, lane, diag, ci0, cj0); break;
+                    case 1: i8_epilogue_tile<1, 2>(p, sm, em, tmem_acc, q, half, lane, diag, ci0, cj0); break;
+                    case 2: i8_epilogue_tile<1, 4>(p, sm, em, tmem_acc, q, half, lane, diag, ci0, cj0); break;
+                    case 4: i8_epilogue_tile<2, 2>(p, sm, em, tmem_acc, q, half, lane, diag, ci0, cj0); break;
+                    case 5: i8_epilogue_tile<2, 4>(p, sm, em, tmem_acc, q, half, lane, diag, ci0, cj0); break;
+                    default: i8_epilogue_tile<4, 4>(p, sm, em, tmem_acc, q, half, lane, diag, ci0, cj0); break;
                 }
             }
             // accumulator drained and records consumed: hand both buffers back
@@ -586,6 +684,7 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
             if (valid) ++it;
             ++ait;
         }
+        i8_emit_flush(p, em, lane);
     }
 
     tcgen05_fence_before();
@@ -847,13 +946,21 @@ static int i8_make_map(Ctx* c, CUtensorMap* map, void* base, uint64_t rows, uint
 
 template <int NCTA> static size_t i8_smem_bytes() {
     return (size_t)I8Cfg<NCTA>::NSTAGES * I8Cfg<NCTA>::STAGE + 2 * ((sizeof(I8EpiSmem) + 15) & ~(size_t)15) +
-           (2 * I8Cfg<NCTA>::NSTAGES + 8 + 3 * I8_QDEPTH) * 8 + 16 + 1024;
+           (2 * I8Cfg<NCTA>::NSTAGES + 8 + 3 * I8_QDEPTH) * 8 + 16;
 }
 
 // SPYDRPICK_B200_I8_PAIR=0 selects the one-CTA-per-tile kernel (A/B comparisons); default: CTA pairs
 static bool i8_use_pair() {
     static int v = -1;
     if (v < 0) { const char* e = getenv("SPYDRPICK_B200_I8_PAIR"); v = (e && e[0] == '0') ? 0 : 1; }
+    return v == 1;
+}
+
+// SPYDRPICK_B200_I8_SEED=0 disables the colmax seed pass (A/B comparisons)
+constexpr uint32_t I8_SEED_STRIDE = 32;
+static bool i8_use_seed() {
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("SPYDRPICK_B200_I8_SEED"); v = (e && e[0] == '0') ? 0 : 1; }
     return v == 1;
 }
 
@@ -923,6 +1030,24 @@ int mi_i8_filter(Ctx* c, const spk_scan_params& p, double band, uint64_t circle)
     gp.ld_threshold = p.ld_threshold; gp.circle = circle; gp.linear = p.linear_genome;
     gp.debug_out = nullptr;
     SPK_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
+    // Seed pass: a 1/I8_SEED_STRIDE sample of the chunks (of ALL partitions), without candidates, to bring every column's
+    // running maximum close to its final value before the main pass. Without it the open-column rule (candidates within
+    // `band` of a column's running maximum while that maximum is below thr + band) fires on every record of a rising
+    // maximum: measured 6.6 M extra candidates and 5.5 ms of slow-path epilogue per launch at 3000 x 100000.
+    if (i8_use_seed() && total_chunks >= 64ull * I8_SEED_STRIDE) {
+        std::vector<unsigned long long> seed;
+        for (uint32_t sr = 0; sr < n_sr; ++sr)
+            for (unsigned long long q = prefix[sr]; q < prefix[sr + 1]; ++q)
+                if ((uint32_t)(q - prefix[sr]) % I8_SEED_STRIDE == sr % I8_SEED_STRIDE) seed.push_back(q);
+        if (!seed.empty() && (size_t)(n_sr + 1 + seed.size()) * 8 <= (1u << 20)) {
+            SPK_CUDA(c, cudaMemcpyAsync(d_prefix + n_sr + 1, seed.data(), seed.size() * 8, cudaMemcpyHostToDevice, c->stream));
+            I8Params sp = gp;
+            sp.seed_chunks = d_prefix + n_sr + 1;
+            sp.n_local_slots = (unsigned long long)seed.size() * (gp.pair ? I8_SUPER / 2 : I8_SUPER);
+            r = i8_launch(c, sp); if (r) return r;
+            SPK_CUDA(c, cudaMemsetAsync(c->d_counters + 5, 0, sizeof(unsigned long long), c->stream));   // rewind the tile cursor
+        }
+    }
     r = i8_launch(c, gp); if (r) return r;
     SPK_CUDA(c, cudaEventRecord(c->ev[3], c->stream));
     SPK_CUDA(c, cudaEventSynchronize(c->ev[3]));
