@@ -237,7 +237,7 @@ def run_b200(args):
             flags = sdist.allgather_flag_shards(flags, ne)       # edge-range partition of K3 -> every rank
         return r, ne, int(flags[:ne].sum().item())
 
-    from spydrpick_b200.capi import pinned_copy
+    from spydrpick_b200.capi import pinned_copy, pinned_empty
     states_pin = pinned_copy(states)                  # the caller's alignment lives in page-locked host memory
     pos_pin = pinned_copy(pos)
 
@@ -251,10 +251,14 @@ def run_b200(args):
         ctx.set_weights(1.0 / c.astype(np.float64)); tw.append(time.perf_counter())
         if world == 1:
             r = ctx.mi_scan(threshold, max_edges=max_edges, sort_desc=True, n_terms=args.n_terms, engine=args.engine,
-                            keep_on_device=False, copy=False); tw.append(time.perf_counter())
-            edges = r["edges"]                        # view of the library's pinned result buffer
-            flags = ctx.aracne(edges, EPS)            # same pointer -> device copy reused, only the flags travel
-            ndirect = int(flags.sum())                # the step's result is read on the host
+                            keep_on_device=False, copy=False, async_download=True); tw.append(time.perf_counter())
+            edges = r["edges"]                        # view of the library's pinned result buffer (download in flight)
+            nonlocal host_flags
+            if host_flags is None or host_flags.shape[0] < len(edges):
+                host_flags = pinned_empty(int(len(edges) * 1.25) + 4096, np.uint8)
+            flags = ctx.aracne(edges, EPS, out=host_flags)   # same pointer -> device copy reused; overlaps the edge download
+            ctx.wait_download()                       # edges + MI-without-gaps lists are now complete on the host
+            ndirect = int(np.count_nonzero(flags))    # the step's result is read on the host
             h2d = states.nbytes + pos.nbytes + 8 * n + len(flags)
             d2h = edges.nbytes + r["edges_wo_gaps"].nbytes + 8 * L + 8 * n + len(flags)
         else:
@@ -268,7 +272,7 @@ def run_b200(args):
             ctx.aracne_device(d_edges, ne, dflags.data_ptr(), EPS, part_index=rank, n_parts=world)
             from spydrpick_b200 import dist as sdist
             dflags = sdist.allgather_flag_shards(dflags, ne)
-            nonlocal host_edges, host_flags
+            nonlocal host_edges
             if host_edges is None or host_edges.numel() < ne * 16:
                 host_edges = torch.empty(int(ne * 16 * 1.25) + 4096, dtype=torch.uint8).pin_memory()
                 host_flags = torch.empty(int(ne * 1.25) + 4096, dtype=torch.uint8).pin_memory()

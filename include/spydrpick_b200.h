@@ -105,7 +105,11 @@ typedef struct {
                                   hi/lo weight split; 1 = fp64 exhaustive (diagnostic, no tensor cores) */
     uint32_t part_index;       /* tile-space partition for multi-GPU: this context scans part_index of n_parts */
     uint32_t n_parts;          /* 0 or 1 = whole upper triangle */
-    int32_t  keep_on_device;   /* 1: do not copy edges to the host (device pointers below stay valid) */
+    int32_t  keep_on_device;   /* 0: edges copied to pinned host buffers before the call returns;
+                                  1: no host copy (device pointers below stay valid);
+                                  2: host copy started on a side stream: the host pointers are returned at once and
+                                     are valid after spk_wait_download(); spk_aracne() on the returned edges pointer
+                                     may run in between (it uses the device copy), so the download overlaps K3 */
 } spk_scan_params;
 
 typedef struct {
@@ -142,6 +146,9 @@ int spk_sort_edges(spk_ctx* ctx, spk_edge* edges, uint64_t n_edges);
  * n_parts <= 1 evaluates all. */
 int spk_aracne(spk_ctx* ctx, const spk_edge* edges, uint64_t n_edges, double edge_threshold,
                uint32_t part_index, uint32_t n_parts, uint8_t* direct_flags /* [n_edges] host */);
+
+/* Blocks until the host copies started by spk_mi_scan(keep_on_device = 2) are complete (no-op otherwise). */
+int spk_wait_download(spk_ctx* ctx);
 
 /* Device-resident variants for callers that keep data in HBM (bench, multi-GPU plumbing):
  * d_edges is a device pointer to n_edges sorted spk_edge records, d_flags device uint8[n_edges]. */

@@ -19,7 +19,7 @@ EXPORTS = ["spk_create", "spk_destroy", "spk_last_error", "spk_set_stream", "spk
            "spk_set_alignment",
            "spk_neighbour_counts", "spk_set_weights", "spk_mi_pairs", "spk_determine_mi_threshold",
            "spk_mi_scan", "spk_outlier_thresholds", "spk_sort_edges", "spk_aracne", "spk_sort_edges_device",
-           "spk_aracne_device", "spk_get_timings", "spk_debug_tile_counts", "spk_debug_i8_layout", "spk_debug_i8_tile",
+           "spk_aracne_device", "spk_wait_download", "spk_get_timings", "spk_debug_tile_counts", "spk_debug_i8_layout", "spk_debug_i8_tile",
            "spk_version"]
 
 
@@ -84,6 +84,7 @@ def load():
     L.spk_aracne_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_double, C.c_uint32, C.c_uint32, C.c_void_p]
     L.spk_get_timings.argtypes = [C.c_void_p, C.POINTER(Timings)]
     L.spk_debug_tile_counts.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_int32, C.c_void_p]
+    L.spk_wait_download.argtypes = [C.c_void_p]
     L.spk_host_alloc.argtypes = [C.c_size_t, C.POINTER(C.c_void_p)]
     L.spk_host_free.restype = None
     L.spk_host_free.argtypes = [C.c_void_p]
@@ -196,9 +197,15 @@ class Context:
 
     def mi_scan(self, threshold, pseudocount=0.5, ld_threshold=0, linear_genome=False, circle_size=0, max_edges=0,
                 sort_desc=True, n_terms=0, band=0.0, engine=0, part_index=0, n_parts=1, keep_on_device=False,
-                copy=True):
+                copy=True, async_download=False):
         """copy=False returns zero-copy views of the library-owned pinned result buffers (valid until the next
-        scan on this context); passing such an `edges` view to aracne() reuses the device copy."""
+        scan on this context); passing such an `edges` view to aracne() reuses the device copy.
+        async_download=True (with copy=False): the views are returned while the download is still running on a
+        side stream; call wait_download() before reading them (aracne() on the view may run in between)."""
+        if async_download:
+            if copy or keep_on_device:
+                raise ValueError("async_download needs copy=False and keep_on_device=False")
+            keep_on_device = 2
         p = ScanParams(threshold, pseudocount, ld_threshold, int(linear_genome), circle_size, max_edges, int(sort_desc),
                        n_terms, band, engine, part_index, n_parts, int(keep_on_device))
         r = ScanResult()
@@ -215,7 +222,7 @@ class Context:
                "max_filter_error": float(r.max_filter_error),
                "colmax": np.ctypeslib.as_array(r.colmax, shape=(self.L,)).copy(),
                "d_edges": r.d_edges, "d_edges_wo_gaps": r.d_edges_wo_gaps, "d_colmax": r.d_colmax}
-        if not keep_on_device:
+        if keep_on_device != 1:
             out["edges"] = grab(r.edges, r.n_edges)
             out["edges_wo_gaps"] = grab(r.edges_wo_gaps, r.n_wo_gaps)
         return out
@@ -231,11 +238,22 @@ class Context:
         self._check(self.lib.spk_sort_edges(self.h, _ptr(e), e.shape[0]))
         return e
 
-    def aracne(self, edges, edge_threshold=2.220446049250313e-16, part_index=0, n_parts=1):
+    def aracne(self, edges, edge_threshold=2.220446049250313e-16, part_index=0, n_parts=1, out=None):
+        """out: optional uint8 array (>= len(edges), e.g. from pinned_empty) that receives the flags."""
         e = np.ascontiguousarray(edges, dtype=EDGE_DTYPE)
-        f = np.zeros(e.shape[0], dtype=np.uint8)
+        if out is None:
+            f = np.zeros(e.shape[0], dtype=np.uint8)
+        else:
+            if out.dtype != np.uint8 or out.shape[0] < e.shape[0] or not out.flags.c_contiguous:
+                raise ValueError("aracne: out must be a contiguous uint8 array with at least len(edges) entries")
+            f = out[:e.shape[0]]
+            if n_parts > 1:
+                f[:] = 0
         self._check(self.lib.spk_aracne(self.h, _ptr(e), e.shape[0], edge_threshold, part_index, n_parts, _ptr(f)))
         return f
+
+    def wait_download(self):
+        self._check(self.lib.spk_wait_download(self.h))
 
     def sort_edges_device(self, d_edges, n):
         self._check(self.lib.spk_sort_edges_device(self.h, C.c_void_p(d_edges), n))

@@ -92,6 +92,9 @@ int spk_create(spk_ctx** out, int device, int verbose) {
     }
     c->stream = c->own_stream;
     for (auto& e : c->ev) cudaEventCreate(&e);
+    cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
+    cudaEventCreateWithFlags(&c->ev_ready, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&c->ev_dl, cudaEventDisableTiming);
     if (cudaMalloc(&c->d_counters, 8 * sizeof(unsigned long long)) != cudaSuccess || cudaMalloc(&c->d_tilemap, 1 << 20) != cudaSuccess) {
         delete c; return fail(nullptr, SPK_E_NOMEM, "context allocation failed");
     }
@@ -109,6 +112,10 @@ void spk_destroy(spk_ctx* c) {
     if (c->hp_wo) cudaFreeHost(c->hp_wo);
     if (c->d_tilemap) { cudaFree(c->d_tilemap); c->d_tilemap = nullptr; }
     for (auto& e : c->ev) if (e) cudaEventDestroy(e);
+    if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
+    if (c->ev_ready) cudaEventDestroy(c->ev_ready);
+    if (c->ev_dl) cudaEventDestroy(c->ev_dl);
+    if (c->d_flags_buf) cudaFree(c->d_flags_buf);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
 }
@@ -302,6 +309,7 @@ int spk_mi_scan(spk_ctx* c, const spk_scan_params* pp, spk_scan_result* res) {
     const uint64_t circle = p.circle_size ? p.circle_size : c->L;
     if (p.n_parts == 0) p.n_parts = 1;
     if (p.part_index >= p.n_parts) return fail(c, SPK_E_INVALID, "mi_scan: part_index >= n_parts");
+    if (c->dl_pending) { SPK_CUDA(c, cudaEventSynchronize(c->ev_dl)); c->dl_pending = false; }
     int r = ensure_scan_buffers(c, p.max_edges, p.engine == 1); if (r) return r;
 
     unsigned long long h_counters[8] = {0};
@@ -364,7 +372,7 @@ int spk_mi_scan(spk_ctx* c, const spk_scan_params* pp, spk_scan_result* res) {
     c->h_colmax.resize(c->L);
     SPK_CUDA(c, cudaMemcpyAsync(c->h_colmax.data(), c->d_colmax, (size_t)c->L * 8, cudaMemcpyDeviceToHost, c->stream));
     c->host_edges_n = 0;
-    if (!p.keep_on_device) {
+    if (p.keep_on_device != 1) {
         // pinned mirrors: D2H at full PCIe rate, no page-fault pass over a fresh std::vector
         auto grow = [&](spk_edge*& buf, uint64_t& cap, uint64_t want) -> int {
             if (want <= cap) return SPK_OK;
@@ -377,13 +385,22 @@ int spk_mi_scan(spk_ctx* c, const spk_scan_params* pp, spk_scan_result* res) {
         };
         if ((r = grow(c->hp_edges, c->hp_edges_cap, ne))) return r;
         if ((r = grow(c->hp_wo, c->hp_wo_cap, nw))) return r;
-        if (ne) SPK_CUDA(c, cudaMemcpyAsync(c->hp_edges, c->d_edges, ne * sizeof(spk_edge), cudaMemcpyDeviceToHost, c->stream));
-        if (nw) SPK_CUDA(c, cudaMemcpyAsync(c->hp_wo, c->d_wo, nw * sizeof(spk_edge), cudaMemcpyDeviceToHost, c->stream));
+        // keep_on_device == 2: the copies run on a side stream and overlap whatever the caller launches next (ARACNE on the
+        // device copy); the host pointers are returned now, their contents are valid after spk_wait_download().
+        cudaStream_t cs = c->stream;
+        if (p.keep_on_device == 2) {
+            SPK_CUDA(c, cudaEventRecord(c->ev_ready, c->stream));
+            SPK_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->ev_ready, 0));
+            cs = c->copy_stream;
+        }
+        if (ne) SPK_CUDA(c, cudaMemcpyAsync(c->hp_edges, c->d_edges, ne * sizeof(spk_edge), cudaMemcpyDeviceToHost, cs));
+        if (nw) SPK_CUDA(c, cudaMemcpyAsync(c->hp_wo, c->d_wo, nw * sizeof(spk_edge), cudaMemcpyDeviceToHost, cs));
+        if (p.keep_on_device == 2) { SPK_CUDA(c, cudaEventRecord(c->ev_dl, cs)); c->dl_pending = true; }
         if (p.sort_desc) c->host_edges_n = ne;
     }
     SPK_CUDA(c, cudaStreamSynchronize(c->stream));
     res->colmax = c->h_colmax.data();
-    if (!p.keep_on_device) { res->edges = c->hp_edges; res->edges_wo_gaps = c->hp_wo; }
+    if (p.keep_on_device != 1) { res->edges = c->hp_edges; res->edges_wo_gaps = c->hp_wo; }
     return SPK_OK;
 }
 
@@ -428,13 +445,19 @@ int spk_aracne(spk_ctx* c, const spk_edge* edges, uint64_t n, double eps, uint32
     if (edges == c->hp_edges && n == c->host_edges_n && c->d_edges) {
         // the caller hands back the sorted edge list of the last scan unchanged (the reference's
         // run_ARACNE(network) right after get_MI_network): the device copy is still valid, skip the upload.
-        uint8_t* f0 = nullptr;                                   // (aracne_device owns the context scratch buffer)
-        if (cudaMalloc(&f0, n) != cudaSuccess) { cudaGetLastError(); return fail(c, SPK_E_NOMEM, "aracne: device allocation failed"); }
-        int r0 = cuda_check(c, cudaMemcpyAsync(f0, flags, n, cudaMemcpyHostToDevice, c->stream), "H2D flags");
+        if (c->d_flags_cap < n) {                                // (aracne_device owns the context scratch buffer)
+            if (c->d_flags_buf) { cudaFree(c->d_flags_buf); c->d_flags_buf = nullptr; c->d_flags_cap = 0; }
+            const uint64_t cap = n + n / 4 + 4096;
+            if (cudaMalloc(&c->d_flags_buf, cap) != cudaSuccess) { cudaGetLastError(); return fail(c, SPK_E_NOMEM, "aracne: device allocation failed"); }
+            c->d_flags_cap = cap;
+        }
+        uint8_t* f0 = c->d_flags_buf;
+        // whole list evaluated: every flag is written; a partition leaves the others as the caller passed them
+        int r0 = (nparts <= 1) ? cuda_check(c, cudaMemsetAsync(f0, 0, n, c->stream), "clear flags")
+                               : cuda_check(c, cudaMemcpyAsync(f0, flags, n, cudaMemcpyHostToDevice, c->stream), "H2D flags");
         if (!r0) r0 = aracne_device(c, c->d_edges, n, eps, part, nparts, f0);
         if (!r0) r0 = cuda_check(c, cudaMemcpyAsync(flags, f0, n, cudaMemcpyDeviceToHost, c->stream), "D2H flags");
         if (!r0) r0 = cuda_check(c, cudaStreamSynchronize(c->stream), "sync");
-        cudaFree(f0);
         return r0;
     }
     spk_edge* d = nullptr; uint8_t* f = nullptr;
@@ -449,6 +472,12 @@ int spk_aracne(spk_ctx* c, const spk_edge* edges, uint64_t n, double eps, uint32
     if (!r) r = cuda_check(c, cudaStreamSynchronize(c->stream), "sync");
     cudaFree(d); cudaFree(f);
     return r;
+}
+
+int spk_wait_download(spk_ctx* c) {
+    if (!c) return SPK_E_INVALID;
+    if (c->dl_pending) { SPK_CUDA(c, cudaEventSynchronize(c->ev_dl)); c->dl_pending = false; }
+    return SPK_OK;
 }
 
 int spk_get_timings(spk_ctx* c, spk_timings* out) {

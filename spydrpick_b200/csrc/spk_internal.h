@@ -138,6 +138,10 @@ struct Ctx {
 
     spk_timings tm = {};
     cudaEvent_t ev[8] = {};
+    cudaStream_t copy_stream = nullptr;   // asynchronous result download (keep_on_device = 2)
+    cudaEvent_t ev_ready = nullptr, ev_dl = nullptr;
+    bool dl_pending = false;
+    uint8_t* d_flags_buf = nullptr; uint64_t d_flags_cap = 0;     // spk_aracne's device flags (grow-only)
 };
 
 int fail(Ctx* c, int code, const char* fmt, ...);

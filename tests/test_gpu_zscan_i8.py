@@ -186,3 +186,39 @@ def test_pinned_buffers_and_aracne_device_reuse(ctx):
     # after a new alignment the old pointer must not be trusted
     ctx.set_alignment(sp, pos)
     assert np.array_equal(ctx.aracne(copy), f_copy)
+
+
+def test_async_download_overlaps_aracne(ctx):
+    """keep_on_device = 2: host views are returned while the download runs; aracne() on the view uses the
+    device copy; after wait_download() the views equal the synchronous result."""
+    from spydrpick_b200.capi import pinned_empty
+    s, pos, _ = generate_alignment(150, 2000, seed=11)
+    ctx.set_alignment(s, pos)
+    ctx.set_weights(orc.weights_from_counts(orc.neighbour_counts(s, int(0.9 * 2000))))
+    ref = ctx.mi_scan(0.04)
+    f_ref = ctx.aracne(ref["edges"])
+    r = ctx.mi_scan(0.04, copy=False, async_download=True)
+    buf = pinned_empty(len(ref["edges"]) + 100, np.uint8)
+    buf[:] = 7
+    f = ctx.aracne(r["edges"], out=buf)
+    ctx.wait_download()
+    assert np.array_equal(r["edges"], ref["edges"])
+    assert np.array_equal(np.sort(r["edges_wo_gaps"], order=("i", "j")), np.sort(ref["edges_wo_gaps"], order=("i", "j")))   # unordered list
+    assert np.array_equal(f, f_ref)
+    assert np.all(buf[len(ref["edges"]):] == 7)          # nothing written past n_edges
+    with pytest.raises(ValueError):
+        ctx.mi_scan(0.04, async_download=True)            # needs copy=False
+
+
+def test_candidate_chunks_have_no_effect_on_results(ctx):
+    """the int8 engine reserves candidate slots per warp in chunks (holes are invalid-marked): edge list and
+    candidate count are those of the threshold/colmax rules, independent of chunking and of the seed pass."""
+    s, pos, _ = generate_alignment(200, 6000, seed=13)
+    ctx.set_alignment(s, pos)
+    ctx.set_weights(orc.weights_from_counts(orc.neighbour_counts(s, int(0.9 * 6000))))
+    a = ctx.mi_scan(0.06, max_edges=6000 * 6000 // 2, ld_threshold=300)
+    b = ctx.mi_scan(0.06, max_edges=6000 * 6000 // 2, ld_threshold=300, engine=2)
+    assert np.array_equal(a["edges"], b["edges"])
+    assert np.array_equal(a["colmax"], b["colmax"])
+    assert a["n_candidates"] >= a["n_edges"]
+    assert a["n_candidates"] <= 6000 * 5999 // 2                   # valid candidates only: holes of the reserved chunks are not counted
