@@ -187,6 +187,28 @@ def test_aracne_vs_oracle_random(ctx, trial):
         lo_, hi_ = len(e) * k // 3, len(e) * (k + 1) // 3
         f[lo_:hi_] = fk[lo_:hi_]
     assert np.array_equal(f, orc.aracne_closed(e, EPS))
+    # a caller-supplied list that is NOT sorted by weight: the predicate is order independent (the device path
+    # detects it and orders the adjacency lists itself)
+    perm = rng.permutation(len(e))
+    es = e[perm]
+    for thr in (EPS, 0.0):
+        assert np.array_equal(ctx.aracne(es, thr), orc.aracne_closed(e, thr)[perm])
+
+
+def test_aracne_many_nodes_fallback(ctx):
+    """node ids beyond what the shared-memory neighbourhood bitmap holds: generic search kernel + separate offset table"""
+    rng = np.random.default_rng(77)
+    hubs = rng.integers(0, 2_000_000, 300)
+    a = rng.choice(hubs, 40000); b = rng.choice(hubs, 40000)
+    keep = a != b
+    lo = np.minimum(a, b)[keep]; hi = np.maximum(a, b)[keep]
+    uniq = np.unique(lo.astype(np.uint64) << 32 | hi.astype(np.uint64))
+    e = np.zeros(len(uniq), dtype=EDGE_DTYPE)
+    e["i"] = (uniq >> 32).astype(np.uint32); e["j"] = (uniq & 0xffffffff).astype(np.uint32)
+    e["mi"] = np.round(rng.random(len(uniq)), 4)
+    e = orc.sort_edges(e)
+    for thr in (EPS, 0.0):
+        assert np.array_equal(ctx.aracne(e, thr), orc.aracne_closed(e, thr))
 
 
 def test_error_behaviour(ctx):
