@@ -221,9 +221,16 @@ def run_b200(args):
         sdist.allreduce_colmax(dev_bytes(torch, r["d_colmax"], L * 8, device).view(torch.float64))
         return merged, merged.data_ptr(), total
 
+    def sharded_counts():
+        """K1: every rank evaluates its share of the sample-tile pairs; partial counts are summed over NCCL."""
+        if world == 1:
+            return ctx.neighbour_counts(min_ident, True)
+        from spydrpick_b200 import dist as sdist
+        return sdist.allreduce_neighbour_counts(ctx.neighbour_counts(min_ident, True, part_index=rank, n_parts=world), device)
+
     def step_device():
         """alignment resident in HBM; results stay in HBM."""
-        c = ctx.neighbour_counts(min_ident, True)
+        c = sharded_counts()
         ctx.set_weights(1.0 / c.astype(np.float64))
         r = ctx.mi_scan(threshold, max_edges=max_edges, sort_desc=(world == 1), n_terms=args.n_terms, engine=args.engine,
                         part_index=rank, n_parts=world, keep_on_device=True)
@@ -247,7 +254,7 @@ def run_b200(args):
         """host buffers through the C-ABI: H2D of the alignment (pinned), D2H of edges + flags inside the step."""
         tw = [time.perf_counter()]
         ctx.set_alignment(states_pin, pos_pin); tw.append(time.perf_counter())
-        c = ctx.neighbour_counts(min_ident, True)
+        c = sharded_counts()
         ctx.set_weights(1.0 / c.astype(np.float64)); tw.append(time.perf_counter())
         if world == 1:
             r = ctx.mi_scan(threshold, max_edges=max_edges, sort_desc=True, n_terms=args.n_terms, engine=args.engine,

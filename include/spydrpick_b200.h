@@ -73,6 +73,11 @@ int spk_set_alignment(spk_ctx* ctx, const uint8_t* states, uint32_t n, uint32_t 
  * (StateVector_impl_block_compressed_alignment_storage.hpp:628-659). */
 int spk_neighbour_counts(spk_ctx* ctx, uint64_t min_identical, int emulate_lastblock_quirk,
                          uint64_t* counts /* [n] host */);
+/* Multi-GPU sharding of K1: the sample-tile pairs are dealt round-robin to n_parts partitions; every partition
+ * returns PARTIAL counts whose element-wise sum over the partitions equals spk_neighbour_counts' result
+ * (partition 0 carries each sample's own multiplicity). n_parts <= 1: identical to spk_neighbour_counts. */
+int spk_neighbour_counts_part(spk_ctx* ctx, uint64_t min_identical, int emulate_lastblock_quirk,
+                              uint32_t part_index, uint32_t n_parts, uint64_t* counts /* [n] host */);
 
 /* Replaces the per-sequence set_weight() done by cache_sample_weights
  * (Alignment_utility.hpp:186-258) / MI_Parameters' weight snapshot (include/mi_parameters.hpp:53-59). */

@@ -17,7 +17,7 @@ SPK_OK, SPK_E_INVALID, SPK_E_CUDA, SPK_E_NOMEM, SPK_E_OVERFLOW, SPK_E_PRECISION 
 
 EXPORTS = ["spk_create", "spk_destroy", "spk_last_error", "spk_set_stream", "spk_host_alloc", "spk_host_free",
            "spk_set_alignment",
-           "spk_neighbour_counts", "spk_set_weights", "spk_mi_pairs", "spk_determine_mi_threshold",
+           "spk_neighbour_counts", "spk_neighbour_counts_part", "spk_set_weights", "spk_mi_pairs", "spk_determine_mi_threshold",
            "spk_mi_scan", "spk_outlier_thresholds", "spk_sort_edges", "spk_aracne", "spk_sort_edges_device",
            "spk_aracne_device", "spk_wait_download", "spk_get_timings", "spk_debug_tile_counts", "spk_debug_i8_layout", "spk_debug_i8_tile",
            "spk_version"]
@@ -72,6 +72,7 @@ def load():
     L.spk_set_stream.argtypes = [C.c_void_p, C.c_void_p]
     L.spk_set_alignment.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p]
     L.spk_neighbour_counts.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_void_p]
+    L.spk_neighbour_counts_part.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_uint32, C.c_uint32, C.c_void_p]
     L.spk_set_weights.argtypes = [C.c_void_p, C.c_void_p]
     L.spk_mi_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_double, C.c_void_p]
     L.spk_determine_mi_threshold.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_double, C.c_uint64,
@@ -173,9 +174,11 @@ class Context:
         self._check(self.lib.spk_set_alignment(self.h, _ptr(s), s.shape[0], s.shape[1], _ptr(p)))
         self.n, self.L = s.shape
 
-    def neighbour_counts(self, min_identical, lastblock_quirk=True):
+    def neighbour_counts(self, min_identical, lastblock_quirk=True, part_index=0, n_parts=1):
+        """n_parts > 1: PARTIAL counts of this partition of the sample-tile pairs (sum over partitions = full counts)."""
         out = np.zeros(self.n, dtype=np.uint64)
-        self._check(self.lib.spk_neighbour_counts(self.h, int(min_identical), int(lastblock_quirk), _ptr(out)))
+        self._check(self.lib.spk_neighbour_counts_part(self.h, int(min_identical), int(lastblock_quirk), part_index, n_parts,
+                                                       _ptr(out)))
         return out
 
     def set_weights(self, w):

@@ -174,14 +174,20 @@ int spk_set_alignment(spk_ctx* c, const uint8_t* states, uint32_t n, uint32_t L,
     return SPK_OK;
 }
 
-int spk_neighbour_counts(spk_ctx* c, uint64_t min_identical, int quirk, uint64_t* counts) {
+int spk_neighbour_counts_part(spk_ctx* c, uint64_t min_identical, int quirk, uint32_t part, uint32_t nparts, uint64_t* counts) {
     if (!c || !counts) return SPK_E_INVALID;
     if (!c->d_states) return fail(c, SPK_E_INVALID, "neighbour_counts: no alignment set");
+    if (nparts == 0) nparts = 1;
+    if (part >= nparts) return fail(c, SPK_E_INVALID, "neighbour_counts: part_index >= n_parts");
     SPK_CUDA(c, cudaSetDevice(c->device));
-    int r = hamming_neighbour_counts(c, min_identical, quirk); if (r) return r;
+    int r = hamming_neighbour_counts(c, min_identical, quirk, part, nparts); if (r) return r;
     SPK_CUDA(c, cudaMemcpyAsync(counts, c->d_counts, (size_t)c->n * 8, cudaMemcpyDeviceToHost, c->stream));
     SPK_CUDA(c, cudaStreamSynchronize(c->stream));
     return SPK_OK;
+}
+
+int spk_neighbour_counts(spk_ctx* c, uint64_t min_identical, int quirk, uint64_t* counts) {
+    return spk_neighbour_counts_part(c, min_identical, quirk, 0, 1, counts);
 }
 
 int spk_set_weights(spk_ctx* c, const double* w) {

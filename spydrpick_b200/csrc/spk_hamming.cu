@@ -18,9 +18,11 @@ constexpr int HPAD = HCH + 1; // bank-conflict-free row pitch
 
 __global__ void __launch_bounds__(256)
 hamming_tile_kernel(const uint32_t* __restrict__ planes, uint32_t n, uint32_t L, uint32_t W32,
-                    unsigned long long min_identical, int quirk, unsigned long long* __restrict__ counts) {
+                    unsigned long long min_identical, int quirk, unsigned long long* __restrict__ counts,
+                    uint32_t part, uint32_t n_parts) {
     const uint32_t ti = blockIdx.y, tj = blockIdx.x;
     if (tj < ti) return;
+    if (n_parts > 1 && (ti * gridDim.x + tj) % n_parts != part) return;        // tile pairs dealt round-robin to the partitions
     __shared__ uint32_t sI[3][HT][HPAD];
     __shared__ uint32_t sJ[3][HT][HPAD];
     __shared__ unsigned int cntI[HT], cntJ[HT];
@@ -93,18 +95,18 @@ hamming_tile_kernel(const uint32_t* __restrict__ planes, uint32_t n, uint32_t L,
     }
 }
 
-__global__ void fill_ones_kernel(unsigned long long* counts, uint32_t n) {
+__global__ void fill_ones_kernel(unsigned long long* counts, uint32_t n, unsigned long long v) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) counts[i] = 1ull;     // multiplicity of the sample itself (weights.hpp:205-206)
+    if (i < n) counts[i] = v;        // 1 = multiplicity of the sample itself (weights.hpp:205-206); partition 0 carries it
 }
 
-int hamming_neighbour_counts(Ctx* c, uint64_t min_identical, int quirk) {
+int hamming_neighbour_counts(Ctx* c, uint64_t min_identical, int quirk, uint32_t part, uint32_t n_parts) {
     const uint32_t nt = (c->n + HT - 1) / HT;
     SPK_CUDA(c, cudaEventRecord(c->ev[0], c->stream));
-    fill_ones_kernel<<<(c->n + 255) / 256, 256, 0, c->stream>>>((unsigned long long*)c->d_counts, c->n);
+    fill_ones_kernel<<<(c->n + 255) / 256, 256, 0, c->stream>>>((unsigned long long*)c->d_counts, c->n, part == 0 ? 1ull : 0ull);
     hamming_tile_kernel<<<dim3(nt, nt), 256, 0, c->stream>>>(c->d_planes, c->n, c->L, c->W32,
                                                              (unsigned long long)min_identical, quirk,
-                                                             (unsigned long long*)c->d_counts);
+                                                             (unsigned long long*)c->d_counts, part, n_parts);
     c->tm.kernel_launches += 2;
     SPK_CUDA(c, cudaEventRecord(c->ev[1], c->stream));
     SPK_CUDA(c, cudaEventSynchronize(c->ev[1]));

@@ -156,7 +156,7 @@ int prep_column_stats(Ctx* c, double pseudocount);            // d_marg, d_colst
 int prep_operands(Ctx* c, int n_terms);                       // d_U, d_V
 
 // ---- K1 (spk_hamming.cu)
-int hamming_neighbour_counts(Ctx* c, uint64_t min_identical, int quirk);
+int hamming_neighbour_counts(Ctx* c, uint64_t min_identical, int quirk, uint32_t part = 0, uint32_t n_parts = 1);
 
 // ---- exact fp64 MI (spk_mi_exact.cu)
 int mi_pairs_exact(Ctx* c, const uint32_t* d_pi, const uint32_t* d_pj, uint64_t npairs, double pc, double* d_mi);

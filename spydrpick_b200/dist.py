@@ -29,6 +29,17 @@ def allgather_edges(mine: torch.Tensor, n_edges: int, group=None):
     return merged, sum(counts), counts
 
 
+def allreduce_neighbour_counts(partial, device=None, group=None):
+    """K1 sharded over sample-tile pairs (spk_neighbour_counts_part): element-wise SUM of the per-rank partial counts.
+    partial: numpy uint64 [n] (host). Returns numpy uint64 [n], identical on every rank."""
+    import numpy as np
+    t = torch.from_numpy(partial.astype(np.int64))
+    if device is not None:
+        t = t.to(device)
+    dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+    return t.cpu().numpy().astype(np.uint64)
+
+
 def allreduce_colmax(colmax: torch.Tensor, group=None):
     """In-place element-wise max over ranks of the float64 per-column maxima (MI_solver::join, mi.hpp:355-361)."""
     dist.all_reduce(colmax, op=dist.ReduceOp.MAX, group=group)

@@ -24,6 +24,19 @@ def _worker(rank, world, port, out):
     dist.init_process_group("gloo", rank=rank, world_size=world)
     s, pos, _ = generate_alignment(60, 240, seed=11)
     w = orc.weights_from_counts(orc.neighbour_counts(s, int(0.9 * 240)))
+    # K1 sharded over sample pairs: partial neighbour counts (partition 0 carries the sample itself) summed over ranks
+    counts_full = orc.neighbour_counts(s, int(0.9 * 240))
+    owner = (np.add.outer(np.arange(60) // 8, np.arange(60) // 8 * 3)) % world
+    owner = np.triu(owner, 1); owner = owner + owner.T                       # symmetric owner of the unordered pair
+    partial = np.zeros(60, dtype=np.uint64)
+    for a in range(60):
+        for b_ in range(60):
+            if a != b_ and owner[a, b_] == rank and orc.neighbour_counts(s[[a, b_]], int(0.9 * 240))[0] == 2:
+                partial[a] += 1
+    if rank == 0:
+        partial += 1
+    counts_sum = sdist.allreduce_neighbour_counts(partial)
+    k1_ok = np.array_equal(counts_sum, counts_full.astype(np.uint64))
     thr = 0.05
     full = orc.mi_scan(s, w, pos, threshold=thr, circle_size=240, threads=2)
     # emulate the tile-space partition: rank r owns pairs whose i-block (32 columns) index % world == r
@@ -50,7 +63,8 @@ def _worker(rank, world, port, out):
     flags = sdist.allgather_flag_shards(torch.from_numpy(shard), total).numpy()
     ref = orc.sort_edges(e)
     ok = (total == len(e) and sum(counts) == total and me.tobytes() == ref.tobytes()
-          and np.array_equal(flags, orc.aracne_closed(ref)) and np.allclose(cm.numpy(), full["colmax"], rtol=1e-12))
+          and np.array_equal(flags, orc.aracne_closed(ref)) and np.allclose(cm.numpy(), full["colmax"], rtol=1e-12)
+          and k1_ok)
     out[rank] = bool(ok)
     dist.destroy_process_group()
 

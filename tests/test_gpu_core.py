@@ -195,6 +195,22 @@ def test_aracne_vs_oracle_random(ctx, trial):
         assert np.array_equal(ctx.aracne(es, thr), orc.aracne_closed(e, thr)[perm])
 
 
+def test_neighbour_counts_partitions_sum_to_full(ctx):
+    """K1 sharding (spk_neighbour_counts_part): partial counts over 1, 2, 3 and 5 partitions add up to the full result."""
+    s, pos, _ = generate_alignment(300, 1000, seed=21)
+    ctx.set_alignment(s, pos)
+    full = ctx.neighbour_counts(int(0.9 * 1000), True)
+    assert np.array_equal(full, orc.neighbour_counts(s, int(0.9 * 1000), True))
+    for parts in (2, 3, 5):
+        tot = np.zeros_like(full)
+        for k in range(parts):
+            tot += ctx.neighbour_counts(int(0.9 * 1000), True, part_index=k, n_parts=parts)
+        assert np.array_equal(tot, full)
+    from spydrpick_b200 import SpkError
+    with pytest.raises(SpkError):
+        ctx.neighbour_counts(900, True, part_index=3, n_parts=3)
+
+
 def test_aracne_many_nodes_fallback(ctx):
     """node ids beyond what the shared-memory neighbourhood bitmap holds: generic search kernel + separate offset table"""
     rng = np.random.default_rng(77)
