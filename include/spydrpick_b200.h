@@ -174,6 +174,7 @@ typedef struct {
     float pairs_ms;                         /* K2b kernel */
     uint64_t gemm_tiles, kernel_launches;   /* tiles processed by the last scan; kernels launched since create */
     uint64_t gemm_pairs;                    /* column pairs covered by those tiles (incl. padding / masked diagonal halves) */
+    float    seed_ms;                       /* int8 engine: the colmax seed launch, included in gemm_ms (main pass = gemm_ms - seed_ms) */
 } spk_timings;
 int spk_get_timings(spk_ctx* ctx, spk_timings* out);
 

@@ -39,7 +39,7 @@ class ScanResult(C.Structure):
 class Timings(C.Structure):
     _fields_ = [(k, C.c_float) for k in ("upload_ms", "prep_ms", "hamming_ms", "expand_ms", "stats_ms", "gemm_ms",
                                         "refine_ms", "compact_ms", "sort_ms", "aracne_build_ms", "aracne_ms", "pairs_ms")] + \
-               [("gemm_tiles", C.c_uint64), ("kernel_launches", C.c_uint64), ("gemm_pairs", C.c_uint64)]
+               [("gemm_tiles", C.c_uint64), ("kernel_launches", C.c_uint64), ("gemm_pairs", C.c_uint64), ("seed_ms", C.c_float)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

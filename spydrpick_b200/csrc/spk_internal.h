@@ -127,7 +127,7 @@ struct Ctx {
     // weight-grouped bit planes for the fp64 kernels (spk_mi_exact.cu): samples are ordered by distinct weight
     // value, every group padded to whole 32-bit words, so N_ab = sum_w gval[w] * popc(Bi_a[w] & Bj_b[w]).
     uint32_t* d_gbits = nullptr;          // [L_pad][5][g_NW] one bit plane per (column, state)
-    double*   d_gval = nullptr;           // [g_NW] weight of the samples of word w (0 for padding words)
+    double*   d_gval = nullptr; uint32_t g_nw_cap = 0;           // [g_NW] weight of the samples of word w (0 for padding words)
     double*   d_gmarg = nullptr;          // [L_pad][5] fp64 weighted marginals summed the same way
     int32_t*  d_gslot = nullptr;          // [g_NW*32] sample index per bit slot, -1 = padding
     double*   d_gH = nullptr;             // [L_pad][5] marginal entropy sum_a p_a ln p_a for partner #states 1..5

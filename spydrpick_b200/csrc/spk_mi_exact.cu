@@ -86,7 +86,9 @@ __global__ void __launch_bounds__(128)
 gbits_build_kernel(const uint8_t* __restrict__ colmajor, const int32_t* __restrict__ gslot, const double* __restrict__ gval,
                    uint32_t* __restrict__ gbits, double* __restrict__ gmarg, uint32_t L, uint32_t n_pad, uint32_t NW) {
     // one CTA per column; a warp builds one 32-sample word per iteration: lane b gathers the state of slot 32w+b
-    // (the column's n_pad bytes are L1-resident) and five ballots give the five plane words.
+    // (the column's n_pad bytes are L1-resident) and five ballots give the five plane words, staged in shared
+    // memory so that the column's 5 x NW words leave in one contiguous, coalesced burst.
+    extern __shared__ uint32_t planes_sm[];                  // [NSTATES][NW]
     __shared__ double red[4][NSTATES];
     const uint32_t c = blockIdx.x, lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
     const uint8_t* col = colmajor + (size_t)c * n_pad;
@@ -98,13 +100,15 @@ gbits_build_kernel(const uint8_t* __restrict__ colmajor, const int32_t* __restri
 #pragma unroll
         for (int a = 0; a < NSTATES; ++a) {
             const uint32_t pl = __ballot_sync(0xffffffffu, x == (uint32_t)a);
-            if (lane == (uint32_t)a) { gbits[((size_t)c * NSTATES + a) * NW + w] = pl; m[a] += v * (double)__popc(pl); }
+            if (lane == (uint32_t)a) { planes_sm[a * NW + w] = pl; m[a] += v * (double)__popc(pl); }
         }
     }
     // lane a of every warp holds that warp's partial marginal of state a
 #pragma unroll
     for (int a = 0; a < NSTATES; ++a) if (lane == (uint32_t)a) red[wid][a] = m[a];
     __syncthreads();
+    uint32_t* out = gbits + (size_t)c * NSTATES * NW;
+    for (uint32_t k = threadIdx.x; k < NSTATES * NW; k += blockDim.x) out[k] = planes_sm[k];
     if (threadIdx.x < NSTATES) gmarg[(size_t)c * NSTATES + threadIdx.x] = red[0][threadIdx.x] + red[1][threadIdx.x] + red[2][threadIdx.x] + red[3][threadIdx.x];
 }
 
@@ -656,7 +660,7 @@ void mi_exact_free(Ctx* c) {
     if (c->d_gmarg) { cudaFree(c->d_gmarg); c->d_gmarg = nullptr; }
     if (c->d_gslot) { cudaFree(c->d_gslot); c->d_gslot = nullptr; }
     if (c->d_gH) { cudaFree(c->d_gH); c->d_gH = nullptr; }
-    c->g_cap_words = 0; c->g_NW = 0; c->g_state = 0; c->g_pc = -1.0;
+    c->g_cap_words = 0; c->g_NW = 0; c->g_state = 0; c->g_pc = -1.0; c->g_nw_cap = 0;
 }
 
 static int ensure_gh(Ctx* c, double pc) {
@@ -702,14 +706,22 @@ static int ensure_grouped(Ctx* c, double pc) {
         }
         c->g_cap_words = words;
     }
-    if (c->d_gval) { cudaFree(c->d_gval); c->d_gval = nullptr; }
-    if (c->d_gslot) { cudaFree(c->d_gslot); c->d_gslot = nullptr; }
-    if (cudaMalloc(&c->d_gval, (size_t)NW * 8) != cudaSuccess || cudaMalloc(&c->d_gslot, (size_t)NW * 32 * 4) != cudaSuccess) {
-        cudaGetLastError(); return fail(c, SPK_E_NOMEM, "grouped bit planes: allocation failed");
+    if (NW > c->g_nw_cap || !c->d_gval || !c->d_gslot) {               // grow-only (cudaFree synchronises the device)
+        if (c->d_gval) { cudaFree(c->d_gval); c->d_gval = nullptr; }
+        if (c->d_gslot) { cudaFree(c->d_gslot); c->d_gslot = nullptr; }
+        c->g_nw_cap = 0;
+        const uint32_t cap = NW + NW / 4 + 16;
+        if (cudaMalloc(&c->d_gval, (size_t)cap * 8) != cudaSuccess || cudaMalloc(&c->d_gslot, (size_t)cap * 32 * 4) != cudaSuccess) {
+            cudaGetLastError(); return fail(c, SPK_E_NOMEM, "grouped bit planes: allocation failed");
+        }
+        c->g_nw_cap = cap;
     }
     SPK_CUDA(c, cudaMemcpyAsync(c->d_gval, val.data(), (size_t)NW * 8, cudaMemcpyHostToDevice, c->stream));
     SPK_CUDA(c, cudaMemcpyAsync(c->d_gslot, slot.data(), (size_t)NW * 32 * 4, cudaMemcpyHostToDevice, c->stream));
-    gbits_build_kernel<<<c->L_pad, 128, 0, c->stream>>>(c->d_colmajor, c->d_gslot, c->d_gval, c->d_gbits, c->d_gmarg, c->L, c->n_pad, NW);
+    const size_t gsm = (size_t)NSTATES * NW * 4;
+    if (gsm > 200 * 1024) { c->g_state = 2; return SPK_OK; }        // one column's planes must fit shared memory
+    if (gsm > 48 * 1024) SPK_CUDA(c, cudaFuncSetAttribute(gbits_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsm));
+    gbits_build_kernel<<<c->L_pad, 128, gsm, c->stream>>>(c->d_colmajor, c->d_gslot, c->d_gval, c->d_gbits, c->d_gmarg, c->L, c->n_pad, NW);
     c->tm.kernel_launches += 1;
     SPK_CUDA(c, cudaGetLastError());
     SPK_CUDA(c, cudaStreamSynchronize(c->stream));                   // slot / val are host temporaries

@@ -1034,6 +1034,8 @@ int mi_i8_filter(Ctx* c, const spk_scan_params& p, double band, uint64_t circle)
     // running maximum close to its final value before the main pass. Without it the open-column rule (candidates within
     // `band` of a column's running maximum while that maximum is below thr + band) fires on every record of a rising
     // maximum: measured 6.6 M extra candidates and 5.5 ms of slow-path epilogue per launch at 3000 x 100000.
+    bool seeded = false;
+    c->tm.seed_ms = 0.f;
     if (i8_use_seed() && total_chunks >= 64ull * I8_SEED_STRIDE) {
         std::vector<unsigned long long> seed;
         for (uint32_t sr = 0; sr < n_sr; ++sr)
@@ -1045,6 +1047,8 @@ int mi_i8_filter(Ctx* c, const spk_scan_params& p, double band, uint64_t circle)
             sp.seed_chunks = d_prefix + n_sr + 1;
             sp.n_local_slots = (unsigned long long)seed.size() * (gp.pair ? I8_SUPER / 2 : I8_SUPER);
             r = i8_launch(c, sp); if (r) return r;
+            seeded = true;
+            SPK_CUDA(c, cudaEventRecord(c->ev[7], c->stream));
             SPK_CUDA(c, cudaMemsetAsync(c->d_counters + 5, 0, sizeof(unsigned long long), c->stream));   // rewind the tile cursor
         }
     }
@@ -1052,6 +1056,7 @@ int mi_i8_filter(Ctx* c, const spk_scan_params& p, double band, uint64_t circle)
     SPK_CUDA(c, cudaEventRecord(c->ev[3], c->stream));
     SPK_CUDA(c, cudaEventSynchronize(c->ev[3]));
     SPK_CUDA(c, cudaEventElapsedTime(&c->tm.gemm_ms, c->ev[2], c->ev[3]));
+    if (seeded) SPK_CUDA(c, cudaEventElapsedTime(&c->tm.seed_ms, c->ev[2], c->ev[7]));
     unsigned long long tiles = 0, pairs = 0;
     auto width = [&](uint32_t t) { return t >= c->i8.tile_start[2] ? 32u : (t >= c->i8.tile_start[1] ? 64u : 128u); };
     for (unsigned long long lq = 0; lq < local_chunks; ++lq) {
