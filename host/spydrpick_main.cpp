@@ -435,6 +435,7 @@ int main(int argc, char** argv) {
     spk_scan_params sp; std::memset(&sp, 0, sizeof sp);
     sp.threshold = mi_threshold; sp.pseudocount = o.mi_pseudocount; sp.ld_threshold = o.ld_threshold; sp.linear_genome = o.linear_genome ? 1 : 0;
     sp.circle_size = 0; sp.max_edges = o.mi_values ? 3 * o.mi_values + 65536 : 0; sp.sort_desc = 1; sp.engine = o.engine; sp.n_parts = 1;
+    sp.keep_on_device = 2;       // the host copies of the edge lists run on a side stream while ARACNE works on the device copy
     spk_scan_result res;
     check(ctx, spk_mi_scan(ctx, &sp, &res), "MI scan");
     double outlier_thr = 0, extreme_thr = 0;
@@ -444,18 +445,22 @@ int main(int argc, char** argv) {
                              << " (" << lap.lap() << " s)\n";
 
     // -- ARACNE (src/SpydrPick.cpp:406-421)
-    std::vector<uint8_t> flags(res.n_edges, 0);
+    void* flag_mem = nullptr;
+    if (spk_host_alloc((size_t)std::max<uint64_t>(res.n_edges, 1), &flag_mem) != SPK_OK) die("could not allocate pinned host memory for the ARACNE flags");
+    uint8_t* flags = (uint8_t*)flag_mem;
+    std::memset(flags, 0, (size_t)res.n_edges);
     if (!o.no_aracne && res.n_edges) {
-        check(ctx, spk_aracne(ctx, res.edges, res.n_edges, o.aracne_edge_threshold, 0, 1, flags.data()), "ARACNE");
-        if (o.verbose) { uint64_t nd = 0; for (uint8_t f : flags) nd += f; std::cout << "SpydrPick: ARACNE keeps " << nd << " direct edges (" << lap.lap() << " s)\n"; }
+        check(ctx, spk_aracne(ctx, res.edges, res.n_edges, o.aracne_edge_threshold, 0, 1, flags), "ARACNE");
+        if (o.verbose) { uint64_t nd = 0; for (uint64_t e = 0; e < res.n_edges; ++e) nd += flags[e]; std::cout << "SpydrPick: ARACNE keeps " << nd << " direct edges (" << lap.lap() << " s)\n"; }
     }
+    check(ctx, spk_wait_download(ctx), "edge download");          // res.edges / res.edges_wo_gaps are complete from here on
 
     // -- outputs (src/SpydrPick.cpp:424-480)
     const std::string couplings = prefix + ".spydrpick_couplings." + std::to_string(o.output_indexing_base) + "-based";
     const std::string edges_file = unique_name(couplings + "." + std::to_string(res.n_edges) + "edges");
-    write_edges(edges_file, res.edges, flags.data(), res.n_edges, A, o);
+    write_edges(edges_file, res.edges, flags, res.n_edges, A, o);
     const std::string outliers_file = unique_name(couplings + ".outliers");
-    const uint64_t n_out = write_outliers(outliers_file, res.edges, flags.data(), res.n_edges, res.edges_wo_gaps, res.n_wo_gaps, outlier_thr, extreme_thr, A, o);
+    const uint64_t n_out = write_outliers(outliers_file, res.edges, flags, res.n_edges, res.edges_wo_gaps, res.n_wo_gaps, outlier_thr, extreme_thr, A, o);
     if (o.verbose) std::cout << "SpydrPick: wrote \"" << edges_file << "\" and \"" << outliers_file << "\" (" << n_out << " outliers; " << lap.lap() << " s)\n";
     if (o.verbose) {
         spk_timings tm; if (spk_get_timings(ctx, &tm) == SPK_OK)
@@ -465,5 +470,6 @@ int main(int argc, char** argv) {
     }
     spk_destroy(ctx);
     spk_host_free(A.states);
+    spk_host_free(flag_mem);
     return EXIT_SUCCESS;
 }
