@@ -37,12 +37,18 @@ def parse_args():
     ap.add_argument("--L", type=int, default=100000)
     ap.add_argument("--seed", type=int, default=20260102)
     ap.add_argument("--n-terms", type=int, default=0)
-    ap.add_argument("--engine", type=int, default=0, help="0/3 = int8 compact one-hot GEMM (default), 2 = dense bf16 GEMM")
+    ap.add_argument("--engine", type=int, default=0, help="0 = default int8 engine (= 4), 3 = int8 compact one-hot GEMM with {hi, lo} 16-bit weight rows, 4 = factorised byte weights (half the tensor work), 2 = dense bf16 GEMM")
     ap.add_argument("--mi-values", type=int, default=0, help="saved pairs target (0 = min(1e7, 100*L))")
     ap.add_argument("--cpu-sample-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
+
+
+# from the committed ncu --set full captures of the main-pass launch at 3000 x 100000 (profiles/r01_ncu_full_summary.csv):
+# dram__bytes_read.sum + dram__bytes_write.sum per launch, sm__pipe_tensor_cycles_active %, per int8 engine
+NCU_TRAFFIC = {3: 52.2e9}
+NCU_TENSOR_PCT = {3: 90.4}
 
 
 def peaks():
@@ -335,13 +341,13 @@ def run_b200(args):
     # tile / pair counts refer to; the roofline is that of the main-pass launch
     k_ms = tm["gemm_ms"] - tm.get("seed_ms", 0.0)
     achieved = flops / (k_ms / 1e3) / 1e12 if k_ms > 0 else 0.0
-    i8 = args.engine in (0, 3)
+    i8 = args.engine in (0, 3, 4)
     n_pad = (n + 127) // 128 * 128
     executed = 2.0 * 128 * 256 * n_pad * tiles * (1 if i8 else (args.n_terms or 2))   # tensor ops actually issued
     executed_tops = executed / (k_ms / 1e3) / 1e12 if k_ms > 0 else 0.0
     # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch from the committed ncu --set full capture
     # (profiles/r01_ncu_full_summary.csv); only valid for the workload it was captured on
-    traffic = 52.2e9 if (i8 and world == 1 and n == 3000 and L == 100000) else None
+    traffic = NCU_TRAFFIC.get(args.engine if args.engine else 4) if (i8 and world == 1 and n == 3000 and L == 100000) else None
     roofline = {"bound": "tensor", "achieved": achieved, "peak": pk["bf16_tflops"], "unit": "TFLOP/s",
                 "frac": achieved / pk["bf16_tflops"], "traffic": traffic,
                 "kernel": "mi_i8_kernel<2> (main pass)" if i8 else "mi_gemm_kernel", "kernel_ms": k_ms, "seed_pass_ms": tm.get("seed_ms", 0.0),
@@ -349,7 +355,7 @@ def run_b200(args):
                 "executed_tops": executed_tops,
                 "executed_frac_of_pipe_peak": executed_tops / (pk["bf16_burst_tflops"] * (2.0 if i8 else 1.0)),
                 "executed_frac_of_nominal_pipe": executed_tops / (4500.0 if i8 else 2250.0),
-                "ncu_tensor_pipe_active_pct": 90.4 if traffic else None,   # main pass of the CTA-pair kernel, profiles/r01_ncu_full_summary.csv
+                "ncu_tensor_pipe_active_pct": NCU_TENSOR_PCT.get(args.engine if args.engine else 4) if traffic else None,   # main pass, profiles/r01_ncu_full_summary.csv
                 "note": ("achieved = SURVEY 8(d)'s algorithmic 32*n flop/pair vs the measured bf16 peak; the int8 compact engine "
                          "issues FEWER tensor ops than that (only the one-hot rows a column needs, u8 x u8 -> s32 at 2x the bf16 "
                          "rate), so frac exceeds 1 -- the honest utilisation figures are executed_frac_of_pipe_peak = issued "
@@ -374,7 +380,7 @@ def run_b200(args):
                 "data": "synthetic",
                 "config": {"workload": "%dx%d synthetic SNP alignment: K1 reweighting + weighted MI scan + sort + ARACNE" % (n, L),
                            "n": n, "L": L, "pairs": pairs_total, "saved_edges": int(ne), "mi_threshold": threshold,
-                           "engine": "int8 compact one-hot" if i8 else "dense bf16 one-hot, n_terms=%d" % (args.n_terms or 2),
+                           "engine": ("int8 compact one-hot, 16-bit weights as {hi, lo} rows" if args.engine == 3 else "int8 compact one-hot, factorised byte weights a*b") if i8 else "dense bf16 one-hot, n_terms=%d" % (args.n_terms or 2),
                            "l2_policy": "inputs (>1.5 GB one-hot operands) larger than L2",
                            "threshold_estimate_s": t_threshold, "parallelism": "tile-space partition x%d + NCCL edge allgather" % world},
                 "clocks": clocks, "gpu_launches": int(launches),

@@ -105,9 +105,13 @@ typedef struct {
     int32_t  sort_desc;        /* 1: edges sorted (weight desc, id asc) = Graph::sort (graph/Graph.hpp:234-242) */
     int32_t  n_terms;          /* engine 2 only: bf16 terms of the weight split, 1..3, 0 = default (2) */
     double   band;             /* filter safety band delta (candidates: mi32 > threshold - band); 0 = default */
-    int32_t  engine;           /* tensor-core filter + fp64 refine: 0 = default (= 3), 3 = int8 compact one-hot GEMM
-                                  (tcgen05 kind::i8, exact s32 counts, 16-bit weights), 2 = dense 4-state bf16 GEMM with
-                                  hi/lo weight split; 1 = fp64 exhaustive (diagnostic, no tensor cores) */
+    int32_t  engine;           /* tensor-core filter + fp64 refine: 0 = default int8 engine (3 or 4);
+                                  3 = int8 compact one-hot GEMM (tcgen05 kind::i8, exact s32 counts), 16-bit weights as
+                                      {hi, lo} byte rows of the N operand;
+                                  4 = the same with factorised weights q = a*b (a in the M operand, b in the N operand):
+                                      half the tensor work per column pair, weights on the coarser byte-product grid;
+                                  2 = dense 4-state bf16 GEMM with hi/lo weight split;
+                                  1 = fp64 exhaustive (diagnostic, no tensor cores) */
     uint32_t part_index;       /* tile-space partition for multi-GPU: this context scans part_index of n_parts */
     uint32_t n_parts;          /* 0 or 1 = whole upper triangle */
     int32_t  keep_on_device;   /* 0: edges copied to pinned host buffers before the call returns;
@@ -187,6 +191,8 @@ int spk_debug_tile_counts(spk_ctx* ctx, uint32_t iblock32, uint32_t jblock64, in
  * class, the permutation (original column per permuted column, 0xffffffff = padding), per-column info
  * (k | kept state codes, 3 bits each from bit 4 | dropped state << 16), quantised 16-bit weights and the
  * weight per quantisation step. perm / info / q / delta may be NULL. */
+/* weight rows of the default int8 engine: 2 = engine 3 ({hi, lo} bytes), 1 = engine 4 (factorised weights) */
+int spk_debug_i8_mode(void);
 int spk_debug_i8_layout(spk_ctx* ctx, uint32_t* ntiles3, uint32_t* col_start3, uint32_t* perm, uint32_t* info,
                         uint64_t perm_cap, uint32_t* q /* [n] */, double* delta);
 /* Raw s32 joint counts (quantised-weight units) of the tile pair (ti <= tj) as produced by the kind::i8

@@ -19,7 +19,7 @@ EXPORTS = ["spk_create", "spk_destroy", "spk_last_error", "spk_set_stream", "spk
            "spk_set_alignment",
            "spk_neighbour_counts", "spk_neighbour_counts_part", "spk_set_weights", "spk_mi_pairs", "spk_determine_mi_threshold",
            "spk_mi_scan", "spk_outlier_thresholds", "spk_sort_edges", "spk_aracne", "spk_sort_edges_device",
-           "spk_aracne_device", "spk_wait_download", "spk_get_timings", "spk_debug_tile_counts", "spk_debug_i8_layout", "spk_debug_i8_tile",
+           "spk_aracne_device", "spk_wait_download", "spk_get_timings", "spk_debug_tile_counts", "spk_debug_i8_mode", "spk_debug_i8_layout", "spk_debug_i8_tile",
            "spk_version"]
 
 
@@ -274,6 +274,10 @@ class Context:
         out = np.zeros((32, 64, 4, 4), dtype=np.float32)
         self._check(self.lib.spk_debug_tile_counts(self.h, ib, jb, n_terms, _ptr(out)))
         return out
+
+    def debug_i8_mode(self):
+        """weight rows of the default int8 engine: 2 = engine 3 ({hi, lo} weight bytes), 1 = engine 4 (factorised weights)"""
+        return int(self.lib.spk_debug_i8_mode())
 
     def debug_i8_layout(self, with_weights=False):
         """int8 compact engine layout: dict(ntiles[3], col_start[3], perm, info[, q, delta])."""

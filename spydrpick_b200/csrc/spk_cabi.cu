@@ -306,11 +306,12 @@ int spk_mi_scan(spk_ctx* c, const spk_scan_params* pp, spk_scan_result* res) {
     if (!(p.pseudocount > 0.0)) return fail(c, SPK_E_INVALID, "mi_scan: pseudocount must be > 0 (0 makes the reference produce NaN via 0*log 0)");
     const int T = p.n_terms ? p.n_terms : 2;
     if (T < 1 || T > 3) return fail(c, SPK_E_INVALID, "mi_scan: n_terms must be 1..3");
-    if (p.engine < 0 || p.engine > 3) return fail(c, SPK_E_INVALID, "mi_scan: engine must be 0..3");
-    const bool use_i8 = (p.engine == 0 || p.engine == 3);
-    // default band: measured filter errors are ~5e-6 (int8 engine), 4e-5 (bf16 T=2), 4e-3 (T=1); when the band is left to
+    if (p.engine < 0 || p.engine > 4) return fail(c, SPK_E_INVALID, "mi_scan: engine must be 0..4");
+    const bool use_i8 = (p.engine == 0 || p.engine == 3 || p.engine == 4);
+    const int i8_wr = p.engine == 3 ? 2 : (p.engine == 4 ? 1 : i8_default_wr());
+    // default band: measured filter errors are ~3e-6 (int8 engine 3), ~1e-5 (engine 4), 4e-5 (bf16 T=2), 4e-3 (T=1); when the band is left to
     // the library and a run's measured error exceeds band/2 the scan is repeated with a wider band (never silently accepted).
-    double band = p.band > 0.0 ? p.band : (use_i8 ? 4e-5 : (T == 1 ? 1e-2 : 2e-4));
+    double band = p.band > 0.0 ? p.band : (use_i8 ? (i8_wr == 2 ? 4e-5 : 2e-4) : (T == 1 ? 1e-2 : 2e-4));
     const bool band_auto = !(p.band > 0.0);
     const uint64_t circle = p.circle_size ? p.circle_size : c->L;
     if (p.n_parts == 0) p.n_parts = 1;
@@ -330,7 +331,7 @@ int spk_mi_scan(spk_ctx* c, const spk_scan_params* pp, spk_scan_result* res) {
         r = mi_scan_exact(c, p, circle); if (r) return r;
     } else {
         if (use_i8) {
-            r = mi_i8_filter(c, p, band, circle); if (r) return r;
+            r = mi_i8_filter(c, p, band, circle, i8_wr); if (r) return r;
         } else {
             r = prep_column_stats(c, p.pseudocount); if (r) return r;
             r = prep_operands(c, T); if (r) return r;
@@ -510,6 +511,8 @@ int spk_debug_tile_counts(spk_ctx* c, uint32_t ib, uint32_t jb, int32_t n_terms,
     cudaFree(d_out);
     return r;
 }
+
+int spk_debug_i8_mode(void) { return i8_default_wr(); }
 
 int spk_debug_i8_layout(spk_ctx* c, uint32_t* ntiles3, uint32_t* col_start3, uint32_t* perm, uint32_t* info, uint64_t perm_cap,
                         uint32_t* q, double* delta) {

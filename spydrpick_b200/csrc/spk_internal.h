@@ -138,6 +138,7 @@ struct Ctx {
 
     spk_timings tm = {};
     cudaEvent_t ev[8] = {};
+    int i8_wr = 0;                         // weight rows the int8 operands / records were prepared for (2 = hi/lo, 1 = factorised)
     cudaStream_t copy_stream = nullptr;   // asynchronous result download (keep_on_device = 2)
     cudaEvent_t ev_ready = nullptr, ev_dl = nullptr;
     bool dl_pending = false;
@@ -175,7 +176,8 @@ int mi_gemm_debug_tile(Ctx* c, uint32_t ib, uint32_t jb, int n_terms, float* d_o
 // ---- K2, int8 compact engine (spk_mi_i8.cu)
 int i8_build_layout(Ctx* c);                                   // after prep_alignment: classes, permutation
 void i8_free(Ctx* c);
-int mi_i8_filter(Ctx* c, const spk_scan_params& p, double band, uint64_t circle);
+int mi_i8_filter(Ctx* c, const spk_scan_params& p, double band, uint64_t circle, int wr);
+int i8_default_wr();
 int mi_i8_debug_tile(Ctx* c, uint32_t ti, uint32_t tj, double pc, uint32_t* d_out);
 
 // ---- graph (spk_graph.cu)

@@ -83,6 +83,8 @@ struct I8Params {
     uint32_t num_kb;                       // K blocks of 128 samples
     uint32_t part, n_parts;
     uint32_t pair;                         // 1: CTA-pair kernel (slot = two vertically adjacent tiles)
+    uint32_t jt;                           // column tiles per B panel: 1 (hi/lo weight rows) or 2 (factorised weights, one row)
+    uint32_t NTJ;                          // number of B panels = NT / jt
     const unsigned long long* seed_chunks; // seed pass: the sampled chunk ids (n_local_slots covers exactly these); nullptr = main pass
     unsigned long long n_local_slots;
     float pcq;                             // pseudocount in quantised-weight units
@@ -92,13 +94,14 @@ struct I8Params {
 };
 
 struct __align__(16) JRec { uint32_t mq[4]; uint32_t smq, k, orig; float cm_lo; };   // cm_lo: running max - band, +inf when closed
-struct I8EpiSmem {                 // column records of one tile, staged by the stager warp one tile ahead
-    JRec jrec[128];
-    unsigned long long jpos[128];
-    float jh[5 * 129];              // H_j table by the i column's number of kept rows
+template <int JMAX>                // JMAX = j columns a B panel can hold: 128 (two weight rows per j row) or 256 (one)
+struct I8EpiSmemT {                // column records of one tile, staged by the stager warp one tile ahead
+    JRec jrec[JMAX];
+    unsigned long long jpos[JMAX];
+    float jh[5 * (JMAX + 1)];       // H_j table by the i column's number of kept rows
     float ih2[2 * 128];             // H_i / 1/Z of the i columns for the two kept-row counts the j class can have
     float iinvz2[2 * 128];
-    uint32_t cmj[128];
+    uint32_t cmj[JMAX];
     uint32_t imq[4 * 128];          // i columns, structure of arrays (lanes read consecutive columns)
     uint32_t imqd[128], ik[128], iorig[128], icm[128];
     unsigned long long ipos[128];
@@ -109,7 +112,7 @@ __device__ __forceinline__ uint32_t i8_class_khi(uint32_t c) { return c == 0u ? 
 
 // local slot -> (ti, tj); SUPER consecutive slots share the B (j) panel
 __device__ __forceinline__ bool i8_slot_to_tile(const I8Params& p, unsigned long long ls, uint32_t& ti, uint32_t& tj) {
-    if (p.debug_out) { ti = p.debug_ti; tj = p.debug_tj; return ls == 0; }
+    if (p.debug_out) { ti = p.debug_ti; tj = p.debug_tj / p.jt; return ls == 0; }
     const uint32_t spc = p.pair ? I8_SUPER / 2 : I8_SUPER;            // slots per chunk (a CTA pair takes two i-tiles per slot)
     const unsigned long long q = p.seed_chunks ? p.seed_chunks[ls / spc] : (ls / spc) * p.n_parts + p.part;
     const uint32_t w = (uint32_t)(ls % spc) << p.pair;
@@ -117,14 +120,15 @@ __device__ __forceinline__ bool i8_slot_to_tile(const I8Params& p, unsigned long
     uint32_t lo = 0, hi = p.n_sr;
     while (hi - lo > 1) { const uint32_t mid = (lo + hi) >> 1; if (p.sr_prefix[mid] <= q) lo = mid; else hi = mid; }
     ti = lo * I8_SUPER + w;
-    tj = lo * I8_SUPER + (uint32_t)(q - p.sr_prefix[lo]);
-    return ti < p.NT && tj < p.NT && ti <= tj;
+    tj = lo * (I8_SUPER / p.jt) + (uint32_t)(q - p.sr_prefix[lo]);           // B panel index: column tiles jt*tj .. jt*tj + jt-1
+    return ti < p.NT && tj < p.NTJ && ti <= p.jt * tj + (p.jt - 1u);
 }
 __device__ __forceinline__ uint32_t i8_tile_class(const I8Params& p, uint32_t t) {
     return (t >= p.tile_start[2]) ? 2u : (t >= p.tile_start[1]) ? 1u : 0u;
 }
 
 template <int W> __device__ __forceinline__ void i8_tmem_ld(uint32_t taddr, uint32_t* r);
+template <> __device__ __forceinline__ void i8_tmem_ld<8>(uint32_t taddr, uint32_t* r) { tmem_ld8_u32(taddr, r); tmem_ld_wait(); }
 template <> __device__ __forceinline__ void i8_tmem_ld<16>(uint32_t taddr, uint32_t* r) { tmem_ld16_u32(taddr, r); tmem_ld_wait(); }
 template <> __device__ __forceinline__ void i8_tmem_ld<32>(uint32_t taddr, uint32_t* r) {
     tmem_ld16_u32(taddr, r); tmem_ld16_u32(taddr + 16u, r + 16); tmem_ld_wait();
@@ -135,7 +139,8 @@ template <> __device__ __forceinline__ void i8_tmem_ld<32>(uint32_t taddr, uint3
 // closed columns carry +inf in cm_lo). Lanes that arrive together and share the j column reduce their
 // maximum with match/redux so a burst emits ~one candidate per warp, not one per lane.
 struct I8OpenRes { float cm_i, cm_i_lo; uint32_t emit; };
-__device__ __noinline__ I8OpenRes i8_open_columns_path(const I8Params& p, I8EpiSmem& sm, float mi32, uint32_t i_local,
+template <int JMAX>
+__device__ __noinline__ I8OpenRes i8_open_columns_path(const I8Params& p, I8EpiSmemT<JMAX>& sm, float mi32, uint32_t i_local,
                                                        uint32_t j_local, uint32_t gcol_j, float cm_i, float cm_i_lo) {
     I8OpenRes res; res.cm_i = cm_i; res.cm_i_lo = cm_i_lo; res.emit = 0u;
     const unsigned long long pos_j = sm.jpos[j_local];
@@ -197,17 +202,19 @@ __device__ __forceinline__ void i8_emit_flush(const I8Params& p, I8Emit& em, uin
 // ---------------------------------------------------------------------------------------------
 // epilogue of one tile for the class pair (KI rows per i column, KJ rows per j column), KI <= KJ
 // ---------------------------------------------------------------------------------------------
-template <int KI, int KJ>
-__device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmem& sm, I8Emit& em, uint32_t tmem_acc, uint32_t q, uint32_t half,
+// WR = weight rows per j row in the N operand: 2 = {hi, lo} bytes of a 16-bit weight, 1 = one byte b_s (A carries a_s)
+template <int KI, int KJ, int WR>
+__device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmemT<256 / WR>& sm, I8Emit& em, uint32_t tmem_acc, uint32_t q, uint32_t half,
                                                  uint32_t lane, bool diag, uint32_t ci0, uint32_t cj0) {
 #if SPK_I8_TWO_PHASE == 1
-    constexpr int LOADW = (KI == 1 && KJ == 1) ? 16 : 32;   // TMEM columns per load (>= 2 independent pairs per lane where possible)
+    constexpr int LOADW = ((KI == 1 && KJ == 1) ? 16 : 32) / (3 - WR);   // TMEM columns per load (>= 2 independent pairs per lane where possible)
 #else
-    constexpr int LOADW = (KI == 4) ? 32 : 16;
+    constexpr int LOADW = ((KI == 4) ? 32 : 16) / (3 - WR);              // WR = 1: half the columns hold the same number of j rows
 #endif
-    constexpr int NJ = LOADW / (2 * KJ);               // j columns per load
+    constexpr int NJ = LOADW / (WR * KJ);              // j columns per load
     constexpr int PPL = NJ / KI;                       // pairs per lane per load
-    constexpr int WJ = 128 / KJ;
+    constexpr int JMAX = 256 / WR;
+    constexpr int WJT = 128 / KJ;                      // j columns of one 128-row column tile (debug output geometry)
     static_assert(PPL >= 1, "tile geometry");
     const uint32_t row = q * 32u + lane;
     const uint32_t i_local = row / KI, g = lane % KI;
@@ -225,7 +232,7 @@ __device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmem& s
     constexpr uint32_t KJ_HI = (KJ == 1) ? 1u : (KJ == 2 ? 2u : 4u);              // j columns of this class keep KJ_HI or (KJ != 2) one row fewer
     const float invZ_lo = sm.iinvz2[i_local], invZ_hi = sm.iinvz2[128 + i_local];
     const float ih_lo = sm.ih2[i_local], ih_hi = sm.ih2[128 + i_local];
-    const float* jh_row = sm.jh + ki * 129u;
+    const float* jh_row = sm.jh + ki * (uint32_t)(JMAX + 1);
     const float ln2 = 0.69314718055994530942f;
 
 #pragma unroll 1
@@ -244,7 +251,8 @@ __device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmem& s
 #pragma unroll
         for (int jj = 0; jj < NJ; ++jj)
 #pragma unroll
-            for (int b = 0; b < KJ; ++b) v[jj * KJ + b] = (r[jj * 2 * KJ + b] << 8) + r[jj * 2 * KJ + KJ + b];
+            for (int b = 0; b < KJ; ++b)
+                v[jj * KJ + b] = (WR == 2) ? (r[jj * 2 * KJ + b] << 8) + r[jj * 2 * KJ + KJ + b] : r[jj * KJ + b];
         // transpose inside the KI-lane group: afterwards v[(s*KI + a)*KJ + b] = N[a][b] of j = s*KI + g
         if (KI == 2) {
 #pragma unroll
@@ -286,14 +294,16 @@ __device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmem& s
         bool need = false; (void)need;
 #pragma unroll
         for (int s = 0; s < PPL; ++s) {
-            const uint32_t j_local = col0 / (2 * KJ) + s * KI + g;
+            const uint32_t j_local = col0 / (WR * KJ) + s * KI + g;
             mi_arr[s] = __int_as_float(0x7fc00000);
             if (p.debug_out) {
+                if (j_local / WJT == p.debug_tj % p.jt) {
 #pragma unroll
-                for (int a = 0; a < KI; ++a)
+                    for (int a = 0; a < KI; ++a)
 #pragma unroll
-                    for (int b = 0; b < KJ; ++b)
-                        p.debug_out[(((size_t)i_local * WJ + j_local) * KI + a) * KJ + b] = v[(s * KI + a) * KJ + b];
+                        for (int b = 0; b < KJ; ++b)
+                            p.debug_out[(((size_t)i_local * WJT + j_local % WJT) * KI + a) * KJ + b] = v[(s * KI + a) * KJ + b];
+                }
                 continue;
             }
             const JRec jr = sm.jrec[j_local];
@@ -351,7 +361,7 @@ __device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmem& s
         // phase 2: threshold / open-column tests and candidate emission
 #pragma unroll
         for (int s = 0; s < PPL; ++s) {
-            const uint32_t j_local = col0 / (2 * KJ) + s * KI + g;
+            const uint32_t j_local = col0 / (WR * KJ) + s * KI + g;
 #endif
             const uint32_t pj = cj0 + j_local;
             const float mi32 = mi_arr[s];
@@ -413,14 +423,20 @@ __device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmem& s
 // issued by the pair's leader: each CTA stages its own A panel and only HALF of the shared B panel, so the
 // L2 -> SM operand traffic per tile falls from 48 KB to 32 KB per 128 samples. (ncu on the 1-CTA kernel:
 // lts2xbar 71 % busy at 69 % tensor-pipe activity -- the L2 feed, not the pipe, was the limiter.)
-template <int NCTA> struct I8Cfg;
-template <> struct I8Cfg<1> { static constexpr uint32_t B_BYTES = 256 * I8_BK, STAGE = I8_A_BYTES + B_BYTES; static constexpr int NSTAGES = 4; };
-template <> struct I8Cfg<2> { static constexpr uint32_t B_BYTES = 128 * I8_BK, STAGE = I8_A_BYTES + B_BYTES; static constexpr int NSTAGES = 6; };
+// WR = 2: the N operand carries the {hi, lo} bytes of a 16-bit weight as two rows per j row (a B panel = one column tile);
+// WR = 1: factorised weights q_s = a_s * b_s, A carries a_s, B carries b_s in ONE row per j row, so a 256-row B panel
+// holds TWO column tiles and every MMA covers twice the pairs (the record buffers double, one operand stage goes).
+template <int NCTA, int WR> struct I8Cfg {
+    static constexpr uint32_t B_BYTES = (NCTA == 2 ? 128u : 256u) * I8_BK, STAGE = I8_A_BYTES + B_BYTES;
+    static constexpr int NSTAGES = (NCTA == 2) ? (WR == 2 ? 6 : 5) : (WR == 2 ? 4 : 3);
+};
 
-template <int NCTA>
+template <int NCTA, int WR>
 __global__ void __launch_bounds__(I8_THREADS, 1)
 mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const I8Params p) {
-    using Cfg = I8Cfg<NCTA>;
+    using Cfg = I8Cfg<NCTA, WR>;
+    using I8EpiSmem = I8EpiSmemT<256 / WR>;
+    constexpr uint32_t JT = 2u / WR;                          // column tiles per B panel
     constexpr bool PAIR = (NCTA == 2);
     constexpr int NST = Cfg::NSTAGES;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -478,7 +494,7 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
     // does THIS CTA have a tile to finish for queue entry (t0, tj)? (pair: the odd CTA idles below the diagonal / past the last tile)
     auto own_valid = [&](uint32_t ti_own, uint32_t tj) {
         if constexpr (!PAIR) return true;
-        return ti_own < p.NT && ti_own <= tj && (!p.debug_out || ti_own == p.debug_ti);
+        return ti_own < p.NT && ti_own <= JT * tj + (JT - 1u) && (!p.debug_out || ti_own == p.debug_ti);
     };
 
     if (warp == 3 + I8_EPI_WARPS) {
@@ -494,7 +510,7 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
             bool debug_done = false;
             while (true) {
                 uint32_t ti = I8_INVALID, tj = 0;
-                if (p.debug_out) { if (!debug_done) { ti = PAIR ? (p.debug_ti & ~1u) : p.debug_ti; tj = p.debug_tj; debug_done = true; } }
+                if (p.debug_out) { if (!debug_done) { ti = PAIR ? (p.debug_ti & ~1u) : p.debug_ti; tj = p.debug_tj / JT; debug_done = true; } }
                 else {
                     while (true) {
                         const unsigned long long ls = atomicAdd(&p.counters[5], 1ull);
@@ -599,10 +615,10 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
             if (!own_valid(ti, tj)) continue;
             const uint32_t buf = it & 1u, ph = (it >> 1) & 1u;
             I8EpiSmem& sm = *(I8EpiSmem*)(sm_base + buf * SM_STRIDE);
-            const uint32_t ci = i8_tile_class(p, ti), cj = i8_tile_class(p, tj);
-            const uint32_t WI = 128u >> ci, WJ = 128u >> cj;
+            const uint32_t ci = i8_tile_class(p, ti), cj = i8_tile_class(p, JT * tj);   // (class tile counts are even: a panel never straddles classes)
+            const uint32_t WI = 128u >> ci, WJ = JT * (128u >> cj);
             const uint32_t ci0 = p.col_start[ci] + (ti - p.tile_start[ci]) * WI;
-            const uint32_t cj0 = p.col_start[cj] + (tj - p.tile_start[cj]) * WJ;
+            const uint32_t cj0 = p.col_start[cj] + (JT * tj - p.tile_start[cj]) * (128u >> cj);
             mbar_wait(&sempty_bar[buf], ph ^ 1u);
             for (uint32_t e = lane; e < WJ; e += 32) {
                 const ColRec8 rc = p.rec[cj0 + e];
@@ -615,7 +631,7 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
                 sm.jrec[e] = jr;
                 sm.jpos[e] = ((unsigned long long)rc.pos_hi << 32) | rc.pos_lo;
 #pragma unroll
-                for (int m = 0; m < 5; ++m) sm.jh[m * 129 + e] = rc.h[m];
+                for (int m = 0; m < 5; ++m) sm.jh[m * (256 / WR + 1) + e] = rc.h[m];
                 sm.cmj[e] = cm;
             }
             const uint32_t klo = i8_class_klo(cj), khi = i8_class_khi(cj);
@@ -659,19 +675,19 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
             if (valid) {
 #endif
                 I8EpiSmem& sm = *(I8EpiSmem*)(sm_base + buf * SM_STRIDE);
-                const uint32_t ci = i8_tile_class(p, ti), cj = i8_tile_class(p, tj);
-                const uint32_t WI = 128u >> ci, WJ = 128u >> cj;
+                const uint32_t ci = i8_tile_class(p, ti), cj = i8_tile_class(p, JT * tj);
+                const uint32_t WI = 128u >> ci;
                 const uint32_t ci0 = p.col_start[ci] + (ti - p.tile_start[ci]) * WI;
-                const uint32_t cj0 = p.col_start[cj] + (tj - p.tile_start[cj]) * WJ;
+                const uint32_t cj0 = p.col_start[cj] + (JT * tj - p.tile_start[cj]) * (128u >> cj);
                 const uint32_t tmem_acc = tmem_base + abuf * 256u;
-                const bool diag = (ti == tj);
+                const bool diag = (ti >= JT * tj);                       // panel touches the diagonal: pairs need pi < pj
                 switch (ci * 3u + cj) {
-                    case 0: i8_epilogue_tile<1, 1>(p, sm, em, tmem_acc, q, half, lane, diag, ci0, cj0); break;
-                    case 1: i8_epilogue_tile<1, 2>(p, sm, em, tmem_acc, q, half, lane, diag, ci0, cj0); break;
-                    case 2: i8_epilogue_tile<1, 4>(p, sm, em, tmem_acc, q, half, lane, diag, ci0, cj0); break;
-                    case 4: i8_epilogue_tile<2, 2>(p, sm, em, tmem_acc, q, half, lane, diag, ci0, cj0); break;
-                    case 5: i8_epilogue_tile<2, 4>(p, sm, em, tmem_acc, q, half, lane, diag, ci0, cj0); break;
-                    default: i8_epilogue_tile<4, 4>(p, sm, em, tmem_acc, q, half, lane, diag, ci0, cj0); break;
+                    case 0: i8_epilogue_tile<1, 1, WR>(p, sm, em, tmem_acc, q, half, lane, diag, ci0, cj0); break;
+                    case 1: i8_epilogue_tile<1, 2, WR>(p, sm, em, tmem_acc, q, half, lane, diag, ci0, cj0); break;
+                    case 2: i8_epilogue_tile<1, 4, WR>(p, sm, em, tmem_acc, q, half, lane, diag, ci0, cj0); break;
+                    case 4: i8_epilogue_tile<2, 2, WR>(p, sm, em, tmem_acc, q, half, lane, diag, ci0, cj0); break;
+                    case 5: i8_epilogue_tile<2, 4, WR>(p, sm, em, tmem_acc, q, half, lane, diag, ci0, cj0); break;
+                    default: i8_epilogue_tile<4, 4, WR>(p, sm, em, tmem_acc, q, half, lane, diag, ci0, cj0); break;
                 }
             }
             // accumulator drained and records consumed: hand both buffers back
@@ -746,11 +762,13 @@ __global__ void i8_colrec_kernel(const uint8_t* __restrict__ colmajor, const uin
     }
 }
 
-// one warp per permuted column; each lane converts 16 consecutive samples per iteration
+// one warp per permuted column; each lane converts 16 consecutive samples per iteration.
+// wr = 2: A = one-hot, B = one-hot x {hi, lo} weight byte (two rows per kept state); wr = 1: A = one-hot x a_s
+// (byte array qhi), B = one-hot x b_s (byte array qlo), one row per kept state at the same row index as in A.
 __global__ void i8_expand_kernel(const uint8_t* __restrict__ colmajor, const uint8_t* __restrict__ qhi, const uint8_t* __restrict__ qlo,
                                  const uint32_t* __restrict__ perm, const uint32_t* __restrict__ info,
                                  uint8_t* __restrict__ A8, uint8_t* __restrict__ B8, uint32_t Lperm, uint32_t n, uint32_t n_pad,
-                                 uint32_t cs1, uint32_t cs2, uint32_t ts1, uint32_t ts2) {
+                                 uint32_t cs1, uint32_t cs2, uint32_t ts1, uint32_t ts2, uint32_t wr) {
     const uint32_t pc = blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32;
     if (pc >= Lperm) return;
     const uint32_t orig = perm[pc];
@@ -762,7 +780,7 @@ __global__ void i8_expand_kernel(const uint8_t* __restrict__ colmajor, const uin
     const uint32_t tstart = cls == 2 ? ts2 : cls == 1 ? ts1 : 0u;
     const uint32_t lc = pc - cstart;
     const size_t rowA = (size_t)128 * tstart + (size_t)lc * kp;
-    const size_t rowB = (size_t)256 * tstart + (size_t)lc * 2 * kp;
+    const size_t rowB = (wr == 2) ? (size_t)256 * tstart + (size_t)lc * 2 * kp : rowA;
     const uint32_t inf = info[pc];
     const uint32_t k = inf & 15u;
     const uint8_t* col = colmajor + (size_t)orig * n_pad;
@@ -778,11 +796,15 @@ __global__ void i8_expand_kernel(const uint8_t* __restrict__ colmajor, const uin
 #pragma unroll
             for (int t = 0; t < 16; ++t) {
                 const bool hit = (x[t] == code) && (s0 + t < n);
-                oa[t] = hit ? 1 : 0; oh[t] = hit ? wh[t] : 0; ol[t] = hit ? wl[t] : 0;
+                oa[t] = hit ? (wr == 2 ? (uint8_t)1 : wh[t]) : (uint8_t)0; oh[t] = hit ? wh[t] : 0; ol[t] = hit ? wl[t] : 0;
             }
             *reinterpret_cast<uint4*>(A8 + (rowA + a) * n_pad + s0) = *reinterpret_cast<const uint4*>(oa);
-            *reinterpret_cast<uint4*>(B8 + (rowB + a) * n_pad + s0) = *reinterpret_cast<const uint4*>(oh);
-            *reinterpret_cast<uint4*>(B8 + (rowB + kp + a) * n_pad + s0) = *reinterpret_cast<const uint4*>(ol);
+            if (wr == 2) {
+                *reinterpret_cast<uint4*>(B8 + (rowB + a) * n_pad + s0) = *reinterpret_cast<const uint4*>(oh);
+                *reinterpret_cast<uint4*>(B8 + (rowB + kp + a) * n_pad + s0) = *reinterpret_cast<const uint4*>(ol);
+            } else {
+                *reinterpret_cast<uint4*>(B8 + (rowB + a) * n_pad + s0) = *reinterpret_cast<const uint4*>(ol);
+            }
         }
     }
 }
@@ -822,8 +844,9 @@ int i8_build_layout(Ctx* c) {
     uint32_t cstart = 0, tstart = 0;
     for (int g = 0; g < 3; ++g) {
         const uint32_t width = 128u >> g;
-        lay.ncols_pad[g] = (lay.ncols[g] + width - 1) / width * width;
-        lay.ntiles[g] = lay.ncols_pad[g] / width;
+        lay.ntiles[g] = (lay.ncols[g] + width - 1) / width;
+        lay.ntiles[g] += lay.ntiles[g] & 1u;                     // even: a 256-row B panel (two column tiles) never straddles classes
+        lay.ncols_pad[g] = lay.ntiles[g] * width;
         lay.col_start[g] = cstart; lay.tile_start[g] = tstart;
         cstart += lay.ncols_pad[g]; tstart += lay.ntiles[g];
     }
@@ -860,12 +883,40 @@ int i8_build_layout(Ctx* c) {
     return SPK_OK;
 }
 
-// 16-bit weight quantisation (host; O(n)), operands, column records
-static int i8_prepare(Ctx* c, double pc) {
+// nearest product a*b (1 <= a, b <= 255) to every target 0..65025: table built once
+static const std::vector<uint16_t>& i8_product_table() {
+    static std::vector<uint16_t> tab;                    // tab[t] = (a << 8) | b with a*b nearest to t (0 for t = 0)
+    if (tab.empty()) {
+        const int T = 255 * 255;
+        std::vector<int> best(T + 1, -1);
+        for (int a = 1; a <= 255; ++a) for (int b = a; b <= 255; ++b) best[a * b] = (a << 8) | b;
+        std::vector<uint16_t> t2(T + 1, 0);
+        int last = -1;
+        std::vector<int> prev(T + 1, -1), next(T + 1, -1);
+        for (int t = 0; t <= T; ++t) { if (best[t] >= 0) last = t; prev[t] = last; }
+        last = -1;
+        for (int t = T; t >= 0; --t) { if (best[t] >= 0) last = t; next[t] = last; }
+        for (int t = 1; t <= T; ++t) {
+            const int lo = prev[t], hi = next[t];
+            const int pick = (lo < 1) ? hi : (hi < 0 ? lo : ((t - lo) <= (hi - t) ? lo : hi));
+            t2[t] = (uint16_t)best[pick];
+        }
+        tab.swap(t2);
+    }
+    return tab;
+}
+
+// weight quantisation (host; O(n)), operands, column records.
+// wr = 2: q_s = round(w_s / w_max * 65535), the N operand carries the two bytes of q_s (exact 16-bit grid);
+// wr = 1: q_s = a_s * b_s, the nearest product of two bytes to w_s / w_max * M (M chosen among a few scales for the
+//         smallest total rounding error): the M operand carries a_s, the N operand b_s -- half the N rows, i.e.
+//         half the tensor work per column pair, on a slightly coarser (but still exact-integer) weight grid.
+static int i8_prepare(Ctx* c, double pc, int wr) {
     const uint32_t n = c->n, n_pad = c->n_pad;
     if (n > 65536u) return fail(c, SPK_E_INVALID, "int8 engine supports at most 65536 samples (s32 accumulators); use engine 2");
     if (c->i8.NT == 0) return fail(c, SPK_E_INVALID, "int8 engine: no layout (set_alignment first)");
     uint8_t* d_qhi = (uint8_t*)(c->d_q + n_pad); uint8_t* d_qlo = d_qhi + n_pad;
+    if (c->i8_wr != wr) { c->i8_weights_valid = false; c->i8_wr = wr; }
     if (!c->i8_weights_valid) {
         if (c->h_w.size() != n) return fail(c, SPK_E_INVALID, "int8 engine: weights not set");
         double wmax = 0.0;
@@ -876,11 +927,36 @@ static int i8_prepare(Ctx* c, double pc) {
         if (!(wmax > 0.0)) return fail(c, SPK_E_INVALID, "int8 engine: all weights are zero");
         std::vector<uint32_t> q(n_pad, 0u); std::vector<uint8_t> qb(2 * (size_t)n_pad, 0);
         unsigned long long tot = 0;
-        for (uint32_t s = 0; s < n; ++s) {
-            const uint32_t v = (uint32_t)std::llround(c->h_w[s] / wmax * 65535.0);
-            q[s] = v; qb[s] = (uint8_t)(v >> 8); qb[n_pad + s] = (uint8_t)(v & 255u); tot += v;
+        if (wr == 2) {
+            for (uint32_t s = 0; s < n; ++s) {
+                const uint32_t v = (uint32_t)std::llround(c->h_w[s] / wmax * 65535.0);
+                q[s] = v; qb[s] = (uint8_t)(v >> 8); qb[n_pad + s] = (uint8_t)(v & 255u); tot += v;
+            }
+            c->i8_delta = wmax / 65535.0;
+        } else {
+            const std::vector<uint16_t>& tab = i8_product_table();
+            double best_err = 1e300, best_M = 65025.0;
+            for (int trial = 0; trial < 24; ++trial) {
+                const double M = 65025.0 * (1.0 - 0.02 * trial);                  // scales between 52 % and 100 % of the byte-product range
+                double err = 0.0;
+                for (uint32_t s = 0; s < n; ++s) {
+                    const double t = c->h_w[s] / wmax * M;
+                    const long ti = std::min<long>(65025, std::llround(t));
+                    const uint16_t ab = tab[ti];
+                    const double qv = (double)(ab >> 8) * (double)(ab & 255u);
+                    err += std::fabs(qv - t) / M;                                  // in units of w_max
+                }
+                if (err < best_err) { best_err = err; best_M = M; }
+            }
+            for (uint32_t s = 0; s < n; ++s) {
+                const long ti = std::min<long>(65025, std::llround(c->h_w[s] / wmax * best_M));
+                const uint16_t ab = tab[ti];
+                const uint32_t a = ab >> 8, b = ab & 255u;
+                q[s] = a * b; qb[s] = (uint8_t)a; qb[n_pad + s] = (uint8_t)b; tot += q[s];
+            }
+            c->i8_delta = wmax / best_M;
         }
-        c->i8_delta = wmax / 65535.0; c->i8_wq_total = tot;
+        c->i8_wq_total = tot;
         SPK_CUDA(c, cudaMemcpyAsync(c->d_q, q.data(), (size_t)n_pad * 4, cudaMemcpyHostToDevice, c->stream));
         SPK_CUDA(c, cudaMemcpyAsync(d_qhi, qb.data(), (size_t)n_pad * 2, cudaMemcpyHostToDevice, c->stream));
         SPK_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -897,10 +973,10 @@ static int i8_prepare(Ctx* c, double pc) {
             }
         }
         SPK_CUDA(c, cudaMemsetAsync(c->d_A8, 0, rowsA * n_pad, c->stream));
-        SPK_CUDA(c, cudaMemsetAsync(c->d_B8, 0, 2 * rowsA * n_pad, c->stream));
+        SPK_CUDA(c, cudaMemsetAsync(c->d_B8, 0, (size_t)wr * rowsA * n_pad, c->stream));
         i8_expand_kernel<<<(c->i8.Lperm + 7) / 8, 256, 0, c->stream>>>(c->d_colmajor, d_qhi, d_qlo, c->d_i8_perm, c->d_i8_info, c->d_A8, c->d_B8,
                                                                       c->i8.Lperm, n, n_pad, c->i8.col_start[1], c->i8.col_start[2],
-                                                                      c->i8.tile_start[1], c->i8.tile_start[2]);
+                                                                      c->i8.tile_start[1], c->i8.tile_start[2], (uint32_t)wr);
         c->tm.kernel_launches += 1;
         SPK_CUDA(c, cudaGetLastError());
         c->i8_operands_valid = true;
@@ -944,9 +1020,9 @@ static int i8_make_map(Ctx* c, CUtensorMap* map, void* base, uint64_t rows, uint
     return SPK_OK;
 }
 
-template <int NCTA> static size_t i8_smem_bytes() {
-    return (size_t)I8Cfg<NCTA>::NSTAGES * I8Cfg<NCTA>::STAGE + 2 * ((sizeof(I8EpiSmem) + 15) & ~(size_t)15) +
-           (2 * I8Cfg<NCTA>::NSTAGES + 8 + 3 * I8_QDEPTH) * 8 + 16;
+template <int NCTA, int WR> static size_t i8_smem_bytes() {
+    return (size_t)I8Cfg<NCTA, WR>::NSTAGES * I8Cfg<NCTA, WR>::STAGE + 2 * ((sizeof(I8EpiSmemT<256 / WR>) + 15) & ~(size_t)15) +
+           (2 * I8Cfg<NCTA, WR>::NSTAGES + 8 + 3 * I8_QDEPTH) * 8 + 16;
 }
 
 // SPYDRPICK_B200_I8_PAIR=0 selects the one-CTA-per-tile kernel (A/B comparisons); default: CTA pairs
@@ -958,32 +1034,37 @@ static bool i8_use_pair() {
 
 // SPYDRPICK_B200_I8_SEED=0 disables the colmax seed pass (A/B comparisons)
 constexpr uint32_t I8_SEED_STRIDE = 32;
+#ifndef SPK_I8_DEFAULT_WR
+#define SPK_I8_DEFAULT_WR 1
+#endif
+constexpr int I8_DEFAULT_WR = SPK_I8_DEFAULT_WR;
 static bool i8_use_seed() {
     static int v = -1;
     if (v < 0) { const char* e = getenv("SPYDRPICK_B200_I8_SEED"); v = (e && e[0] == '0') ? 0 : 1; }
     return v == 1;
 }
 
-static int i8_launch(Ctx* c, I8Params& gp) {
+template <int WR> static int i8_launch_wr(Ctx* c, I8Params& gp) {
     const bool pair = gp.pair != 0;
     CUtensorMap ma, mb;
     int r = i8_make_map(c, &ma, c->d_A8, (uint64_t)128 * c->i8.NT, c->n_pad, 128); if (r) return r;
-    r = i8_make_map(c, &mb, c->d_B8, (uint64_t)256 * c->i8.NT, c->n_pad, pair ? 128 : 256); if (r) return r;
+    r = i8_make_map(c, &mb, c->d_B8, (uint64_t)(128 * WR) * c->i8.NT, c->n_pad, pair ? 128 : 256); if (r) return r;
     gp.rec = c->d_i8_rec;
     gp.num_kb = c->n_pad / I8_BK;
     gp.NT = c->i8.NT;
+    gp.jt = 2u / WR; gp.NTJ = c->i8.NT / gp.jt;
     for (int g = 0; g < 3; ++g) { gp.tile_start[g] = c->i8.tile_start[g]; gp.col_start[g] = c->i8.col_start[g]; }
     gp.colmax32 = c->d_i8_colmax32;
     gp.counters = c->d_counters;
     const unsigned long long slots = gp.debug_out ? 1ull : gp.n_local_slots;
     if (!pair) {
         const unsigned grid = (unsigned)(slots < (unsigned long long)c->sm_count ? (slots ? slots : 1) : (unsigned long long)c->sm_count);
-        const size_t smem = i8_smem_bytes<1>();
-        SPK_CUDA(c, cudaFuncSetAttribute(mi_i8_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        mi_i8_kernel<1><<<grid, I8_THREADS, smem, c->stream>>>(ma, mb, gp);
+        const size_t smem = i8_smem_bytes<1, WR>();
+        SPK_CUDA(c, cudaFuncSetAttribute(mi_i8_kernel<1, WR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        mi_i8_kernel<1, WR><<<grid, I8_THREADS, smem, c->stream>>>(ma, mb, gp);
     } else {
-        const size_t smem = i8_smem_bytes<2>();
-        SPK_CUDA(c, cudaFuncSetAttribute(mi_i8_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        const size_t smem = i8_smem_bytes<2, WR>();
+        SPK_CUDA(c, cudaFuncSetAttribute(mi_i8_kernel<2, WR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         cudaLaunchConfig_t cfg; memset(&cfg, 0, sizeof cfg);
         cudaLaunchAttribute attr[1];
         attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -991,27 +1072,37 @@ static int i8_launch(Ctx* c, I8Params& gp) {
         cfg.blockDim = dim3(I8_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = c->stream; cfg.attrs = attr; cfg.numAttrs = 1;
         cfg.gridDim = dim3(2u * (unsigned)(c->sm_count / 2));
         int max_clusters = 0;
-        if (cudaOccupancyMaxActiveClusters(&max_clusters, mi_i8_kernel<2>, &cfg) != cudaSuccess || max_clusters < 1) {
+        if (cudaOccupancyMaxActiveClusters(&max_clusters, mi_i8_kernel<2, WR>, &cfg) != cudaSuccess || max_clusters < 1) {
             cudaGetLastError();
             max_clusters = c->sm_count / 2;
         }
         unsigned long long pairs = (unsigned long long)max_clusters;
         if (slots < pairs) pairs = slots ? slots : 1;
         cfg.gridDim = dim3(2u * (unsigned)pairs);
-        SPK_CUDA(c, cudaLaunchKernelEx(&cfg, mi_i8_kernel<2>, ma, mb, gp));
+        SPK_CUDA(c, cudaLaunchKernelEx(&cfg, mi_i8_kernel<2, WR>, ma, mb, gp));
     }
     c->tm.kernel_launches += 1;
     SPK_CUDA(c, cudaGetLastError());
     return SPK_OK;
 }
+static int i8_launch(Ctx* c, I8Params& gp, int wr) { return wr == 2 ? i8_launch_wr<2>(c, gp) : i8_launch_wr<1>(c, gp); }
 
-int mi_i8_filter(Ctx* c, const spk_scan_params& p, double band, uint64_t circle) {
-    int r = i8_prepare(c, p.pseudocount); if (r) return r;
+// weight rows of the default int8 engine (engine 0): SPYDRPICK_B200_I8_WR=2 selects the exact 16-bit {hi, lo} rows,
+// =1 the factorised single-row weights
+int i8_default_wr() {
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("SPYDRPICK_B200_I8_WR"); v = (e && e[0] == '2') ? 2 : ((e && e[0] == '1') ? 1 : I8_DEFAULT_WR); }
+    return v;
+}
+
+int mi_i8_filter(Ctx* c, const spk_scan_params& p, double band, uint64_t circle, int wr) {
+    int r = i8_prepare(c, p.pseudocount, wr); if (r) return r;
     I8Params gp; memset(&gp, 0, sizeof gp);
     const uint32_t NT = c->i8.NT;
+    const uint32_t JT = 2u / (uint32_t)wr, NTJ = NT / JT, SJ = I8_SUPER / JT;      // B panels; panels per super-row step
     const uint32_t n_sr = (NT + I8_SUPER - 1) / I8_SUPER;
     std::vector<unsigned long long> prefix(n_sr + 1, 0);
-    for (uint32_t sr = 0; sr < n_sr; ++sr) prefix[sr + 1] = prefix[sr] + (NT - sr * I8_SUPER);
+    for (uint32_t sr = 0; sr < n_sr; ++sr) prefix[sr + 1] = prefix[sr] + (NTJ - sr * SJ);
     if ((size_t)(n_sr + 1) * 8 > (1u << 20)) return fail(c, SPK_E_INVALID, "int8 engine: too many column tiles");
     const uint32_t nparts = p.n_parts ? p.n_parts : 1;
     if (p.part_index >= nparts) return fail(c, SPK_E_INVALID, "part_index >= n_parts");
@@ -1046,26 +1137,27 @@ int mi_i8_filter(Ctx* c, const spk_scan_params& p, double band, uint64_t circle)
             I8Params sp = gp;
             sp.seed_chunks = d_prefix + n_sr + 1;
             sp.n_local_slots = (unsigned long long)seed.size() * (gp.pair ? I8_SUPER / 2 : I8_SUPER);
-            r = i8_launch(c, sp); if (r) return r;
+            r = i8_launch(c, sp, wr); if (r) return r;
             seeded = true;
             SPK_CUDA(c, cudaEventRecord(c->ev[7], c->stream));
             SPK_CUDA(c, cudaMemsetAsync(c->d_counters + 5, 0, sizeof(unsigned long long), c->stream));   // rewind the tile cursor
         }
     }
-    r = i8_launch(c, gp); if (r) return r;
+    r = i8_launch(c, gp, wr); if (r) return r;
     SPK_CUDA(c, cudaEventRecord(c->ev[3], c->stream));
     SPK_CUDA(c, cudaEventSynchronize(c->ev[3]));
     SPK_CUDA(c, cudaEventElapsedTime(&c->tm.gemm_ms, c->ev[2], c->ev[3]));
     if (seeded) SPK_CUDA(c, cudaEventElapsedTime(&c->tm.seed_ms, c->ev[2], c->ev[7]));
+    // tiles = M128 x N256 MMA tiles of the main pass; pairs = column pairs they cover (incl. padding / below-diagonal halves)
     unsigned long long tiles = 0, pairs = 0;
     auto width = [&](uint32_t t) { return t >= c->i8.tile_start[2] ? 32u : (t >= c->i8.tile_start[1] ? 64u : 128u); };
     for (unsigned long long lq = 0; lq < local_chunks; ++lq) {
         const unsigned long long q = lq * nparts + p.part_index;
         const uint32_t sr = (uint32_t)(std::upper_bound(prefix.begin(), prefix.end(), q) - prefix.begin()) - 1;
-        const uint32_t tj = sr * I8_SUPER + (uint32_t)(q - prefix[sr]);
+        const uint32_t tj = sr * SJ + (uint32_t)(q - prefix[sr]);
         for (uint32_t w = 0; w < I8_SUPER; ++w) {
             const uint32_t ti = sr * I8_SUPER + w;
-            if (ti < NT && tj < NT && ti <= tj) { ++tiles; pairs += (unsigned long long)width(ti) * width(tj); }
+            if (ti < NT && tj < NTJ && ti <= JT * tj + (JT - 1)) { ++tiles; pairs += (unsigned long long)width(ti) * JT * width(JT * tj); }
         }
     }
     c->tm.gemm_tiles = tiles; c->tm.gemm_pairs = pairs;
@@ -1074,7 +1166,8 @@ int mi_i8_filter(Ctx* c, const spk_scan_params& p, double band, uint64_t circle)
 
 // raw integer tables of one tile pair: out[(128/KI)][(128/KJ)][KI][KJ] (<= 16384 words)
 int mi_i8_debug_tile(Ctx* c, uint32_t ti, uint32_t tj, double pc, uint32_t* d_out) {
-    int r = i8_prepare(c, pc); if (r) return r;
+    const int wr = i8_default_wr();
+    int r = i8_prepare(c, pc, wr); if (r) return r;
     if (ti > tj || tj >= c->i8.NT) return fail(c, SPK_E_INVALID, "int8 debug tile: need ti <= tj < NT");
     I8Params gp; memset(&gp, 0, sizeof gp);
     gp.sr_prefix = (const unsigned long long*)c->d_tilemap;
@@ -1082,7 +1175,7 @@ int mi_i8_debug_tile(Ctx* c, uint32_t ti, uint32_t tj, double pc, uint32_t* d_ou
     gp.n_parts = 1; gp.n_local_slots = 1;
     gp.pcq = (float)(pc / c->i8_delta);
     gp.debug_out = d_out; gp.debug_ti = ti; gp.debug_tj = tj;
-    r = i8_launch(c, gp); if (r) return r;
+    r = i8_launch(c, gp, wr); if (r) return r;
     SPK_CUDA(c, cudaStreamSynchronize(c->stream));
     return SPK_OK;
 }

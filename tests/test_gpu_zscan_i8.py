@@ -104,11 +104,15 @@ def test_i8_tile_counts_bit_exact(ctx, weighted):
     first = ctx.debug_i8_tile(0, 0)                              # also quantises the weights
     lay = ctx.debug_i8_layout(with_weights=True)
     q = lay["q"]
-    if not weighted:
-        assert (q == 65535).all()
-    else:
-        wq = q.astype(np.float64) * lay["delta"]
-        assert np.abs(wq - w).max() <= 0.5 * lay["delta"] * (1 + 1e-9)
+    wq = q.astype(np.float64) * lay["delta"]
+    if ctx.debug_i8_mode() == 2:                                 # 16-bit grid
+        if not weighted:
+            assert (q == 65535).all()
+        else:
+            assert np.abs(wq - w).max() <= 0.5 * lay["delta"] * (1 + 1e-9)
+    else:                                                        # byte-product grid: q = a*b, a, b <= 255
+        assert q.max() <= 255 * 255
+        assert np.abs(wq - (w if weighted else 1.0)).max() <= 2e-3 * (w.max() if weighted else 1.0)
     for ti, tj in pairs:
         got = ctx.debug_i8_tile(ti, tj) if (ti, tj) != (0, 0) else first
         exp, shape = _expected_tables(s, q, lay, ti, tj)
@@ -117,25 +121,27 @@ def test_i8_tile_counts_bit_exact(ctx, weighted):
         assert np.array_equal(g, exp), (ti, tj, shape, int(np.abs(g.astype(np.int64) - exp.astype(np.int64)).max()))
 
 
+@pytest.mark.parametrize("engine", [3, 4])
 @pytest.mark.parametrize("n,L,linear,ld", [(200, 500, False, 0), (130, 333, True, 30), (257, 700, False, 100),
                                             (64, 64, False, 0), (90, 1100, False, 0), (300, 2100, False, 0)])
-def test_scan_i8_vs_oracle(ctx, n, L, linear, ld):
+def test_scan_i8_vs_oracle(ctx, n, L, linear, ld, engine):
     s, pos, _ = generate_alignment(n, L, seed=n + L)
     w = orc.weights_from_counts(orc.neighbour_counts(s, int(0.9 * L)))
     ctx.set_alignment(s, pos); ctx.set_weights(w)
     thr = 0.05
     exp = orc.mi_scan(s, w, pos, threshold=thr, ld_threshold=ld, linear_genome=linear, circle_size=L)
-    got = ctx.mi_scan(thr, ld_threshold=ld, linear_genome=linear, engine=3, sort_desc=True, max_edges=L * L // 2)
+    got = ctx.mi_scan(thr, ld_threshold=ld, linear_genome=linear, engine=engine, sort_desc=True, max_edges=L * L // 2)
     e_exp = orc.sort_edges(exp["edges"]); e_got = got["edges"]
     assert got["n_candidates"] >= len(e_exp)
     assert len(e_got) == len(e_exp) > 0
     assert_edges_match(e_got, e_exp, rtol=1e-5, atol=0)            # north-star tolerance
     assert_edges_match(e_got, e_exp, rtol=1e-10, atol=1e-13)       # what the fp64 refine actually gives
     assert np.allclose(got["colmax"], exp["colmax"], rtol=1e-10, atol=1e-13)
-    assert got["max_filter_error"] < 5e-5
+    assert got["max_filter_error"] < (5e-5 if engine == 3 else 2e-3)
 
 
-def test_scan_i8_mixed_classes_and_monomorphic(ctx):
+@pytest.mark.parametrize("engine", [3, 4])
+def test_scan_i8_mixed_classes_and_monomorphic(ctx, engine):
     """every class pair incl. monomorphic columns (k = 0) and all-five-state columns, uneven weights."""
     n, L = 150, 900
     s = _mixed_alignment(n, L, 9)
@@ -144,24 +150,25 @@ def test_scan_i8_mixed_classes_and_monomorphic(ctx):
     ctx.set_alignment(s, pos); ctx.set_weights(w)
     thr = 0.02
     exp = orc.mi_scan(s, w, pos, threshold=thr, ld_threshold=50, circle_size=L)
-    got = ctx.mi_scan(thr, ld_threshold=50, engine=3)
+    got = ctx.mi_scan(thr, ld_threshold=50, engine=engine)
     exact = ctx.mi_scan(thr, ld_threshold=50, engine=1)
     assert got["edges"].tobytes() == exact["edges"].tobytes()
     assert np.array_equal(got["colmax"], exact["colmax"])
     assert_edges_match(got["edges"], orc.sort_edges(exp["edges"]), rtol=1e-10, atol=1e-13)
     assert np.allclose(got["colmax"], exp["colmax"], rtol=1e-10, atol=1e-13)
-    assert got["max_filter_error"] < 5e-5
+    assert got["max_filter_error"] < (5e-5 if engine == 3 else 2e-3)
 
 
-def test_scan_i8_partitions_and_engines_agree(ctx):
+@pytest.mark.parametrize("engine", [3, 4])
+def test_scan_i8_partitions_and_engines_agree(ctx, engine):
     s, pos, _ = generate_alignment(150, 2500, seed=78)
     w = orc.weights_from_counts(orc.neighbour_counts(s, int(0.9 * 2500)))
     ctx.set_alignment(s, pos); ctx.set_weights(w)
-    whole = ctx.mi_scan(0.06, engine=3)
+    whole = ctx.mi_scan(0.06, engine=engine)
     dense = ctx.mi_scan(0.06, engine=2)
     assert whole["edges"].tobytes() == dense["edges"].tobytes()
     assert np.array_equal(whole["colmax"], dense["colmax"])
-    parts = [ctx.mi_scan(0.06, part_index=k, n_parts=3, engine=3) for k in range(3)]
+    parts = [ctx.mi_scan(0.06, part_index=k, n_parts=3, engine=engine) for k in range(3)]
     assert sum(p["n_edges"] for p in parts) == whole["n_edges"]
     merged = np.concatenate([p["edges"] for p in parts])
     assert ctx.sort_edges(merged).tobytes() == whole["edges"].tobytes()
