@@ -49,8 +49,8 @@ namespace spk {
 #define SPK_I8_EPI_WARPS 16           // epilogue warps: 8 (two per TMEM lane quadrant) or 16 (four per quadrant)
 #endif
 #ifndef SPK_I8_TWO_PHASE
-#define SPK_I8_TWO_PHASE 0           // 1: MI of all pairs of a load first (branch-free), emission tests afterwards
-#endif
+#define SPK_I8_TWO_PHASE 2           // 0: test + emit pair by pair; 1: MI of all pairs of a (wider) load first, tests afterwards;
+#endif                               // 2: as 1 at the normal load width, and ONE warp vote skips the tests of a load nothing in which can pass
 constexpr int I8_EPI_WARPS = SPK_I8_EPI_WARPS;
 constexpr int I8_EPI_THREADS = I8_EPI_WARPS * 32;
 constexpr int I8_THREADS = 64 + I8_EPI_THREADS + 64;        // + TMA warp, MMA warp, record-staging warp, tile-scheduler warp
