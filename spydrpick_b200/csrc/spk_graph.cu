@@ -14,13 +14,21 @@
 
 namespace spk {
 
-__global__ void sort_keys_kernel(const spk_edge* __restrict__ e, unsigned long long n,
+// id key (node2 << bits) | node1 with bits = ceil(log2(#nodes)): same order as (node2 << 32) | node1 in 2*bits radix bits
+__global__ void sort_keys_kernel(const spk_edge* __restrict__ e, unsigned long long n, uint32_t bits,
                                  unsigned long long* __restrict__ key_id, uint32_t* __restrict__ idx) {
     const unsigned long long k = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n) return;
     const uint32_t a = min(e[k].i, e[k].j), b = max(e[k].i, e[k].j);
-    key_id[k] = ((unsigned long long)b << 32) | a;
+    key_id[k] = ((unsigned long long)b << bits) | a;
     idx[k] = (uint32_t)k;
+}
+__global__ void max_node_kernel(const spk_edge* __restrict__ e, unsigned long long n, unsigned int* __restrict__ out) {
+    const unsigned long long k = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned int m = 0;
+    if (k < n) m = max(e[k].i, e[k].j);
+    for (int o = 16; o; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x % 32) == 0 && m) atomicMax(out, m);
 }
 __global__ void weight_keys_kernel(const spk_edge* __restrict__ e, const uint32_t* __restrict__ idx, unsigned long long n,
                                    unsigned long long* __restrict__ key_w) {
@@ -54,8 +62,20 @@ int sort_edges_device(Ctx* c, spk_edge* d_edges, uint64_t n) {
     void* tmp = base + 2 * kb + 2 * ib + eb;
     const unsigned g = (unsigned)((n + 255) / 256);
     SPK_CUDA(c, cudaEventRecord(c->ev[0], c->stream));
-    sort_keys_kernel<<<g, 256, 0, c->stream>>>(d_edges, n, k0, i0);
-    SPK_CUDA(c, cub::DeviceRadixSort::SortPairs(tmp, tmp2, k0, k1, i0, i1, (int)n, 0, 64, c->stream));   // by id asc
+    // node ids of a scan are < L: 2*ceil(log2 L) radix bits instead of 64; caller-supplied lists: largest id found first
+    uint32_t nn = c->L;
+    if (!c->d_states || d_edges != c->d_edges) {
+        unsigned int* d_max = (unsigned int*)k1;
+        SPK_CUDA(c, cudaMemsetAsync(d_max, 0, 4, c->stream));
+        max_node_kernel<<<g, 256, 0, c->stream>>>(d_edges, n, d_max);
+        unsigned int h_max = 0;
+        SPK_CUDA(c, cudaMemcpyAsync(&h_max, d_max, 4, cudaMemcpyDeviceToHost, c->stream));
+        SPK_CUDA(c, cudaStreamSynchronize(c->stream));
+        nn = h_max + 1;
+    }
+    uint32_t bits = 1; while (bits < 32 && (1ull << bits) < (unsigned long long)nn) ++bits;
+    sort_keys_kernel<<<g, 256, 0, c->stream>>>(d_edges, n, bits, k0, i0);
+    SPK_CUDA(c, cub::DeviceRadixSort::SortPairs(tmp, tmp2, k0, k1, i0, i1, (int)n, 0, (int)(2 * bits), c->stream));   // by id asc
     weight_keys_kernel<<<g, 256, 0, c->stream>>>(d_edges, i1, n, k0);
     SPK_CUDA(c, cub::DeviceRadixSort::SortPairs(tmp, tmp2, k0, k1, i1, i0, (int)n, 0, 64, c->stream));   // stable by weight desc
     gather_edges_kernel<<<g, 256, 0, c->stream>>>(d_edges, i0, n, ebuf);

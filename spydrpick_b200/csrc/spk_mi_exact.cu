@@ -92,20 +92,31 @@ gbits_build_kernel(const uint8_t* __restrict__ colmajor, const int32_t* __restri
     __shared__ double red[4][NSTATES];
     const uint32_t c = blockIdx.x, lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
     const uint8_t* col = colmajor + (size_t)c * n_pad;
-    double m[NSTATES] = {0, 0, 0, 0, 0};
     for (uint32_t w = wid; w < NW; w += 4) {
         const int32_t sidx = gslot[w * 32 + lane];
         const uint32_t x = (c < L && sidx >= 0) ? (uint32_t)col[sidx] : 255u;
-        const double v = gval[w];
-#pragma unroll
-        for (int a = 0; a < NSTATES; ++a) {
-            const uint32_t pl = __ballot_sync(0xffffffffu, x == (uint32_t)a);
-            if (lane == (uint32_t)a) { planes_sm[a * NW + w] = pl; m[a] += v * (double)__popc(pl); }
+        // four votes; the fifth plane is what is left of the occupied slots
+        const uint32_t p0 = __ballot_sync(0xffffffffu, x == 0u), p1 = __ballot_sync(0xffffffffu, x == 1u);
+        const uint32_t p2 = __ballot_sync(0xffffffffu, x == 2u), p3 = __ballot_sync(0xffffffffu, x == 3u);
+        const uint32_t occ = __ballot_sync(0xffffffffu, x < (uint32_t)NSTATES);
+        if (lane < (uint32_t)NSTATES) {
+            const uint32_t pl = lane == 0 ? p0 : lane == 1 ? p1 : lane == 2 ? p2 : lane == 3 ? p3 : (occ & ~(p0 | p1 | p2 | p3));
+            planes_sm[lane * NW + w] = pl;
         }
     }
-    // lane a of every warp holds that warp's partial marginal of state a
+    __syncthreads();
+    // marginals from the staged planes: warp `wid` sums its share of the words, lane a of the warp ends with state a
+    double m[NSTATES] = {0, 0, 0, 0, 0};
+    for (uint32_t w = threadIdx.x; w < NW; w += blockDim.x) {
+        const double v = gval[w];
 #pragma unroll
-    for (int a = 0; a < NSTATES; ++a) if (lane == (uint32_t)a) red[wid][a] = m[a];
+        for (int a = 0; a < NSTATES; ++a) m[a] += v * (double)__popc(planes_sm[a * NW + w]);
+    }
+#pragma unroll
+    for (int a = 0; a < NSTATES; ++a) {
+        for (int o = 16; o; o >>= 1) m[a] += __shfl_xor_sync(0xffffffffu, m[a], o);
+        if (lane == 0) red[wid][a] = m[a];
+    }
     __syncthreads();
     uint32_t* out = gbits + (size_t)c * NSTATES * NW;
     for (uint32_t k = threadIdx.x; k < NSTATES * NW; k += blockDim.x) out[k] = planes_sm[k];
