@@ -182,6 +182,9 @@ def run_b200(args):
         raise SystemExit("bench.py: no CUDA device -- the B200 path has no CPU fallback")
     torch.cuda.set_device(local_rank)
     device = torch.device("cuda", local_rank)
+    # stdout carries the ONE JSON line: anything native libraries print (NCCL's version banner) goes to stderr
+    sys.stdout.flush()
+    json_fd = os.dup(1); os.dup2(2, 1)
     if world > 1:
         if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
             os.environ["NCCL_DEBUG"] = "WARN"            # keep stdout to the single JSON line
@@ -254,13 +257,23 @@ def run_b200(args):
     from spydrpick_b200.capi import pinned_copy, pinned_empty
     states_pin = pinned_copy(states)                  # the caller's alignment lives in page-locked host memory
     pos_pin = pinned_copy(pos)
+    states_pin_t = torch.from_numpy(states_pin)       # same page-locked memory, as a tensor for the row-shard upload
 
-    host_edges = host_flags = None
+    host_edges = host_flags = side = None
 
     def step_e2e():
         """host buffers through the C-ABI: H2D of the alignment (pinned), D2H of edges + flags inside the step."""
         tw = [time.perf_counter()]
-        ctx.set_alignment(states_pin, pos_pin); tw.append(time.perf_counter())
+        if world == 1:
+            ctx.set_alignment(states_pin, pos_pin)
+        else:
+            # every rank uploads n/G rows over its own PCIe link; the slices are all-gathered over NVLink
+            from spydrpick_b200 import dist as sdist
+            ra, rb = sdist.row_shard(n, world, rank)
+            d_states = sdist.allgather_alignment_rows(states_pin_t[ra:rb].reshape(-1), n, L, device)
+            ctx.set_alignment_device(d_states.data_ptr(), n, L, pos_pin)
+            del d_states
+        tw.append(time.perf_counter())
         c = sharded_counts()
         ctx.set_weights(1.0 / c.astype(np.float64)); tw.append(time.perf_counter())
         if world == 1:
@@ -281,21 +294,25 @@ def run_b200(args):
             r = ctx.mi_scan(threshold, max_edges=max_edges, sort_desc=False, n_terms=args.n_terms, engine=args.engine,
                             part_index=rank, n_parts=world, keep_on_device=True); tw.append(time.perf_counter())
             keep, d_edges, ne = merge_across_ranks(r)
-            ctx.sort_edges_device(d_edges, ne)
+            ctx.sort_edges_device(d_edges, ne)        # returns with the sorted list complete in HBM
+            nonlocal host_edges, side
+            if host_edges is None or host_edges.numel() < ne * 16:
+                host_edges = torch.empty(int(ne * 16 * 1.25) + 4096, dtype=torch.uint8).pin_memory()
+                host_flags = torch.empty(int(ne * 1.25) + 4096, dtype=torch.uint8).pin_memory()
+                side = torch.cuda.Stream(device)
+            if rank == 0:                             # the caller's process receives the merged list: download overlaps K3
+                with torch.cuda.stream(side):
+                    host_edges[:ne * 16].copy_(dev_bytes(torch, d_edges, ne * 16, device), non_blocking=True)
             dflags = torch.zeros(max(ne, 1), dtype=torch.uint8, device=device)
             ctx.aracne_device(d_edges, ne, dflags.data_ptr(), EPS, part_index=rank, n_parts=world)
             from spydrpick_b200 import dist as sdist
             dflags = sdist.allgather_flag_shards(dflags, ne)
-            nonlocal host_edges
-            if host_edges is None or host_edges.numel() < ne * 16:
-                host_edges = torch.empty(int(ne * 16 * 1.25) + 4096, dtype=torch.uint8).pin_memory()
-                host_flags = torch.empty(int(ne * 1.25) + 4096, dtype=torch.uint8).pin_memory()
-            host_edges[:ne * 16].copy_(dev_bytes(torch, d_edges, ne * 16, device), non_blocking=True)
-            host_flags[:ne].copy_(dflags[:ne], non_blocking=True)
+            if rank == 0:
+                host_flags[:ne].copy_(dflags[:ne], non_blocking=True)
             torch.cuda.synchronize()
-            ndirect = int(host_flags[:ne].numpy().sum())
-            h2d = states.nbytes + pos.nbytes + 8 * n
-            d2h = ne * 16 + ne + 8 * L + 8 * n
+            ndirect = int(host_flags[:ne].numpy().sum()) if rank == 0 else 0
+            h2d = (rb - ra) * L + pos.nbytes + 8 * n  # per rank; whole job = the alignment once + G x (pos, weights)
+            d2h = ne * 16 + ne + 8 * L + 8 * n        # rank 0
         tw.append(time.perf_counter())
         if os.environ.get("SPK_BENCH_E2E_BREAKDOWN"):
             tmx = ctx.timings()
@@ -390,10 +407,14 @@ def run_b200(args):
                 "candidates": r["n_candidates"], "max_filter_error": r["max_filter_error"],
                 "roofline": roofline}
         if e2e:
+            e2e["path"] = ("spk_set_alignment (pinned host states) -> K1 -> scan -> sort -> ARACNE, edges + flags downloaded" if world == 1 else
+                           "per rank: H2D of n/G alignment rows + NVLink all-gather -> spk_set_alignment_device -> sharded K1/scan -> "
+                           "NCCL edge all-gather -> sort -> sharded ARACNE; rank 0 downloads the merged edges + flags "
+                           "(h2d bytes are per rank, d2h bytes are rank 0's)")
             line["e2e"] = e2e
         if cpu:
             line["cpu_baseline"] = cpu
-        print(json.dumps(line))
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
     ctx.close()
     if world > 1:
         dist.destroy_process_group()

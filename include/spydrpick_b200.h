@@ -63,6 +63,12 @@ void spk_host_free(void* p);
  * apegrunt/Alignment_impl_block_compressed_storage.hpp:1089-1128). pos may be NULL (= 0..L-1).
  * Weights are reset to 1 (StateVector default weight). */
 int spk_set_alignment(spk_ctx* ctx, const uint8_t* states, uint32_t n, uint32_t L, const uint64_t* pos);
+/* Same, with the dense states already resident in the context's device memory (row-major uint8[n][L]); pos stays a
+ * host array. For the one-process-per-GPU layout: every rank uploads n/G rows over its own PCIe link and the slices
+ * are all-gathered over NVLink ("alignment broadcast once") instead of G full host-to-device copies.
+ * The buffer must be complete when the call is made (it is read on the context's stream, which is not ordered after
+ * the caller's other streams); it is copied, and the caller may free it after the call returns. */
+int spk_set_alignment_device(spk_ctx* ctx, const void* d_states, uint32_t n, uint32_t L, const uint64_t* pos);
 
 /* ---- K1: sample reweighting ----------------------------------------------------------- */
 /* Replaces apegrunt::calculate_weights (Alignment_StateVector_weights.hpp:192-353) up to the

@@ -16,7 +16,7 @@ assert EDGE_DTYPE.itemsize == 16
 SPK_OK, SPK_E_INVALID, SPK_E_CUDA, SPK_E_NOMEM, SPK_E_OVERFLOW, SPK_E_PRECISION = 0, -1, -2, -3, -4, -5
 
 EXPORTS = ["spk_create", "spk_destroy", "spk_last_error", "spk_set_stream", "spk_host_alloc", "spk_host_free",
-           "spk_set_alignment",
+           "spk_set_alignment", "spk_set_alignment_device",
            "spk_neighbour_counts", "spk_neighbour_counts_part", "spk_set_weights", "spk_mi_pairs", "spk_determine_mi_threshold",
            "spk_mi_scan", "spk_outlier_thresholds", "spk_sort_edges", "spk_aracne", "spk_sort_edges_device",
            "spk_aracne_device", "spk_wait_download", "spk_get_timings", "spk_debug_tile_counts", "spk_debug_i8_mode", "spk_debug_i8_layout", "spk_debug_i8_tile",
@@ -71,6 +71,7 @@ def load():
     L.spk_create.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int]
     L.spk_set_stream.argtypes = [C.c_void_p, C.c_void_p]
     L.spk_set_alignment.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p]
+    L.spk_set_alignment_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p]
     L.spk_neighbour_counts.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_void_p]
     L.spk_neighbour_counts_part.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_uint32, C.c_uint32, C.c_void_p]
     L.spk_set_weights.argtypes = [C.c_void_p, C.c_void_p]
@@ -173,6 +174,12 @@ class Context:
         p = None if pos is None else np.ascontiguousarray(pos, dtype=np.uint64)
         self._check(self.lib.spk_set_alignment(self.h, _ptr(s), s.shape[0], s.shape[1], _ptr(p)))
         self.n, self.L = s.shape
+
+    def set_alignment_device(self, d_states, n, L, pos=None):
+        """d_states: raw device pointer (int) to row-major uint8[n][L] in this context's device memory."""
+        p = None if pos is None else np.ascontiguousarray(pos, dtype=np.uint64)
+        self._check(self.lib.spk_set_alignment_device(self.h, C.c_void_p(int(d_states)), int(n), int(L), _ptr(p)))
+        self.n, self.L = int(n), int(L)
 
     def neighbour_counts(self, min_identical, lastblock_quirk=True, part_index=0, n_parts=1):
         """n_parts > 1: PARTIAL counts of this partition of the sample-tile pairs (sum over partitions = full counts)."""

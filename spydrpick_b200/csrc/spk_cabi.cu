@@ -129,7 +129,7 @@ int spk_set_stream(spk_ctx* c, void* s) {
     return SPK_OK;
 }
 
-int spk_set_alignment(spk_ctx* c, const uint8_t* states, uint32_t n, uint32_t L, const uint64_t* pos) {
+static int set_alignment_impl(spk_ctx* c, const uint8_t* states, uint32_t n, uint32_t L, const uint64_t* pos, cudaMemcpyKind kind) {
     if (!c || !states || n == 0 || L < 2) return c ? fail(c, SPK_E_INVALID, "set_alignment: need states, n >= 1, L >= 2") : SPK_E_INVALID;
     if (L >= (1u << 29)) return fail(c, SPK_E_INVALID, "L too large");
     SPK_CUDA(c, cudaSetDevice(c->device));
@@ -155,7 +155,7 @@ int spk_set_alignment(spk_ctx* c, const uint8_t* states, uint32_t n, uint32_t L,
     }
     c->operands_terms = 0; c->stats_valid = false; c->host_edges_n = 0; c->g_state = 0;
     SPK_CUDA(c, cudaEventRecord(c->ev[0], c->stream));
-    SPK_CUDA(c, cudaMemcpyAsync(c->d_states, states, (size_t)n * L, cudaMemcpyHostToDevice, c->stream));
+    SPK_CUDA(c, cudaMemcpyAsync(c->d_states, states, (size_t)n * L, kind, c->stream));
     std::vector<uint64_t> hp(c->L_pad, 0);
     for (uint32_t k = 0; k < L; ++k) hp[k] = pos ? pos[k] : k;
     SPK_CUDA(c, cudaMemcpyAsync(c->d_pos, hp.data(), (size_t)c->L_pad * 8, cudaMemcpyHostToDevice, c->stream));
@@ -172,6 +172,22 @@ int spk_set_alignment(spk_ctx* c, const uint8_t* states, uint32_t n, uint32_t L,
     SPK_CUDA(c, cudaEventElapsedTime(&c->tm.upload_ms, c->ev[0], c->ev[1]));
     SPK_CUDA(c, cudaEventElapsedTime(&c->tm.prep_ms, c->ev[1], c->ev[2]));
     return SPK_OK;
+}
+
+int spk_set_alignment(spk_ctx* c, const uint8_t* states, uint32_t n, uint32_t L, const uint64_t* pos) {
+    return set_alignment_impl(c, states, n, L, pos, cudaMemcpyHostToDevice);
+}
+
+// states already in this device's memory (e.g. row slices uploaded by the ranks of a box and all-gathered over NVLink)
+int spk_set_alignment_device(spk_ctx* c, const void* d_states, uint32_t n, uint32_t L, const uint64_t* pos) {
+    if (c && d_states) {
+        cudaPointerAttributes at{};
+        if (cudaPointerGetAttributes(&at, d_states) != cudaSuccess || at.type != cudaMemoryTypeDevice || at.device != c->device) {
+            cudaGetLastError();
+            return fail(c, SPK_E_INVALID, "set_alignment_device: d_states is not memory of device %d", c->device);
+        }
+    }
+    return set_alignment_impl(c, (const uint8_t*)d_states, n, L, pos, cudaMemcpyDeviceToDevice);
 }
 
 int spk_neighbour_counts_part(spk_ctx* c, uint64_t min_identical, int quirk, uint32_t part, uint32_t nparts, uint64_t* counts) {

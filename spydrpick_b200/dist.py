@@ -61,3 +61,32 @@ def allgather_flag_shards(flags: torch.Tensor, n_edges: int, group=None):
     parts = [torch.empty_like(mine) for _ in range(world)]
     dist.all_gather(parts, mine, group=group)
     return torch.cat([parts[k][:b[k + 1] - b[k]] for k in range(world)])
+
+
+def row_shard(n: int, world: int, rank: int):
+    """Rows of the alignment rank `rank` uploads: equal blocks of ceil(n / world) rows (the last may be short or empty)."""
+    per = (n + world - 1) // world
+    return min(n, rank * per), min(n, (rank + 1) * per)
+
+
+def allgather_alignment_rows(my_rows: torch.Tensor, n: int, L: int, device=None, group=None):
+    """"Alignment broadcast once"  as G small uploads + one all-gather: `my_rows` is this rank's
+    row_shard() slice of the row-major uint8[n][L] states in (pinned) host memory. It goes up this rank's own PCIe link,
+    the slices are all-gathered over NVLink, and every rank ends with the full uint8[n, L] tensor on its device
+    (feed its data_ptr() to spk_set_alignment_device)."""
+    world = dist.get_world_size(group); rank = dist.get_rank(group)
+    per = (n + world - 1) // world
+    a, b = row_shard(n, world, rank)
+    assert my_rows.dtype == torch.uint8 and my_rows.numel() == (b - a) * L
+    dev = device if device is not None else my_rows.device
+    full = torch.empty((world * per, L), dtype=torch.uint8, device=dev)
+    mine = full[rank * per:(rank + 1) * per]
+    if b > a:
+        mine[:b - a].copy_(my_rows.view(b - a, L), non_blocking=True)
+    if b - a < per:
+        mine[b - a:].zero_()
+    dist.all_gather_into_tensor(full, mine, group=group)
+    if full.is_cuda:
+        # the library copies on ITS stream: the gathered rows must be complete before the pointer is handed over
+        torch.cuda.current_stream(full.device).synchronize()
+    return full[:n]

@@ -62,7 +62,12 @@ def _worker(rank, world, port, out):
     shard = np.zeros(total, dtype=np.uint8); shard[b[rank]:b[rank + 1]] = flags_full[b[rank]:b[rank + 1]]
     flags = sdist.allgather_flag_shards(torch.from_numpy(shard), total).numpy()
     ref = orc.sort_edges(e)
-    ok = (total == len(e) and sum(counts) == total and me.tobytes() == ref.tobytes()
+    # alignment row shards: every rank contributes its rows, all ranks end with the whole alignment (uneven: 61 rows)
+    s61 = np.ascontiguousarray(np.vstack([s, s[:1]]))
+    ra, rb = sdist.row_shard(61, world, rank)
+    whole = sdist.allgather_alignment_rows(torch.from_numpy(s61[ra:rb].copy()).reshape(-1), 61, 240)
+    rows_ok = np.array_equal(whole.numpy(), s61) and sdist.row_shard(5, 8, 7) == (5, 5)
+    ok = (total == len(e) and sum(counts) == total and rows_ok and me.tobytes() == ref.tobytes()
           and np.array_equal(flags, orc.aracne_closed(ref)) and np.allclose(cm.numpy(), full["colmax"], rtol=1e-12)
           and k1_ok)
     out[rank] = bool(ok)

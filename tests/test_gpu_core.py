@@ -239,3 +239,25 @@ def test_error_behaviour(ctx):
     with pytest.raises(SpkError):
         c2.mi_scan(0.1, pseudocount=0.0)
     c2.close()
+
+
+def test_set_alignment_device_equals_host_upload(ctx):
+    """spk_set_alignment_device (states already in HBM, e.g. all-gathered row shards) = spk_set_alignment."""
+    import torch
+    from spydrpick_b200 import SpkError
+    s, pos, _ = generate_alignment(90, 333, seed=5)
+    ctx.set_alignment(s, pos)
+    c_host = ctx.neighbour_counts(int(0.9 * 333), True)
+    ctx.set_weights(1.0 / c_host.astype(np.float64))
+    r_host = ctx.mi_scan(0.05)
+    d = torch.from_numpy(s).cuda()
+    ctx.set_alignment_device(d.data_ptr(), 90, 333, pos)
+    del d
+    c_dev = ctx.neighbour_counts(int(0.9 * 333), True)
+    assert np.array_equal(c_host, c_dev)
+    ctx.set_weights(1.0 / c_dev.astype(np.float64))
+    r_dev = ctx.mi_scan(0.05)
+    assert r_dev["edges"].tobytes() == r_host["edges"].tobytes() and len(r_host["edges"]) > 0
+    assert np.array_equal(r_dev["colmax"], r_host["colmax"])
+    with pytest.raises(SpkError):
+        ctx.set_alignment_device(s.ctypes.data, 90, 333, pos)       # pageable host pointer is rejected, not copied

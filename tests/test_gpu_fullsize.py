@@ -76,6 +76,8 @@ def _check_config(cfg):
         e = got["edges"]
         E = len(e)
         print("threshold %.6f -> %d edges, %d candidates" % (thr, E, got["n_candidates"]))
+        tm = ctx.timings()
+        print("device ms: " + ", ".join("%s %.1f" % (k[:-3], tm[k]) for k in ("hamming_ms", "gemm_ms", "refine_ms", "compact_ms", "sort_ms")))
         assert 0.3 * cfg["mi_values"] < E < 2.5 * cfg["mi_values"]
         assert np.all(e["i"] < e["j"]) and int(e["j"].max()) < L
         assert np.all(e["mi"] > thr)
