@@ -8,6 +8,15 @@
 // (pad bits are 0 in every plane, so they never count as mismatches).
 // Integer arithmetic, bit-exact. Each block owns a 64x64 tile of sample pairs and streams the
 // bit planes through shared memory in 16-word chunks; each thread keeps a 4x4 register tile.
+//
+// hamming_csa_kernel (default) is bound by instruction issue, not by POPC: the mismatch words of two consecutive
+// plane words go through a carry-save adder per pair cell (ones' = ones ^ m1 ^ m2, carry = maj(ones, m1, m2);
+// mismatches = 2 * sum popc(carry) + popc(ones)), so there is ONE popcount per two words (POPC runs at a quarter
+// of the LOP3 rate). The chunk is stored transposed and XOR-swizzled in shared memory ([plane][word][64 samples]),
+// so a thread's four rows / four columns of one word are ONE 16-byte LDS (6 LDS.128 per word instead of 24 LDS.32),
+// and chunks arrive by cp.async (zero-fill outside the alignment) into a two-stage ring. Only the upper-triangle
+// tile pairs are launched. hamming_tile_kernel is the first version, kept for A/B runs (SPYDRPICK_B200_K1=0).
+#include <cstdlib>
 #include "spk_internal.h"
 
 namespace spk {
@@ -95,6 +104,138 @@ hamming_tile_kernel(const uint32_t* __restrict__ planes, uint32_t n, uint32_t L,
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// CSA version. Shared layout per stage: [which: I/J][plane 0..2][word k 0..15][group g' 0..15][4 samples],
+// sample r of the tile = 4*g + s is stored in group g' = g ^ k (the swizzle keeps the transposing cp.async
+// stores at most 2-way bank-conflicted; the 16-byte reads are conflict-free / broadcast).
+constexpr int HC_STAGE_WORDS = 2 * 3 * HCH * HT;            // 6144 words = 24 KB per stage
+constexpr int HC_STAGES = 2;
+constexpr int HC_SMEM_BYTES = HC_STAGES * HC_STAGE_WORDS * 4;
+
+__device__ __forceinline__ void hc_cp_async4(uint32_t dst_smem, const void* src, uint32_t src_bytes) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst_smem), "l"(src), "r"(src_bytes) : "memory");
+}
+
+__device__ __forceinline__ void hc_issue_chunk(uint32_t stage_base, const uint32_t* __restrict__ planes, size_t plane, uint32_t n,
+                                               uint32_t W32, uint32_t i0, uint32_t j0, uint32_t w0) {
+    // 2 * 3 * 64 * 16 = 6144 words, 24 per thread; lanes run over the 16 words of one sample row (64-byte runs)
+#pragma unroll 4
+    for (uint32_t e = threadIdx.x; e < (uint32_t)HC_STAGE_WORDS; e += 256) {
+        const uint32_t k = e % HCH, r = (e / HCH) % HT, pw = e / (HCH * HT);      // pw = which * 3 + plane
+        const uint32_t p = pw % 3u, which = pw / 3u;
+        const uint32_t s = (which ? j0 : i0) + r, w = w0 + k;
+        const bool ok = (s < n) && (w < W32);
+        const uint32_t* src = ok ? planes + p * plane + (size_t)s * W32 + w : planes;
+        const uint32_t dst = stage_base + 4u * ((pw * HCH + k) * HT + 4u * ((r >> 2) ^ k) + (r & 3u));
+        hc_cp_async4(dst, src, ok ? 4u : 0u);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+}
+
+__global__ void __launch_bounds__(256, 2)
+hamming_csa_kernel(const uint32_t* __restrict__ planes, uint32_t n, uint32_t L, uint32_t W32, uint32_t nt,
+                   unsigned long long min_identical, int quirk, unsigned long long* __restrict__ counts,
+                   uint32_t part, uint32_t n_parts) {
+    extern __shared__ __align__(16) uint32_t hc_smem[];
+    __shared__ unsigned int cntI[HT], cntJ[HT];
+    // linear index over the upper-triangle tile pairs (ti <= tj), dealt round-robin to the partitions
+    const uint32_t b = part + blockIdx.x * n_parts;
+    uint32_t ti = (uint32_t)(((float)(2 * nt + 1) - sqrtf(fmaxf((float)(2 * nt + 1) * (float)(2 * nt + 1) - 8.f * (float)b, 0.f))) * 0.5f);
+    if (ti >= nt) ti = nt - 1;
+    // row ti starts at ti*nt - ti(ti-1)/2
+    while (ti > 0 && ti * nt - ti * (ti - 1) / 2 > b) --ti;
+    while ((ti + 1) * nt - (ti + 1) * ti / 2 <= b) ++ti;
+    const uint32_t tj = ti + (b - (ti * nt - ti * (ti - 1) / 2));
+    const uint32_t tx = threadIdx.x % 16, ty = threadIdx.x / 16;
+    const uint32_t i0 = ti * HT, j0 = tj * HT;
+    const size_t plane = (size_t)n * W32;
+    if (threadIdx.x < HT) { cntI[threadIdx.x] = 0; cntJ[threadIdx.x] = 0; }
+    const uint32_t smem_base = (uint32_t)__cvta_generic_to_shared(hc_smem);
+
+    uint32_t acc2[4][4], ones[4][4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+#pragma unroll
+        for (int q = 0; q < 4; ++q) { acc2[r][q] = 0; ones[r][q] = 0; }
+
+    const uint32_t nchunks = (W32 + HCH - 1) / HCH;
+    hc_issue_chunk(smem_base, planes, plane, n, W32, i0, j0, 0);
+    for (uint32_t ch = 0; ch < nchunks; ++ch) {
+        if (ch + 1 < nchunks) {
+            hc_issue_chunk(smem_base + ((ch + 1) % HC_STAGES) * HC_STAGE_WORDS * 4, planes, plane, n, W32, i0, j0, (ch + 1) * HCH);
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+        } else {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+        }
+        __syncthreads();
+        const uint4* st = reinterpret_cast<const uint4*>(hc_smem + (ch % HC_STAGES) * HC_STAGE_WORDS);
+        // uint4 index of (which, plane, k, group g) = ((which*3 + plane) * HCH + k) * 16 + (g ^ k)
+#pragma unroll 2
+        for (int k = 0; k < HCH; k += 2) {
+            uint32_t m1[4][4];
+            {
+                const uint4 a0 = st[((0 * HCH) + k) * 16 + (ty ^ k)], a1 = st[((1 * HCH) + k) * 16 + (ty ^ k)], a2 = st[((2 * HCH) + k) * 16 + (ty ^ k)];
+                const uint4 b0 = st[((3 * HCH) + k) * 16 + (tx ^ k)], b1 = st[((4 * HCH) + k) * 16 + (tx ^ k)], b2 = st[((5 * HCH) + k) * 16 + (tx ^ k)];
+                const uint32_t A0[4] = {a0.x, a0.y, a0.z, a0.w}, A1[4] = {a1.x, a1.y, a1.z, a1.w}, A2[4] = {a2.x, a2.y, a2.z, a2.w};
+                const uint32_t B0[4] = {b0.x, b0.y, b0.z, b0.w}, B1[4] = {b1.x, b1.y, b1.z, b1.w}, B2[4] = {b2.x, b2.y, b2.z, b2.w};
+#pragma unroll
+                for (int r = 0; r < 4; ++r)
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) m1[r][q] = (A0[r] ^ B0[q]) | (A1[r] ^ B1[q]) | (A2[r] ^ B2[q]);
+            }
+            {
+                const int k1 = k + 1;
+                const uint4 a0 = st[((0 * HCH) + k1) * 16 + (ty ^ k1)], a1 = st[((1 * HCH) + k1) * 16 + (ty ^ k1)], a2 = st[((2 * HCH) + k1) * 16 + (ty ^ k1)];
+                const uint4 b0 = st[((3 * HCH) + k1) * 16 + (tx ^ k1)], b1 = st[((4 * HCH) + k1) * 16 + (tx ^ k1)], b2 = st[((5 * HCH) + k1) * 16 + (tx ^ k1)];
+                const uint32_t A0[4] = {a0.x, a0.y, a0.z, a0.w}, A1[4] = {a1.x, a1.y, a1.z, a1.w}, A2[4] = {a2.x, a2.y, a2.z, a2.w};
+                const uint32_t B0[4] = {b0.x, b0.y, b0.z, b0.w}, B1[4] = {b1.x, b1.y, b1.z, b1.w}, B2[4] = {b2.x, b2.y, b2.z, b2.w};
+#pragma unroll
+                for (int r = 0; r < 4; ++r)
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const uint32_t m2 = (A0[r] ^ B0[q]) | (A1[r] ^ B1[q]) | (A2[r] ^ B2[q]);
+                        const uint32_t o = ones[r][q], x = m1[r][q];
+                        acc2[r][q] += __popc((o & x) | (o & m2) | (x & m2));        // carry: weight 2
+                        ones[r][q] = o ^ x ^ m2;
+                    }
+            }
+        }
+        __syncthreads();                                  // the stage is refilled by the next iteration's cp.async
+    }
+
+    const bool do_quirk = quirk && (L % 32u == 0u) && W32 > 0;
+    unsigned int myI[4] = {0, 0, 0, 0}, myJ[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        const uint32_t si = i0 + 4 * ty + r;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const uint32_t sj = j0 + 4 * tx + q;
+            if (si < n && sj < n && si < sj) {
+                unsigned long long eff = (unsigned long long)L - (2u * acc2[r][q] + (uint32_t)__popc(ones[r][q]));
+                if (do_quirk) {
+                    // reference double-counts the final 32-column block when L % 32 == 0
+                    const size_t oi = (size_t)si * W32 + (W32 - 1), oj = (size_t)sj * W32 + (W32 - 1);
+                    const uint32_t d = (planes[oi] ^ planes[oj]) | (planes[plane + oi] ^ planes[plane + oj]) |
+                                       (planes[2 * plane + oi] ^ planes[2 * plane + oj]);
+                    eff += 32u - __popc(d);
+                }
+                if (eff >= min_identical) { myI[r]++; myJ[q]++; }
+            }
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < 4; ++r) if (myI[r]) atomicAdd(&cntI[4 * ty + r], myI[r]);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) if (myJ[q]) atomicAdd(&cntJ[4 * tx + q], myJ[q]);
+    __syncthreads();
+    if (threadIdx.x < HT) {
+        const uint32_t si = i0 + threadIdx.x, sj = j0 + threadIdx.x;
+        if (si < n && cntI[threadIdx.x]) atomicAdd(&counts[si], (unsigned long long)cntI[threadIdx.x]);
+        if (sj < n && cntJ[threadIdx.x]) atomicAdd(&counts[sj], (unsigned long long)cntJ[threadIdx.x]);
+    }
+}
+
 __global__ void fill_ones_kernel(unsigned long long* counts, uint32_t n, unsigned long long v) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) counts[i] = v;        // 1 = multiplicity of the sample itself (weights.hpp:205-206); partition 0 carries it
@@ -104,9 +245,24 @@ int hamming_neighbour_counts(Ctx* c, uint64_t min_identical, int quirk, uint32_t
     const uint32_t nt = (c->n + HT - 1) / HT;
     SPK_CUDA(c, cudaEventRecord(c->ev[0], c->stream));
     fill_ones_kernel<<<(c->n + 255) / 256, 256, 0, c->stream>>>((unsigned long long*)c->d_counts, c->n, part == 0 ? 1ull : 0ull);
-    hamming_tile_kernel<<<dim3(nt, nt), 256, 0, c->stream>>>(c->d_planes, c->n, c->L, c->W32,
-                                                             (unsigned long long)min_identical, quirk,
-                                                             (unsigned long long*)c->d_counts, part, n_parts);
+    static const bool v1 = [] { const char* e = getenv("SPYDRPICK_B200_K1"); return e && e[0] == '0'; }();
+    if (n_parts == 0) n_parts = 1;
+    const unsigned long long T = (unsigned long long)nt * (nt + 1) / 2;
+    if (v1 || nt >= 16384u)
+        hamming_tile_kernel<<<dim3(nt, nt), 256, 0, c->stream>>>(c->d_planes, c->n, c->L, c->W32,
+                                                                 (unsigned long long)min_identical, quirk,
+                                                                 (unsigned long long*)c->d_counts, part, n_parts);
+    else if (T > part) {
+        static bool attr_set = false;
+        if (!attr_set) {
+            SPK_CUDA(c, cudaFuncSetAttribute(hamming_csa_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HC_SMEM_BYTES));
+            attr_set = true;
+        }
+        const unsigned grid = (unsigned)((T - part + n_parts - 1) / n_parts);
+        hamming_csa_kernel<<<grid, 256, HC_SMEM_BYTES, c->stream>>>(c->d_planes, c->n, c->L, c->W32, nt,
+                                                                    (unsigned long long)min_identical, quirk,
+                                                                    (unsigned long long*)c->d_counts, part, n_parts);
+    }
     c->tm.kernel_launches += 2;
     SPK_CUDA(c, cudaEventRecord(c->ev[1], c->stream));
     SPK_CUDA(c, cudaEventSynchronize(c->ev[1]));

@@ -295,6 +295,10 @@ mi_refine_grouped_kernel(const uint8_t* __restrict__ masks, const Candidate* __r
 // K2 tile, so the threads of a warp mostly share the class pair (little divergence) and one of the two columns
 // (broadcast loads).
 // =============================================================================================
+__device__ __forceinline__ double popc_f64(uint32_t x) {
+    return __hiloint2double(0x43300000, __popc(x)) - 4503599627370496.0;
+}
+
 template <int KI, int KJ>
 __device__ __forceinline__ void pair_eval(const uint32_t* __restrict__ gbits, const double* __restrict__ gval,
                                        const double* __restrict__ gmarg, const double* __restrict__ gH, uint32_t NW,
@@ -331,11 +335,12 @@ __device__ __forceinline__ void pair_eval(const uint32_t* __restrict__ gbits, co
         for (int a = 0; a < KI; ++a)
 #pragma unroll
             for (int b = 0; b < KJ; ++b) {
+                // popcount -> double without I2F.F64 (which shares the quarter-rate pipe with POPC): 2^52 + c, minus 2^52 (exact)
                 double t = acc[a][b];
-                t = fma((double)__popc(xi[a].x & xj[b].x), v01.x, t);
-                t = fma((double)__popc(xi[a].y & xj[b].y), v01.y, t);
-                t = fma((double)__popc(xi[a].z & xj[b].z), v23.x, t);
-                t = fma((double)__popc(xi[a].w & xj[b].w), v23.y, t);
+                t = fma(popc_f64(xi[a].x & xj[b].x), v01.x, t);
+                t = fma(popc_f64(xi[a].y & xj[b].y), v01.y, t);
+                t = fma(popc_f64(xi[a].z & xj[b].z), v23.x, t);
+                t = fma(popc_f64(xi[a].w & xj[b].w), v23.y, t);
                 acc[a][b] = t;
             }
     }
