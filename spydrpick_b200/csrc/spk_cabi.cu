@@ -389,6 +389,26 @@ int spk_mi_scan(spk_ctx* c, const spk_scan_params* pp, spk_scan_result* res) {
     }
     break;
     }
+    // pinned mirrors: D2H at full PCIe rate, no page-fault pass over a fresh std::vector
+    auto grow = [&](spk_edge*& buf, uint64_t& cap, uint64_t want) -> int {
+        if (want <= cap) return SPK_OK;
+        if (buf) { cudaFreeHost(buf); buf = nullptr; cap = 0; }
+        const uint64_t newcap = want + want / 4 + 1024;
+        if (cudaHostAlloc((void**)&buf, newcap * sizeof(spk_edge), cudaHostAllocDefault) != cudaSuccess) {
+            cudaGetLastError(); return fail(c, SPK_E_NOMEM, "pinned host allocation failed (%llu edges)", (unsigned long long)newcap);
+        }
+        cap = newcap; return SPK_OK;
+    };
+    bool wo_in_flight = false;
+    if (p.keep_on_device == 2 && nw) {
+        // the MI-without-gaps list is final after compaction (the sort only touches the edge list): its download
+        // starts now on the side stream and runs under the edge sort
+        if ((r = grow(c->hp_wo, c->hp_wo_cap, nw))) return r;
+        SPK_CUDA(c, cudaEventRecord(c->ev_ready, c->stream));
+        SPK_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->ev_ready, 0));
+        SPK_CUDA(c, cudaMemcpyAsync(c->hp_wo, c->d_wo, nw * sizeof(spk_edge), cudaMemcpyDeviceToHost, c->copy_stream));
+        wo_in_flight = true;
+    }
     if (p.sort_desc) { r = sort_edges_device(c, c->d_edges, ne); if (r) return r; }
     res->n_edges = ne; res->n_wo_gaps = nw;
     res->d_edges = c->d_edges; res->d_edges_wo_gaps = c->d_wo; res->d_colmax = c->d_colmax;
@@ -396,16 +416,6 @@ int spk_mi_scan(spk_ctx* c, const spk_scan_params* pp, spk_scan_result* res) {
     SPK_CUDA(c, cudaMemcpyAsync(c->h_colmax.data(), c->d_colmax, (size_t)c->L * 8, cudaMemcpyDeviceToHost, c->stream));
     c->host_edges_n = 0;
     if (p.keep_on_device != 1) {
-        // pinned mirrors: D2H at full PCIe rate, no page-fault pass over a fresh std::vector
-        auto grow = [&](spk_edge*& buf, uint64_t& cap, uint64_t want) -> int {
-            if (want <= cap) return SPK_OK;
-            if (buf) { cudaFreeHost(buf); buf = nullptr; cap = 0; }
-            const uint64_t newcap = want + want / 4 + 1024;
-            if (cudaHostAlloc((void**)&buf, newcap * sizeof(spk_edge), cudaHostAllocDefault) != cudaSuccess) {
-                cudaGetLastError(); return fail(c, SPK_E_NOMEM, "pinned host allocation failed (%llu edges)", (unsigned long long)newcap);
-            }
-            cap = newcap; return SPK_OK;
-        };
         if ((r = grow(c->hp_edges, c->hp_edges_cap, ne))) return r;
         if ((r = grow(c->hp_wo, c->hp_wo_cap, nw))) return r;
         // keep_on_device == 2: the copies run on a side stream and overlap whatever the caller launches next (ARACNE on the
@@ -417,7 +427,7 @@ int spk_mi_scan(spk_ctx* c, const spk_scan_params* pp, spk_scan_result* res) {
             cs = c->copy_stream;
         }
         if (ne) SPK_CUDA(c, cudaMemcpyAsync(c->hp_edges, c->d_edges, ne * sizeof(spk_edge), cudaMemcpyDeviceToHost, cs));
-        if (nw) SPK_CUDA(c, cudaMemcpyAsync(c->hp_wo, c->d_wo, nw * sizeof(spk_edge), cudaMemcpyDeviceToHost, cs));
+        if (nw && !wo_in_flight) SPK_CUDA(c, cudaMemcpyAsync(c->hp_wo, c->d_wo, nw * sizeof(spk_edge), cudaMemcpyDeviceToHost, cs));
         if (p.keep_on_device == 2) { SPK_CUDA(c, cudaEventRecord(c->ev_dl, cs)); c->dl_pending = true; }
         if (p.sort_desc) c->host_edges_n = ne;
     }

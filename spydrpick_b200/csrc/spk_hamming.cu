@@ -9,10 +9,10 @@
 // Integer arithmetic, bit-exact. Each block owns a 64x64 tile of sample pairs and streams the
 // bit planes through shared memory in 16-word chunks; each thread keeps a 4x4 register tile.
 //
-// hamming_csa_kernel (default) is bound by instruction issue, not by POPC: the mismatch words of two consecutive
-// plane words go through a carry-save adder per pair cell (ones' = ones ^ m1 ^ m2, carry = maj(ones, m1, m2);
-// mismatches = 2 * sum popc(carry) + popc(ones)), so there is ONE popcount per two words (POPC runs at a quarter
-// of the LOP3 rate). The chunk is stored transposed and XOR-swizzled in shared memory ([plane][word][64 samples]),
+// hamming_csa_kernel (default) balances the two pipes the loop needs (LOP3 on the ALU pipe, POPC on the quarter-rate
+// XU pipe): in 3 of the 16 pair cells of a thread the mismatch words of two consecutive plane words go through a
+// carry-save adder (ones' = ones ^ m1 ^ m2, carry = maj(ones, m1, m2); mismatches = 2 * sum popc(carry) + popc(ones)),
+// i.e. ONE popcount per two words for one more LOP3; the other 13 cells count every word. The chunk is stored transposed and XOR-swizzled in shared memory ([plane][word][64 samples]),
 // so a thread's four rows / four columns of one word are ONE 16-byte LDS (6 LDS.128 per word instead of 24 LDS.32),
 // and chunks arrive by cp.async (zero-fill outside the alignment) into a two-stage ring. Only the upper-triangle
 // tile pairs are launched. hamming_tile_kernel is the first version, kept for A/B runs (SPYDRPICK_B200_K1=0).
@@ -116,18 +116,35 @@ __device__ __forceinline__ void hc_cp_async4(uint32_t dst_smem, const void* src,
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst_smem), "l"(src), "r"(src_bytes) : "memory");
 }
 
-__device__ __forceinline__ void hc_issue_chunk(uint32_t stage_base, const uint32_t* __restrict__ planes, size_t plane, uint32_t n,
-                                               uint32_t W32, uint32_t i0, uint32_t j0, uint32_t w0) {
-    // 2 * 3 * 64 * 16 = 6144 words, 24 per thread; lanes run over the 16 words of one sample row (64-byte runs)
-#pragma unroll 4
-    for (uint32_t e = threadIdx.x; e < (uint32_t)HC_STAGE_WORDS; e += 256) {
-        const uint32_t k = e % HCH, r = (e / HCH) % HT, pw = e / (HCH * HT);      // pw = which * 3 + plane
-        const uint32_t p = pw % 3u, which = pw / 3u;
-        const uint32_t s = (which ? j0 : i0) + r, w = w0 + k;
-        const bool ok = (s < n) && (w < W32);
-        const uint32_t* src = ok ? planes + p * plane + (size_t)s * W32 + w : planes;
-        const uint32_t dst = stage_base + 4u * ((pw * HCH + k) * HT + 4u * ((r >> 2) ^ k) + (r & 3u));
-        hc_cp_async4(dst, src, ok ? 4u : 0u);
+// Per-thread constants of the chunk copy. Thread t copies word k = t % 16 of rows r0 + 16*ri (r0 = t / 16, ri = 0..3) of
+// the six (I/J, plane) sub-arrays: 24 cp.async of 4 bytes per chunk, lanes running over the 16 words of a row (64-byte
+// runs). Everything that does not depend on the chunk is computed once, so that a copy costs a handful of instructions
+// (the generic index arithmetic had cost more ALU work than the 48 LOP3 of the mismatch words it feeds).
+// Pipe balance: LOP3 / IADD3 issue at 16 lanes per clock and SM sub-partition, POPC at 4. A plain cell costs 3 LOP3 + 1 POPC
+// (+ half an IADD3) per word, a carry-save cell 4 LOP3 + half a POPC: 13 plain + 3 carry-save cells of the 4x4 register tile
+// load the two pipes about equally (ncu of the all-carry-save version: ALU pipe 87 % busy, XU 29 %).
+__host__ __device__ constexpr bool hc_csa_cell(int r, int q) { return q == 3 && r < 3; }
+
+struct HcCopy {
+    uint32_t offI, offJ;        // word offset of (row i0 + r0, word k) / (row j0 + r0, word k) inside plane 0
+    uint32_t rstride;           // 16 rows further: 16 * W32 words
+    uint32_t plane32;           // words per plane
+    int limI, limJ;             // rows r0 + 16*ri exist while 16*ri < lim
+    uint32_t dthread;           // byte offset of (k, low swizzle bits, r0 & 3) inside a (I/J, plane) sub-array
+    uint32_t kh64;              // 64 * (k >> 2): xor-ed with 64 * ri (the high swizzle bits)
+    uint32_t k;
+};
+
+__device__ __forceinline__ void hc_issue_chunk(uint32_t stage_base, const uint32_t* __restrict__ planes, const HcCopy& cp,
+                                               uint32_t W32, uint32_t w0) {
+    const bool wok = w0 + cp.k < W32;
+#pragma unroll
+    for (int it = 0; it < 24; ++it) {
+        const int ri = it % 4, pw = it / 4, p = pw % 3, which = pw / 3;      // pw = which * 3 + plane
+        const bool ok = wok && (16 * ri < (which ? cp.limJ : cp.limI));
+        const uint32_t off = (which ? cp.offJ : cp.offI) + (uint32_t)ri * cp.rstride + (uint32_t)p * cp.plane32 + w0;
+        const uint32_t dst = stage_base + cp.dthread + (uint32_t)pw * (HCH * HT * 4) + (cp.kh64 ^ (uint32_t)(64 * ri));
+        hc_cp_async4(dst, planes + (ok ? off : 0u), ok ? 4u : 0u);
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
 }
@@ -159,10 +176,21 @@ hamming_csa_kernel(const uint32_t* __restrict__ planes, uint32_t n, uint32_t L, 
         for (int q = 0; q < 4; ++q) { acc2[r][q] = 0; ones[r][q] = 0; }
 
     const uint32_t nchunks = (W32 + HCH - 1) / HCH;
-    hc_issue_chunk(smem_base, planes, plane, n, W32, i0, j0, 0);
+    HcCopy cp;
+    {
+        const uint32_t k = threadIdx.x % HCH, r0 = threadIdx.x / HCH;       // r0 = 0..15
+        cp.k = k;
+        cp.offI = (i0 + r0) * W32 + k; cp.offJ = (j0 + r0) * W32 + k;
+        cp.rstride = 16u * W32; cp.plane32 = n * W32;
+        cp.limI = (int)n - (int)(i0 + r0); cp.limJ = (int)n - (int)(j0 + r0);
+        // row r = r0 + 16*ri: group r >> 2 = (r0 >> 2) + 4*ri, swizzled with k: low bits (r0 >> 2) ^ (k & 3), high bits ri ^ (k >> 2)
+        cp.dthread = 4u * (k * HT + 4u * ((r0 >> 2) ^ (k & 3u)) + (r0 & 3u));
+        cp.kh64 = 64u * (k >> 2);
+    }
+    hc_issue_chunk(smem_base, planes, cp, W32, 0);
     for (uint32_t ch = 0; ch < nchunks; ++ch) {
         if (ch + 1 < nchunks) {
-            hc_issue_chunk(smem_base + ((ch + 1) % HC_STAGES) * HC_STAGE_WORDS * 4, planes, plane, n, W32, i0, j0, (ch + 1) * HCH);
+            hc_issue_chunk(smem_base + ((ch + 1) % HC_STAGES) * HC_STAGE_WORDS * 4, planes, cp, W32, (ch + 1) * HCH);
             asm volatile("cp.async.wait_group 1;" ::: "memory");
         } else {
             asm volatile("cp.async.wait_group 0;" ::: "memory");
@@ -194,9 +222,14 @@ hamming_csa_kernel(const uint32_t* __restrict__ planes, uint32_t n, uint32_t L, 
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
                         const uint32_t m2 = (A0[r] ^ B0[q]) | (A1[r] ^ B1[q]) | (A2[r] ^ B2[q]);
-                        const uint32_t o = ones[r][q], x = m1[r][q];
-                        acc2[r][q] += __popc((o & x) | (o & m2) | (x & m2));        // carry: weight 2
-                        ones[r][q] = o ^ x ^ m2;
+                        const uint32_t x = m1[r][q];
+                        if (hc_csa_cell(r, q)) {
+                            const uint32_t o = ones[r][q];
+                            acc2[r][q] += __popc((o & x) | (o & m2) | (x & m2));    // carry: weight 2
+                            ones[r][q] = o ^ x ^ m2;
+                        } else {
+                            acc2[r][q] += __popc(x) + __popc(m2);                    // plain cell: one IADD3 for two popcounts
+                        }
                     }
             }
         }
@@ -212,7 +245,7 @@ hamming_csa_kernel(const uint32_t* __restrict__ planes, uint32_t n, uint32_t L, 
         for (int q = 0; q < 4; ++q) {
             const uint32_t sj = j0 + 4 * tx + q;
             if (si < n && sj < n && si < sj) {
-                unsigned long long eff = (unsigned long long)L - (2u * acc2[r][q] + (uint32_t)__popc(ones[r][q]));
+                unsigned long long eff = (unsigned long long)L - (hc_csa_cell(r, q) ? 2u * acc2[r][q] + (uint32_t)__popc(ones[r][q]) : acc2[r][q]);
                 if (do_quirk) {
                     // reference double-counts the final 32-column block when L % 32 == 0
                     const size_t oi = (size_t)si * W32 + (W32 - 1), oj = (size_t)sj * W32 + (W32 - 1);
@@ -248,7 +281,7 @@ int hamming_neighbour_counts(Ctx* c, uint64_t min_identical, int quirk, uint32_t
     static const bool v1 = [] { const char* e = getenv("SPYDRPICK_B200_K1"); return e && e[0] == '0'; }();
     if (n_parts == 0) n_parts = 1;
     const unsigned long long T = (unsigned long long)nt * (nt + 1) / 2;
-    if (v1 || nt >= 16384u)
+    if (v1 || nt >= 16384u || (unsigned long long)3 * c->n * c->W32 >= (1ull << 32))
         hamming_tile_kernel<<<dim3(nt, nt), 256, 0, c->stream>>>(c->d_planes, c->n, c->L, c->W32,
                                                                  (unsigned long long)min_identical, quirk,
                                                                  (unsigned long long*)c->d_counts, part, n_parts);

@@ -7,6 +7,7 @@
 // samples and accumulate into lane-private shared-memory bins (no atomics, deterministic), then
 // lane l < 25 owns cell l = b*5+a and the entropy terms are evaluated one log per lane.
 #include <cfloat>
+#include <cstdlib>
 #include <algorithm>
 #include <vector>
 #include "spk_internal.h"
@@ -299,51 +300,35 @@ __device__ __forceinline__ double popc_f64(uint32_t x) {
     return __hiloint2double(0x43300000, __popc(x)) - 4503599627370496.0;
 }
 
+// kept one-hot rows of a column pair: si / sj = plane (state) of each kept row (an absent state's all-zero plane
+// beyond ki / kj), di / dj = the recovered state (highest present: the gap if the column has gaps)
 template <int KI, int KJ>
-__device__ __forceinline__ void pair_eval(const uint32_t* __restrict__ gbits, const double* __restrict__ gval,
-                                       const double* __restrict__ gmarg, const double* __restrict__ gH, uint32_t NW,
-                                       uint32_t i, uint32_t j, uint32_t mask_i, uint32_t mask_j, double w_total, double pc,
-                                       double wo_threshold, double* out_m, double* out_m2) {
+struct PairRows { uint32_t si[KI], sj[KJ], ki, kj, di, dj; };
+
+template <int KI, int KJ>
+__device__ __forceinline__ PairRows<KI, KJ> pair_rows(uint32_t mask_i, uint32_t mask_j) {
+    PairRows<KI, KJ> R;
+    uint32_t* si = R.si; uint32_t* sj = R.sj;
     const uint32_t di = 31u - __clz(mask_i | 1u), dj = 31u - __clz(mask_j | 1u);      // recovered states (gap if present)
     const uint32_t zi = __ffs(~mask_i & 31u) - 1, zj = __ffs(~mask_j & 31u) - 1;      // an absent state: all-zero plane
-    uint32_t si[KI], sj[KJ];
     uint32_t mk = mask_i & ~(1u << di), ki = 0, kj = 0;
 #pragma unroll
     for (int a = 0; a < KI; ++a) { if (mk) { si[a] = __ffs(mk) - 1; mk &= mk - 1; ++ki; } else si[a] = zi; }
     mk = mask_j & ~(1u << dj);
 #pragma unroll
     for (int b = 0; b < KJ; ++b) { if (mk) { sj[b] = __ffs(mk) - 1; mk &= mk - 1; ++kj; } else sj[b] = zj; }
-    const uint4* Bi[KI]; const uint4* Bj[KJ];
-#pragma unroll
-    for (int a = 0; a < KI; ++a) Bi[a] = reinterpret_cast<const uint4*>(gbits + ((size_t)i * NSTATES + si[a]) * NW);
-#pragma unroll
-    for (int b = 0; b < KJ; ++b) Bj[b] = reinterpret_cast<const uint4*>(gbits + ((size_t)j * NSTATES + sj[b]) * NW);
-    double acc[KI][KJ];
-#pragma unroll
-    for (int a = 0; a < KI; ++a)
-#pragma unroll
-        for (int b = 0; b < KJ; ++b) acc[a][b] = 0.0;
-    const double2* gv2 = reinterpret_cast<const double2*>(gval);
-    for (uint32_t w4 = 0; w4 < NW / 4; ++w4) {
-        const double2 v01 = gv2[2 * w4], v23 = gv2[2 * w4 + 1];
-        uint4 xi[KI], xj[KJ];
-#pragma unroll
-        for (int a = 0; a < KI; ++a) xi[a] = __ldg(Bi[a] + w4);
-#pragma unroll
-        for (int b = 0; b < KJ; ++b) xj[b] = __ldg(Bj[b] + w4);
-#pragma unroll
-        for (int a = 0; a < KI; ++a)
-#pragma unroll
-            for (int b = 0; b < KJ; ++b) {
-                // popcount -> double without I2F.F64 (which shares the quarter-rate pipe with POPC): 2^52 + c, minus 2^52 (exact)
-                double t = acc[a][b];
-                t = fma(popc_f64(xi[a].x & xj[b].x), v01.x, t);
-                t = fma(popc_f64(xi[a].y & xj[b].y), v01.y, t);
-                t = fma(popc_f64(xi[a].z & xj[b].z), v23.x, t);
-                t = fma(popc_f64(xi[a].w & xj[b].w), v23.y, t);
-                acc[a][b] = t;
-            }
-    }
+    R.ki = ki; R.kj = kj; R.di = di; R.dj = dj;
+    return R;
+}
+
+// from the KI x KJ kept cells to MI (and, for saved pairs touching a gap column, the literal MI-without-gaps)
+template <int KI, int KJ>
+__device__ __forceinline__ void pair_tail(const double (&acc)[KI][KJ], const PairRows<KI, KJ>& R,
+                                       const double* __restrict__ gmarg, const double* __restrict__ gH,
+                                       uint32_t i, uint32_t j, uint32_t mask_i, uint32_t mask_j, double w_total, double pc,
+                                       double wo_threshold, double* out_m, double* out_m2) {
+    const uint32_t* si = R.si; const uint32_t* sj = R.sj;
+    const uint32_t ki = R.ki, kj = R.kj, di = R.di;
     // full table over (kept rows + recovered row) x (kept cols + recovered col); index KI / KJ = recovered state
     double N[KI + 1][KJ + 1];
     double colsum[KJ];
@@ -421,6 +406,47 @@ __device__ __forceinline__ void pair_eval(const uint32_t* __restrict__ gbits, co
         m2 = jH - rH - cH;
     }
     *out_m2 = m2;
+}
+
+template <int KI, int KJ>
+__device__ __forceinline__ void pair_eval(const uint32_t* __restrict__ gbits, const double* __restrict__ gval,
+                                       const double* __restrict__ gmarg, const double* __restrict__ gH, uint32_t NW,
+                                       uint32_t i, uint32_t j, uint32_t mask_i, uint32_t mask_j, double w_total, double pc,
+                                       double wo_threshold, double* out_m, double* out_m2) {
+    const PairRows<KI, KJ> R = pair_rows<KI, KJ>(mask_i, mask_j);
+    const uint32_t* si = R.si; const uint32_t* sj = R.sj;
+    const uint4* Bi[KI]; const uint4* Bj[KJ];
+#pragma unroll
+    for (int a = 0; a < KI; ++a) Bi[a] = reinterpret_cast<const uint4*>(gbits + ((size_t)i * NSTATES + si[a]) * NW);
+#pragma unroll
+    for (int b = 0; b < KJ; ++b) Bj[b] = reinterpret_cast<const uint4*>(gbits + ((size_t)j * NSTATES + sj[b]) * NW);
+    double acc[KI][KJ];
+#pragma unroll
+    for (int a = 0; a < KI; ++a)
+#pragma unroll
+        for (int b = 0; b < KJ; ++b) acc[a][b] = 0.0;
+    const double2* gv2 = reinterpret_cast<const double2*>(gval);
+    for (uint32_t w4 = 0; w4 < NW / 4; ++w4) {
+        const double2 v01 = gv2[2 * w4], v23 = gv2[2 * w4 + 1];
+        uint4 xi[KI], xj[KJ];
+#pragma unroll
+        for (int a = 0; a < KI; ++a) xi[a] = __ldg(Bi[a] + w4);
+#pragma unroll
+        for (int b = 0; b < KJ; ++b) xj[b] = __ldg(Bj[b] + w4);
+#pragma unroll
+        for (int a = 0; a < KI; ++a)
+#pragma unroll
+            for (int b = 0; b < KJ; ++b) {
+                // popcount -> double without I2F.F64 (which shares the quarter-rate pipe with POPC): 2^52 + c, minus 2^52 (exact)
+                double t = acc[a][b];
+                t = fma(popc_f64(xi[a].x & xj[b].x), v01.x, t);
+                t = fma(popc_f64(xi[a].y & xj[b].y), v01.y, t);
+                t = fma(popc_f64(xi[a].z & xj[b].z), v23.x, t);
+                t = fma(popc_f64(xi[a].w & xj[b].w), v23.y, t);
+                acc[a][b] = t;
+            }
+    }
+    pair_tail<KI, KJ>(acc, R, gmarg, gH, i, j, mask_i, mask_j, w_total, pc, wo_threshold, out_m, out_m2);
 }
 
 template <int KI, int KJ>
@@ -549,6 +575,100 @@ mi_refine_class_kernel(const uint8_t* __restrict__ masks, const Candidate* __res
 #pragma unroll
     for (int o = 16; o; o >>= 1) err = fmax(err, __shfl_xor_sync(0xffffffffu, err, o));
     if ((threadIdx.x & 31) == 0 && err > 0.0) atomicMax(&counters[3], f64_ordered(err));
+}
+
+// Cooperative version of mi_refine_class_kernel. Thread-per-pair plane loads are 32 scattered 16-byte requests per
+// instruction: ncu showed the class kernels L1TEX-bound (l1tex throughput 86-96 %, issue slots 18-36 % busy). Here a
+// group of G lanes walks the planes of ONE pair together (G x 16 contiguous bytes per load: whole 128-byte lines for
+// G = 8), one pair of the group after the other; the G partial tables of the group's G pairs are then summed with a
+// transposing butterfly (G-1 exchanges per cell instead of G log G) that leaves lane t of the group with the complete
+// table of ITS pair, and the entropy tail runs thread-per-pair as before. G = min(8, 32 / (KI*KJ)) bounds the
+// partial tables at 32 doubles per thread.
+template <int KI, int KJ, int G>
+__global__ void __launch_bounds__(128)
+mi_refine_coop_kernel(const uint8_t* __restrict__ masks, const Candidate* __restrict__ cand, unsigned long long ncand,
+                      double pc, double w_total, double wo_threshold,
+                      spk_edge* __restrict__ refined, double* __restrict__ refined_wo, unsigned long long* __restrict__ counters,
+                      const uint32_t* __restrict__ gbits, const double* __restrict__ gval, const double* __restrict__ gmarg,
+                      const double* __restrict__ gH, uint32_t NW) {
+    constexpr int C = KI * KJ;
+    const unsigned long long p = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t lane = threadIdx.x % 32, sub = lane % G;
+    const bool live = p < ncand;
+    Candidate cd; cd.i = 0; cd.j = 0; cd.mi32 = 0.f;
+    if (live) cd = cand[p];
+    const uint32_t mask_i = masks[cd.i], mask_j = masks[cd.j];
+    const PairRows<KI, KJ> R = pair_rows<KI, KJ>(mask_i, mask_j);
+    uint32_t rowi[KI], rowj[KJ];                    // plane row index (column * NSTATES + state)
+#pragma unroll
+    for (int a = 0; a < KI; ++a) rowi[a] = cd.i * NSTATES + R.si[a];
+#pragma unroll
+    for (int b = 0; b < KJ; ++b) rowj[b] = cd.j * NSTATES + R.sj[b];
+    const double2* gv2 = reinterpret_cast<const double2*>(gval);
+    const uint32_t nchunk = NW / 4;                  // uint4 chunks per plane row (NW is a multiple of 32)
+
+    double part[G][C];
+#pragma unroll
+    for (int t = 0; t < G; ++t) {
+        const uint4* Bi[KI]; const uint4* Bj[KJ];
+#pragma unroll
+        for (int a = 0; a < KI; ++a) Bi[a] = reinterpret_cast<const uint4*>(gbits + (size_t)__shfl_sync(0xffffffffu, rowi[a], t, G) * NW);
+#pragma unroll
+        for (int b = 0; b < KJ; ++b) Bj[b] = reinterpret_cast<const uint4*>(gbits + (size_t)__shfl_sync(0xffffffffu, rowj[b], t, G) * NW);
+        double acc[C];
+#pragma unroll
+        for (int q = 0; q < C; ++q) acc[q] = 0.0;
+        for (uint32_t w4 = sub; w4 < nchunk; w4 += G) {
+            const double2 v01 = gv2[2 * w4], v23 = gv2[2 * w4 + 1];
+            uint4 xi[KI], xj[KJ];
+#pragma unroll
+            for (int a = 0; a < KI; ++a) xi[a] = __ldg(Bi[a] + w4);
+#pragma unroll
+            for (int b = 0; b < KJ; ++b) xj[b] = __ldg(Bj[b] + w4);
+#pragma unroll
+            for (int a = 0; a < KI; ++a)
+#pragma unroll
+                for (int b = 0; b < KJ; ++b) {
+                    double v = acc[a * KJ + b];
+                    v = fma(popc_f64(xi[a].x & xj[b].x), v01.x, v);
+                    v = fma(popc_f64(xi[a].y & xj[b].y), v01.y, v);
+                    v = fma(popc_f64(xi[a].z & xj[b].z), v23.x, v);
+                    v = fma(popc_f64(xi[a].w & xj[b].w), v23.y, v);
+                    acc[a * KJ + b] = v;
+                }
+        }
+#pragma unroll
+        for (int q = 0; q < C; ++q) part[t][q] = acc[q];
+    }
+    // transposing butterfly: after the step with distance h, slot k holds the partial table of pair k + (sub & ~(h-1)... )
+#pragma unroll
+    for (int h = G / 2; h >= 1; h /= 2) {
+        const bool up = (sub & h) != 0;
+#pragma unroll
+        for (int k = 0; k < h; ++k)
+#pragma unroll
+            for (int q = 0; q < C; ++q) {
+                const double send = up ? part[k][q] : part[k + h][q];
+                const double keep = up ? part[k + h][q] : part[k][q];
+                part[k][q] = keep + __shfl_xor_sync(0xffffffffu, send, h);
+            }
+    }
+    double acc2[KI][KJ];
+#pragma unroll
+    for (int a = 0; a < KI; ++a)
+#pragma unroll
+        for (int b = 0; b < KJ; ++b) acc2[a][b] = part[0][a * KJ + b];
+    double err = 0.0;
+    if (live) {
+        double m = 0.0, m2 = 0.0;
+        pair_tail<KI, KJ>(acc2, R, gmarg, gH, cd.i, cd.j, mask_i, mask_j, w_total, pc, wo_threshold, &m, &m2);
+        spk_edge e; e.i = cd.i; e.j = cd.j; e.mi = m;
+        refined[p] = e; refined_wo[p] = m2;
+        if (cd.mi32 == cd.mi32) err = fabs((double)cd.mi32 - m);
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) err = fmax(err, __shfl_xor_sync(0xffffffffu, err, o));
+    if (lane == 0 && err > 0.0) atomicMax(&counters[3], f64_ordered(err));
 }
 
 // ---- K2b: explicit pair list ---------------------------------------------------------------
@@ -798,8 +918,13 @@ int mi_refine_candidates(Ctx* c, uint64_t ncand, double pc, double wo_threshold,
             const unsigned long long n_q = h_cnt[q], o_q = h_off[q];
             if (!n_q) continue;
             const unsigned g = (unsigned)((n_q + 127) / 128);
-#define SPK_RCASE(Q, A, B) case Q: mi_refine_class_kernel<A, B><<<g, 128, 0, c->stream>>>(c->d_masks, c->d_cand2 + o_q, n_q, pc, c->w_total, wo_threshold, \
-                c->d_refined + o_q, c->d_refined_wo + o_q, c->d_counters, c->d_gbits, c->d_gval, c->d_gmarg, c->d_gH, c->g_NW); break;
+            static const bool coop = [] { const char* e = getenv("SPYDRPICK_B200_REFINE_COOP"); return !(e && e[0] == '0'); }();
+#define SPK_RCASE(Q, A, B) case Q: \
+                if (coop) mi_refine_coop_kernel<A, B, ((A) * (B) <= 4 ? 8 : ((A) * (B) == 8 ? 4 : 2))><<<g, 128, 0, c->stream>>>(c->d_masks, c->d_cand2 + o_q, n_q, pc, c->w_total, wo_threshold, \
+                    c->d_refined + o_q, c->d_refined_wo + o_q, c->d_counters, c->d_gbits, c->d_gval, c->d_gmarg, c->d_gH, c->g_NW); \
+                else mi_refine_class_kernel<A, B><<<g, 128, 0, c->stream>>>(c->d_masks, c->d_cand2 + o_q, n_q, pc, c->w_total, wo_threshold, \
+                    c->d_refined + o_q, c->d_refined_wo + o_q, c->d_counters, c->d_gbits, c->d_gval, c->d_gmarg, c->d_gH, c->g_NW); \
+                break;
             switch (q) {
                 SPK_RCASE(0, 1, 1) SPK_RCASE(1, 1, 2) SPK_RCASE(2, 1, 4)
                 SPK_RCASE(3, 2, 1) SPK_RCASE(4, 2, 2) SPK_RCASE(5, 2, 4)
