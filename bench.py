@@ -227,8 +227,13 @@ def run_b200(args):
         if world == 1:
             return None, r["d_edges"], ne
         mine = dev_bytes(torch, r["d_edges"], ne * 16, device)
-        merged, total, _ = sdist.allgather_edges(mine, ne)
+        merged, total, counts = sdist.allgather_edges(mine, ne)
         sdist.allreduce_colmax(dev_bytes(torch, r["d_colmax"], L * 8, device).view(torch.float64))
+        # every rank sorted its own edges inside the scan: the gathered list is G sorted runs -> G-1 merges, not a full sort.
+        # torch filled `merged` on ITS current stream (the legacy default stream, which the library's non-blocking stream
+        # does not wait for): the list must be complete before the pointer is handed over
+        torch.cuda.current_stream(device).synchronize()
+        ctx.merge_sorted_runs_device(merged.data_ptr(), counts)
         return merged, merged.data_ptr(), total
 
     def sharded_counts():
@@ -242,11 +247,9 @@ def run_b200(args):
         """alignment resident in HBM; results stay in HBM."""
         c = sharded_counts()
         ctx.set_weights(1.0 / c.astype(np.float64))
-        r = ctx.mi_scan(threshold, max_edges=max_edges, sort_desc=(world == 1), n_terms=args.n_terms, engine=args.engine,
+        r = ctx.mi_scan(threshold, max_edges=max_edges, sort_desc=True, n_terms=args.n_terms, engine=args.engine,
                         part_index=rank, n_parts=world, keep_on_device=True)
         keep, d_edges, ne = merge_across_ranks(r)
-        if world > 1:
-            ctx.sort_edges_device(d_edges, ne)
         flags = torch.zeros(max(ne, 1), dtype=torch.uint8, device=device)
         ctx.aracne_device(d_edges, ne, flags.data_ptr(), EPS, part_index=rank, n_parts=world)
         if world > 1:
@@ -291,10 +294,9 @@ def run_b200(args):
         else:
             # N > 1: the partial edge lists never visit the host -- NCCL allgather over NVLink, device sort + K3, then ONE
             # D2H of the merged list and the flags into pinned host buffers (what a caller of the multi-GPU path receives)
-            r = ctx.mi_scan(threshold, max_edges=max_edges, sort_desc=False, n_terms=args.n_terms, engine=args.engine,
+            r = ctx.mi_scan(threshold, max_edges=max_edges, sort_desc=True, n_terms=args.n_terms, engine=args.engine,
                             part_index=rank, n_parts=world, keep_on_device=True); tw.append(time.perf_counter())
-            keep, d_edges, ne = merge_across_ranks(r)
-            ctx.sort_edges_device(d_edges, ne)        # returns with the sorted list complete in HBM
+            keep, d_edges, ne = merge_across_ranks(r)   # returns with the merged, sorted list complete in HBM
             nonlocal host_edges, side
             if host_edges is None or host_edges.numel() < ne * 16:
                 host_edges = torch.empty(int(ne * 16 * 1.25) + 4096, dtype=torch.uint8).pin_memory()
@@ -397,7 +399,7 @@ def run_b200(args):
                 "dtype": "u8 x u8 -> s32 tensor filter + f64 refine" if i8 else "bf16 tensor filter + f64 refine",
                 "data": "synthetic",
                 "config": {"workload": "%dx%d synthetic SNP alignment: K1 reweighting + weighted MI scan + sort + ARACNE" % (n, L),
-                           "n": n, "L": L, "pairs": pairs_total, "saved_edges": int(ne), "mi_threshold": threshold,
+                           "n": n, "L": L, "pairs": pairs_total, "saved_edges": int(ne), "direct_edges": int(ndirect), "mi_threshold": threshold,
                            "engine": ("int8 compact one-hot, 16-bit weights as {hi, lo} rows" if args.engine == 3 else "int8 compact one-hot, factorised byte weights a*b") if i8 else "dense bf16 one-hot, n_terms=%d" % (args.n_terms or 2),
                            "l2_policy": "inputs (>1.5 GB one-hot operands) larger than L2",
                            "threshold_estimate_s": t_threshold, "parallelism": "tile-space partition x%d + NCCL edge allgather" % world},
@@ -409,7 +411,7 @@ def run_b200(args):
         if e2e:
             e2e["path"] = ("spk_set_alignment (pinned host states) -> K1 -> scan -> sort -> ARACNE, edges + flags downloaded" if world == 1 else
                            "per rank: H2D of n/G alignment rows + NVLink all-gather -> spk_set_alignment_device -> sharded K1/scan -> "
-                           "NCCL edge all-gather -> sort -> sharded ARACNE; rank 0 downloads the merged edges + flags "
+                           "per-rank edge sort -> NCCL edge all-gather -> run merge -> sharded ARACNE; rank 0 downloads the merged edges + flags "
                            "(h2d bytes are per rank, d2h bytes are rank 0's)")
             line["e2e"] = e2e
         if cpu:

@@ -168,6 +168,10 @@ int spk_wait_download(spk_ctx* ctx);
 /* Device-resident variants for callers that keep data in HBM (bench, multi-GPU plumbing):
  * d_edges is a device pointer to n_edges sorted spk_edge records, d_flags device uint8[n_edges]. */
 int spk_sort_edges_device(spk_ctx* ctx, void* d_edges, uint64_t n_edges);
+/* d_edges holds n_runs consecutive runs of run_counts[r] edges, each already in Graph::sort order (graph/Graph.hpp:234-242;
+ * e.g. the per-rank lists of a sharded scan, each sorted by its own GPU, after the all-gather): merged in place into the
+ * one sorted list -- the same list spk_sort_edges_device gives, for G-1 merges instead of a full sort on every rank. */
+int spk_merge_sorted_runs_device(spk_ctx* ctx, void* d_edges, const uint64_t* run_counts, uint32_t n_runs);
 int spk_aracne_device(spk_ctx* ctx, const void* d_edges, uint64_t n_edges, double edge_threshold,
                       uint32_t part_index, uint32_t n_parts, void* d_flags);
 

@@ -19,7 +19,7 @@ EXPORTS = ["spk_create", "spk_destroy", "spk_last_error", "spk_set_stream", "spk
            "spk_set_alignment", "spk_set_alignment_device",
            "spk_neighbour_counts", "spk_neighbour_counts_part", "spk_set_weights", "spk_mi_pairs", "spk_determine_mi_threshold",
            "spk_mi_scan", "spk_outlier_thresholds", "spk_sort_edges", "spk_aracne", "spk_sort_edges_device",
-           "spk_aracne_device", "spk_wait_download", "spk_get_timings", "spk_debug_tile_counts", "spk_debug_i8_mode", "spk_debug_i8_layout", "spk_debug_i8_tile",
+           "spk_aracne_device", "spk_merge_sorted_runs_device", "spk_wait_download", "spk_get_timings", "spk_debug_tile_counts", "spk_debug_i8_mode", "spk_debug_i8_layout", "spk_debug_i8_tile",
            "spk_version"]
 
 
@@ -83,6 +83,7 @@ def load():
     L.spk_sort_edges.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
     L.spk_aracne.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_double, C.c_uint32, C.c_uint32, C.c_void_p]
     L.spk_sort_edges_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
+    L.spk_merge_sorted_runs_device.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64), C.c_uint32]
     L.spk_aracne_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_double, C.c_uint32, C.c_uint32, C.c_void_p]
     L.spk_get_timings.argtypes = [C.c_void_p, C.POINTER(Timings)]
     L.spk_debug_tile_counts.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_int32, C.c_void_p]
@@ -267,6 +268,11 @@ class Context:
 
     def sort_edges_device(self, d_edges, n):
         self._check(self.lib.spk_sort_edges_device(self.h, C.c_void_p(d_edges), n))
+
+    def merge_sorted_runs_device(self, d_edges, run_counts):
+        """d_edges: concatenation of len(run_counts) runs, each in Graph::sort order -> merged in place."""
+        arr = (C.c_uint64 * len(run_counts))(*[int(x) for x in run_counts])
+        self._check(self.lib.spk_merge_sorted_runs_device(self.h, C.c_void_p(d_edges), arr, len(run_counts)))
 
     def aracne_device(self, d_edges, n, d_flags, edge_threshold=2.220446049250313e-16, part_index=0, n_parts=1):
         self._check(self.lib.spk_aracne_device(self.h, C.c_void_p(d_edges), n, edge_threshold, part_index, n_parts,

@@ -347,6 +347,8 @@ int spk_mi_scan(spk_ctx* c, const spk_scan_params* pp, spk_scan_result* res) {
         r = mi_scan_exact(c, p, circle); if (r) return r;
     } else {
         if (use_i8) {
+            // the refine's plane build only needs the weights: queued first, it runs on the GPU while the host prepares the filter
+            if (attempt == 0) { r = mi_refine_prepare(c, p.pseudocount); if (r) return r; }
             r = mi_i8_filter(c, p, band, circle, i8_wr); if (r) return r;
         } else {
             r = prep_column_stats(c, p.pseudocount); if (r) return r;
@@ -457,6 +459,15 @@ int spk_sort_edges(spk_ctx* c, spk_edge* edges, uint64_t n) {
     if (!r) r = cuda_check(c, cudaStreamSynchronize(c->stream), "sync");
     cudaFree(d);
     return r;
+}
+
+int spk_merge_sorted_runs_device(spk_ctx* c, void* d_edges, const uint64_t* run_counts, uint32_t n_runs) {
+    if (!c || !run_counts) return SPK_E_INVALID;
+    uint64_t n = 0;
+    for (uint32_t r = 0; r < n_runs; ++r) n += run_counts[r];
+    if (n && !d_edges) return SPK_E_INVALID;
+    SPK_CUDA(c, cudaSetDevice(c->device));
+    return merge_sorted_runs_device(c, (spk_edge*)d_edges, run_counts, n_runs);
 }
 
 int spk_aracne_device(spk_ctx* c, const void* d_edges, uint64_t n, double eps, uint32_t part, uint32_t nparts, void* d_flags) {

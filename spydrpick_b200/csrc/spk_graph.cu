@@ -10,6 +10,7 @@
 // Each edge writes only its own flag: no atomics.
 #include <algorithm>
 #include <cub/cub.cuh>
+#include <vector>
 #include "spk_internal.h"
 
 namespace spk {
@@ -81,6 +82,58 @@ int sort_edges_device(Ctx* c, spk_edge* d_edges, uint64_t n) {
     gather_edges_kernel<<<g, 256, 0, c->stream>>>(d_edges, i0, n, ebuf);
     SPK_CUDA(c, cudaMemcpyAsync(d_edges, ebuf, n * sizeof(spk_edge), cudaMemcpyDeviceToDevice, c->stream));
     c->tm.kernel_launches += 3 + 2 * 8;     // 3 own kernels + radix passes (CUB library kernels)
+    SPK_CUDA(c, cudaEventRecord(c->ev[1], c->stream));
+    SPK_CUDA(c, cudaEventSynchronize(c->ev[1]));
+    SPK_CUDA(c, cudaEventElapsedTime(&c->tm.sort_ms, c->ev[0], c->ev[1]));
+    SPK_CUDA(c, cudaGetLastError());
+    return SPK_OK;
+}
+
+// ---- merge of sorted runs (multi-GPU: every rank sorts its own edges, the all-gathered list is a concatenation of G
+// sorted runs) -- Graph::sort's order (weight descending, id ascending; graph/Graph.hpp:234-242) is a strict total
+// order on distinct edges, so a pairwise merge tree gives exactly the list a full sort gives.
+struct EdgeBefore {
+    __host__ __device__ bool operator()(const spk_edge& a, const spk_edge& b) const {
+        if (a.mi != b.mi) return a.mi > b.mi;
+        const unsigned long long ia = ((unsigned long long)a.j << 32) | a.i, ib = ((unsigned long long)b.j << 32) | b.i;
+        return ia < ib;
+    }
+};
+
+int merge_sorted_runs_device(Ctx* c, spk_edge* d_edges, const uint64_t* run_counts, uint32_t n_runs) {
+    std::vector<uint64_t> off(1, 0);
+    for (uint32_t r = 0; r < n_runs; ++r) if (run_counts[r]) off.push_back(off.back() + run_counts[r]);
+    const uint64_t n = off.back();
+    if (off.size() <= 2) return SPK_OK;                               // zero or one non-empty run
+    if (n > 0x7fffffffull) return fail(c, SPK_E_INVALID, "run merge supports < 2^31 edges");
+    size_t tmpb = 0;
+    cub::DeviceMerge::MergeKeys(nullptr, tmpb, (const spk_edge*)nullptr, (int)n, (const spk_edge*)nullptr, (int)n, (spk_edge*)nullptr, EdgeBefore{}, c->stream);
+    const size_t eb = align256(n * sizeof(spk_edge));
+    uint8_t* base = (uint8_t*)scratch(c, eb + align256(tmpb) + 256);
+    if (!base) return fail(c, SPK_E_NOMEM, "scratch allocation failed (run merge)");
+    spk_edge* src = d_edges; spk_edge* dst = (spk_edge*)base;
+    void* tmp = base + eb;
+    SPK_CUDA(c, cudaEventRecord(c->ev[0], c->stream));
+    while (off.size() > 2) {
+        std::vector<uint64_t> next(1, 0);
+        for (size_t r = 0; r + 1 < off.size(); r += 2) {
+            const uint64_t a0 = off[r], a1 = off[r + 1];
+            if (r + 2 < off.size()) {
+                const uint64_t b1 = off[r + 2];
+                size_t tb = tmpb;
+                SPK_CUDA(c, cub::DeviceMerge::MergeKeys(tmp, tb, (const spk_edge*)(src + a0), (int)(a1 - a0), (const spk_edge*)(src + a1), (int)(b1 - a1),
+                                                        dst + a0, EdgeBefore{}, c->stream));
+                c->tm.kernel_launches += 2;
+                next.push_back(b1);
+            } else {                                                   // odd run out: carried to the next round
+                SPK_CUDA(c, cudaMemcpyAsync(dst + a0, src + a0, (a1 - a0) * sizeof(spk_edge), cudaMemcpyDeviceToDevice, c->stream));
+                next.push_back(a1);
+            }
+        }
+        off.swap(next);
+        std::swap(src, dst);
+    }
+    if (src != d_edges) SPK_CUDA(c, cudaMemcpyAsync(d_edges, src, n * sizeof(spk_edge), cudaMemcpyDeviceToDevice, c->stream));
     SPK_CUDA(c, cudaEventRecord(c->ev[1], c->stream));
     SPK_CUDA(c, cudaEventSynchronize(c->ev[1]));
     SPK_CUDA(c, cudaEventElapsedTime(&c->tm.sort_ms, c->ev[0], c->ev[1]));

@@ -130,6 +130,7 @@ struct Ctx {
     double*   d_gval = nullptr; uint32_t g_nw_cap = 0;           // [g_NW] weight of the samples of word w (0 for padding words)
     double*   d_gmarg = nullptr;          // [L_pad][5] fp64 weighted marginals summed the same way
     int32_t*  d_gslot = nullptr;          // [g_NW*32] sample index per bit slot, -1 = padding
+    std::vector<int32_t> h_gslot; std::vector<double> h_gval;       // host sources of the two uploads (kept alive: no sync after the async copies)
     double*   d_gH = nullptr;             // [L_pad][5] marginal entropy sum_a p_a ln p_a for partner #states 1..5
     double    g_pc = -1.0;                // pseudocount d_gH was built for
     uint32_t  g_NW = 0;                   // words per plane (multiple of 32)
@@ -162,6 +163,7 @@ int hamming_neighbour_counts(Ctx* c, uint64_t min_identical, int quirk, uint32_t
 // ---- exact fp64 MI (spk_mi_exact.cu)
 int mi_pairs_exact(Ctx* c, const uint32_t* d_pi, const uint32_t* d_pj, uint64_t npairs, double pc, double* d_mi);
 // refine candidates -> d_refined (i,j,mi64), d_refined_wo (NaN when no gap column involved)
+int mi_refine_prepare(Ctx* c, double pc);     // weight-grouped bit planes + entropy tables of the fp64 refine (asynchronous; idempotent until the weights change)
 int mi_refine_candidates(Ctx* c, uint64_t ncand, double pc, double wo_threshold, uint64_t* n_valid = nullptr);   // MI-without-gaps only when mi > wo_threshold
 // exhaustive diagnostic engine: emits every pair of the partition as a candidate-free exact scan
 int mi_scan_exact(Ctx* c, const spk_scan_params& p, uint64_t circle);
@@ -182,6 +184,7 @@ int mi_i8_debug_tile(Ctx* c, uint32_t ti, uint32_t tj, double pc, uint32_t* d_ou
 
 // ---- graph (spk_graph.cu)
 int sort_edges_device(Ctx* c, spk_edge* d_edges, uint64_t n);
+int merge_sorted_runs_device(Ctx* c, spk_edge* d_edges, const uint64_t* run_counts, uint32_t n_runs);
 int aracne_device(Ctx* c, const spk_edge* d_edges, uint64_t n, double eps, uint32_t part, uint32_t nparts, uint8_t* d_flags);
 
 // ordered-int encodings for atomic max on floating point

@@ -819,7 +819,9 @@ static int ensure_grouped(Ctx* c, double pc) {
     std::vector<uint32_t> order(n);
     for (uint32_t s = 0; s < n; ++s) order[s] = s;
     std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return c->h_w[a] < c->h_w[b]; });
-    std::vector<int32_t> slot; std::vector<double> val;
+    // pageable sources of the async uploads below: the copies stage them before returning, but the vectors live in the context anyway
+    std::vector<int32_t>& slot = c->h_gslot; std::vector<double>& val = c->h_gval;
+    slot.clear(); val.clear();
     slot.reserve((size_t)n + 4096);
     for (uint32_t k = 0; k < n;) {
         uint32_t e = k;
@@ -860,7 +862,6 @@ static int ensure_grouped(Ctx* c, double pc) {
     gbits_build_kernel<<<c->L_pad, 128, gsm, c->stream>>>(c->d_colmajor, c->d_gslot, c->d_gval, c->d_gbits, c->d_gmarg, c->L, c->n_pad, NW);
     c->tm.kernel_launches += 1;
     SPK_CUDA(c, cudaGetLastError());
-    SPK_CUDA(c, cudaStreamSynchronize(c->stream));                   // slot / val are host temporaries
     c->g_NW = NW; c->g_state = 1; c->g_pc = -1.0;
     return ensure_gh(c, pc);
 }
@@ -870,6 +871,8 @@ static int refine_grid(Ctx* c, unsigned long long n) {
     const unsigned long long cap = (unsigned long long)c->sm_count * 16;
     return (int)(blocks < cap ? (blocks ? blocks : 1) : cap);
 }
+
+int mi_refine_prepare(Ctx* c, double pc) { return ensure_grouped(c, pc); }
 
 int mi_pairs_exact(Ctx* c, const uint32_t* d_pi, const uint32_t* d_pj, uint64_t npairs, double pc, double* d_mi) {
     if (npairs == 0) return SPK_OK;

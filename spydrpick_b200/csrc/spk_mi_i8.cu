@@ -935,16 +935,26 @@ static int i8_prepare(Ctx* c, double pc, int wr) {
             c->i8_delta = wmax / 65535.0;
         } else {
             const std::vector<uint16_t>& tab = i8_product_table();
+            // sample weights take few distinct values (1 / #neighbours): the scale search runs over (value, multiplicity)
+            std::vector<double> sorted_w(c->h_w.begin(), c->h_w.begin() + n);
+            std::sort(sorted_w.begin(), sorted_w.end());
+            std::vector<std::pair<double, double>> distinct;                      // (w / w_max, count)
+            for (uint32_t s = 0; s < n;) {
+                uint32_t e = s;
+                while (e < n && sorted_w[e] == sorted_w[s]) ++e;
+                distinct.emplace_back(sorted_w[s] / wmax, (double)(e - s));
+                s = e;
+            }
             double best_err = 1e300, best_M = 65025.0;
             for (int trial = 0; trial < 24; ++trial) {
                 const double M = 65025.0 * (1.0 - 0.02 * trial);                  // scales between 52 % and 100 % of the byte-product range
                 double err = 0.0;
-                for (uint32_t s = 0; s < n; ++s) {
-                    const double t = c->h_w[s] / wmax * M;
+                for (const auto& d : distinct) {
+                    const double t = d.first * M;
                     const long ti = std::min<long>(65025, std::llround(t));
                     const uint16_t ab = tab[ti];
                     const double qv = (double)(ab >> 8) * (double)(ab & 255u);
-                    err += std::fabs(qv - t) / M;                                  // in units of w_max
+                    err += d.second * (std::fabs(qv - t) / M);                     // in units of w_max
                 }
                 if (err < best_err) { best_err = err; best_M = M; }
             }

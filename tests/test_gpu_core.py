@@ -157,6 +157,29 @@ def test_sort_edges_bit_exact(ctx):
     assert [[int(a), int(b), float(c)] for a, b, c in ctx.sort_edges(k)] == KAT["sort"]["sorted"]
 
 
+@pytest.mark.parametrize("runs", [[5000], [1, 4999], [1700, 0, 1650, 1650], [700, 600, 900, 800, 500, 400, 600, 500], [1000, 1000, 3000]])
+def test_merge_sorted_runs_equals_full_sort(ctx, runs):
+    """spk_merge_sorted_runs_device (multi-GPU: every rank sorts its own edges, the gathered list is merged) gives
+    the list Graph::sort gives, bit for bit, for empty, odd and unequal runs."""
+    import torch
+    rng = np.random.default_rng(len(runs))
+    n = sum(runs)
+    e = np.zeros(n, dtype=EDGE_DTYPE)
+    e["i"] = rng.integers(0, 300, n); e["j"] = e["i"] + 1 + rng.integers(0, 300, n)
+    e["mi"] = np.round(rng.random(n), 2)               # many ties -> id tie-break exercised
+    _, first = np.unique((e["j"].astype(np.uint64) << np.uint64(32)) | e["i"], return_index=True)
+    e = e[np.sort(first)]                              # distinct edges (a graph has no duplicate ids)
+    runs = list(runs); runs[-1] -= n - len(e); n = len(e)
+    parts, o = [], 0
+    for r in runs:
+        parts.append(orc.sort_edges(e[o:o + r])); o += r
+    cat = np.concatenate(parts)
+    d = torch.from_numpy(cat.view(np.uint8).copy()).cuda()
+    ctx.merge_sorted_runs_device(d.data_ptr(), runs)
+    got = d.cpu().numpy().view(EDGE_DTYPE)
+    assert got.tobytes() == orc.sort_edges(e).tobytes()
+
+
 @pytest.mark.parametrize("case", KAT["aracne"], ids=lambda c: c["name"])
 def test_aracne_known_answers(ctx, case):
     assert list(ctx.aracne(_edges(case["edges"]), EPS)) == case["direct"]
