@@ -204,7 +204,10 @@ def run_b200(args):
     mi_values = args.mi_values or min(10_000_000, 100 * L)
 
     ctx = Context(device=local_rank)
-    stream = torch.cuda.current_stream(device)
+    # ONE stream for torch's own ops (allocator fills, NCCL hand-offs, CUDA events) and the library's kernels: torch's
+    # default current stream is the legacy stream 0, which spk_set_stream reads as "use your own stream"
+    stream = torch.cuda.Stream(device)
+    torch.cuda.set_stream(stream)
     ctx.set_stream(stream.cuda_stream)
     ctx.set_alignment(states, pos)
     min_ident = int(0.9 * float(L))
