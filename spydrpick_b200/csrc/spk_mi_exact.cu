@@ -607,7 +607,12 @@ mi_refine_coop_kernel(const uint8_t* __restrict__ masks, const Candidate* __rest
     const double2* gv2 = reinterpret_cast<const double2*>(gval);
     const uint32_t nchunk = NW / 4;                  // uint4 chunks per plane row (NW is a multiple of 32)
 
-    double part[G][C];
+    // Partial tables are folded as soon as a sibling is complete (a binary counter: after pair t, one fold per trailing one
+    // bit of t), so at most log2(G) folded tables are alive instead of G partial ones. The fold at distance h keeps the
+    // lower sibling in lanes whose bit h is clear and the upper one in the others: lane t of the group ends with pair t.
+    constexpr int LOG2G = (G == 8) ? 3 : (G == 4 ? 2 : 1);
+    double stack[LOG2G][C];
+    double acc2[KI][KJ];
 #pragma unroll
     for (int t = 0; t < G; ++t) {
         const uint4* Bi[KI]; const uint4* Bj[KJ];
@@ -637,27 +642,31 @@ mi_refine_coop_kernel(const uint8_t* __restrict__ masks, const Candidate* __rest
                     acc[a * KJ + b] = v;
                 }
         }
+        int ones = 0;                                   // trailing one bits of t (compile-time after unrolling)
+        while ((t >> ones) & 1) ++ones;
 #pragma unroll
-        for (int q = 0; q < C; ++q) part[t][q] = acc[q];
-    }
-    // transposing butterfly: after the step with distance h, slot k holds the partial table of pair k + (sub & ~(h-1)... )
+        for (int lvl = 0; lvl < LOG2G; ++lvl) {
+            if (lvl < ones) {
+                const int h = 1 << lvl;
+                const bool up = (sub & h) != 0;
 #pragma unroll
-    for (int h = G / 2; h >= 1; h /= 2) {
-        const bool up = (sub & h) != 0;
-#pragma unroll
-        for (int k = 0; k < h; ++k)
-#pragma unroll
-            for (int q = 0; q < C; ++q) {
-                const double send = up ? part[k][q] : part[k + h][q];
-                const double keep = up ? part[k + h][q] : part[k][q];
-                part[k][q] = keep + __shfl_xor_sync(0xffffffffu, send, h);
+                for (int q = 0; q < C; ++q) {
+                    const double send = up ? stack[lvl][q] : acc[q];
+                    const double keep = up ? acc[q] : stack[lvl][q];
+                    acc[q] = keep + __shfl_xor_sync(0xffffffffu, send, h);
+                }
             }
+        }
+        if (ones < LOG2G) {
+#pragma unroll
+            for (int q = 0; q < C; ++q) stack[ones][q] = acc[q];
+        } else {
+#pragma unroll
+            for (int a = 0; a < KI; ++a)
+#pragma unroll
+                for (int b = 0; b < KJ; ++b) acc2[a][b] = acc[a * KJ + b];
+        }
     }
-    double acc2[KI][KJ];
-#pragma unroll
-    for (int a = 0; a < KI; ++a)
-#pragma unroll
-        for (int b = 0; b < KJ; ++b) acc2[a][b] = part[0][a * KJ + b];
     double err = 0.0;
     if (live) {
         double m = 0.0, m2 = 0.0;

@@ -433,7 +433,7 @@ template <int NCTA, int WR> struct I8Cfg {
 
 template <int NCTA, int WR>
 __global__ void __launch_bounds__(I8_THREADS, 1)
-mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const I8Params p) {
+mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const __grid_constant__ I8Params p) {
     using Cfg = I8Cfg<NCTA, WR>;
     using I8EpiSmem = I8EpiSmemT<256 / WR>;
     constexpr uint32_t JT = 2u / WR;                          // column tiles per B panel
