@@ -46,10 +46,10 @@ def parse_args():
 
 
 # from the committed ncu --set full captures of the main-pass launch at 3000 x 100000
-# (engine 4: profiles/r01e4_ncu_full_summary.csv; engine 3: profiles/r01_ncu_full_summary.csv):
+# (engine 4: profiles/r01f_ncu_full_summary.csv; engine 3: profiles/r01_ncu_full_summary.csv):
 # dram__bytes_read.sum + dram__bytes_write.sum per launch, sm__pipe_tensor_cycles_active %, per int8 engine
 NCU_TRAFFIC = {3: 52.2e9, 4: 26.7e9}
-NCU_TENSOR_PCT = {3: 90.4, 4: 79.2}
+NCU_TENSOR_PCT = {3: 90.4, 4: 79.1}
 
 
 def peaks():
@@ -369,7 +369,7 @@ def run_b200(args):
     executed = 2.0 * 128 * 256 * n_pad * tiles * (1 if i8 else (args.n_terms or 2))   # tensor ops actually issued
     executed_tops = executed / (k_ms / 1e3) / 1e12 if k_ms > 0 else 0.0
     # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch from the committed ncu --set full capture
-    # (profiles/r01e4_ncu_full_summary.csv); only valid for the workload it was captured on
+    # (profiles/r01f_ncu_full_summary.csv); only valid for the workload it was captured on
     traffic = NCU_TRAFFIC.get(args.engine if args.engine else 4) if (i8 and world == 1 and n == 3000 and L == 100000) else None
     roofline = {"bound": "tensor", "achieved": achieved, "peak": pk["bf16_tflops"], "unit": "TFLOP/s",
                 "frac": achieved / pk["bf16_tflops"], "traffic": traffic,
@@ -378,12 +378,12 @@ def run_b200(args):
                 "executed_tops": executed_tops,
                 "executed_frac_of_pipe_peak": executed_tops / (pk["bf16_burst_tflops"] * (2.0 if i8 else 1.0)),
                 "executed_frac_of_nominal_pipe": executed_tops / (4500.0 if i8 else 2250.0),
-                "ncu_tensor_pipe_active_pct": NCU_TENSOR_PCT.get(args.engine if args.engine else 4) if traffic else None,   # main pass, profiles/r01e4_ncu_full_summary.csv
+                "ncu_tensor_pipe_active_pct": NCU_TENSOR_PCT.get(args.engine if args.engine else 4) if traffic else None,   # main pass, profiles/r01f_ncu_full_summary.csv
                 "note": ("achieved = SURVEY 8(d)'s algorithmic 32*n flop/pair vs the measured bf16 peak; the int8 compact engine "
                          "issues FEWER tensor ops than that (only the one-hot rows a column needs, u8 x u8 -> s32 at 2x the bf16 "
                          "rate), so frac exceeds 1 -- the honest utilisation figures are executed_frac_of_pipe_peak = issued "
                          "int8 ops / (2 x measured bf16 burst peak), executed_frac_of_nominal_pipe = issued / 4.5 POP/s, and "
-                         "ncu's sm__pipe_tensor_cycles_active (profiles/r01e4_ncu_full_summary.csv)") if i8 else
+                         "ncu's sm__pipe_tensor_cycles_active (profiles/r01f_ncu_full_summary.csv)") if i8 else
                         "algorithmic 32*n flop/pair; executed tensor flops are n_terms x that (bf16 weight split)"}
 
     e2e = None
