@@ -52,6 +52,7 @@ struct Options {
     std::string mapping_list, sample_weights_file, outfile;
     int input_indexing_base = 1, output_indexing_base = 1;
     bool no_filter_alignment = false;
+    bool host_filter = false;              // column filter on the host (default: on the device)
     double maf_threshold = 0.01, gap_threshold = 0.15;
     bool no_sample_reweighting = false, rescale_sample_weights = false, output_sample_weights = false;
     double sample_reweighting_threshold = 0.9;
@@ -95,6 +96,7 @@ void print_help() {
         "  --input-indexing-base arg (=1)     Base index for input.\n"
         "  --output-indexing-base arg (=1)    Base index for output.\n"
         "  --no-filter-alignment              Do not filter alignment columns by applying MAF and GAP thresholds.\n"
+        "  --host-filter                      Count state frequencies and extract the kept columns on the host (default: device).\n"
         "  --maf-threshold arg (=0.01)        Minor state frequency threshold.\n"
         "  --gap-threshold arg (=0.15)        Gap frequency threshold.\n"
         "  --no-sample-reweighting            Turn sample reweighting off.\n"
@@ -151,6 +153,7 @@ Options parse_options(int argc, char** argv) {
         else if (name == "input-indexing-base") o.input_indexing_base = std::atoi(need(i, name, inl, has_inl).c_str());
         else if (name == "output-indexing-base") o.output_indexing_base = std::atoi(need(i, name, inl, has_inl).c_str());
         else if (name == "no-filter-alignment") o.no_filter_alignment = true;
+        else if (name == "host-filter") o.host_filter = true;
         else if (name == "maf-threshold") o.maf_threshold = D(need(i, name, inl, has_inl));
         else if (name == "gap-threshold") o.gap_threshold = D(need(i, name, inl, has_inl));
         else if (name == "no-sample-reweighting") o.no_sample_reweighting = true;
@@ -388,14 +391,31 @@ int main(int argc, char** argv) {
     }
     if (o.genome_size) A.n_original_positions = o.genome_size;
 
-    // -- column filter (src/SpydrPick.cpp:234-297)
-    if (!o.no_filter_alignment) { A.id += "." + filter_alignment(A, o, o.verbose); if (o.verbose) std::cout << "SpydrPick: filtered alignment has " << A.L << " loci (" << lap.lap() << " s)\n"; }
-    if (A.L >= (1ull << 29)) die("too many loci");
-    const uint32_t n = A.n, L = (uint32_t)A.L;
-
     spk_ctx* ctx = nullptr;
     if (spk_create(&ctx, o.device, o.verbose ? 1 : 0) != SPK_OK) die(std::string("cannot initialise the CUDA context: ") + spk_last_error(nullptr));
-    check(ctx, spk_set_alignment(ctx, A.states, n, L, A.pos.data()), "alignment upload");
+
+    // -- column filter (src/SpydrPick.cpp:234-297) + alignment upload: the raw matrix goes up once, state frequencies are
+    //    counted and the kept columns extracted on the device (spk_set_alignment_filtered); --host-filter keeps the host pass
+    if (!o.no_filter_alignment && !o.host_filter) {
+        if (A.L >= (1ull << 32)) die("too many loci");
+        std::vector<uint8_t> keep(A.L); uint64_t n_kept = 0;
+        check(ctx, spk_set_alignment_filtered(ctx, A.states, A.n, A.L, A.pos.data(), o.maf_threshold, o.gap_threshold, keep.data(), &n_kept),
+              "column filter + alignment upload");
+        if (o.verbose) std::cout << "SpydrPick: column filter keeps " << n_kept << " of " << A.L << " loci\n";
+        std::vector<uint64_t> npos; npos.reserve(n_kept);
+        for (uint64_t c = 0; c < A.L; ++c) if (keep[c]) npos.push_back(A.pos[c]);
+        A.L = n_kept; A.pos.swap(npos);
+        char id[128];
+        std::snprintf(id, sizeof id, "filtered_ge%03zumaf_le%03zugf_gt01-lt05states", (size_t)(o.maf_threshold * 100.), (size_t)(o.gap_threshold * 100.));
+        A.id += std::string(".") + id;
+        if (o.verbose) std::cout << "SpydrPick: filtered alignment has " << A.L << " loci (" << lap.lap() << " s)\n";
+        if (A.L >= (1ull << 29)) die("too many loci");
+    } else {
+        if (!o.no_filter_alignment) { A.id += "." + filter_alignment(A, o, o.verbose); if (o.verbose) std::cout << "SpydrPick: filtered alignment has " << A.L << " loci (" << lap.lap() << " s)\n"; }
+        if (A.L >= (1ull << 29)) die("too many loci");
+        check(ctx, spk_set_alignment(ctx, A.states, A.n, (uint32_t)A.L, A.pos.data()), "alignment upload");
+    }
+    const uint32_t n = A.n, L = (uint32_t)A.L;
 
     // -- sample weights (src/SpydrPick.cpp:321; apegrunt/Alignment_utility.hpp:186-258)
     std::vector<double> w(n, 1.0);

@@ -71,6 +71,19 @@ int spk_set_alignment(spk_ctx* ctx, const uint8_t* states, uint32_t n, uint32_t 
 int spk_set_alignment_device(spk_ctx* ctx, const void* d_states, uint32_t n, uint32_t L, const uint64_t* pos);
 
 /* ---- K1: sample reweighting ----------------------------------------------------------- */
+/* Column filter pre-pass. Replaces apegrunt::Alignment_filter's frequency scan + column extraction
+ * (externals/apegrunt/include/apegrunt/Alignment_filter.hpp:250-339, called from src/SpydrPick.cpp:234-297).
+ * spk_column_state_counts: counts[L*5] = unweighted number of samples in state a of column c (counts[c*5 + a]) of the RAW
+ *   alignment states[n][L] (host, row-major, codes 0..4).
+ * spk_set_alignment_filtered: uploads the raw alignment ONCE, counts on the device, applies the reference's rule on the
+ *   host in its arithmetic (keep iff more than one non-gap state has frequency >= maf_threshold and the gap frequency
+ *   is <= gap_threshold), extracts the kept columns on the device and makes them the context's alignment (as
+ *   spk_set_alignment would with the filtered matrix and positions). keep[L] receives 1/0 per raw column, *n_kept the
+ *   number kept; fewer than 2 kept columns is SPK_E_INVALID. pos may be NULL (= column index). */
+int spk_column_state_counts(spk_ctx* ctx, const uint8_t* states, uint32_t n, uint64_t L, uint32_t* counts);
+int spk_set_alignment_filtered(spk_ctx* ctx, const uint8_t* states, uint32_t n, uint64_t L, const uint64_t* pos,
+                               double maf_threshold, double gap_threshold, uint8_t* keep, uint64_t* n_kept);
+
 /* Replaces apegrunt::calculate_weights (Alignment_StateVector_weights.hpp:192-353) up to the
  * integer neighbour counts: counts[i] = 1 + #{j != i : similar(i,j)} with
  * similar = ident(i,j) >= min_identical, min_identical = (size_t)(threshold*(double)L) computed

@@ -16,7 +16,7 @@ assert EDGE_DTYPE.itemsize == 16
 SPK_OK, SPK_E_INVALID, SPK_E_CUDA, SPK_E_NOMEM, SPK_E_OVERFLOW, SPK_E_PRECISION = 0, -1, -2, -3, -4, -5
 
 EXPORTS = ["spk_create", "spk_destroy", "spk_last_error", "spk_set_stream", "spk_host_alloc", "spk_host_free",
-           "spk_set_alignment", "spk_set_alignment_device",
+           "spk_set_alignment", "spk_set_alignment_device", "spk_column_state_counts", "spk_set_alignment_filtered",
            "spk_neighbour_counts", "spk_neighbour_counts_part", "spk_set_weights", "spk_mi_pairs", "spk_determine_mi_threshold",
            "spk_mi_scan", "spk_outlier_thresholds", "spk_sort_edges", "spk_aracne", "spk_sort_edges_device",
            "spk_aracne_device", "spk_merge_sorted_runs_device", "spk_wait_download", "spk_get_timings", "spk_debug_tile_counts", "spk_debug_i8_mode", "spk_debug_i8_layout", "spk_debug_i8_tile",
@@ -83,6 +83,9 @@ def load():
     L.spk_sort_edges.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
     L.spk_aracne.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_double, C.c_uint32, C.c_uint32, C.c_void_p]
     L.spk_sort_edges_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
+    L.spk_column_state_counts.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint64, C.c_void_p]
+    L.spk_set_alignment_filtered.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint64, C.c_void_p, C.c_double, C.c_double,
+                                             C.c_void_p, C.POINTER(C.c_uint64)]
     L.spk_merge_sorted_runs_device.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64), C.c_uint32]
     L.spk_aracne_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_double, C.c_uint32, C.c_uint32, C.c_void_p]
     L.spk_get_timings.argtypes = [C.c_void_p, C.POINTER(Timings)]
@@ -175,6 +178,27 @@ class Context:
         p = None if pos is None else np.ascontiguousarray(pos, dtype=np.uint64)
         self._check(self.lib.spk_set_alignment(self.h, _ptr(s), s.shape[0], s.shape[1], _ptr(p)))
         self.n, self.L = s.shape
+
+    def column_state_counts(self, states):
+        """Unweighted state counts [L, 5] of a RAW alignment (counted on the device)."""
+        s = np.ascontiguousarray(states, dtype=np.uint8)
+        assert s.ndim == 2
+        out = np.zeros((s.shape[1], 5), dtype=np.uint32)
+        self._check(self.lib.spk_column_state_counts(self.h, _ptr(s), s.shape[0], s.shape[1], _ptr(out)))
+        return out
+
+    def set_alignment_filtered(self, states, pos=None, maf_threshold=0.01, gap_threshold=0.15):
+        """Column filter (Alignment_filter.hpp:250-339) + set_alignment of the kept columns, the raw matrix uploaded once.
+        Returns the boolean keep mask over the raw columns."""
+        s = np.ascontiguousarray(states, dtype=np.uint8)
+        assert s.ndim == 2
+        p = None if pos is None else np.ascontiguousarray(pos, dtype=np.uint64)
+        keep = np.zeros(s.shape[1], dtype=np.uint8)
+        nk = C.c_uint64(0)
+        self._check(self.lib.spk_set_alignment_filtered(self.h, _ptr(s), s.shape[0], s.shape[1], _ptr(p), float(maf_threshold),
+                                                        float(gap_threshold), _ptr(keep), C.byref(nk)))
+        self.n, self.L = s.shape[0], int(nk.value)
+        return keep.astype(bool)
 
     def set_alignment_device(self, d_states, n, L, pos=None):
         """d_states: raw device pointer (int) to row-major uint8[n][L] in this context's device memory."""

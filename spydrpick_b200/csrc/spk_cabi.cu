@@ -190,6 +190,66 @@ int spk_set_alignment_device(spk_ctx* c, const void* d_states, uint32_t n, uint3
     return set_alignment_impl(c, (const uint8_t*)d_states, n, L, pos, cudaMemcpyDeviceToDevice);
 }
 
+// ---- column filter pre-pass (apegrunt/Alignment_filter.hpp:250-339) ----
+namespace {
+struct RawUpload {                                       // the raw alignment in HBM for the duration of one call
+    uint8_t* d_raw = nullptr; uint32_t* d_counts = nullptr;
+    ~RawUpload() { if (d_raw) cudaFree(d_raw); if (d_counts) cudaFree(d_counts); }
+};
+int upload_and_count(spk_ctx* c, const uint8_t* states, uint32_t n, uint64_t L, RawUpload& u, std::vector<uint32_t>& counts) {
+    if (cudaMalloc(&u.d_raw, (size_t)n * L) != cudaSuccess || cudaMalloc(&u.d_counts, (size_t)L * NSTATES * 4) != cudaSuccess) {
+        cudaGetLastError(); return fail(c, SPK_E_NOMEM, "column filter: cannot allocate %zu bytes for the raw alignment", (size_t)n * L);
+    }
+    SPK_CUDA(c, cudaMemcpyAsync(u.d_raw, states, (size_t)n * L, cudaMemcpyHostToDevice, c->stream));
+    int r = column_state_counts_device(c, u.d_raw, n, L, u.d_counts); if (r) return r;
+    counts.resize((size_t)L * NSTATES);
+    SPK_CUDA(c, cudaMemcpyAsync(counts.data(), u.d_counts, (size_t)L * NSTATES * 4, cudaMemcpyDeviceToHost, c->stream));
+    SPK_CUDA(c, cudaStreamSynchronize(c->stream));
+    return SPK_OK;
+}
+}  // namespace
+
+int spk_column_state_counts(spk_ctx* c, const uint8_t* states, uint32_t n, uint64_t L, uint32_t* counts) {
+    if (!c || !states || !counts || n == 0 || L == 0) return c ? fail(c, SPK_E_INVALID, "column_state_counts: need states, counts, n >= 1, L >= 1") : SPK_E_INVALID;
+    SPK_CUDA(c, cudaSetDevice(c->device));
+    RawUpload u; std::vector<uint32_t> h;
+    int r = upload_and_count(c, states, n, L, u, h); if (r) return r;
+    std::memcpy(counts, h.data(), h.size() * 4);
+    return SPK_OK;
+}
+
+int spk_set_alignment_filtered(spk_ctx* c, const uint8_t* states, uint32_t n, uint64_t L, const uint64_t* pos,
+                               double maf_threshold, double gap_threshold, uint8_t* keep, uint64_t* n_kept) {
+    if (!c || !states || !keep || !n_kept || n == 0 || L < 2) return c ? fail(c, SPK_E_INVALID, "set_alignment_filtered: need states, keep, n_kept, n >= 1, L >= 2") : SPK_E_INVALID;
+    SPK_CUDA(c, cudaSetDevice(c->device));
+    RawUpload u; std::vector<uint32_t> cnt;
+    int r = upload_and_count(c, states, n, L, u, cnt); if (r) return r;
+    // the decision is the reference's, in its arithmetic (frequencies as doubles; Alignment_filter.hpp:284-318)
+    std::vector<uint32_t> idx; std::vector<uint64_t> kpos;
+    for (uint64_t col = 0; col < L; ++col) {
+        int nsig = 0;
+        for (int a = 0; a < GAP; ++a) if (double(cnt[col * NSTATES + a]) / double(n) >= maf_threshold) ++nsig;
+        const bool k = nsig > 1 && double(cnt[col * NSTATES + GAP]) / double(n) <= gap_threshold;
+        keep[col] = k ? 1 : 0;
+        if (k) { idx.push_back((uint32_t)col); kpos.push_back(pos ? pos[col] : col); }
+    }
+    *n_kept = idx.size();
+    if (idx.size() < 2) return fail(c, SPK_E_INVALID, "fewer than 2 columns pass the MAF / gap filter");
+    if (L > 0xffffffffull) return fail(c, SPK_E_INVALID, "L too large");
+    const uint32_t Lk = (uint32_t)idx.size();
+    uint32_t* d_idx = nullptr; uint8_t* d_f = nullptr;
+    if (cudaMalloc(&d_idx, (size_t)Lk * 4) != cudaSuccess || cudaMalloc(&d_f, (size_t)n * Lk) != cudaSuccess) {
+        cudaGetLastError(); if (d_idx) cudaFree(d_idx);
+        return fail(c, SPK_E_NOMEM, "column filter: device allocation failed");
+    }
+    r = cuda_check(c, cudaMemcpyAsync(d_idx, idx.data(), (size_t)Lk * 4, cudaMemcpyHostToDevice, c->stream), "H2D kept columns");
+    if (!r) r = gather_columns_device(c, u.d_raw, n, L, d_idx, Lk, d_f);
+    if (!r) r = cuda_check(c, cudaStreamSynchronize(c->stream), "sync");
+    if (!r) r = set_alignment_impl(c, d_f, n, Lk, kpos.data(), cudaMemcpyDeviceToDevice);
+    cudaFree(d_idx); cudaFree(d_f);
+    return r;
+}
+
 int spk_neighbour_counts_part(spk_ctx* c, uint64_t min_identical, int quirk, uint32_t part, uint32_t nparts, uint64_t* counts) {
     if (!c || !counts) return SPK_E_INVALID;
     if (!c->d_states) return fail(c, SPK_E_INVALID, "neighbour_counts: no alignment set");

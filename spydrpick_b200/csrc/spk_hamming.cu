@@ -286,11 +286,8 @@ int hamming_neighbour_counts(Ctx* c, uint64_t min_identical, int quirk, uint32_t
                                                                  (unsigned long long)min_identical, quirk,
                                                                  (unsigned long long*)c->d_counts, part, n_parts);
     else if (T > part) {
-        static bool attr_set = false;
-        if (!attr_set) {
-            SPK_CUDA(c, cudaFuncSetAttribute(hamming_csa_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HC_SMEM_BYTES));
-            attr_set = true;
-        }
+        // per device, so set on every launch (a process may hold contexts on several GPUs)
+        SPK_CUDA(c, cudaFuncSetAttribute(hamming_csa_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HC_SMEM_BYTES));
         const unsigned grid = (unsigned)((T - part + n_parts - 1) / n_parts);
         hamming_csa_kernel<<<grid, 256, HC_SMEM_BYTES, c->stream>>>(c->d_planes, c->n, c->L, c->W32, nt,
                                                                     (unsigned long long)min_identical, quirk,

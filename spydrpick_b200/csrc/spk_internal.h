@@ -156,6 +156,8 @@ void* scratch(Ctx* c, size_t bytes);   // grows the context scratch buffer; null
 int prep_alignment(Ctx* c);                                   // colmajor, planes, masks from d_states
 int prep_column_stats(Ctx* c, double pseudocount);            // d_marg, d_colstat, w_total
 int prep_operands(Ctx* c, int n_terms);                       // d_U, d_V
+int column_state_counts_device(Ctx* c, const uint8_t* d_raw, uint32_t n, uint64_t L, uint32_t* d_counts);   // [L][5] unweighted state counts
+int gather_columns_device(Ctx* c, const uint8_t* d_raw, uint32_t n, uint64_t L, const uint32_t* d_idx, uint32_t Lk, uint8_t* d_out);
 
 // ---- K1 (spk_hamming.cu)
 int hamming_neighbour_counts(Ctx* c, uint64_t min_identical, int quirk, uint32_t part = 0, uint32_t n_parts = 1);

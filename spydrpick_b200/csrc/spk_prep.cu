@@ -194,4 +194,64 @@ int prep_operands(Ctx* c, int n_terms) {
     return SPK_OK;
 }
 
+// ---- column filter pre-pass -------------------------------------------------------------------
+// Replaces the frequency scan of apegrunt::Alignment_filter (apegrunt/Alignment_filter.hpp:250-339): unweighted counts of
+// the five states per column over the RAW alignment, O(n L) bytes read once (HBM-bound: n*L bytes in, 20 L bytes out).
+// One thread per column (a warp reads 32 consecutive bytes of a row: whole sectors), rows dealt to blockIdx.y in chunks;
+// every thread adds its five partial counts to the global table.
+__global__ void __launch_bounds__(256)
+column_counts_kernel(const uint8_t* __restrict__ states, uint32_t n, unsigned long long L, uint32_t rows_per_chunk,
+                     uint32_t* __restrict__ counts) {
+    const unsigned long long c = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= L) return;
+    const uint32_t r0 = blockIdx.y * rows_per_chunk, r1 = min(n, r0 + rows_per_chunk);
+    uint32_t k0 = 0, k1 = 0, k2 = 0, k3 = 0, k4 = 0;
+    const uint8_t* ptr = states + (size_t)r0 * L + c;
+#pragma unroll 4
+    for (uint32_t s = r0; s < r1; ++s, ptr += L) {
+        const uint32_t x = *ptr;
+        k0 += (x == 0u); k1 += (x == 1u); k2 += (x == 2u); k3 += (x == 3u); k4 += (x >= 4u);
+    }
+    uint32_t* out = counts + c * NSTATES;
+    if (k0) atomicAdd(out + 0, k0);
+    if (k1) atomicAdd(out + 1, k1);
+    if (k2) atomicAdd(out + 2, k2);
+    if (k3) atomicAdd(out + 3, k3);
+    if (k4) atomicAdd(out + 4, k4);
+}
+
+// filtered[s][k] = raw[s][idx[k]] (idx ascending: reads nearly coalesced, writes coalesced)
+__global__ void __launch_bounds__(256)
+gather_columns_kernel(const uint8_t* __restrict__ raw, unsigned long long L, const uint32_t* __restrict__ idx, uint32_t Lk,
+                      uint8_t* __restrict__ out) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= Lk) return;
+    const size_t s = blockIdx.y;
+    out[s * Lk + k] = raw[s * L + idx[k]];
+}
+
+int column_state_counts_device(Ctx* c, const uint8_t* d_raw, uint32_t n, uint64_t L, uint32_t* d_counts) {
+    SPK_CUDA(c, cudaMemsetAsync(d_counts, 0, (size_t)L * NSTATES * 4, c->stream));
+    const uint32_t rows_per_chunk = 128;
+    const unsigned gx = (unsigned)((L + 255) / 256), gy = (n + rows_per_chunk - 1) / rows_per_chunk;
+    column_counts_kernel<<<dim3(gx, gy), 256, 0, c->stream>>>(d_raw, n, (unsigned long long)L, rows_per_chunk, d_counts);
+    c->tm.kernel_launches += 1;
+    SPK_CUDA(c, cudaGetLastError());
+    return SPK_OK;
+}
+
+int gather_columns_device(Ctx* c, const uint8_t* d_raw, uint32_t n, uint64_t L, const uint32_t* d_idx, uint32_t Lk, uint8_t* d_out) {
+    if (n > 65535u) {                                    // gridDim.y limit: rows in slabs
+        for (uint32_t r0 = 0; r0 < n; r0 += 65535u) {
+            const uint32_t rows = min(65535u, n - r0);
+            gather_columns_kernel<<<dim3((Lk + 255) / 256, rows), 256, 0, c->stream>>>(d_raw + (size_t)r0 * L, (unsigned long long)L, d_idx, Lk, d_out + (size_t)r0 * Lk);
+        }
+    } else {
+        gather_columns_kernel<<<dim3((Lk + 255) / 256, n), 256, 0, c->stream>>>(d_raw, (unsigned long long)L, d_idx, Lk, d_out);
+    }
+    c->tm.kernel_launches += 1;
+    SPK_CUDA(c, cudaGetLastError());
+    return SPK_OK;
+}
+
 } // namespace spk

@@ -284,3 +284,41 @@ def test_set_alignment_device_equals_host_upload(ctx):
     assert np.array_equal(r_dev["colmax"], r_host["colmax"])
     with pytest.raises(SpkError):
         ctx.set_alignment_device(s.ctypes.data, 90, 333, pos)       # pageable host pointer is rejected, not copied
+
+
+# ---------------------------------------------------------------- column filter pre-pass
+@pytest.mark.parametrize("n,L", [(37, 5), (150, 1003), (300, 4096)])
+def test_column_filter_vs_oracle(ctx, n, L):
+    """spk_column_state_counts / spk_set_alignment_filtered (Alignment_filter.hpp:250-339): counts bit-exact, keep mask =
+    the oracle's, and the context afterwards equals one given the host-filtered matrix."""
+    rng = np.random.default_rng(L)
+    raw = rng.integers(0, 4, size=(n, L)).astype(np.uint8)
+    inv = rng.random(L) < 0.3
+    raw[:, inv] = rng.integers(0, 4, size=int(inv.sum()))[None, :]                      # invariant columns
+    rare = rng.random(L) < 0.2
+    raw[:, rare] = np.where(rng.random((n, int(rare.sum()))) < 0.004, 1, 0)              # minor allele below maf
+    gappy = rng.random(L) < 0.2
+    raw[:, gappy] = np.where(rng.random((n, int(gappy.sum()))) < 0.3, 4, raw[:, gappy])  # ~30 % gaps
+    pos = (np.arange(L, dtype=np.uint64) * 3 + 7)
+    cnt = ctx.column_state_counts(raw)
+    exp_cnt = np.stack([(raw == a).sum(axis=0) for a in range(5)], axis=1).astype(np.uint32)
+    assert np.array_equal(cnt, exp_cnt)
+    exp_keep = orc.filter_columns(raw, 0.01, 0.15).astype(bool)
+    if exp_keep.sum() < 2:
+        from spydrpick_b200 import SpkError
+        with pytest.raises(SpkError):
+            ctx.set_alignment_filtered(raw, pos, 0.01, 0.15)
+        return
+    keep = ctx.set_alignment_filtered(raw, pos, 0.01, 0.15)
+    assert np.array_equal(keep, exp_keep) and ctx.L == int(exp_keep.sum())
+    f = np.ascontiguousarray(raw[:, exp_keep]); fpos = pos[exp_keep]
+    Lf = f.shape[1]
+    c_dev = ctx.neighbour_counts(int(0.9 * Lf), True)
+    assert np.array_equal(c_dev, orc.neighbour_counts(f, int(0.9 * Lf), True))
+    ctx.set_weights(1.0 / c_dev.astype(np.float64))
+    r_dev = ctx.mi_scan(0.02, ld_threshold=10)
+    ctx.set_alignment(f, fpos)
+    ctx.set_weights(1.0 / c_dev.astype(np.float64))
+    r_host = ctx.mi_scan(0.02, ld_threshold=10)
+    assert r_dev["edges"].tobytes() == r_host["edges"].tobytes()
+    assert np.array_equal(r_dev["colmax"], r_host["colmax"])
