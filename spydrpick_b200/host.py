@@ -64,6 +64,28 @@ class Alignment:
         self.ctx = ctx or Context(device=device)
         self.ctx.set_alignment(self.states, self.pos)
 
+    @classmethod
+    def filtered(cls, raw_states, pos=None, n_original_positions=None, id_string="alignment", maf_threshold=0.01,
+                 gap_threshold=0.15, ctx: Optional[Context] = None, device=-1):
+        """apegrunt::Alignment_filter (Alignment_filter.hpp:250-339; src/SpydrPick.cpp:234-297) on the device: the RAW
+        alignment is uploaded once, state frequencies are counted and the accepted columns extracted in HBM
+        (spk_set_alignment_filtered). Returns the filtered Alignment; `.keep` is the accept mask over the raw columns."""
+        raw = np.ascontiguousarray(raw_states, dtype=np.uint8)
+        if raw.ndim != 2 or raw.max(initial=0) > 4:
+            raise ValueError("states must be a 2D array of codes 0..4 (a,t,c,g,GAP)")
+        rpos = np.arange(raw.shape[1], dtype=np.uint64) if pos is None else np.ascontiguousarray(pos, dtype=np.uint64)
+        self = cls.__new__(cls)
+        self.ctx = ctx or Context(device=device)
+        self.keep = self.ctx.set_alignment_filtered(raw, rpos, maf_threshold, gap_threshold)
+        self.states = np.ascontiguousarray(raw[:, self.keep])          # host view of what the device extracted
+        self.n, self.L = self.states.shape
+        self.pos = rpos[self.keep]
+        self.n_original_positions = int(n_original_positions) if n_original_positions is not None else int(rpos[-1]) + 1
+        self.id_string = "%s.filtered_ge%03dmaf_le%03dgf_gt01-lt05states" % (id_string, int(maf_threshold * 100.), int(gap_threshold * 100.))
+        self.weights = np.ones(self.n, dtype=np.float64)
+        self.neighbour_counts = None
+        return self
+
     def n_loci(self):
         return self.L
 

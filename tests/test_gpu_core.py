@@ -322,3 +322,23 @@ def test_column_filter_vs_oracle(ctx, n, L):
     r_host = ctx.mi_scan(0.02, ld_threshold=10)
     assert r_dev["edges"].tobytes() == r_host["edges"].tobytes()
     assert np.array_equal(r_dev["colmax"], r_host["colmax"])
+
+
+def test_host_mirror_filtered_alignment():
+    """host.Alignment.filtered = the reference's filter step + upload; the pipeline on it equals the pipeline on the host-filtered matrix."""
+    from spydrpick_b200 import host
+    s, pos, gsize = generate_alignment(100, 400, seed=11)
+    raw = np.zeros((100, 800), dtype=np.uint8)
+    raw[:, 0::2] = s
+    raw[:, 1::2] = 2                                                   # invariant columns the filter drops
+    rpos = np.arange(800, dtype=np.uint64)
+    a = host.Alignment.filtered(raw, rpos, n_original_positions=800)
+    exp_keep = orc.filter_columns(raw, 0.01, 0.15).astype(bool)
+    assert np.array_equal(a.keep, exp_keep) and a.L == int(exp_keep.sum()) and a.id_string.endswith("filtered_ge001maf_le015gf_gt01-lt05states")
+    opt = host.Options(mi_threshold=0.05)
+    net = host.run_pipeline(a, opt)
+    b = host.Alignment(np.ascontiguousarray(raw[:, exp_keep]), rpos[exp_keep], n_original_positions=800, ctx=a.ctx)
+    net2 = host.run_pipeline(b, opt)
+    assert net.network.tobytes() == net2.network.tobytes() and len(net.network) > 0
+    assert np.array_equal(net.flags, net2.flags)
+    a.ctx.close()
