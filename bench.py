@@ -290,8 +290,14 @@ def run_b200(args):
             if host_flags is None or host_flags.shape[0] < len(edges):
                 host_flags = pinned_empty(int(len(edges) * 1.25) + 4096, np.uint8)
             flags = ctx.aracne(edges, EPS, out=host_flags)   # same pointer -> device copy reused; overlaps the edge download
+            t_ar = time.perf_counter()
             ctx.wait_download()                       # edges + MI-without-gaps lists are now complete on the host
+            t_wd = time.perf_counter()
             ndirect = int(np.count_nonzero(flags))    # the step's result is read on the host
+            if os.environ.get("SPK_BENCH_E2E_BREAKDOWN"):
+                tma = ctx.timings()
+                sys.stderr.write("e2e aracne phase ms: spk_aracne %.2f (device: CSR build %.2f, K3 %.2f) | wait_download %.2f | count flags %.2f\n" % (
+                    1e3 * (t_ar - tw[-1]), tma["aracne_build_ms"], tma["aracne_ms"], 1e3 * (t_wd - t_ar), 1e3 * (time.perf_counter() - t_wd)))
             h2d = states.nbytes + pos.nbytes + 8 * n + len(flags)
             d2h = edges.nbytes + r["edges_wo_gaps"].nbytes + 8 * L + 8 * n + len(flags)
         else:

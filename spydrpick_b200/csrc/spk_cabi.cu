@@ -153,7 +153,7 @@ static int set_alignment_impl(spk_ctx* c, const uint8_t* states, uint32_t n, uin
         if ((r = dev_alloc(c, c->d_colmax32, (size_t)c->L_pad * 4, "colmax32"))) return r;
         if ((r = dev_alloc(c, c->d_counts, (size_t)n * 8, "counts"))) return r;
     }
-    c->operands_terms = 0; c->stats_valid = false; c->host_edges_n = 0; c->g_state = 0;
+    c->operands_terms = 0; c->stats_valid = false; c->host_edges_n = 0; c->g_state = 0; c->d_edges_sorted_n = 0;
     SPK_CUDA(c, cudaEventRecord(c->ev[0], c->stream));
     SPK_CUDA(c, cudaMemcpyAsync(c->d_states, states, (size_t)n * L, kind, c->stream));
     std::vector<uint64_t> hp(c->L_pad, 0);
@@ -461,6 +461,9 @@ int spk_mi_scan(spk_ctx* c, const spk_scan_params* pp, spk_scan_result* res) {
         }
         cap = newcap; return SPK_OK;
     };
+    // colmax is final after compaction: read back BEFORE the bulk downloads are queued (one D2H copy engine, in issue order)
+    c->h_colmax.resize(c->L);
+    SPK_CUDA(c, cudaMemcpyAsync(c->h_colmax.data(), c->d_colmax, (size_t)c->L * 8, cudaMemcpyDeviceToHost, c->stream));
     bool wo_in_flight = false;
     if (p.keep_on_device == 2 && nw) {
         // the MI-without-gaps list is final after compaction (the sort only touches the edge list): its download
@@ -471,11 +474,10 @@ int spk_mi_scan(spk_ctx* c, const spk_scan_params* pp, spk_scan_result* res) {
         SPK_CUDA(c, cudaMemcpyAsync(c->hp_wo, c->d_wo, nw * sizeof(spk_edge), cudaMemcpyDeviceToHost, c->copy_stream));
         wo_in_flight = true;
     }
-    if (p.sort_desc) { r = sort_edges_device(c, c->d_edges, ne); if (r) return r; }
+    c->d_edges_sorted_n = 0;
+    if (p.sort_desc) { r = sort_edges_device(c, c->d_edges, ne); if (r) return r; c->d_edges_sorted_n = ne; }
     res->n_edges = ne; res->n_wo_gaps = nw;
     res->d_edges = c->d_edges; res->d_edges_wo_gaps = c->d_wo; res->d_colmax = c->d_colmax;
-    c->h_colmax.resize(c->L);
-    SPK_CUDA(c, cudaMemcpyAsync(c->h_colmax.data(), c->d_colmax, (size_t)c->L * 8, cudaMemcpyDeviceToHost, c->stream));
     c->host_edges_n = 0;
     if (p.keep_on_device != 1) {
         if ((r = grow(c->hp_edges, c->hp_edges_cap, ne))) return r;
