@@ -116,6 +116,7 @@ void spk_destroy(spk_ctx* c) {
     if (c->ev_ready) cudaEventDestroy(c->ev_ready);
     if (c->ev_dl) cudaEventDestroy(c->ev_dl);
     if (c->d_flags_buf) cudaFree(c->d_flags_buf);
+    if (c->h_mail) cudaFreeHost(c->h_mail);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
 }

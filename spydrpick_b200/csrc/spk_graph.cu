@@ -167,6 +167,11 @@ __global__ void edge_scan_kernel(const spk_edge* __restrict__ e, unsigned long l
     bad = __any_sync(0xffffffffu, bad);
     if ((threadIdx.x % 32) == 0) { if (m) atomicMax(&out[0], m); if (bad) out[2] = 1u; }
 }
+// device words -> mapped host memory (visible to the host once the stream has drained)
+__global__ void publish_words_kernel(const unsigned int* __restrict__ src, unsigned int* __restrict__ dst, int nwords) {
+    if ((int)threadIdx.x < nwords) dst[threadIdx.x] = src[threadIdx.x];
+    __threadfence_system();
+}
 // entry order for an unsorted list: key = ~ordered(weight) so that an ascending stable sort puts strong edges first
 __global__ void entry_weight_keys_kernel(const spk_edge* __restrict__ e, unsigned long long m,
                                          unsigned long long* __restrict__ keys, uint32_t* __restrict__ ents) {
@@ -351,9 +356,19 @@ int aracne_device(Ctx* c, const spk_edge* d_edges, uint64_t n, double eps, uint3
     if (d_edges == c->d_edges && c->d_edges_sorted_n == n && c->d_states) {
         h_scan[0] = c->L - 1;
     } else {
+        // caller-supplied list: the 16 bytes come back through a mapped page-locked mailbox written by a kernel, not through
+        // cudaMemcpy -- a caller that downloads the list on another stream meanwhile (multi-GPU rank 0) owns the copy engine
+        if (!c->h_mail) {
+            if (cudaHostAlloc((void**)&c->h_mail, 64, cudaHostAllocMapped) != cudaSuccess ||
+                cudaHostGetDevicePointer((void**)&c->d_mail, c->h_mail, 0) != cudaSuccess) {
+                cudaGetLastError(); if (c->h_mail) { cudaFreeHost(c->h_mail); c->h_mail = nullptr; }
+                return fail(c, SPK_E_NOMEM, "mapped mailbox allocation failed");
+            }
+        }
         edge_scan_kernel<<<ge, 256, 0, c->stream>>>(d_edges, n, d_scan);
-        SPK_CUDA(c, cudaMemcpyAsync(h_scan, d_scan, 16, cudaMemcpyDeviceToHost, c->stream));
+        publish_words_kernel<<<1, 32, 0, c->stream>>>(d_scan, c->d_mail, 4);
         SPK_CUDA(c, cudaStreamSynchronize(c->stream));
+        for (int k = 0; k < 4; ++k) h_scan[k] = ((volatile unsigned int*)c->h_mail)[k];
     }
     const uint32_t nn = h_scan[0] + 1;
     uint32_t bits = 1; while (bits < 32 && (1ull << bits) < (unsigned long long)nn) ++bits;

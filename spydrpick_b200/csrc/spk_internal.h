@@ -130,6 +130,7 @@ struct Ctx {
     double*   d_gval = nullptr; uint32_t g_nw_cap = 0;           // [g_NW] weight of the samples of word w (0 for padding words)
     double*   d_gmarg = nullptr;          // [L_pad][5] fp64 weighted marginals summed the same way
     int32_t*  d_gslot = nullptr;          // [g_NW*32] sample index per bit slot, -1 = padding
+    unsigned int* h_mail = nullptr; unsigned int* d_mail = nullptr;   // 64-byte page-locked mailbox, mapped into the device: small read-backs that must not queue on the D2H copy engine
     uint64_t d_edges_sorted_n = 0;        // > 0: d_edges holds this many edges of the last scan in Graph::sort order (node ids < L)
     std::vector<int32_t> h_gslot; std::vector<double> h_gval;       // host sources of the two uploads (kept alive: no sync after the async copies)
     double*   d_gH = nullptr;             // [L_pad][5] marginal entropy sum_a p_a ln p_a for partner #states 1..5
