@@ -222,6 +222,7 @@ int spk_column_state_counts(spk_ctx* c, const uint8_t* states, uint32_t n, uint6
 int spk_set_alignment_filtered(spk_ctx* c, const uint8_t* states, uint32_t n, uint64_t L, const uint64_t* pos,
                                double maf_threshold, double gap_threshold, uint8_t* keep, uint64_t* n_kept) {
     if (!c || !states || !keep || !n_kept || n == 0 || L < 2) return c ? fail(c, SPK_E_INVALID, "set_alignment_filtered: need states, keep, n_kept, n >= 1, L >= 2") : SPK_E_INVALID;
+    if (L > 0xffffffffull) return fail(c, SPK_E_INVALID, "L too large");
     SPK_CUDA(c, cudaSetDevice(c->device));
     RawUpload u; std::vector<uint32_t> cnt;
     int r = upload_and_count(c, states, n, L, u, cnt); if (r) return r;
@@ -236,7 +237,6 @@ int spk_set_alignment_filtered(spk_ctx* c, const uint8_t* states, uint32_t n, ui
     }
     *n_kept = idx.size();
     if (idx.size() < 2) return fail(c, SPK_E_INVALID, "fewer than 2 columns pass the MAF / gap filter");
-    if (L > 0xffffffffull) return fail(c, SPK_E_INVALID, "L too large");
     const uint32_t Lk = (uint32_t)idx.size();
     uint32_t* d_idx = nullptr; uint8_t* d_f = nullptr;
     if (cudaMalloc(&d_idx, (size_t)Lk * 4) != cudaSuccess || cudaMalloc(&d_f, (size_t)n * Lk) != cudaSuccess) {
