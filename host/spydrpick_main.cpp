@@ -386,9 +386,8 @@ int main(int argc, char** argv) {
     if (!o.mapping_list.empty()) {
         std::vector<uint64_t> m = read_index_list(o.mapping_list, o.input_indexing_base);
         if (m.size() != A.L) die("mapping list and alignment sizes are mismatched (" + std::to_string(m.size()) + " and " + std::to_string(A.L) + ")");
-        A.pos.swap(m);
-        A.n_original_positions = A.pos.back() + 1;
-    }
+        A.pos.swap(m);                     // the mapping list only replaces the loci translation: n_original_positions stays the
+    }                                      // FASTA column count unless --genome-size is given (Alignment_utility.hpp:128-160)
     if (o.genome_size) A.n_original_positions = o.genome_size;
 
     spk_ctx* ctx = nullptr;
@@ -427,10 +426,10 @@ int main(int argc, char** argv) {
         } else {
             std::vector<uint64_t> counts(n);
             const uint64_t min_identical = (uint64_t)(o.sample_reweighting_threshold * double(L));          // weights.hpp:228,251
-            check(ctx, spk_neighbour_counts(ctx, min_identical, 1, counts.data()), "sample reweighting");
+            check(ctx, spk_neighbour_counts(ctx, min_identical, SPK_QUIRKS_REFERENCE, counts.data()), "sample reweighting");
             for (uint32_t s = 0; s < n; ++s) w[s] = 1.0 / double(counts[s]);                                   // weights.hpp:349
         }
-        if (o.rescale_sample_weights) { double sum = 0; for (double x : w) sum += x; for (double& x : w) x *= double(n) / sum; }   // Alignment_utility.hpp:238-242
+        if (o.rescale_sample_weights) { double n_eff = 0; for (double x : w) n_eff += x; for (double& x : w) x = x * double(n) / n_eff; }   // (w * n) / n_eff, Alignment_utility.hpp:215,245
         check(ctx, spk_set_weights(ctx, w.data()), "sample weights");
     }
     double neff = 0; for (double x : w) neff += x;

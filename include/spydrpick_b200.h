@@ -87,15 +87,23 @@ int spk_set_alignment_filtered(spk_ctx* ctx, const uint8_t* states, uint32_t n, 
 /* Replaces apegrunt::calculate_weights (Alignment_StateVector_weights.hpp:192-353) up to the
  * integer neighbour counts: counts[i] = 1 + #{j != i : similar(i,j)} with
  * similar = ident(i,j) >= min_identical, min_identical = (size_t)(threshold*(double)L) computed
- * by the caller as the reference does (:228,251). emulate_lastblock_quirk != 0 reproduces
- * is_similar_to_impl's double count of the final 32-column block when L % 32 == 0
- * (StateVector_impl_block_compressed_alignment_storage.hpp:628-659). */
-int spk_neighbour_counts(spk_ctx* ctx, uint64_t min_identical, int emulate_lastblock_quirk,
+ * by the caller as the reference does (:228,251). `quirks` is a mask of the reference behaviours to reproduce
+ * (both pinned against the compiled reference, tests/test_ref_pins.py; SPK_QUIRKS_REFERENCE = what the reference does):
+ *   SPK_QUIRK_LASTBLOCK  is_similar_to_impl counts the final 32-column block twice when L % 32 == 0
+ *                        (StateVector_impl_block_compressed_alignment_storage.hpp:628-659);
+ *   SPK_QUIRK_SAMPLE0    calculate_weights compares sample 0 with every sample (itself included) in its cache-priming pass
+ *                        (range_primer, Alignment_StateVector_weights.hpp:218-238, 275-283) and then again in the triangular
+ *                        pass (:240-262): counts[0] = 3 + 2 * #{j > 0 similar to 0}, and every j > 0 similar to sample 0
+ *                        carries one extra count. */
+#define SPK_QUIRK_LASTBLOCK  1
+#define SPK_QUIRK_SAMPLE0    2
+#define SPK_QUIRKS_REFERENCE 3
+int spk_neighbour_counts(spk_ctx* ctx, uint64_t min_identical, int quirks,
                          uint64_t* counts /* [n] host */);
 /* Multi-GPU sharding of K1: the sample-tile pairs are dealt round-robin to n_parts partitions; every partition
  * returns PARTIAL counts whose element-wise sum over the partitions equals spk_neighbour_counts' result
  * (partition 0 carries each sample's own multiplicity). n_parts <= 1: identical to spk_neighbour_counts. */
-int spk_neighbour_counts_part(spk_ctx* ctx, uint64_t min_identical, int emulate_lastblock_quirk,
+int spk_neighbour_counts_part(spk_ctx* ctx, uint64_t min_identical, int quirks,
                               uint32_t part_index, uint32_t n_parts, uint64_t* counts /* [n] host */);
 
 /* Replaces the per-sequence set_weight() done by cache_sample_weights

@@ -4,10 +4,15 @@
 // product: only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl
 // reference legs may load it. The product path (spydrpick_b200/csrc) never links it.
 //
-// PARITY UNPINNED by the reference's own tests: the reference (santeripuranen/SpydrPick
-// @ f6bc110, apegrunt @ 5c61810) ships no tests, golden vectors or fixtures, and cannot
-// be compiled here (needs Boost + legacy TBB, neither installed). The pins
-// are hand-computed known-answer vectors in tests/golden/ (see tests/test_oracle_*.py).
+// PINNED AGAINST THE REAL REFERENCE. The reference (santeripuranen/SpydrPick @ f6bc110, apegrunt @ 5c61810) ships no tests,
+// golden vectors or fixtures of its own, and its build system needs Boost + legacy TBB (not installed). Its sources however
+// compile IN PLACE against the small Boost / TBB stand-ins of oracle/ref_shims (oracle/Makefile.ref -> oracle/_ref/SpydrPick_ref,
+// the reference program with its own main(); oracle/_ref/libspkref.so, C entry points over the same templates). This file is
+// checked against that compiled reference: tests/test_ref_pins.py (normalize_and_get_mi_single bit-exact on > 1e5 tables,
+// calculate_weights integer-exact incl. both quirks, the scan / MI-without-gaps / fences to 1e-14, Graph::sort, run_ARACNE and
+// both writers byte-equal) and against the listings the reference program wrote for 16 runs (tests/golden/ref,
+// tests/test_ref_golden.py). Known, documented deviation: the reference's per-pair path MI_solver::single (threshold
+// estimator only) is defective for ~2 % of the pairs -- it disagrees with the reference's own scan; orc_mi_pairs follows the scan.
 //
 // Every function cites the reference file:line it restates. "ref:" paths are relative to
 // /root/reference; "apegrunt/" = externals/apegrunt/include/apegrunt/, "misc/" =
@@ -157,34 +162,43 @@ extern "C" {
 //   L % 32 == 0 : ident(i,j) + ident_lastblock(i,j) >= min_identical when lastblock_quirk != 0
 //                 (the reference's post-loop code counts the final block twice), else exact.
 // ---------------------------------------------------------------------------------------
+// `quirks` is a bit mask (include/spydrpick_b200.h SPK_QUIRK_*): bit 0 = the L % 32 == 0 final-block double count above;
+// bit 1 = the SAMPLE-0 double count: calculate_weights first compares sample 0 with EVERY sample j in [0, n) -- itself
+// included -- in its cache-priming pass (range_primer, Alignment_StateVector_weights.hpp:218-238, primer_ranges :275-283 cover
+// [0, n)), and then compares all pairs i in [1, n), j in [0, i) -- sample 0 again -- in range_worker (:240-262, :287-295).
+// So int_weights[0] = 1 + 2 (the self pair credits both ends) + 2 * #{j > 0 similar to 0}, and every j > 0 similar to
+// sample 0 carries one extra count. Pinned against the compiled reference (tests/test_ref_pins.py).
 int orc_neighbour_counts(const uint8_t* states, uint64_t n, uint64_t L, uint64_t min_identical,
-                         int lastblock_quirk, int threads, uint64_t* counts) {
+                         int quirks, int threads, uint64_t* counts) {
     std::vector<std::atomic<uint64_t>> acc(n);
     for (auto& a : acc) a.store(1);
-    const bool quirk = lastblock_quirk && L > 0 && (L % BS == 0);
+    const bool quirk = (quirks & 1) && L > 0 && (L % BS == 0);
     const size_t last0 = L >= BS ? L - BS : 0;
+    auto similar = [&](size_t i, size_t j) {
+        const uint8_t* ri = states + i * L; const uint8_t* rj = states + j * L;
+        uint64_t eff = 0;
+        for (size_t c = 0; c < L; ++c) eff += (ri[c] == rj[c]);
+        if (quirk) { for (size_t c = last0; c < L; ++c) eff += (ri[c] == rj[c]); }
+        return eff >= min_identical;
+    };
     parallel_for(1, n, threads, [&](size_t i, int) {
-        const uint8_t* ri = states + i * L;
-        for (size_t j = 0; j < i; ++j) {
-            const uint8_t* rj = states + j * L;
-            uint64_t ident = 0;
-            for (size_t c = 0; c < L; ++c) ident += (ri[c] == rj[c]);
-            uint64_t eff = ident;
-            if (quirk) { for (size_t c = last0; c < L; ++c) eff += (ri[c] == rj[c]); }
-            if (eff >= min_identical) { acc[i].fetch_add(1); acc[j].fetch_add(1); }
-        }
+        for (size_t j = 0; j < i; ++j)
+            if (similar(i, j)) { acc[i].fetch_add(1); acc[j].fetch_add(1); }
     });
+    if ((quirks & 2) && n > 0)
+        for (size_t j = 0; j < n; ++j)
+            if (similar(0, j)) { acc[0].fetch_add(1); acc[j].fetch_add(1); }
     for (size_t i = 0; i < n; ++i) counts[i] = acc[i].load();
     return 0;
 }
 
 // weights[i] = 1/counts[i]; ref: apegrunt/Alignment_StateVector_weights.hpp:349
-// optional rescale w *= n / sum(w): ref apegrunt/Alignment_utility.hpp:238-242
+// optional rescale (w * n) / sum(w): ref apegrunt/Alignment_utility.hpp:215,245
 int orc_weights_from_counts(const uint64_t* counts, uint64_t n, int rescale, double* w) {
     for (uint64_t i = 0; i < n; ++i) w[i] = 1.0 / double(counts[i]);
     if (rescale) {
         double s = 0; for (uint64_t i = 0; i < n; ++i) s += w[i];
-        for (uint64_t i = 0; i < n; ++i) w[i] *= double(n) / s;
+        for (uint64_t i = 0; i < n; ++i) w[i] = w[i] * double(n) / s;      // (w * n) / n_eff, left to right like the reference
     }
     return 0;
 }

@@ -1,7 +1,8 @@
 """ctypes wrapper around oracle/liboracle.so -- TEST INFRASTRUCTURE ONLY.
 
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
-import this module. Parity unpinned by the reference's own tests (it has none); see oracle.cpp.
+import this module. The reference ships no tests of its own; the oracle is pinned against the REAL reference compiled in
+place (oracle/ref.py, oracle/Makefile.ref): tests/test_ref_pins.py (unit level) and tests/test_ref_golden.py (listings).
 """
 import ctypes as C
 import os
@@ -60,11 +61,16 @@ def hardware_threads():
     return int(lib().orc_hardware_threads())
 
 
-def neighbour_counts(states, min_identical, lastblock_quirk=True, threads=0):
+QUIRK_LASTBLOCK, QUIRK_SAMPLE0, QUIRKS_REFERENCE = 1, 2, 3
+
+
+def neighbour_counts(states, min_identical, quirks=True, threads=0):
+    """quirks: True = everything the reference does (QUIRKS_REFERENCE), False = the plain rule, or a QUIRK_* bit mask."""
     s = _states(states); n, L = s.shape
     out = np.zeros(n, dtype=np.uint64)
+    q = QUIRKS_REFERENCE if quirks is True else (0 if quirks is False else int(quirks))
     lib().orc_neighbour_counts(_p(s), C.c_uint64(n), C.c_uint64(L), C.c_uint64(int(min_identical)),
-                               C.c_int(int(lastblock_quirk)), C.c_int(threads), _p(out))
+                               C.c_int(q), C.c_int(threads), _p(out))
     return out
 
 

@@ -13,6 +13,7 @@ LIB_PATH = os.environ.get("SPYDRPICK_B200_LIB") or os.path.join(_HERE, "libspydr
 EDGE_DTYPE = np.dtype([("i", np.uint32), ("j", np.uint32), ("mi", np.float64)], align=True)
 assert EDGE_DTYPE.itemsize == 16
 
+QUIRK_LASTBLOCK, QUIRK_SAMPLE0, QUIRKS_REFERENCE = 1, 2, 3
 SPK_OK, SPK_E_INVALID, SPK_E_CUDA, SPK_E_NOMEM, SPK_E_OVERFLOW, SPK_E_PRECISION = 0, -1, -2, -3, -4, -5
 
 EXPORTS = ["spk_create", "spk_destroy", "spk_last_error", "spk_set_stream", "spk_host_alloc", "spk_host_free",
@@ -206,11 +207,12 @@ class Context:
         self._check(self.lib.spk_set_alignment_device(self.h, C.c_void_p(int(d_states)), int(n), int(L), _ptr(p)))
         self.n, self.L = int(n), int(L)
 
-    def neighbour_counts(self, min_identical, lastblock_quirk=True, part_index=0, n_parts=1):
-        """n_parts > 1: PARTIAL counts of this partition of the sample-tile pairs (sum over partitions = full counts)."""
+    def neighbour_counts(self, min_identical, quirks=True, part_index=0, n_parts=1):
+        """quirks: True = SPK_QUIRKS_REFERENCE (everything the reference does), False = the plain rule, or a SPK_QUIRK_* mask.
+        n_parts > 1: PARTIAL counts of this partition of the sample-tile pairs (sum over partitions = full counts)."""
         out = np.zeros(self.n, dtype=np.uint64)
-        self._check(self.lib.spk_neighbour_counts_part(self.h, int(min_identical), int(lastblock_quirk), part_index, n_parts,
-                                                       _ptr(out)))
+        q = QUIRKS_REFERENCE if quirks is True else (0 if quirks is False else int(quirks))
+        self._check(self.lib.spk_neighbour_counts_part(self.h, int(min_identical), q, part_index, n_parts, _ptr(out)))
         return out
 
     def set_weights(self, w):

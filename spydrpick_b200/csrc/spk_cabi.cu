@@ -260,6 +260,7 @@ int spk_neighbour_counts_part(spk_ctx* c, uint64_t min_identical, int quirk, uin
     int r = hamming_neighbour_counts(c, min_identical, quirk, part, nparts); if (r) return r;
     SPK_CUDA(c, cudaMemcpyAsync(counts, c->d_counts, (size_t)c->n * 8, cudaMemcpyDeviceToHost, c->stream));
     SPK_CUDA(c, cudaStreamSynchronize(c->stream));
+    SPK_CUDA(c, cudaEventElapsedTime(&c->tm.hamming_ms, c->ev[0], c->ev[1]));
     return SPK_OK;
 }
 

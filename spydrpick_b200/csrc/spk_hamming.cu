@@ -269,13 +269,39 @@ hamming_csa_kernel(const uint32_t* __restrict__ planes, uint32_t n, uint32_t L, 
     }
 }
 
+// The reference's SAMPLE-0 double count (SPK_QUIRK_SAMPLE0): calculate_weights compares sample 0 with every sample j in
+// [0, n) -- itself included -- in its cache-priming pass (range_primer, Alignment_StateVector_weights.hpp:218-238) and then
+// again as pair (j, 0) of the triangular pass (range_worker, :240-262). One warp per sample j: ident(0, j) over the planes,
+// the same final-block rule as above, and one more count for both ends of every similar pair (j = 0: the self pair).
+__global__ void __launch_bounds__(256)
+hamming_row0_kernel(const uint32_t* __restrict__ planes, uint32_t n, uint32_t L, uint32_t W32,
+                    unsigned long long min_identical, int lastblock_quirk, unsigned long long* __restrict__ counts) {
+    const uint32_t j = blockIdx.x * 8 + threadIdx.x / 32, lane = threadIdx.x % 32;
+    if (j >= n) return;
+    const size_t plane = (size_t)n * W32;
+    const uint32_t* r0 = planes; const uint32_t* rj = planes + (size_t)j * W32;
+    uint32_t mism = 0;
+    for (uint32_t w = lane; w < W32; w += 32)
+        mism += __popc((r0[w] ^ rj[w]) | (r0[plane + w] ^ rj[plane + w]) | (r0[2 * plane + w] ^ rj[2 * plane + w]));
+    mism = __reduce_add_sync(0xffffffffu, mism);
+    if (lane == 0) {
+        unsigned long long eff = (unsigned long long)L - mism;
+        if (lastblock_quirk && (L % 32u == 0u) && W32 > 0) {
+            const uint32_t w = W32 - 1;
+            eff += 32u - __popc((r0[w] ^ rj[w]) | (r0[plane + w] ^ rj[plane + w]) | (r0[2 * plane + w] ^ rj[2 * plane + w]));
+        }
+        if (eff >= min_identical) { atomicAdd(&counts[j], 1ull); atomicAdd(&counts[0], 1ull); }
+    }
+}
+
 __global__ void fill_ones_kernel(unsigned long long* counts, uint32_t n, unsigned long long v) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) counts[i] = v;        // 1 = multiplicity of the sample itself (weights.hpp:205-206); partition 0 carries it
 }
 
-int hamming_neighbour_counts(Ctx* c, uint64_t min_identical, int quirk, uint32_t part, uint32_t n_parts) {
+int hamming_neighbour_counts(Ctx* c, uint64_t min_identical, int quirks, uint32_t part, uint32_t n_parts) {
     const uint32_t nt = (c->n + HT - 1) / HT;
+    const int quirk = quirks & SPK_QUIRK_LASTBLOCK;
     SPK_CUDA(c, cudaEventRecord(c->ev[0], c->stream));
     fill_ones_kernel<<<(c->n + 255) / 256, 256, 0, c->stream>>>((unsigned long long*)c->d_counts, c->n, part == 0 ? 1ull : 0ull);
     static const bool v1 = [] { const char* e = getenv("SPYDRPICK_B200_K1"); return e && e[0] == '0'; }();
@@ -294,9 +320,12 @@ int hamming_neighbour_counts(Ctx* c, uint64_t min_identical, int quirk, uint32_t
                                                                     (unsigned long long*)c->d_counts, part, n_parts);
     }
     c->tm.kernel_launches += 2;
+    if ((quirks & SPK_QUIRK_SAMPLE0) && part == 0) {           // partition 0 carries the extra counts
+        hamming_row0_kernel<<<(c->n + 7) / 8, 256, 0, c->stream>>>(c->d_planes, c->n, c->L, c->W32, (unsigned long long)min_identical,
+                                                                   quirk, (unsigned long long*)c->d_counts);
+        c->tm.kernel_launches += 1;
+    }
     SPK_CUDA(c, cudaEventRecord(c->ev[1], c->stream));
-    SPK_CUDA(c, cudaEventSynchronize(c->ev[1]));
-    SPK_CUDA(c, cudaEventElapsedTime(&c->tm.hamming_ms, c->ev[0], c->ev[1]));
     SPK_CUDA(c, cudaGetLastError());
     return SPK_OK;
 }

@@ -41,7 +41,8 @@ class Options:
     output_indexing_base: int = 1
     # additions of this implementation
     seed: int = 1                         # the reference seeds from the clock (SpydrPick.hpp:178)
-    emulate_lastblock_quirk: bool = True  # is_similar_to_impl double count when L % 32 == 0
+    reference_quirks: object = True       # True = SPK_QUIRKS_REFERENCE: the L % 32 == 0 final-block double count and the
+                                          # sample-0 double count of calculate_weights; False = the plain rule; or a SPK_QUIRK_* mask
     n_terms: int = 0                      # bf16 weight-split terms of the tensor-core filter (0 = default)
     band: float = 0.0
     engine: int = 0                       # 0 = tcgen05 filter + fp64 refine, 1 = fp64 exhaustive (diagnostic)
@@ -57,7 +58,9 @@ class Alignment:
             raise ValueError("states must be a 2D array of codes 0..4 (a,t,c,g,GAP)")
         self.n, self.L = self.states.shape
         self.pos = np.arange(self.L, dtype=np.uint64) if pos is None else np.ascontiguousarray(pos, dtype=np.uint64)
-        self.n_original_positions = int(n_original_positions) if n_original_positions is not None else int(self.pos[-1]) + 1
+        # the reference: genome_size if given, else the number of columns of the parsed FASTA (Alignment_parsers.hpp:67,133);
+        # a mapping list does not change it (Alignment_utility.hpp:128-160)
+        self.n_original_positions = int(n_original_positions) if n_original_positions is not None else self.L
         self.id_string = id_string
         self.weights = np.ones(self.n, dtype=np.float64)       # StateVector default weight = 1
         self.neighbour_counts = None
@@ -80,7 +83,7 @@ class Alignment:
         self.states = np.ascontiguousarray(raw[:, self.keep])          # host view of what the device extracted
         self.n, self.L = self.states.shape
         self.pos = rpos[self.keep]
-        self.n_original_positions = int(n_original_positions) if n_original_positions is not None else int(rpos[-1]) + 1
+        self.n_original_positions = int(n_original_positions) if n_original_positions is not None else raw.shape[1]
         self.id_string = "%s.filtered_ge%03dmaf_le%03dgf_gt01-lt05states" % (id_string, int(maf_threshold * 100.), int(gap_threshold * 100.))
         self.weights = np.ones(self.n, dtype=np.float64)
         self.neighbour_counts = None
@@ -108,11 +111,14 @@ def cache_sample_weights(alignment: Alignment, options: Options = None, sample_w
     else:
         # min_identical = size_t(threshold * double(L)): Alignment_StateVector_weights.hpp:228,251
         min_identical = int(options.sample_reweighting_threshold * float(alignment.L))
-        counts = alignment.ctx.neighbour_counts(min_identical, options.emulate_lastblock_quirk)
+        counts = alignment.ctx.neighbour_counts(min_identical, options.reference_quirks)
         alignment.neighbour_counts = counts
         w = 1.0 / counts.astype(np.float64)                    # weights.hpp:349
     if options.rescale_sample_weights:
-        w = w * (alignment.n / w.sum())                        # Alignment_utility.hpp:238-242
+        n_eff = 0.0
+        for x in w.tolist():                                   # std::accumulate, left to right (Alignment_utility.hpp:208,233)
+            n_eff += x
+        w = (w * float(alignment.n)) / n_eff                   # (w * n) / n_eff: Alignment_utility.hpp:215,245
     alignment.weights = w
     alignment.ctx.set_weights(w)
     return w

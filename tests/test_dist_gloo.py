@@ -25,13 +25,13 @@ def _worker(rank, world, port, out):
     s, pos, _ = generate_alignment(60, 240, seed=11)
     w = orc.weights_from_counts(orc.neighbour_counts(s, int(0.9 * 240)))
     # K1 sharded over sample pairs: partial neighbour counts (partition 0 carries the sample itself) summed over ranks
-    counts_full = orc.neighbour_counts(s, int(0.9 * 240))
+    counts_full = orc.neighbour_counts(s, int(0.9 * 240), quirks=orc.QUIRK_LASTBLOCK)   # the pair rule only (the sample-0 extra counts ride on partition 0)
     owner = (np.add.outer(np.arange(60) // 8, np.arange(60) // 8 * 3)) % world
     owner = np.triu(owner, 1); owner = owner + owner.T                       # symmetric owner of the unordered pair
     partial = np.zeros(60, dtype=np.uint64)
     for a in range(60):
         for b_ in range(60):
-            if a != b_ and owner[a, b_] == rank and orc.neighbour_counts(s[[a, b_]], int(0.9 * 240))[0] == 2:
+            if a != b_ and owner[a, b_] == rank and orc.neighbour_counts(s[[a, b_]], int(0.9 * 240), quirks=orc.QUIRK_LASTBLOCK)[0] == 2:
                 partial[a] += 1
     if rank == 0:
         partial += 1

@@ -76,16 +76,21 @@ def test_neighbour_rule_lastblock_quirk():
     a = np.zeros(L, dtype=np.uint8); b = np.zeros(L, dtype=np.uint8)
     b[:10] = 1                                   # 10 mismatches in the FIRST block -> ident = 54
     s = np.stack([a, b])
-    assert list(orc.neighbour_counts(s, 55, lastblock_quirk=True)) == [2, 2]    # 54 + 32 >= 55
-    assert list(orc.neighbour_counts(s, 55, lastblock_quirk=False)) == [1, 1]
-    assert list(orc.neighbour_counts(s, 87, lastblock_quirk=True)) == [1, 1]    # 54 + 32 < 87
+    assert list(orc.neighbour_counts(s, 55, quirks=orc.QUIRK_LASTBLOCK)) == [2, 2]    # 54 + 32 >= 55
+    assert list(orc.neighbour_counts(s, 55, quirks=False)) == [1, 1]
+    assert list(orc.neighbour_counts(s, 87, quirks=orc.QUIRK_LASTBLOCK)) == [1, 1]    # 54 + 32 < 87
     # L=65: no quirk regardless of the flag
     s65 = np.concatenate([s, np.zeros((2, 1), dtype=np.uint8)], axis=1)          # ident = 55
-    assert list(orc.neighbour_counts(s65, 56, lastblock_quirk=True)) == [1, 1]
-    assert list(orc.neighbour_counts(s65, 55, lastblock_quirk=True)) == [2, 2]
+    assert list(orc.neighbour_counts(s65, 56, quirks=orc.QUIRK_LASTBLOCK)) == [1, 1]
+    assert list(orc.neighbour_counts(s65, 55, quirks=orc.QUIRK_LASTBLOCK)) == [2, 2]
     # gap == gap counts as identical
     g = np.full((2, 40), 4, dtype=np.uint8)
-    assert list(orc.neighbour_counts(g, 40)) == [2, 2]
+    assert list(orc.neighbour_counts(g, 40, quirks=False)) == [2, 2]
+    # the reference's sample-0 double count (pinned against the compiled reference in tests/test_ref_pins.py):
+    # counts[0] = 1 + 2 (self pair) + 2 * #neighbours of 0, every neighbour of sample 0 carries one extra count
+    assert list(orc.neighbour_counts(g, 40, quirks=True)) == [5, 3]
+    three = np.zeros((3, 40), dtype=np.uint8); three[2] = 1                      # sample 2 is nobody's neighbour
+    assert list(orc.neighbour_counts(three, 36, quirks=True)) == [5, 3, 1]
 
 
 def test_neighbour_counts_bruteforce():
@@ -95,7 +100,10 @@ def test_neighbour_counts_bruteforce():
     last = (s[:, None, 64:] == s[None, :, 64:]).sum(-1)
     exp_q = ((ident + last) >= thr).sum(1)       # includes self
     exp = (ident >= thr).sum(1)
-    assert np.array_equal(orc.neighbour_counts(s, thr, True), exp_q.astype(np.uint64))
+    assert np.array_equal(orc.neighbour_counts(s, thr, orc.QUIRK_LASTBLOCK), exp_q.astype(np.uint64))
+    sim0 = (ident + last)[0] >= thr                                        # sample 0 vs everyone, itself included, once more
+    exp_ref = exp_q.copy(); exp_ref += sim0; exp_ref[0] += sim0.sum()
+    assert np.array_equal(orc.neighbour_counts(s, thr, True), exp_ref.astype(np.uint64))
     assert np.array_equal(orc.neighbour_counts(s, thr, False), exp.astype(np.uint64))
     w = orc.weights_from_counts(exp)
     assert np.allclose(w, 1.0 / exp)

@@ -1,0 +1,72 @@
+"""CPU: the oracle (oracle/oracle.cpp, the restatement every GPU parity test is checked against) against the fixtures the REAL
+reference program produced (tests/golden/ref/, see tests/golden/make_ref_golden.py). This is what pins the oracle: every listing
+the compiled reference wrote for these runs -- edges, ARACNE flags, outliers with the MI-without-gaps quirk, sample weights
+with both K1 quirks, mapping lists with and without --genome-size, include / exclude lists, rescaled and user-supplied weights --
+is reproduced by the oracle within the comparison rules of tests/refcmp.py."""
+import numpy as np
+import pytest
+
+import oracle.oracle as orc
+import refcase
+import refcmp
+
+PINNED = [c for c in refcmp.cases() if c != "auto_threshold"]
+
+
+def test_fixtures_present():
+    assert len(PINNED) >= 14 and "auto_threshold" in refcmp.cases()
+
+
+@pytest.mark.parametrize("name", PINNED)
+def test_oracle_reproduces_reference_listings(name):
+    case = refcmp.load_case(name)
+    got = refcase.oracle_run(case)
+    edges_fn = refcmp.output_named(case, "edges")
+    # the reference names its files <stem>.L<L>n<n>.spydrpick_couplings.<base>-based.<E>edges
+    assert edges_fn.startswith("%s.L%dn%d.spydrpick_couplings.%d-based." % (got["stem"], got["L"], got["n"], got["out_base"])), edges_fn
+    ref_edges = refcmp.read_gz(case, edges_fn)
+    rep = refcmp.compare_edges(got["edges"], ref_edges, got["threshold"], got["eps"])
+    assert rep["edges"] > 100
+    # the oracle follows the reference's arithmetic to ~1e-15: everything but tie triangles is byte-identical
+    assert rep["only_ours"] == 0 and rep["only_ref"] == 0
+    assert rep["flag_ties"] <= 0.005 * rep["edges"] + 4          # every one of them verified to sit in a tie triangle by compare_edges
+    refcmp.compare_outliers(got["outliers"], refcmp.read_gz(case, refcmp.output_named(case, "outliers")), got["eps"], ref_edges)
+    wfn = refcmp.output_named(case, ".weights")
+    if wfn:
+        assert got["weights"] == refcmp.read_gz(case, wfn), "sample weights (8 significant digits) differ from the reference"
+    if "effective_sample_size_printed" in case:
+        assert abs(float(got["w"].sum()) - float(case["effective_sample_size_printed"])) <= 0.006
+    if "outlier_threshold_printed" in case:
+        assert abs(got["outlier"] - float(case["outlier_threshold_printed"])) <= 1e-6
+        assert abs(got["extreme"] - float(case["extreme_outlier_threshold_printed"])) <= 1e-6
+
+
+def test_outlier_cases_are_not_empty():
+    """at least the LD cases print outliers with a gap effect, so the MI-without-gaps quirk is really compared"""
+    n = 0
+    for name in ("c1_ld_linear", "c1_ld_circular", "map_genome", "map_nogenome"):
+        case = refcmp.load_case(name)
+        rows = [ln.split() for ln in refcmp.read_gz(case, refcmp.output_named(case, "outliers")).splitlines()]
+        assert len(rows) >= 1
+        n += sum(1 for r in rows if r[4] != r[5])
+    assert n >= 5
+
+
+def test_oracle_threshold_estimator_vs_reference_runs():
+    """--mi-threshold -1: the reference's estimator is clock-seeded; 7 reference runs give its spread (+-0.25 %).
+    The oracle's estimator (same algorithm, explicit seed) lands 0.5-1.2 % ABOVE it, and that offset is a defect of the reference,
+    not of the restatement: MI_solver::single (the estimator's per-pair path, misc/Crosstable.hpp:429-481) builds its
+    contingency table from a multi-way union of hybrid bitset/range index sets (IntegerSequence_Hybrid_bitset_range_operations.hpp
+    :1417-1530) that loses samples for ~2 % of the column pairs, so those pairs get an MI that differs from what the reference's
+    OWN scan computes for the same pair (tests/test_ref_pins.py::test_reference_single_disagrees_with_its_own_scan). The oracle
+    and the CUDA path give every sampled pair the scan's value. The accepted band is therefore one-sided and stated: within
+    +1.5 % / -0.5 % of the mean of the reference's runs."""
+    case = refcmp.load_case("auto_threshold")
+    ref_thr = np.array(case["mi_save_thresholds_printed"])
+    states, _ = refcmp.fasta_states(refcmp.read_gz(case, "auto_threshold.fasta"))
+    keep = orc.filter_columns(states)
+    f = np.ascontiguousarray(states[:, keep])
+    w = orc.weights_from_counts(orc.neighbour_counts(f, int(0.9 * f.shape[1]), True))
+    for seed in (1, 2, 3):
+        t = orc.determine_mi_threshold(f, w, 20000, seed=seed)
+        assert -0.005 <= t / ref_thr.mean() - 1.0 <= 0.015, (t, ref_thr)
