@@ -1,16 +1,19 @@
 #!/usr/bin/env python
 """bench.py -- headline benchmark of the hot path: weighted all-pairs MI scan + ARACNE.
 
-Workload (BASELINE.json configs[1]): synthetic bacterial-like alignment, 3,000 sequences x 100,000
-filtered SNP columns. One STEP = one pass of the hot path: K1 neighbour counts -> weights -> K2 scan
-(tcgen05 filter + fp64 refine + compaction) -> edge sort -> K3 ARACNE. `value` = column pairs per
-second with the alignment already resident in HBM; `e2e` = the same step through the host-buffer
-C-ABI (alignment H2D and edges / flags D2H inside the timed region).
+Workload (BASELINE.json configs[1]): synthetic bacterial-like alignment, 3,000 sequences x 100,000 filtered SNP columns.
+One STEP = one pass of the hot path: K1 neighbour counts -> weights -> K2 scan (tcgen05 filter + audit + fp64 refine +
+compaction) -> edge sort -> [multi-GPU: NCCL exchange + run merge] -> K3 ARACNE. `value` = column pairs per second with the
+alignment already resident in HBM; `e2e` = the same step through the host-buffer C-ABI (alignment H2D and edges / flags D2H
+inside the timed region). N > 1: one process per GPU (torchrun); every rank owns one spk context that belongs to the library's
+own NCCL communicator (spk_comm_init_rank) and makes the same collective C-ABI calls -- the exchange is inside the library.
 
   python bench.py --gpus N --steps K --warmup W            (N>1: launched by torch.distributed.run)
-  python bench.py --impl reference ...                      (CPU port of the reference, bounded sample)
+  python bench.py --impl reference ...                      (the REAL reference compiled in place, bounded sample, host cores)
+  python bench.py --n 3000 --L 50000 --mi-values 50000000   (config 5)   --n 20000 --L 250000 --linear-genome (config 4)
 """
 import argparse
+import glob
 import json
 import os
 import subprocess
@@ -25,6 +28,7 @@ sys.path.insert(0, ROOT)
 
 METRIC = "weighted_mi_scan_gpairs_per_s"
 UNIT = "Gpairs/s"
+EPS = 2.220446049250313e-16
 
 
 def parse_args():
@@ -39,27 +43,55 @@ def parse_args():
     ap.add_argument("--n-terms", type=int, default=0)
     ap.add_argument("--engine", type=int, default=0, help="0 = default int8 engine (= 4), 3 = int8 compact one-hot GEMM with {hi, lo} 16-bit weight rows, 4 = factorised byte weights (half the tensor work), 2 = dense bf16 GEMM")
     ap.add_argument("--mi-values", type=int, default=0, help="saved pairs target (0 = min(1e7, 100*L))")
+    ap.add_argument("--linear-genome", action="store_true")
     ap.add_argument("--cpu-sample-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-peaks", action="store_true", help="skip the in-run int8 / bf16 tensor peak measurement")
     return ap.parse_args()
 
 
-# from the committed ncu --set full captures of the main-pass launch at 3000 x 100000
-# (engine 4: profiles/r01f_ncu_full_summary.csv; engine 3: profiles/r01_ncu_full_summary.csv):
-# dram__bytes_read.sum + dram__bytes_write.sum per launch, sm__pipe_tensor_cycles_active %, per int8 engine
-NCU_TRAFFIC = {3: 52.2e9, 4: 26.7e9}
-NCU_TENSOR_PCT = {3: 90.4, 4: 79.1}
-
-
-def peaks():
+def driver_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
         d = json.load(open(p))
-        return {"bf16_tflops": d.get("bf16_tflops_sustained", d.get("bf16_tflops", 1400.0)), "hbm_gbs": d.get("hbm_gbs", 6650.0),
-                "bf16_burst_tflops": d.get("bf16_tflops", 1650.0),
-                "source": "measured (MEASURED_PEAKS.json, sustained bf16)"}
-    return {"bf16_tflops": 1400.0, "bf16_burst_tflops": 1650.0, "hbm_gbs": 6650.0, "source": "fallback (B200_PROFILING.md)"}
+        return {"bf16_tflops_sustained": d.get("bf16_tflops_sustained"), "bf16_tflops_burst": d.get("bf16_tflops"), "hbm_gbs": d.get("hbm_gbs", 6534.8),
+                "source": "MEASURED_PEAKS.json (driver-written)"}
+    return {"bf16_tflops_sustained": 1400.0, "bf16_tflops_burst": 1650.0, "hbm_gbs": 6500.0, "source": "fallback (B200_PROFILING.md)"}
+
+
+def measure_tensor_peaks(torch, device, seconds=2.0):
+    """Dense int8 (s8 x s8 -> s32, torch._int_mm = cuBLASLt) and bf16 peaks on THIS box in THIS run: 8192^3, best of 10 (burst)
+    and back to back for `seconds` (sustained). The MI filter issues tcgen05 kind::i8 MMAs, so its utilisation is quoted against
+    the measured int8 number; the driver's bf16 figures are printed next to it."""
+    out = {}
+    M = 8192
+    ops = 2.0 * M * M * M
+    try:
+        a = torch.randint(-8, 8, (M, M), dtype=torch.int8, device=device); b = torch.randint(-8, 8, (M, M), dtype=torch.int8, device=device)
+        f = lambda: torch._int_mm(a, b)
+        for name, fn in (("int8", f),):
+            for _ in range(3):
+                fn()
+            torch.cuda.synchronize(device)
+            best = 1e9
+            for _ in range(10):
+                e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+                e0.record(); fn(); e1.record(); torch.cuda.synchronize(device)
+                best = min(best, e0.elapsed_time(e1))
+            e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+            reps = max(10, int(seconds * 1e3 / best))
+            e0.record()
+            for _ in range(reps):
+                fn()
+            e1.record(); torch.cuda.synchronize(device)
+            out["int8_tops_burst"] = ops / (best * 1e-3) / 1e12
+            out["int8_tops_sustained"] = ops * reps / (e0.elapsed_time(e1) * 1e-3) / 1e12
+        out["int8_source"] = "torch._int_mm 8192^3 (cuBLASLt s8 x s8 -> s32) in this run: best of 10 (burst), back to back for %.0f s (sustained)" % seconds
+        del a, b
+    except Exception as ex:                               # no int8 GEMM available: fall back to 2 x the driver's bf16 figure, say so
+        out["int8_error"] = str(ex)[:200]
+    return out
 
 
 class ClockSampler:
@@ -101,81 +133,130 @@ def make_workload(args):
     return generate_alignment(args.n, args.L, seed=args.seed)
 
 
+def workload_name(args):
+    tag = {(3000, 100000): "config 2/3", (20000, 250000): "config 4", (3000, 50000): "config 5", (200, 5000): "config 1"}.get((args.n, args.L), "custom")
+    return "%dx%d synthetic SNP alignment (%s): K1 reweighting + weighted MI scan + sort + ARACNE" % (args.n, args.L, tag)
+
+
 # ------------------------------------------------------------------------------------------------
-# CPU baseline: the oracle port of the reference, all host threads, bounded sample of the workload
+# CPU baseline: the REAL reference (oracle/_ref, compiled in place from /root/reference), all host threads, bounded sample
 # ------------------------------------------------------------------------------------------------
-def cpu_baseline(states, pos, weights, threshold, seconds):
-    import oracle.oracle as orc
+def reference_sample(states, pos, threshold, seconds, linear=False, fixed_cols=None):
+    """Times cache_sample_weights + get_MI_network + Graph::sort + run_ARACNE of the compiled reference (oracle/_ref/libspkref.so)
+    on the first Ls columns (all samples) of the workload; Ls sized for ~`seconds` of work. Falls back to the oracle port if the
+    reference was never built. Returns the cpu_baseline dict."""
     n, L = states.shape
-    cores = orc.hardware_threads()
-    # calibrate on a small column subset, then size the sample for ~`seconds` of work
-    Lc = min(L, 400)
-    t0 = time.time(); orc.mi_scan(states[:, :Lc], weights, pos[:Lc], threshold=threshold, circle_size=Lc); dt = time.time() - t0
-    rate = (Lc * (Lc - 1) / 2) / max(dt, 1e-6)
-    Ls = int(min(L, max(Lc, (2 * seconds * rate) ** 0.5)))
-    t0 = time.time()
-    r = orc.mi_scan(states[:, :Ls], weights, pos[:Ls], threshold=threshold, circle_size=Ls)
-    e = orc.sort_edges(r["edges"]); orc.aracne_closed(e)
-    dt = time.time() - t0
+    try:
+        import oracle.ref as ref
+        have_ref = ref.available()
+    except Exception:
+        have_ref = False
+    if have_ref:
+        cores = os.cpu_count() or 1
+        opts = ["--mi-threshold", repr(threshold), "-t", str(cores)] + (["--linear-genome"] if linear else [])
+        ref.configure(*opts)
+
+        def run(Ls):
+            sub = np.ascontiguousarray(states[:, :Ls])
+            A = ref.Alignment.from_states(sub, "bench", pos[:Ls])          # parse + block compression: outside the timed region
+            t0 = time.time()
+            A.cache_sample_weights()
+            t1 = time.time()
+            net = A.scan(threshold)
+            t2 = time.time()
+            net.sort()
+            t3 = time.time()
+            net.aracne()
+            t4 = time.time()
+            return t4 - t0, (t1 - t0, t2 - t1, t3 - t2, t4 - t3), int(len(net.edges()[0]))
+        kind, label = "reference", "santeripuranen/SpydrPick f6bc110 compiled in place (oracle/_ref/libspkref.so; tbb::parallel_* on std::thread)"
+    else:
+        import oracle.oracle as orc
+        cores = orc.hardware_threads()
+
+        def run(Ls):
+            sub = np.ascontiguousarray(states[:, :Ls])
+            t0 = time.time()
+            w = orc.weights_from_counts(orc.neighbour_counts(sub, int(0.9 * Ls), True))
+            t1 = time.time()
+            r = orc.mi_scan(sub, w, pos[:Ls], threshold=threshold, linear_genome=linear, circle_size=Ls)
+            t2 = time.time()
+            e = orc.sort_edges(r["edges"])
+            t3 = time.time()
+            orc.aracne_closed(e)
+            t4 = time.time()
+            return t4 - t0, (t1 - t0, t2 - t1, t3 - t2, t4 - t3), len(e)
+        kind, label = "port", "oracle/oracle.cpp (CPU restatement; oracle/_ref not built)"
+    if fixed_cols:
+        Ls = int(min(L, fixed_cols))
+    else:
+        Lc = int(min(L, 600))
+        dt, _, _ = run(Lc)
+        rate = (Lc * (Lc - 1) / 2) / max(dt, 1e-6)
+        Ls = int(min(L, max(Lc, (2 * seconds * rate) ** 0.5)))
+    dt, stages, ne = run(Ls)
     pairs = Ls * (Ls - 1) / 2
-    return {"value": pairs / dt / 1e9, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": "first %d of %d columns (all %d samples): %d pairs, scan+sort+ARACNE in %.1f s" % (Ls, L, n, pairs, dt)}
+    # rate on the full workload: the reweighting pass grows with L, scan / sort / ARACNE with the number of pairs -- a column subset
+    # over-represents the former, so the sample is extrapolated stage by stage (the raw sample rate is kept next to it)
+    full_pairs = L * (L - 1) / 2
+    t_full = stages[0] * (L / Ls) + (stages[1] + stages[2] + stages[3]) * (full_pairs / pairs)
+    return {"value": full_pairs / t_full / 1e9, "unit": UNIT, "cores": cores, "kind": kind, "implementation": label,
+            "sample": "first %d of %d columns (all %d samples): %d pairs; weights %.2f s + scan %.2f s + sort %.2f s + ARACNE %.2f s = %.2f s; %d edges; "
+                      "alignment parse / block compression outside the timed region; value = pairs/s of the full %d-column workload extrapolated stage by stage "
+                      "(weights ~ L, the rest ~ pairs: %.0f s)" % (Ls, L, n, pairs, stages[0], stages[1], stages[2], stages[3], dt, ne, L, t_full),
+            "sample_rate": pairs / dt / 1e9, "seconds": dt, "columns": Ls, "full_workload_seconds_extrapolated": t_full}
 
 
 def run_reference(args):
-    """--impl reference: the reference's CPU path (oracle port: the reference binary needs Boost + TBB,
-    absent here), all host threads, bounded sample per step."""
+    """--impl reference: the reference's own CPU implementation of the path on the box's host cores, bounded sample per step."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    import oracle.oracle as orc
     states, pos, _ = make_workload(args)
     n, L = states.shape
-    Ls = min(L, 1500)          # bounded sample: ~1.1M pairs per step
-    sub = np.ascontiguousarray(states[:, :Ls])
     thr = 0.05
+    # one calibration run sizes the sample so that warmup + steps end within a few minutes
+    first = reference_sample(states, pos, thr, 20.0 / max(1, args.warmup + args.steps) + 2.0, linear=args.linear_genome)
+    cols = first["columns"]
     times = []
     for it in range(args.warmup + args.steps):
-        t0 = time.time()
-        counts = orc.neighbour_counts(sub, int(0.9 * Ls), True)
-        w = orc.weights_from_counts(counts)
-        r = orc.mi_scan(sub, w, pos[:Ls], threshold=thr, circle_size=Ls)
-        e = orc.sort_edges(r["edges"]); orc.aracne_closed(e)
+        r = reference_sample(states, pos, thr, 0, linear=args.linear_genome, fixed_cols=cols)
         if it >= args.warmup:
-            times.append(time.time() - t0)
-    pairs = Ls * (Ls - 1) / 2
+            times.append(r["seconds"])
     ms = 1e3 * sum(times) / len(times)
-    v = pairs / (ms / 1e3) / 1e9
-    sample = "first %d of %d columns, all %d samples (%d pairs per step)" % (Ls, L, n, pairs)
+    v = r["value"] * r["seconds"] / (ms / 1e3)            # the extrapolated full-workload rate, on the mean step time
+    cb = dict(r); cb["value"] = v
     print(json.dumps({"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
                       "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                       "dtype": "f64", "data": "synthetic",
-                      "config": {"workload": "3000x100000 synthetic SNP alignment, MI scan + ARACNE (CPU port on a bounded sample)",
-                                 "n": n, "L": L, "sample": sample},
-                      "cpu_baseline": {"value": v, "unit": UNIT, "cores": orc.hardware_threads(), "kind": "port", "sample": sample},
+                      "config": {"workload": workload_name(args) + " -- CPU reference on a bounded sample", "n": n, "L": L, "sample": cb["sample"]},
+                      "cpu_baseline": cb,
                       "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 
 
 # ------------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------------
-class _DevView:
-    """Wraps a raw device pointer so torch can view it (__cuda_array_interface__)."""
-
-    def __init__(self, ptr, nbytes):
-        self.__cuda_array_interface__ = {"shape": (int(nbytes),), "typestr": "|u1", "data": (int(ptr), False), "version": 2}
-
-
-def dev_bytes(torch, ptr, nbytes, device):
-    if nbytes == 0:
-        return torch.empty(0, dtype=torch.uint8, device=device)
-    return torch.as_tensor(_DevView(ptr, nbytes), device=device)
+def ncu_profile_entry(engine, n, L, world):
+    """traffic (dram bytes read + written per launch) and tensor-pipe-active % of the main-pass launch from the committed
+    ncu --set full summary that matches this engine / shape (profiles/*ncu_full_summary*.csv via profiles/index.json), else None."""
+    idx = os.path.join(ROOT, "profiles", "index.json")
+    if not os.path.exists(idx):
+        return None
+    try:
+        for ent in json.load(open(idx)).get("ncu_full", []):
+            if ent.get("engine") == engine and ent.get("n") == n and ent.get("L") == L and ent.get("n_gpus", 1) == world:
+                return ent
+    except Exception:
+        return None
+    return None
 
 
 def run_b200(args):
     import torch
     import torch.distributed as dist
     from spydrpick_b200 import Context
+    from spydrpick_b200.capi import pinned_copy, pinned_empty
     world = int(os.environ.get("WORLD_SIZE", "1")); rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if not torch.cuda.is_available():
@@ -190,8 +271,14 @@ def run_b200(args):
             os.environ["NCCL_DEBUG"] = "WARN"            # keep stdout to the single JSON line
         dist.init_process_group("nccl", device_id=device)
 
-    # ---- workload: rank 0 generates, alignment broadcast ONCE over NCCL (outside the timed region)
     n, L = args.n, args.L
+    i8 = args.engine in (0, 3, 4)
+    eng = args.engine if args.engine else 4
+    tensor_peaks = {}
+    if rank == 0 and not args.no_peaks:
+        tensor_peaks = measure_tensor_peaks(torch, device)
+
+    # ---- workload: rank 0 generates, alignment broadcast ONCE over NCCL (outside the timed region)
     if rank == 0:
         states, pos, gsize = make_workload(args)
     if world > 1:
@@ -204,132 +291,78 @@ def run_b200(args):
     mi_values = args.mi_values or min(10_000_000, 100 * L)
 
     ctx = Context(device=local_rank)
-    # ONE stream for torch's own ops (allocator fills, NCCL hand-offs, CUDA events) and the library's kernels: torch's
-    # default current stream is the legacy stream 0, which spk_set_stream reads as "use your own stream"
+    # ONE stream for torch's events and the library's kernels
     stream = torch.cuda.Stream(device)
     torch.cuda.set_stream(stream)
     ctx.set_stream(stream.cuda_stream)
-    ctx.set_alignment(states, pos)
-    min_ident = int(0.9 * float(L))
-    counts = ctx.neighbour_counts(min_ident, True)
-    weights = 1.0 / counts.astype(np.float64)
-    ctx.set_weights(weights)
-    # pinned save threshold from one K2b estimate (untimed; the reference's estimate is clock-seeded)
-    t0 = time.time()
-    threshold = ctx.determine_mi_threshold(mi_values, iterations=10, seed=args.seed)
-    t_threshold = time.time() - t0
     if world > 1:
-        tt = torch.tensor([threshold], dtype=torch.float64, device=device); dist.broadcast(tt, 0); threshold = float(tt.item())
-    max_edges = int(mi_values * 2.5) + 65536
-    EPS = 2.220446049250313e-16
-
-    def merge_across_ranks(r):
-        """Edge allgather over NCCL/NVLink before ARACNE (+ colmax allreduce-max). Returns (keepalive, ptr, n_edges)."""
-        from spydrpick_b200 import dist as sdist
-        ne = r["n_edges"]
-        if world == 1:
-            return None, r["d_edges"], ne
-        mine = dev_bytes(torch, r["d_edges"], ne * 16, device)
-        merged, total, counts = sdist.allgather_edges(mine, ne)
-        sdist.allreduce_colmax(dev_bytes(torch, r["d_colmax"], L * 8, device).view(torch.float64))
-        # every rank sorted its own edges inside the scan: the gathered list is G sorted runs -> G-1 merges, not a full sort.
-        # torch filled `merged` on ITS current stream (the legacy default stream, which the library's non-blocking stream
-        # does not wait for): the list must be complete before the pointer is handed over
-        torch.cuda.current_stream(device).synchronize()
-        ctx.merge_sorted_runs_device(merged.data_ptr(), counts)
-        return merged, merged.data_ptr(), total
-
-    def sharded_counts():
-        """K1: every rank evaluates its share of the sample-tile pairs; partial counts are summed over NCCL."""
-        if world == 1:
-            return ctx.neighbour_counts(min_ident, True)
-        from spydrpick_b200 import dist as sdist
-        return sdist.allreduce_neighbour_counts(ctx.neighbour_counts(min_ident, True, part_index=rank, n_parts=world), device)
+        # the library's own communicator: rank 0 makes the id, torch.distributed only carries the 128 bytes
+        uid = torch.zeros(128, dtype=torch.uint8, device=device)
+        if rank == 0:
+            uid.copy_(torch.frombuffer(bytearray(Context.comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(uid, 0)
+        ctx.comm_init_rank(bytes(uid.cpu().numpy().tobytes()), rank, world)
+    states_pin = pinned_copy(states)                  # the caller's alignment lives in page-locked host memory
+    pos_pin = pinned_copy(pos)
+    ctx.set_alignment(states_pin, pos_pin)            # collective for world > 1: n/G rows per rank + all-gather over NVLink
+    min_ident = int(0.9 * float(L))
+    weights, counts = ctx.reweight(min_ident, True)
+    # save threshold from one K2b estimate with the reference's sampler (deterministic: every rank computes the same value)
+    threshold = ctx.determine_mi_threshold(mi_values, iterations=10, seed=args.seed)
+    max_edges = int(mi_values * 2.5) // world + 65536
+    scan_kw = dict(max_edges=max_edges, sort_desc=True, n_terms=args.n_terms, engine=args.engine, linear_genome=args.linear_genome,
+                   n_parts=0 if world > 1 else 1)
+    host_flags = None
 
     def step_device():
         """alignment resident in HBM; results stay in HBM."""
-        c = sharded_counts()
-        ctx.set_weights(1.0 / c.astype(np.float64))
-        r = ctx.mi_scan(threshold, max_edges=max_edges, sort_desc=True, n_terms=args.n_terms, engine=args.engine,
-                        part_index=rank, n_parts=world, keep_on_device=True)
-        keep, d_edges, ne = merge_across_ranks(r)
-        flags = torch.zeros(max(ne, 1), dtype=torch.uint8, device=device)
-        ctx.aracne_device(d_edges, ne, flags.data_ptr(), EPS, part_index=rank, n_parts=world)
-        if world > 1:
-            from spydrpick_b200 import dist as sdist
-            flags = sdist.allgather_flag_shards(flags, ne)       # edge-range partition of K3 -> every rank
-        return r, ne, int(flags[:ne].sum().item())
+        ctx.reweight(min_ident, True)
+        r = ctx.mi_scan(threshold, keep_on_device=True, **scan_kw)
+        ne = r["n_edges"]
+        flags = torch.empty(max(ne, 1), dtype=torch.uint8, device=device)
+        ctx.aracne_device(r["d_edges"], ne, flags.data_ptr(), EPS, part_index=0, n_parts=0 if world > 1 else 1)
+        return r, ne, flags
 
-    from spydrpick_b200.capi import pinned_copy, pinned_empty
-    states_pin = pinned_copy(states)                  # the caller's alignment lives in page-locked host memory
-    pos_pin = pinned_copy(pos)
-    states_pin_t = torch.from_numpy(states_pin)       # same page-locked memory, as a tensor for the row-shard upload
-
-    host_edges = host_flags = side = None
+    def step_wall():
+        """SURVEY 8(d) metric (ii): K1 + threshold estimate + scan + sort + ARACNE, results in HBM."""
+        ctx.reweight(min_ident, True)
+        thr = ctx.determine_mi_threshold(mi_values, iterations=10, seed=args.seed, sampler="device")
+        r = ctx.mi_scan(thr, keep_on_device=True, **scan_kw)
+        ne = r["n_edges"]
+        flags = torch.empty(max(ne, 1), dtype=torch.uint8, device=device)
+        ctx.aracne_device(r["d_edges"], ne, flags.data_ptr(), EPS, part_index=0, n_parts=0 if world > 1 else 1)
+        return r, ne, flags
 
     def step_e2e():
         """host buffers through the C-ABI: H2D of the alignment (pinned), D2H of edges + flags inside the step."""
+        nonlocal host_flags
         tw = [time.perf_counter()]
-        if world == 1:
-            ctx.set_alignment(states_pin, pos_pin)
-        else:
-            # every rank uploads n/G rows over its own PCIe link; the slices are all-gathered over NVLink
-            from spydrpick_b200 import dist as sdist
-            ra, rb = sdist.row_shard(n, world, rank)
-            d_states = sdist.allgather_alignment_rows(states_pin_t[ra:rb].reshape(-1), n, L, device)
-            ctx.set_alignment_device(d_states.data_ptr(), n, L, pos_pin)
-            del d_states
-        tw.append(time.perf_counter())
-        c = sharded_counts()
-        ctx.set_weights(1.0 / c.astype(np.float64)); tw.append(time.perf_counter())
-        if world == 1:
-            r = ctx.mi_scan(threshold, max_edges=max_edges, sort_desc=True, n_terms=args.n_terms, engine=args.engine,
-                            keep_on_device=False, copy=False, async_download=True); tw.append(time.perf_counter())
+        ctx.set_alignment(states_pin, pos_pin); tw.append(time.perf_counter())
+        ctx.reweight(min_ident, True); tw.append(time.perf_counter())
+        r = ctx.mi_scan(threshold, keep_on_device=False, copy=False, async_download=True, **scan_kw); tw.append(time.perf_counter())
+        ne = r["n_edges"]
+        if world == 1 or rank == 0:
             edges = r["edges"]                        # view of the library's pinned result buffer (download in flight)
-            nonlocal host_flags
-            if host_flags is None or host_flags.shape[0] < len(edges):
-                host_flags = pinned_empty(int(len(edges) * 1.25) + 4096, np.uint8)
-            flags = ctx.aracne(edges, EPS, out=host_flags)   # same pointer -> device copy reused; overlaps the edge download
-            t_ar = time.perf_counter()
+            if host_flags is None or host_flags.shape[0] < ne:
+                host_flags = pinned_empty(int(ne * 1.25) + 4096, np.uint8)
+            if world == 1:
+                flags = ctx.aracne(edges, EPS, out=host_flags)   # same pointer -> device copy reused; overlaps the edge download
+            else:
+                flags = ctx.aracne_collective(ne, EPS, out=host_flags, edges=edges)
             ctx.wait_download()                       # edges + MI-without-gaps lists are now complete on the host
-            t_wd = time.perf_counter()
             ndirect = int(np.count_nonzero(flags))    # the step's result is read on the host
-            if os.environ.get("SPK_BENCH_E2E_BREAKDOWN"):
-                tma = ctx.timings()
-                sys.stderr.write("e2e aracne phase ms: spk_aracne %.2f (device: CSR build %.2f, K3 %.2f) | wait_download %.2f | count flags %.2f\n" % (
-                    1e3 * (t_ar - tw[-1]), tma["aracne_build_ms"], tma["aracne_ms"], 1e3 * (t_wd - t_ar), 1e3 * (time.perf_counter() - t_wd)))
-            h2d = states.nbytes + pos.nbytes + 8 * n + len(flags)
-            d2h = edges.nbytes + r["edges_wo_gaps"].nbytes + 8 * L + 8 * n + len(flags)
+            d2h = edges.nbytes + r["edges_wo_gaps"].nbytes + 8 * L + 8 * n + ne
         else:
-            # N > 1: the partial edge lists never visit the host -- NCCL allgather over NVLink, device sort + K3, then ONE
-            # D2H of the merged list and the flags into pinned host buffers (what a caller of the multi-GPU path receives)
-            r = ctx.mi_scan(threshold, max_edges=max_edges, sort_desc=True, n_terms=args.n_terms, engine=args.engine,
-                            part_index=rank, n_parts=world, keep_on_device=True); tw.append(time.perf_counter())
-            keep, d_edges, ne = merge_across_ranks(r)   # returns with the merged, sorted list complete in HBM
-            nonlocal host_edges, side
-            if host_edges is None or host_edges.numel() < ne * 16:
-                host_edges = torch.empty(int(ne * 16 * 1.25) + 4096, dtype=torch.uint8).pin_memory()
-                host_flags = torch.empty(int(ne * 1.25) + 4096, dtype=torch.uint8).pin_memory()
-                side = torch.cuda.Stream(device)
-            if rank == 0:                             # the caller's process receives the merged list: download overlaps K3
-                with torch.cuda.stream(side):
-                    host_edges[:ne * 16].copy_(dev_bytes(torch, d_edges, ne * 16, device), non_blocking=True)
-            dflags = torch.zeros(max(ne, 1), dtype=torch.uint8, device=device)
-            ctx.aracne_device(d_edges, ne, dflags.data_ptr(), EPS, part_index=rank, n_parts=world)
-            from spydrpick_b200 import dist as sdist
-            dflags = sdist.allgather_flag_shards(dflags, ne)
-            if rank == 0:
-                host_flags[:ne].copy_(dflags[:ne], non_blocking=True)
-            torch.cuda.synchronize()
-            ndirect = int(host_flags[:ne].numpy().sum()) if rank == 0 else 0
-            h2d = (rb - ra) * L + pos.nbytes + 8 * n  # per rank; whole job = the alignment once + G x (pos, weights)
-            d2h = ne * 16 + ne + 8 * L + 8 * n        # rank 0
+            ctx.aracne_collective(ne, EPS)
+            ndirect = 0; d2h = 8 * L + 8 * n
+        rows = (n + world - 1) // world
+        h2d = min(rows, max(0, n - rank * rows)) * L + pos.nbytes + 8 * n
         tw.append(time.perf_counter())
-        if os.environ.get("SPK_BENCH_E2E_BREAKDOWN"):
+        if os.environ.get("SPK_BENCH_E2E_BREAKDOWN") and rank == 0:
             tmx = ctx.timings()
-            sys.stderr.write("e2e wall ms: set_alignment %.1f (upload %.1f prep %.1f) | counts+weights %.1f | scan %.1f | aracne %.1f\n" % (
+            sys.stderr.write("e2e wall ms: set_alignment %.1f (upload %.1f prep %.1f) | reweight %.1f | scan %.1f | aracne + wait %.1f\n" % (
                 1e3 * (tw[1] - tw[0]), tmx["upload_ms"], tmx["prep_ms"], 1e3 * (tw[2] - tw[1]), 1e3 * (tw[3] - tw[2]), 1e3 * (tw[4] - tw[3])))
-        return h2d, d2h
+        return h2d, d2h, ndirect
 
     def timed(fn, steps, warmup, with_clocks=False):
         for _ in range(warmup):
@@ -342,9 +375,14 @@ def run_b200(args):
         if sampler:
             sampler.__enter__()
         lt0 = ctx.timings()["kernel_launches"]
+        stage_sum = {}
         e0.record(stream)
         for _ in range(steps):
             out = fn()
+            tmk = ctx.timings()
+            for k, v in tmk.items():
+                if k.endswith("_ms"):
+                    stage_sum[k] = stage_sum.get(k, 0.0) + v
         e1.record(stream)
         torch.cuda.synchronize()
         if world > 1:
@@ -355,73 +393,104 @@ def run_b200(args):
         launches = (ctx.timings()["kernel_launches"] - lt0) // max(steps, 1)
         if world > 1:
             t = torch.tensor([ms], dtype=torch.float64, device=device); dist.all_reduce(t, op=dist.ReduceOp.MAX); ms = float(t.item())
-        return ms, out, launches, (sampler.summary() if sampler else None)
+        return ms, out, launches, (sampler.summary() if sampler else None), {k: v / steps for k, v in stage_sum.items()}
 
-    ms, (r, ne, ndirect), launches, clocks = timed(step_device, args.steps, args.warmup, with_clocks=True)
+    ms, (r, ne, dflags), launches, clocks, stages = timed(step_device, args.steps, args.warmup, with_clocks=True)
+    ndirect = int(dflags[:ne].sum().item())
     tm = ctx.timings()
     value = pairs_total / (ms / 1e3) / 1e9
+    wms, (rw, new, _), _, _, wstages = timed(step_wall, max(1, min(args.steps, 3)), 1)
 
-    # roofline of the dominant kernel (K2 tcgen05 GEMM): algorithmic flops = 2*16*n per pair
-    pk = peaks()
+    # ---- roofline of the dominant kernel (K2 main pass): issued tensor ops / measured peak of the pipe it uses
+    pk = driver_peaks()
     tiles = tm["gemm_tiles"]
     pairs_launch = tm["gemm_pairs"]                      # pairs one launch (this rank) covers, incl. padding / masked diagonal halves
-    flops = 2.0 * 16.0 * n * pairs_launch
-    # the int8 engine launches the kernel twice per scan: a small colmax seed pass (seed_ms) and the main pass the
-    # tile / pair counts refer to; the roofline is that of the main-pass launch
-    k_ms = tm["gemm_ms"] - tm.get("seed_ms", 0.0)
-    achieved = flops / (k_ms / 1e3) / 1e12 if k_ms > 0 else 0.0
-    i8 = args.engine in (0, 3, 4)
+    k_ms = stages.get("gemm_ms", 0.0) - stages.get("seed_ms", 0.0)   # main pass = filter interval minus the seed pass
     n_pad = (n + 127) // 128 * 128
-    executed = 2.0 * 128 * 256 * n_pad * tiles * (1 if i8 else (args.n_terms or 2))   # tensor ops actually issued
-    executed_tops = executed / (k_ms / 1e3) / 1e12 if k_ms > 0 else 0.0
-    # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch from the committed ncu --set full capture
-    # (profiles/r01f_ncu_full_summary.csv); only valid for the workload it was captured on
-    traffic = NCU_TRAFFIC.get(args.engine if args.engine else 4) if (i8 and world == 1 and n == 3000 and L == 100000) else None
-    roofline = {"bound": "tensor", "achieved": achieved, "peak": pk["bf16_tflops"], "unit": "TFLOP/s",
-                "frac": achieved / pk["bf16_tflops"], "traffic": traffic,
-                "kernel": "mi_i8_kernel<2> (main pass)" if i8 else "mi_gemm_kernel", "kernel_ms": k_ms, "seed_pass_ms": tm.get("seed_ms", 0.0),
-                "peak_source": pk["source"],
-                "executed_tops": executed_tops,
-                "executed_frac_of_pipe_peak": executed_tops / (pk["bf16_burst_tflops"] * (2.0 if i8 else 1.0)),
-                "executed_frac_of_nominal_pipe": executed_tops / (4500.0 if i8 else 2250.0),
-                "ncu_tensor_pipe_active_pct": NCU_TENSOR_PCT.get(args.engine if args.engine else 4) if traffic else None,   # main pass, profiles/r01f_ncu_full_summary.csv
-                "note": ("achieved = SURVEY 8(d)'s algorithmic 32*n flop/pair vs the measured bf16 peak; the int8 compact engine "
-                         "issues FEWER tensor ops than that (only the one-hot rows a column needs, u8 x u8 -> s32 at 2x the bf16 "
-                         "rate), so frac exceeds 1 -- the honest utilisation figures are executed_frac_of_pipe_peak = issued "
-                         "int8 ops / (2 x measured bf16 burst peak), executed_frac_of_nominal_pipe = issued / 4.5 POP/s, and "
-                         "ncu's sm__pipe_tensor_cycles_active (profiles/r01f_ncu_full_summary.csv)") if i8 else
-                        "algorithmic 32*n flop/pair; executed tensor flops are n_terms x that (bf16 weight split)"}
+    issued = 2.0 * 128 * 256 * n_pad * tiles * (1 if i8 else (args.n_terms or 2))   # tensor ops actually issued by one launch
+    issued_tops = issued / (k_ms / 1e3) / 1e12 if k_ms > 0 else 0.0
+    alg_flops = 2.0 * 16.0 * n * pairs_launch           # 32*n flop per column pair (dense 4x4 cells)
+    if i8:
+        peak = tensor_peaks.get("int8_tops_sustained")
+        peak_src = tensor_peaks.get("int8_source")
+        if not peak:
+            peak = 2.0 * (pk["bf16_tflops_sustained"] or 1400.0)
+            peak_src = "2 x the driver's sustained bf16 figure (no int8 GEMM measurement in this run: %s)" % tensor_peaks.get("int8_error", "--no-peaks")
+        unit = "TOP/s"
+    else:
+        peak = pk["bf16_tflops_sustained"]; peak_src = pk["source"]; unit = "TFLOP/s"
+    prof = ncu_profile_entry(eng, n, L, world)
+    roofline = {"bound": "tensor", "achieved": issued_tops, "peak": peak, "unit": unit, "frac": issued_tops / peak if peak else None,
+                "traffic": prof.get("dram_bytes_per_launch") if prof else None,
+                "kernel": ("mi_i8_kernel<2,%d> (main pass)" % (1 if eng == 4 else 2)) if i8 else "mi_gemm_kernel", "kernel_ms": k_ms,
+                "seed_pass_ms": stages.get("seed_ms", 0.0), "tiles_per_launch": int(tiles), "pairs_per_launch": int(pairs_launch),
+                "peak_source": peak_src,
+                "peaks_measured_in_run": tensor_peaks, "peaks_driver": pk,
+                "frac_of_burst_peak": issued_tops / tensor_peaks["int8_tops_burst"] if i8 and tensor_peaks.get("int8_tops_burst") else None,
+                "algorithmic_equiv_tflops": alg_flops / (k_ms / 1e3) / 1e12 if k_ms > 0 else 0.0,
+                "ncu_tensor_pipe_active_pct": prof.get("tensor_pipe_active_pct") if prof else None,
+                "ncu_source": prof.get("file") if prof else None,
+                "note": "achieved = u8 x u8 tensor ops ISSUED by one main-pass launch (2 * 128 * 256 * n_pad per M128 N256 tile; the one-hot row compaction "
+                        "issues ~3.4 cells per column pair instead of 16) / launch time, against the dense int8 peak measured in this run; "
+                        "algorithmic_equiv_tflops is SURVEY 8(d)'s 32*n flop/pair figure (no fraction: it counts work the compact layout never issues)"}
+    # ---- secondary kernels: achieved rates against the roofline that bounds each
+    hbm = pk["hbm_gbs"]
+    W32 = (L + 31) // 32
+    k1_ms = stages.get("hamming_ms", 0.0)
+    k1_words = n * (n - 1) / 2.0 * W32 / world
+    sm_mhz = (clocks or {}).get("sm_mhz") or 1900.0
+    popc_peak = 16.0 * 148 * sm_mhz * 1e6 / 1e9          # 16 POPC / clk / SM
+    ncand = r["n_candidates"]
+    ref_ms = stages.get("refine_ms", 0.0)
+    kernels = {
+        "K1 hamming_csa_kernel": {"ms": k1_ms, "bound": "issue (POPC/LOP3)", "gpopc_per_s": k1_words / (k1_ms * 1e-3) / 1e9 if k1_ms else None,
+                                  "popc_peak_gpopc_per_s": popc_peak, "frac": (k1_words / (k1_ms * 1e-3) / 1e9) / popc_peak if k1_ms else None,
+                                  "algorithmic_GBps": 3.0 * n * W32 * 4 / (k1_ms * 1e-3) / 1e9 if k1_ms else None},
+        "K2r mi_refine_coop_kernel x9": {"ms": ref_ms, "bound": "L2 bandwidth (planes are L2-resident)", "candidates": int(ncand),
+                                          "algorithmic_GBps": ncand * 2.5e3 / (ref_ms * 1e-3) / 1e9 if ref_ms else None, "hbm_peak_GBps": hbm},
+        "sort (CUB radix x2 + gather)": {"ms": stages.get("sort_ms", 0.0), "bound": "hbm",
+                                         "algorithmic_GBps": (ne / world) * 16 * 6 / (stages["sort_ms"] * 1e-3) / 1e9 if stages.get("sort_ms") else None, "hbm_peak_GBps": hbm},
+        "K3 CSR build (CUB radix x2)": {"ms": stages.get("aracne_build_ms", 0.0), "bound": "hbm",
+                                        "algorithmic_GBps": 2 * ne * (8 + 4) * 2 * 4 / (stages["aracne_build_ms"] * 1e-3) / 1e9 if stages.get("aracne_build_ms") else None, "hbm_peak_GBps": hbm},
+        "K3 aracne_bitmap_kernel": {"ms": stages.get("aracne_ms", 0.0), "bound": "issue / L1 (lists L2-resident; measured DRAM traffic 0.7 GB)"},
+        "exchange (NCCL + run merge)": {"ms": stages.get("exchange_ms", 0.0)},
+        "filter audit": {"ms": stages.get("audit_ms", 0.0), "pairs": r["audit_pairs"], "max_error": r["audit_max_error"]},
+    }
 
     e2e = None
     if not args.no_e2e:
-        ems, (h2d, d2h), _, _ = timed(step_e2e, max(1, min(args.steps, 3)), 2)
+        ems, (h2d, d2h, nd2), _, _, _ = timed(step_e2e, max(1, min(args.steps, 3)), 2)
         e2e = {"value": pairs_total / (ems / 1e3) / 1e9, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                "ms_per_step": ems}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cpu = cpu_baseline(states, pos, weights, threshold, args.cpu_sample_seconds)
+        cpu = reference_sample(states, pos, threshold, args.cpu_sample_seconds, linear=args.linear_genome)
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": "u8 x u8 -> s32 tensor filter + f64 refine" if i8 else "bf16 tensor filter + f64 refine",
                 "data": "synthetic",
-                "config": {"workload": "%dx%d synthetic SNP alignment: K1 reweighting + weighted MI scan + sort + ARACNE" % (n, L),
+                "config": {"workload": workload_name(args),
                            "n": n, "L": L, "pairs": pairs_total, "saved_edges": int(ne), "direct_edges": int(ndirect), "mi_threshold": threshold,
-                           "engine": ("int8 compact one-hot, 16-bit weights as {hi, lo} rows" if args.engine == 3 else "int8 compact one-hot, factorised byte weights a*b") if i8 else "dense bf16 one-hot, n_terms=%d" % (args.n_terms or 2),
+                           "linear_genome": bool(args.linear_genome),
+                           "engine": ("int8 compact one-hot, 16-bit weights as {hi, lo} rows" if eng == 3 else "int8 compact one-hot, factorised byte weights a*b") if i8 else "dense bf16 one-hot, n_terms=%d" % (args.n_terms or 2),
                            "l2_policy": "inputs (>1.5 GB one-hot operands) larger than L2",
-                           "threshold_estimate_s": t_threshold, "parallelism": "tile-space partition x%d + NCCL edge allgather" % world},
+                           "parallelism": "tile-space partition x%d; exchange inside the library (spk_comm_*: NCCL all-gather of edge lists, all-reduce of colmax / K1 counts)" % world},
                 "clocks": clocks, "gpu_launches": int(launches),
-                "stages_ms": {k: tm[k] for k in ("hamming_ms", "stats_ms", "expand_ms", "gemm_ms", "refine_ms", "compact_ms",
-                                                 "sort_ms", "aracne_build_ms", "aracne_ms")},
+                "stages_ms": {k: stages.get(k, 0.0) for k in ("hamming_ms", "stats_ms", "expand_ms", "gemm_ms", "seed_ms", "audit_ms", "refine_ms", "compact_ms",
+                                                              "sort_ms", "exchange_ms", "aracne_build_ms", "aracne_ms")},
+                "mi_aracne_wall_ms": wms,
+                "mi_aracne_wall": {"ms": wms, "definition": "SURVEY 8(d) metric (ii): t(K1) + t(threshold estimate, 10 x %d pairs, device sampler) + t(scan) + t(sort) + t(ARACNE), "
+                                                             "device-timed, results in HBM" % (100000), "threshold_ms": wstages.get("threshold_ms", 0.0),
+                                   "saved_edges": int(new)},
                 "candidates": r["n_candidates"], "max_filter_error": r["max_filter_error"],
-                "roofline": roofline}
+                "audit": {"pairs": r["audit_pairs"], "violations": r["audit_violations"], "max_error": r["audit_max_error"], "band": r["band"]},
+                "roofline": roofline, "kernels": kernels}
         if e2e:
-            e2e["path"] = ("spk_set_alignment (pinned host states) -> K1 -> scan -> sort -> ARACNE, edges + flags downloaded" if world == 1 else
-                           "per rank: H2D of n/G alignment rows + NVLink all-gather -> spk_set_alignment_device -> sharded K1/scan -> "
-                           "per-rank edge sort -> NCCL edge all-gather -> run merge -> sharded ARACNE; rank 0 downloads the merged edges + flags "
-                           "(h2d bytes are per rank, d2h bytes are rank 0's)")
+            e2e["path"] = ("spk_set_alignment (pinned host states%s) -> spk_reweight -> spk_mi_scan -> spk_aracne, edges + MI-without-gaps + flags downloaded%s" %
+                           (", n/G rows per rank + NCCL all-gather" if world > 1 else "", " on rank 0 (h2d bytes are per rank)" if world > 1 else ""))
             line["e2e"] = e2e
         if cpu:
             line["cpu_baseline"] = cpu

@@ -32,7 +32,7 @@ extern "C" {
 #define SPK_E_INVALID    -1   /* bad argument / call order */
 #define SPK_E_CUDA       -2   /* CUDA runtime / driver error, or no usable device */
 #define SPK_E_NOMEM      -3   /* device or host allocation failed */
-#define SPK_E_OVERFLOW   -4   /* candidate / edge buffer too small (raise max_edges) */
+#define SPK_E_OVERFLOW   -4   /* candidate / edge buffers could not be grown to the size the scan needs */
 #define SPK_E_PRECISION  -5   /* fp32 filter error exceeded the safety band (raise n_terms / band) */
 
 typedef struct spk_ctx spk_ctx;
@@ -106,6 +106,11 @@ int spk_neighbour_counts(spk_ctx* ctx, uint64_t min_identical, int quirks,
 int spk_neighbour_counts_part(spk_ctx* ctx, uint64_t min_identical, int quirks,
                               uint32_t part_index, uint32_t n_parts, uint64_t* counts /* [n] host */);
 
+/* K1 + the computed branch of cache_sample_weights in one call (Alignment_utility.hpp:219-251): neighbour counts -> w = 1 / count
+ * -> optional rescale (w * n) / n_eff (:245) -> the context's weights. weights_out / counts_out ([n], host) may be NULL.
+ * On a context that belongs to a communicator this is a collective call (tile pairs sharded, partial counts all-reduced). */
+int spk_reweight(spk_ctx* ctx, uint64_t min_identical, int quirks, int rescale, double* weights_out, uint64_t* counts_out);
+
 /* Replaces the per-sequence set_weight() done by cache_sample_weights
  * (Alignment_utility.hpp:186-258) / MI_Parameters' weight snapshot (include/mi_parameters.hpp:53-59). */
 int spk_set_weights(spk_ctx* ctx, const double* w /* [n] host */);
@@ -120,6 +125,15 @@ int spk_mi_pairs(spk_ctx* ctx, const uint32_t* pi, const uint32_t* pj, uint64_t 
  * seeds std::mt19937 from the clock (:178); here the seed is explicit (seed+iteration). */
 int spk_determine_mi_threshold(spk_ctx* ctx, uint64_t n_values, uint64_t threshold_pairs /*0=auto*/,
                                uint32_t iterations, double pseudocount, uint64_t seed, double* threshold);
+/* The same estimator with a choice of pair sampler. Either way all iterations go through one K2b launch and one segmented sort on
+ * the device; only `iterations` doubles come back. n_values >= L(L-1)/2 is SPK_E_INVALID (the reference indexes out of range).
+ *   SPK_SAMPLER_REFERENCE  the reference's sample_pairs() (std::mt19937(seed + iteration), duplicates rejected; SpydrPick.hpp:171-207),
+ *                          one host thread per iteration -- what spk_determine_mi_threshold uses; reproducible against the oracle
+ *   SPK_SAMPLER_DEVICE     distinct pairs from a keyed Feistel permutation of the pair index space, generated on the device */
+#define SPK_SAMPLER_REFERENCE 0
+#define SPK_SAMPLER_DEVICE    1
+int spk_determine_mi_threshold_ex(spk_ctx* ctx, uint64_t n_values, uint64_t threshold_pairs, uint32_t iterations,
+                                  double pseudocount, uint64_t seed, int sampler, double* threshold);
 
 /* ---- K2: all-pairs scan --------------------------------------------------------------- */
 typedef struct {
@@ -128,7 +142,8 @@ typedef struct {
     uint64_t ld_threshold;     /* --ld-threshold; colmax uses distance > this    (include/mi.hpp:423,447) */
     int32_t  linear_genome;    /* 0 = circular (default), 1 = linear             (include/mi.hpp:313-320) */
     uint64_t circle_size;      /* 0 = L (the reference's choice, apegrunt/Distance.hpp:67-71) */
-    uint64_t max_edges;        /* capacity hint for saved edges; 0 = 2*min(1e7,100*L)+slack */
+    uint64_t max_edges;        /* capacity hint for saved edges; 0 = 2*min(1e7,100*L)+slack. A scan that needs more grows its
+                                  buffers and repeats itself (the reference stores any number of edges) */
     int32_t  sort_desc;        /* 1: edges sorted (weight desc, id asc) = Graph::sort (graph/Graph.hpp:234-242) */
     int32_t  n_terms;          /* engine 2 only: bf16 terms of the weight split, 1..3, 0 = default (2) */
     double   band;             /* filter safety band delta (candidates: mi32 > threshold - band); 0 = default */
@@ -139,8 +154,10 @@ typedef struct {
                                       half the tensor work per column pair, weights on the coarser byte-product grid;
                                   2 = dense 4-state bf16 GEMM with hi/lo weight split;
                                   1 = fp64 exhaustive (diagnostic, no tensor cores) */
-    uint32_t part_index;       /* tile-space partition for multi-GPU: this context scans part_index of n_parts */
-    uint32_t n_parts;          /* 0 or 1 = whole upper triangle */
+    uint32_t part_index;       /* tile-space partition: this context scans part_index of n_parts (caller-driven sharding) */
+    uint32_t n_parts;          /* 1 = whole upper triangle. 0 = automatic: the whole triangle on a single-device context; on a context
+                                  that belongs to a communicator (spk_comm_*) the COLLECTIVE scan: this rank's partition, then the
+                                  exchange (edge lists all-gathered and merged, colmax max-reduced, MI-without-gaps gathered on rank 0) */
     int32_t  keep_on_device;   /* 0: edges copied to pinned host buffers before the call returns;
                                   1: no host copy (device pointers below stay valid);
                                   2: host copy started on a side stream: the host pointers are returned at once and
@@ -158,6 +175,14 @@ typedef struct {
     const void*     d_colmax;
     uint64_t n_candidates;       /* pairs refined in fp64 */
     double   max_filter_error;   /* max |mi_fp32 - mi_fp64| over the candidates */
+    /* Audit of the tensor-core filter (int8 engines): an UNBIASED sample of pairs on both sides of the candidate cut-off
+     * (every pair of a 1/32 sample of the tiles with mi_fp32 > threshold - 4*band) is recomputed in fp64. A pair with
+     * mi_fp64 > threshold whose mi_fp32 was not above threshold - band would have been LOST by the filter: any such pair, or an
+     * audit error above band/2, makes the scan repeat with a wider band (band = 0) or fail with SPK_E_PRECISION (band given). */
+    uint64_t audit_pairs;        /* pairs audited (this rank's share in a collective scan) */
+    uint64_t audit_violations;   /* audited pairs the filter would have lost (0 in any result that is returned) */
+    double   audit_max_error;    /* max |mi_fp32 - mi_fp64| over the audited pairs */
+    double   band;               /* the band the returned result was produced with */
 } spk_scan_result;
 
 /* Replaces spydrpick::get_MI_network up to (not including) the quartile step
@@ -196,6 +221,19 @@ int spk_merge_sorted_runs_device(spk_ctx* ctx, void* d_edges, const uint64_t* ru
 int spk_aracne_device(spk_ctx* ctx, const void* d_edges, uint64_t n_edges, double edge_threshold,
                       uint32_t part_index, uint32_t n_parts, void* d_flags);
 
+/* ---- multi-GPU: one context per device, SPMD -------------------------------------------------------------------------
+ * A context can belong to an NCCL communicator (one rank per context / device). The calls below that say "collective" must then
+ * be made by EVERY rank's context with the same arguments -- from one host thread per context (single process, spk_comm_init_all)
+ * or from one process per GPU (spk_comm_unique_id on rank 0, the 128 bytes passed to the others out of band, spk_comm_init_rank).
+ * Collective calls: spk_set_alignment (rows uploaded per rank + all-gather), spk_reweight / spk_neighbour_counts,
+ * spk_determine_mi_threshold[_ex] (iterations dealt to the ranks), spk_mi_scan with n_parts = 0, spk_aracne / spk_aracne_device
+ * with n_parts = 0. This replaces the TBB split / join of the reference (include/SpydrPick.hpp:141-146, include/mi.hpp:338-361)
+ * across devices. NCCL (libnccl.so.2) is loaded on first use. */
+int spk_comm_init_all(spk_ctx** ctxs, int n);                       /* single process: n contexts on n distinct devices */
+int spk_comm_unique_id(void* id128 /* 128 bytes out */);
+int spk_comm_init_rank(spk_ctx* ctx, const void* id128, int rank, int world);
+int spk_comm_rank(const spk_ctx* ctx, int* rank, int* world);
+
 /* ---- instrumentation -------------------------------------------------------------------- */
 /* Device time (CUDA events on the context's stream) of the stages of the most recent calls, ms. */
 typedef struct {
@@ -210,6 +248,9 @@ typedef struct {
     uint64_t gemm_tiles, kernel_launches;   /* tiles processed by the last scan; kernels launched since create */
     uint64_t gemm_pairs;                    /* column pairs covered by those tiles (incl. padding / masked diagonal halves) */
     float    seed_ms;                       /* int8 engine: the colmax seed launch, included in gemm_ms (main pass = gemm_ms - seed_ms) */
+    float    exchange_ms;                   /* collective scan: counts + edge all-gather + colmax all-reduce + run merge */
+    float    audit_ms;                      /* filter audit kernel */
+    float    threshold_ms;                  /* threshold estimator: sampling + K2b + segmented sort (device part) */
 } spk_timings;
 int spk_get_timings(spk_ctx* ctx, spk_timings* out);
 

@@ -18,7 +18,8 @@ SPK_OK, SPK_E_INVALID, SPK_E_CUDA, SPK_E_NOMEM, SPK_E_OVERFLOW, SPK_E_PRECISION 
 
 EXPORTS = ["spk_create", "spk_destroy", "spk_last_error", "spk_set_stream", "spk_host_alloc", "spk_host_free",
            "spk_set_alignment", "spk_set_alignment_device", "spk_column_state_counts", "spk_set_alignment_filtered",
-           "spk_neighbour_counts", "spk_neighbour_counts_part", "spk_set_weights", "spk_mi_pairs", "spk_determine_mi_threshold",
+           "spk_neighbour_counts", "spk_neighbour_counts_part", "spk_reweight", "spk_set_weights", "spk_mi_pairs", "spk_determine_mi_threshold",
+           "spk_determine_mi_threshold_ex", "spk_comm_init_all", "spk_comm_unique_id", "spk_comm_init_rank", "spk_comm_rank",
            "spk_mi_scan", "spk_outlier_thresholds", "spk_sort_edges", "spk_aracne", "spk_sort_edges_device",
            "spk_aracne_device", "spk_merge_sorted_runs_device", "spk_wait_download", "spk_get_timings", "spk_debug_tile_counts", "spk_debug_i8_mode", "spk_debug_i8_layout", "spk_debug_i8_tile",
            "spk_version"]
@@ -34,13 +35,15 @@ class ScanParams(C.Structure):
 class ScanResult(C.Structure):
     _fields_ = [("edges", C.c_void_p), ("n_edges", C.c_uint64), ("edges_wo_gaps", C.c_void_p), ("n_wo_gaps", C.c_uint64),
                 ("colmax", C.POINTER(C.c_double)), ("d_edges", C.c_void_p), ("d_edges_wo_gaps", C.c_void_p),
-                ("d_colmax", C.c_void_p), ("n_candidates", C.c_uint64), ("max_filter_error", C.c_double)]
+                ("d_colmax", C.c_void_p), ("n_candidates", C.c_uint64), ("max_filter_error", C.c_double),
+                ("audit_pairs", C.c_uint64), ("audit_violations", C.c_uint64), ("audit_max_error", C.c_double), ("band", C.c_double)]
 
 
 class Timings(C.Structure):
     _fields_ = [(k, C.c_float) for k in ("upload_ms", "prep_ms", "hamming_ms", "expand_ms", "stats_ms", "gemm_ms",
                                         "refine_ms", "compact_ms", "sort_ms", "aracne_build_ms", "aracne_ms", "pairs_ms")] + \
-               [("gemm_tiles", C.c_uint64), ("kernel_launches", C.c_uint64), ("gemm_pairs", C.c_uint64), ("seed_ms", C.c_float)]
+               [("gemm_tiles", C.c_uint64), ("kernel_launches", C.c_uint64), ("gemm_pairs", C.c_uint64), ("seed_ms", C.c_float),
+                ("exchange_ms", C.c_float), ("audit_ms", C.c_float), ("threshold_ms", C.c_float)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -79,6 +82,13 @@ def load():
     L.spk_mi_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_double, C.c_void_p]
     L.spk_determine_mi_threshold.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_double, C.c_uint64,
                                              C.POINTER(C.c_double)]
+    L.spk_determine_mi_threshold_ex.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_double, C.c_uint64, C.c_int,
+                                                C.POINTER(C.c_double)]
+    L.spk_reweight.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+    L.spk_comm_unique_id.argtypes = [C.c_void_p]
+    L.spk_comm_init_rank.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+    L.spk_comm_init_all.argtypes = [C.POINTER(C.c_void_p), C.c_int]
+    L.spk_comm_rank.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     L.spk_mi_scan.argtypes = [C.c_void_p, C.POINTER(ScanParams), C.POINTER(ScanResult)]
     L.spk_outlier_thresholds.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     L.spk_sort_edges.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
@@ -148,6 +158,7 @@ class Context:
             raise SpkError(rc, (self.lib.spk_last_error(None) or b"").decode())
         self.h = h
         self.n = self.L = 0
+        self.rank, self.world = 0, 1
 
     def close(self):
         if getattr(self, "h", None):
@@ -215,6 +226,27 @@ class Context:
         self._check(self.lib.spk_neighbour_counts_part(self.h, int(min_identical), q, part_index, n_parts, _ptr(out)))
         return out
 
+    def reweight(self, min_identical, quirks=True, rescale=False):
+        """K1 + weights in one call (collective on a context with a communicator). Returns (weights, counts)."""
+        q = QUIRKS_REFERENCE if quirks is True else (0 if quirks is False else int(quirks))
+        w = np.zeros(self.n, dtype=np.float64); cnt = np.zeros(self.n, dtype=np.uint64)
+        self._check(self.lib.spk_reweight(self.h, int(min_identical), q, int(rescale), _ptr(w), _ptr(cnt)))
+        return w, cnt
+
+    # ---- multi-GPU: one context per device / process (SPMD)
+    @staticmethod
+    def comm_unique_id():
+        lib = load(); buf = (C.c_char * 128)()
+        rc = lib.spk_comm_unique_id(buf)
+        if rc != SPK_OK:
+            raise SpkError(rc, (lib.spk_last_error(None) or b"").decode())
+        return bytes(buf)
+
+    def comm_init_rank(self, unique_id: bytes, rank: int, world: int):
+        assert len(unique_id) == 128
+        self._check(self.lib.spk_comm_init_rank(self.h, C.c_char_p(unique_id), int(rank), int(world)))
+        self.rank, self.world = int(rank), int(world)
+
     def set_weights(self, w):
         w = np.ascontiguousarray(w, dtype=np.float64)
         assert w.shape == (self.n,)
@@ -226,10 +258,12 @@ class Context:
         self._check(self.lib.spk_mi_pairs(self.h, _ptr(pi), _ptr(pj), pi.shape[0], pseudocount, _ptr(out)))
         return out
 
-    def determine_mi_threshold(self, n_values, threshold_pairs=0, iterations=10, pseudocount=0.5, seed=1):
+    def determine_mi_threshold(self, n_values, threshold_pairs=0, iterations=10, pseudocount=0.5, seed=1, sampler="reference"):
+        """sampler: "reference" = the reference's mt19937 sample_pairs() (seeded, reproducible), "device" = Feistel
+        permutation of the pair index space generated on the device."""
         thr = C.c_double()
-        self._check(self.lib.spk_determine_mi_threshold(self.h, int(n_values), int(threshold_pairs), int(iterations),
-                                                        pseudocount, int(seed), C.byref(thr)))
+        self._check(self.lib.spk_determine_mi_threshold_ex(self.h, int(n_values), int(threshold_pairs), int(iterations),
+                                                           pseudocount, int(seed), 1 if sampler == "device" else 0, C.byref(thr)))
         return float(thr.value)
 
     def mi_scan(self, threshold, pseudocount=0.5, ld_threshold=0, linear_genome=False, circle_size=0, max_edges=0,
@@ -256,10 +290,11 @@ class Context:
             return v.copy() if copy else v
 
         out = {"n_edges": int(r.n_edges), "n_wo_gaps": int(r.n_wo_gaps), "n_candidates": int(r.n_candidates),
-               "max_filter_error": float(r.max_filter_error),
+               "max_filter_error": float(r.max_filter_error), "audit_pairs": int(r.audit_pairs),
+               "audit_violations": int(r.audit_violations), "audit_max_error": float(r.audit_max_error), "band": float(r.band),
                "colmax": np.ctypeslib.as_array(r.colmax, shape=(self.L,)).copy(),
                "d_edges": r.d_edges, "d_edges_wo_gaps": r.d_edges_wo_gaps, "d_colmax": r.d_colmax}
-        if keep_on_device != 1:
+        if keep_on_device != 1 and r.edges:
             out["edges"] = grab(r.edges, r.n_edges)
             out["edges_wo_gaps"] = grab(r.edges_wo_gaps, r.n_wo_gaps)
         return out
@@ -274,6 +309,17 @@ class Context:
         e = np.ascontiguousarray(edges, dtype=EDGE_DTYPE).copy()
         self._check(self.lib.spk_sort_edges(self.h, _ptr(e), e.shape[0]))
         return e
+
+    def aracne_collective(self, n_edges, edge_threshold=2.220446049250313e-16, out=None, edges=None):
+        """Collective ARACNE on the list of the last collective scan (n_parts = 0). Rank 0 passes its host view of the edges and
+        receives the flags; the other ranks pass nothing."""
+        f = None
+        if out is not None:
+            f = out[:n_edges]
+        elif edges is not None:
+            f = np.zeros(n_edges, dtype=np.uint8)
+        self._check(self.lib.spk_aracne(self.h, _ptr(edges) if edges is not None else None, int(n_edges), edge_threshold, 0, 0, _ptr(f) if f is not None else None))
+        return f
 
     def aracne(self, edges, edge_threshold=2.220446049250313e-16, part_index=0, n_parts=1, out=None):
         """out: optional uint8 array (>= len(edges), e.g. from pinned_empty) that receives the flags."""

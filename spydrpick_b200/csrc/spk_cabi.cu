@@ -5,7 +5,9 @@
 #include <cstdarg>
 #include <cstring>
 #include <random>
+#include <thread>
 #include <unordered_set>
+#include <cub/cub.cuh>
 #include "spk_internal.h"
 
 namespace spk {
@@ -45,7 +47,26 @@ static void free_alignment(Ctx* c) {
 }
 static void free_scan(Ctx* c) {
     free_dev(c->d_cand); free_dev(c->d_cand2); c->cand2_cap = 0; free_dev(c->d_edges); free_dev(c->d_wo); free_dev(c->d_refined); free_dev(c->d_refined_wo);
-    c->cand_cap = c->edges_cap = c->wo_cap = c->refined_cap = 0;
+    free_dev(c->d_merge); free_dev(c->d_wo_all); free_dev(c->d_audit); free_dev(c->d_xcnt);
+    c->cand_cap = c->edges_cap = c->wo_cap = c->refined_cap = c->merge_cap = c->wo_all_cap = c->audit_cap = 0;
+    c->d_edges_view = nullptr;
+}
+
+// turns the outstanding (start, stop) event pairs into spk_timings fields; the stream must be idle
+void resolve_timings(Ctx* c) {
+    struct { uint32_t bit; int a, b; float* out; } tab[] = {
+        {TMP_UPLOAD, EV_UP0, EV_UP1, &c->tm.upload_ms}, {TMP_PREP, EV_UP1, EV_PREP1, &c->tm.prep_ms}, {TMP_K1, EV_K1_0, EV_K1_1, &c->tm.hamming_ms},
+        {TMP_EXPAND, EV_EXP0, EV_EXP1, &c->tm.expand_ms}, {TMP_STATS, EV_EXP1, EV_STAT1, &c->tm.stats_ms}, {TMP_GEMM, EV_GEMM0, EV_GEMM1, &c->tm.gemm_ms},
+        {TMP_SEED, EV_GEMM0, EV_SEED1, &c->tm.seed_ms}, {TMP_REFINE, EV_REF0, EV_REF1, &c->tm.refine_ms}, {TMP_COMPACT, EV_REF1, EV_CMP1, &c->tm.compact_ms},
+        {TMP_SORT, EV_SORT0, EV_SORT1, &c->tm.sort_ms}, {TMP_XCH, EV_XCH0, EV_XCH1, &c->tm.exchange_ms}, {TMP_ARB, EV_AR0, EV_AR1, &c->tm.aracne_build_ms},
+        {TMP_AR, EV_AR1, EV_AR2, &c->tm.aracne_ms}, {TMP_PAIRS, EV_PAIRS0, EV_PAIRS1, &c->tm.pairs_ms}, {TMP_AUDIT, EV_AUD0, EV_AUD1, &c->tm.audit_ms},
+        {TMP_THR, EV_THR0, EV_THR1, &c->tm.threshold_ms}};
+    for (auto& t : tab) {
+        if (!(c->tm_pending & t.bit)) continue;
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, c->ev[t.a], c->ev[t.b]) == cudaSuccess) *t.out = ms; else cudaGetLastError();
+    }
+    c->tm_pending = 0;
 }
 
 template <class P> static int dev_alloc(Ctx* c, P*& p, size_t bytes, const char* what) {
@@ -62,15 +83,19 @@ __global__ void fill_u64_kernel(unsigned long long* p, unsigned long long v, siz
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) p[i] = v;
 }
+// w[s] = 1 / count[s] (multiplicity is always 1: Alignment_StateVector_weights.hpp:349); pad samples 0
+__global__ void weights_from_counts_kernel(const unsigned long long* __restrict__ counts, double* __restrict__ w, uint32_t n, uint32_t n_pad) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n_pad) w[i] = i < n ? 1.0 / (double)counts[i] : 0.0;
+}
 
 } // namespace spk
 
 using namespace spk;
-struct spk_ctx : public spk::Ctx {};
 
 extern "C" {
 
-const char* spk_version(void) { return "spydrpick_b200 0.1 (sm_100a)"; }
+const char* spk_version(void) { return "spydrpick_b200 0.2 (sm_100a)"; }
 
 int spk_create(spk_ctx** out, int device, int verbose) {
     if (!out) return SPK_E_INVALID;
@@ -92,10 +117,11 @@ int spk_create(spk_ctx** out, int device, int verbose) {
     }
     c->stream = c->own_stream;
     for (auto& e : c->ev) cudaEventCreate(&e);
+    c->d_edges_view = nullptr;
     cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
     cudaEventCreateWithFlags(&c->ev_ready, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&c->ev_dl, cudaEventDisableTiming);
-    if (cudaMalloc(&c->d_counters, 8 * sizeof(unsigned long long)) != cudaSuccess || cudaMalloc(&c->d_tilemap, 1 << 20) != cudaSuccess) {
+    if (cudaMalloc(&c->d_counters, 16 * sizeof(unsigned long long)) != cudaSuccess || cudaMalloc(&c->d_tilemap, 1 << 20) != cudaSuccess) {
         delete c; return fail(nullptr, SPK_E_NOMEM, "context allocation failed");
     }
     *out = c;
@@ -106,6 +132,7 @@ void spk_destroy(spk_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
+    comm_free(c);
     free_alignment(c); free_scan(c);
     free_dev(c->d_scratch); free_dev(c->d_counters);
     if (c->hp_edges) cudaFreeHost(c->hp_edges);
@@ -135,6 +162,9 @@ static int set_alignment_impl(spk_ctx* c, const uint8_t* states, uint32_t n, uin
     if (L >= (1u << 29)) return fail(c, SPK_E_INVALID, "L too large");
     SPK_CUDA(c, cudaSetDevice(c->device));
     const bool same_shape = (c->n == n && c->L == L && c->d_states);
+    // multi-GPU, host source: every rank uploads its block of rows over its own PCIe link, the blocks are all-gathered over
+    // NVLink ("alignment broadcast once") -- the row buffer is padded to world * rows_per_rank rows for that
+    const uint32_t per = (c->world > 1) ? (n + (uint32_t)c->world - 1) / (uint32_t)c->world : n;
     if (!same_shape) {
         free_alignment(c);
         c->n = n; c->L = L;
@@ -142,7 +172,7 @@ static int set_alignment_impl(spk_ctx* c, const uint8_t* states, uint32_t n, uin
         c->L_pad = (L + TILE_J - 1) / TILE_J * TILE_J;
         c->W32 = (L + 31) / 32;
         int r;
-        if ((r = dev_alloc(c, c->d_states, (size_t)n * L, "states"))) return r;
+        if ((r = dev_alloc(c, c->d_states, (size_t)per * (size_t)(c->world > 1 ? c->world : 1) * L, "states"))) return r;
         if ((r = dev_alloc(c, c->d_colmajor, (size_t)c->L_pad * c->n_pad, "colmajor"))) return r;
         if ((r = dev_alloc(c, c->d_planes, (size_t)3 * n * c->W32 * 4, "planes"))) return r;
         if ((r = dev_alloc(c, c->d_pos, (size_t)c->L_pad * 8, "pos"))) return r;
@@ -154,9 +184,15 @@ static int set_alignment_impl(spk_ctx* c, const uint8_t* states, uint32_t n, uin
         if ((r = dev_alloc(c, c->d_colmax32, (size_t)c->L_pad * 4, "colmax32"))) return r;
         if ((r = dev_alloc(c, c->d_counts, (size_t)n * 8, "counts"))) return r;
     }
-    c->operands_terms = 0; c->stats_valid = false; c->host_edges_n = 0; c->g_state = 0; c->d_edges_sorted_n = 0;
-    SPK_CUDA(c, cudaEventRecord(c->ev[0], c->stream));
-    SPK_CUDA(c, cudaMemcpyAsync(c->d_states, states, (size_t)n * L, kind, c->stream));
+    c->operands_terms = 0; c->stats_valid = false; c->host_edges_n = 0; c->g_state = 0; c->d_edges_sorted_n = 0; c->i8_seed_valid = false;
+    SPK_CUDA(c, cudaEventRecord(c->ev[EV_UP0], c->stream));
+    if (c->world > 1 && kind == cudaMemcpyHostToDevice) {
+        const uint32_t r0 = std::min(n, per * (uint32_t)c->rank), r1 = std::min(n, r0 + per);
+        if (r1 > r0) SPK_CUDA(c, cudaMemcpyAsync(c->d_states + (size_t)r0 * L, states + (size_t)r0 * L, (size_t)(r1 - r0) * L, kind, c->stream));
+        int rx = comm_allgather_inplace(c, c->d_states, (size_t)per * L); if (rx) return rx;
+    } else {
+        SPK_CUDA(c, cudaMemcpyAsync(c->d_states, states, (size_t)n * L, kind, c->stream));
+    }
     std::vector<uint64_t> hp(c->L_pad, 0);
     for (uint32_t k = 0; k < L; ++k) hp[k] = pos ? pos[k] : k;
     SPK_CUDA(c, cudaMemcpyAsync(c->d_pos, hp.data(), (size_t)c->L_pad * 8, cudaMemcpyHostToDevice, c->stream));
@@ -165,13 +201,12 @@ static int set_alignment_impl(spk_ctx* c, const uint8_t* states, uint32_t n, uin
     SPK_CUDA(c, cudaMemcpyAsync(c->d_w, ones.data(), (size_t)c->n_pad * 8, cudaMemcpyHostToDevice, c->stream));
     c->w_total = (double)n;
     c->h_w.assign(n, 1.0);
-    SPK_CUDA(c, cudaEventRecord(c->ev[1], c->stream));
+    SPK_CUDA(c, cudaEventRecord(c->ev[EV_UP1], c->stream));
     int r = prep_alignment(c); if (r) return r;
-    SPK_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
-    SPK_CUDA(c, cudaEventSynchronize(c->ev[2]));
-    r = i8_build_layout(c); if (r) return r;
-    SPK_CUDA(c, cudaEventElapsedTime(&c->tm.upload_ms, c->ev[0], c->ev[1]));
-    SPK_CUDA(c, cudaEventElapsedTime(&c->tm.prep_ms, c->ev[1], c->ev[2]));
+    SPK_CUDA(c, cudaEventRecord(c->ev[EV_PREP1], c->stream));
+    c->tm_pending |= TMP_UPLOAD | TMP_PREP;
+    r = i8_build_layout(c); if (r) return r;             // reads the presence masks back: the stream is idle afterwards
+    resolve_timings(c);
     return SPK_OK;
 }
 
@@ -251,37 +286,75 @@ int spk_set_alignment_filtered(spk_ctx* c, const uint8_t* states, uint32_t n, ui
     return r;
 }
 
-int spk_neighbour_counts_part(spk_ctx* c, uint64_t min_identical, int quirk, uint32_t part, uint32_t nparts, uint64_t* counts) {
+int spk_neighbour_counts_part(spk_ctx* c, uint64_t min_identical, int quirks, uint32_t part, uint32_t nparts, uint64_t* counts) {
     if (!c || !counts) return SPK_E_INVALID;
     if (!c->d_states) return fail(c, SPK_E_INVALID, "neighbour_counts: no alignment set");
     if (nparts == 0) nparts = 1;
     if (part >= nparts) return fail(c, SPK_E_INVALID, "neighbour_counts: part_index >= n_parts");
     SPK_CUDA(c, cudaSetDevice(c->device));
-    int r = hamming_neighbour_counts(c, min_identical, quirk, part, nparts); if (r) return r;
+    int r = hamming_neighbour_counts(c, min_identical, quirks, part, nparts); if (r) return r;
     SPK_CUDA(c, cudaMemcpyAsync(counts, c->d_counts, (size_t)c->n * 8, cudaMemcpyDeviceToHost, c->stream));
     SPK_CUDA(c, cudaStreamSynchronize(c->stream));
-    SPK_CUDA(c, cudaEventElapsedTime(&c->tm.hamming_ms, c->ev[0], c->ev[1]));
+    resolve_timings(c);
     return SPK_OK;
 }
 
-int spk_neighbour_counts(spk_ctx* c, uint64_t min_identical, int quirk, uint64_t* counts) {
-    return spk_neighbour_counts_part(c, min_identical, quirk, 0, 1, counts);
+int spk_neighbour_counts(spk_ctx* c, uint64_t min_identical, int quirks, uint64_t* counts) {
+    if (c && c->world > 1) {
+        // collective: this rank's share of the sample-tile pairs, partial counts summed over NVLink
+        if (!counts) return SPK_E_INVALID;
+        if (!c->d_states) return fail(c, SPK_E_INVALID, "neighbour_counts: no alignment set");
+        SPK_CUDA(c, cudaSetDevice(c->device));
+        int r = hamming_neighbour_counts(c, min_identical, quirks, (uint32_t)c->rank, (uint32_t)c->world); if (r) return r;
+        r = comm_allreduce_sum_u64(c, (unsigned long long*)c->d_counts, c->n); if (r) return r;
+        SPK_CUDA(c, cudaMemcpyAsync(counts, c->d_counts, (size_t)c->n * 8, cudaMemcpyDeviceToHost, c->stream));
+        SPK_CUDA(c, cudaStreamSynchronize(c->stream));
+        resolve_timings(c);
+        return SPK_OK;
+    }
+    return spk_neighbour_counts_part(c, min_identical, quirks, 0, 1, counts);
+}
+
+static int set_weights_host(spk_ctx* c, const double* w) {
+    std::vector<double> hw(c->n_pad, 0.0);
+    double tot = 0.0;
+    for (uint32_t s = 0; s < c->n; ++s) { hw[s] = w[s]; tot += w[s]; }
+    SPK_CUDA(c, cudaMemcpyAsync(c->d_w, hw.data(), (size_t)c->n_pad * 8, cudaMemcpyHostToDevice, c->stream));   // pageable source: staged before the call returns
+    c->w_total = tot;
+    c->h_w.assign(w, w + c->n);
+    c->i8_weights_valid = false; c->g_state = 0; c->i8_seed_valid = false;
+    c->operands_terms = 0; c->stats_valid = false;
+    return SPK_OK;
 }
 
 int spk_set_weights(spk_ctx* c, const double* w) {
     if (!c || !w) return SPK_E_INVALID;
     if (!c->d_states) return fail(c, SPK_E_INVALID, "set_weights: no alignment set");
     SPK_CUDA(c, cudaSetDevice(c->device));
-    std::vector<double> hw(c->n_pad, 0.0);
-    double tot = 0.0;
-    for (uint32_t s = 0; s < c->n; ++s) { hw[s] = w[s]; tot += w[s]; }
-    SPK_CUDA(c, cudaMemcpyAsync(c->d_w, hw.data(), (size_t)c->n_pad * 8, cudaMemcpyHostToDevice, c->stream));
+    return set_weights_host(c, w);
+}
+
+// K1 + cache_sample_weights' computed branch in one call: counts -> w = 1/count -> optional rescale -> context weights.
+int spk_reweight(spk_ctx* c, uint64_t min_identical, int quirks, int rescale, double* weights_out, uint64_t* counts_out) {
+    if (!c) return SPK_E_INVALID;
+    if (!c->d_states) return fail(c, SPK_E_INVALID, "reweight: no alignment set");
+    SPK_CUDA(c, cudaSetDevice(c->device));
+    const uint32_t part = c->world > 1 ? (uint32_t)c->rank : 0u, nparts = c->world > 1 ? (uint32_t)c->world : 1u;
+    int r = hamming_neighbour_counts(c, min_identical, quirks, part, nparts); if (r) return r;
+    r = comm_allreduce_sum_u64(c, (unsigned long long*)c->d_counts, c->n); if (r) return r;
+    std::vector<uint64_t> hc(c->n);
+    SPK_CUDA(c, cudaMemcpyAsync(hc.data(), c->d_counts, (size_t)c->n * 8, cudaMemcpyDeviceToHost, c->stream));
     SPK_CUDA(c, cudaStreamSynchronize(c->stream));
-    c->w_total = tot;
-    c->h_w.assign(w, w + c->n);
-    c->i8_weights_valid = false; c->g_state = 0;
-    c->operands_terms = 0; c->stats_valid = false;
-    return SPK_OK;
+    resolve_timings(c);
+    std::vector<double> w(c->n);
+    for (uint32_t s = 0; s < c->n; ++s) w[s] = 1.0 / double(hc[s]);                      // weights.hpp:349
+    if (rescale) {                                                                     // (w * n) / n_eff, Alignment_utility.hpp:233,245
+        double n_eff = 0.0; for (double x : w) n_eff += x;
+        for (double& x : w) x = x * double(c->n) / n_eff;
+    }
+    if (counts_out) std::memcpy(counts_out, hc.data(), (size_t)c->n * 8);
+    if (weights_out) std::memcpy(weights_out, w.data(), (size_t)c->n * 8);
+    return set_weights_host(c, w.data());
 }
 
 int spk_mi_pairs(spk_ctx* c, const uint32_t* pi, const uint32_t* pj, uint64_t npairs, double pc, double* mi) {
@@ -299,17 +372,69 @@ int spk_mi_pairs(spk_ctx* c, const uint32_t* pi, const uint32_t* pj, uint64_t np
     int r = mi_pairs_exact(c, d_pi, d_pj, npairs, pc, d_mi); if (r) return r;
     SPK_CUDA(c, cudaMemcpyAsync(mi, d_mi, ob, cudaMemcpyDeviceToHost, c->stream));
     SPK_CUDA(c, cudaStreamSynchronize(c->stream));
+    resolve_timings(c);
     return SPK_OK;
 }
 
-// host logic of determine_MI_threshold (include/SpydrPick.hpp:258-343)
-int spk_determine_mi_threshold(spk_ctx* c, uint64_t n_values, uint64_t threshold_pairs, uint32_t iterations,
-                               double pc, uint64_t seed, double* threshold) {
+} // extern "C"
+
+namespace spk {
+// ---- threshold estimator, device side -----------------------------------------------------------------------------
+// SPK_SAMPLER_DEVICE: `count` DISTINCT pairs per iteration without any rejection loop -- slot k of iteration `it` is pair
+// number perm(k) of the L(L-1)/2 upper-triangle pairs, perm = a keyed 4-round Feistel permutation of [0, 4^h) walked until
+// it lands inside [0, P) (cycle walking keeps it a bijection on [0, P)). Same distribution as the reference's sample_pairs()
+// (a uniformly random set of distinct pairs, include/SpydrPick.hpp:171-207), different random numbers -- the reference's are
+// clock-seeded anyway.
+__device__ __forceinline__ uint32_t feistel_round(uint32_t x, uint64_t key, uint32_t round) {
+    uint64_t z = (uint64_t)x * 0x9E3779B97F4A7C15ull + key + (uint64_t)round * 0xBF58476D1CE4E5B9ull;
+    z ^= z >> 31; z *= 0x94D049BB133111EBull; z ^= z >> 29; z *= 0xD6E8FEB86659FD93ull; z ^= z >> 32;
+    return (uint32_t)z;
+}
+__global__ void sample_pairs_kernel(uint32_t* __restrict__ pi, uint32_t* __restrict__ pj, uint64_t count, uint32_t iterations,
+                                    uint32_t it0, uint32_t it_stride, uint64_t L, uint64_t P, uint32_t half_bits, uint64_t seed) {
+    const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= count * iterations) return;
+    const uint32_t slot_it = (uint32_t)(t / count);
+    const uint64_t k = t % count;
+    const uint64_t key = seed + 0x632BE59BD9B4E019ull * (uint64_t)(it0 + slot_it * it_stride + 1);
+    const uint32_t hmask = (half_bits >= 32) ? 0xffffffffu : ((1u << half_bits) - 1u);
+    uint64_t x = k;
+    do {
+        uint32_t l = (uint32_t)(x >> half_bits) & hmask, r = (uint32_t)x & hmask;
+#pragma unroll
+        for (uint32_t rd = 0; rd < 4; ++rd) { const uint32_t f = feistel_round(r, key, rd) & hmask; const uint32_t nl = r; r = l ^ f; l = nl; }
+        x = ((uint64_t)l << half_bits) | r;
+    } while (x >= P);
+    // pair number x -> (i, j), i < j: row i holds L-1-i pairs
+    const double b = 2.0 * (double)L - 1.0;
+    uint64_t i = (uint64_t)((b - sqrt(fmax(b * b - 8.0 * (double)x, 0.0))) * 0.5);
+    if (i > L - 2) i = L - 2;
+    auto row_start = [&](uint64_t q) { return q * (2 * L - q - 1) / 2; };
+    while (i > 0 && row_start(i) > x) --i;
+    while (row_start(i + 1) <= x) ++i;
+    pi[t] = (uint32_t)i; pj[t] = (uint32_t)(i + 1 + (x - row_start(i)));
+}
+__global__ void pick_kth_kernel(const double* __restrict__ sorted, uint64_t count, uint64_t idx, uint32_t iterations, double* __restrict__ out) {
+    const uint32_t it = blockIdx.x * blockDim.x + threadIdx.x;
+    if (it < iterations) out[it] = sorted[(uint64_t)it * count + idx];
+}
+}  // namespace spk
+
+extern "C" {
+
+// determine_MI_threshold (include/SpydrPick.hpp:258-343): per iteration, the MI of `threshold_pairs` distinct random pairs and
+// the element at index pct * threshold_pairs of their ascending order; the result is the lower median over the iterations.
+// All iterations go through ONE K2b launch and one segmented sort on the device; only `iterations` doubles come back.
+int spk_determine_mi_threshold_ex(spk_ctx* c, uint64_t n_values, uint64_t threshold_pairs, uint32_t iterations,
+                                  double pc, uint64_t seed, int sampler, double* threshold) {
     if (!c || !threshold || iterations == 0) return SPK_E_INVALID;
     if (!c->d_states) return fail(c, SPK_E_INVALID, "determine_mi_threshold: no alignment set");
+    if (sampler != SPK_SAMPLER_REFERENCE && sampler != SPK_SAMPLER_DEVICE) return fail(c, SPK_E_INVALID, "determine_mi_threshold: unknown sampler");
     const uint64_t L = c->L;
     const uint64_t possible = L * (L - 1) / 2;
     const double pct = 1.0 - double(n_values) / double(possible);
+    if (!(pct > 0.0)) return fail(c, SPK_E_INVALID, "determine_mi_threshold: n_values (%llu) is not smaller than the number of pairs (%llu): every pair would be saved "
+                                  "(the reference's estimator indexes out of range here); use threshold 0", (unsigned long long)n_values, (unsigned long long)possible);
     uint64_t tp = threshold_pairs;
     if (tp == 0) {                                           // SpydrPick.hpp:263-273
         tp = 100000;
@@ -317,28 +442,83 @@ int spk_determine_mi_threshold(spk_ctx* c, uint64_t n_values, uint64_t threshold
     }
     if (possible / 10 < tp) tp = possible / 10;              // SpydrPick.hpp:276-279
     if (tp == 0) return fail(c, SPK_E_INVALID, "alignment too small for threshold estimation");
-    const uint64_t idx = (uint64_t)(pct * double(tp));
-    std::vector<uint32_t> pi(tp), pj(tp);
-    std::vector<double> mi(tp), thresholds;
-    for (uint32_t it = 0; it < iterations; ++it) {
-        std::mt19937 gen((uint32_t)(seed + it));
-        std::uniform_int_distribution<uint64_t> dist(0, L - 1);
-        std::unordered_set<uint64_t> seen; seen.reserve(tp * 2);
-        uint64_t k = 0;
-        while (k < tp) {
-            uint64_t a = dist(gen), b = dist(gen);
-            while (a == b) { a = dist(gen); b = dist(gen); }
-            if (a > b) std::swap(a, b);
-            if (seen.insert((a << 32) | b).second) { pi[k] = (uint32_t)a; pj[k] = (uint32_t)b; ++k; }
+    uint64_t idx = (uint64_t)(pct * double(tp));
+    if (idx >= tp) idx = tp - 1;
+    SPK_CUDA(c, cudaSetDevice(c->device));
+    // multi-GPU: iterations are dealt to the ranks, the per-iteration thresholds are summed into place (zeros elsewhere)
+    const uint32_t world = (uint32_t)std::max(1, c->world), rank = (uint32_t)c->rank;
+    std::vector<uint32_t> my_its;
+    for (uint32_t it = rank; it < iterations; it += world) my_its.push_back(it);
+    const uint32_t nit = (uint32_t)my_its.size();
+    int r = mi_refine_prepare(c, pc); if (r) return r;       // every rank (the plane build may be a collective)
+    const uint64_t total = tp * nit;
+    if (total > 0x7fffffffull) return fail(c, SPK_E_INVALID, "determine_mi_threshold: too many sampled pairs");
+    const size_t ib = (total * 4 + 255) & ~(size_t)255, ob = (total * 8 + 255) & ~(size_t)255;
+    size_t tmpb = 0;
+    std::vector<int> h_off(nit + 1);
+    for (uint32_t k = 0; k <= nit; ++k) h_off[k] = (int)(tp * k);
+    if (nit) cub::DeviceSegmentedRadixSort::SortKeys(nullptr, tmpb, (const double*)nullptr, (double*)nullptr, (int)total, (int)nit, (const int*)nullptr, (const int*)nullptr, 0, 64, c->stream);
+    const size_t offb = ((size_t)(nit + 1) * 4 + 255) & ~(size_t)255, thrb = ((size_t)iterations * 8 + 255) & ~(size_t)255;
+    uint8_t* base = (uint8_t*)scratch(c, 2 * ib + 2 * ob + offb + thrb + ((tmpb + 255) & ~(size_t)255) + 256);
+    if (!base) return fail(c, SPK_E_NOMEM, "scratch allocation failed");
+    uint32_t* d_pi = (uint32_t*)base; uint32_t* d_pj = (uint32_t*)(base + ib);
+    double* d_mi = (double*)(base + 2 * ib); double* d_sorted = (double*)(base + 2 * ib + ob);
+    int* d_off = (int*)(base + 2 * ib + 2 * ob); double* d_thr = (double*)(base + 2 * ib + 2 * ob + offb);
+    void* d_tmp = base + 2 * ib + 2 * ob + offb + thrb;
+    SPK_CUDA(c, cudaMemsetAsync(d_thr, 0, (size_t)iterations * 8, c->stream));
+    if (nit) {
+        if (sampler == SPK_SAMPLER_REFERENCE) {
+            // the reference's sample_pairs() with an explicit seed (it seeds from the clock, SpydrPick.hpp:178): one host thread per iteration
+            std::vector<uint32_t> pi(total), pj(total);
+            std::vector<std::thread> th;
+            for (uint32_t k = 0; k < nit; ++k)
+                th.emplace_back([&, k]() {
+                    std::mt19937 gen((uint32_t)(seed + my_its[k]));
+                    std::uniform_int_distribution<uint64_t> dist(0, L - 1);
+                    std::unordered_set<uint64_t> seen; seen.reserve(tp * 2);
+                    uint64_t q = 0; uint32_t* oi = pi.data() + (size_t)k * tp; uint32_t* oj = pj.data() + (size_t)k * tp;
+                    while (q < tp) {
+                        uint64_t a = dist(gen), b = dist(gen);
+                        while (a == b) { a = dist(gen); b = dist(gen); }
+                        if (a > b) std::swap(a, b);
+                        if (seen.insert((a << 32) | b).second) { oi[q] = (uint32_t)a; oj[q] = (uint32_t)b; ++q; }
+                    }
+                });
+            for (auto& t : th) t.join();
+            SPK_CUDA(c, cudaMemcpyAsync(d_pi, pi.data(), total * 4, cudaMemcpyHostToDevice, c->stream));
+            SPK_CUDA(c, cudaMemcpyAsync(d_pj, pj.data(), total * 4, cudaMemcpyHostToDevice, c->stream));
+            SPK_CUDA(c, cudaEventRecord(c->ev[EV_THR0], c->stream));
+        } else {
+            uint32_t half_bits = 1; while (half_bits < 32 && (1ull << (2 * half_bits)) < possible) ++half_bits;
+            SPK_CUDA(c, cudaEventRecord(c->ev[EV_THR0], c->stream));
+            sample_pairs_kernel<<<(unsigned)((total + 255) / 256), 256, 0, c->stream>>>(d_pi, d_pj, tp, nit, rank, world, L, possible, half_bits, seed);
+            c->tm.kernel_launches += 1;
         }
-        int r = spk_mi_pairs(c, pi.data(), pj.data(), tp, pc, mi.data()); if (r) return r;
-        std::nth_element(mi.begin(), mi.begin() + idx, mi.end());
-        thresholds.push_back(mi[idx]);
+        r = mi_pairs_exact(c, d_pi, d_pj, total, pc, d_mi); if (r) return r;
+        SPK_CUDA(c, cudaMemcpyAsync(d_off, h_off.data(), (size_t)(nit + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+        SPK_CUDA(c, cub::DeviceSegmentedRadixSort::SortKeys(d_tmp, tmpb, (const double*)d_mi, d_sorted, (int)total, (int)nit, d_off, d_off + 1, 0, 64, c->stream));
+        // this rank's iterations sit at rank, rank + world, ...: write them to their global slots
+        std::vector<double*> dummy;
+        for (uint32_t k = 0; k < nit; ++k)
+            pick_kth_kernel<<<1, 32, 0, c->stream>>>(d_sorted + (size_t)k * tp, tp, idx, 1, d_thr + my_its[k]);
+        c->tm.kernel_launches += 9 + nit;
+        SPK_CUDA(c, cudaEventRecord(c->ev[EV_THR1], c->stream));
+        c->tm_pending |= TMP_THR;
     }
-    const size_t med = thresholds.size() / 2 - (thresholds.size() % 2 ? 0 : 1);
+    r = comm_allreduce_sum_f64(c, d_thr, iterations); if (r) return r;
+    std::vector<double> thresholds(iterations);
+    SPK_CUDA(c, cudaMemcpyAsync(thresholds.data(), d_thr, (size_t)iterations * 8, cudaMemcpyDeviceToHost, c->stream));
+    SPK_CUDA(c, cudaStreamSynchronize(c->stream));
+    resolve_timings(c);
+    const size_t med = thresholds.size() / 2 - (thresholds.size() % 2 ? 0 : 1);       // SpydrPick.hpp:338-341
     std::nth_element(thresholds.begin(), thresholds.begin() + med, thresholds.end());
     *threshold = thresholds[med];
     return SPK_OK;
+}
+
+int spk_determine_mi_threshold(spk_ctx* c, uint64_t n_values, uint64_t threshold_pairs, uint32_t iterations,
+                               double pc, uint64_t seed, double* threshold) {
+    return spk_determine_mi_threshold_ex(c, n_values, threshold_pairs, iterations, pc, seed, SPK_SAMPLER_REFERENCE, threshold);
 }
 
 int spk_outlier_thresholds(const double* colmax, uint64_t L, double* outlier, double* extreme) {
@@ -351,28 +531,42 @@ int spk_outlier_thresholds(const double* colmax, uint64_t L, double* outlier, do
     return SPK_OK;
 }
 
-static int ensure_scan_buffers(Ctx* c, uint64_t max_edges, bool exhaustive) {
-    uint64_t want_edges = max_edges;
-    if (want_edges == 0) want_edges = 2 * std::min<uint64_t>(10000000ull, 100ull * c->L) + 65536;
+static int ensure_scan_buffers(Ctx* c, uint64_t want_edges, uint64_t want_cand, bool exhaustive) {
     const uint64_t possible = (uint64_t)c->L * (c->L - 1) / 2;
     want_edges = std::min<uint64_t>(want_edges, possible + 1);
-    uint64_t want_cand = want_edges + want_edges / 2 + (uint64_t)c->L * 64 + (1u << 20);
     want_cand = std::min<uint64_t>(want_cand, possible + 1);
     want_cand += (uint64_t)c->sm_count * 16 * 2 * 128;        // int8 engine: two partly used emission chunks per epilogue warp
     if (exhaustive) want_cand = std::max<uint64_t>(std::min<uint64_t>(possible + 1, 1ull << 24), (uint64_t)c->L);
     int r;
     if (c->edges_cap < want_edges) {
+        cudaStreamSynchronize(c->stream);
         if ((r = dev_alloc(c, c->d_edges, want_edges * sizeof(spk_edge), "edges"))) return r;
         if ((r = dev_alloc(c, c->d_wo, want_edges * sizeof(spk_edge), "edges_wo_gaps"))) return r;
         c->edges_cap = c->wo_cap = want_edges;
     }
     if (c->cand_cap < want_cand) {
+        cudaStreamSynchronize(c->stream);
         if ((r = dev_alloc(c, c->d_cand, want_cand * sizeof(Candidate), "candidates"))) return r;
         if ((r = dev_alloc(c, c->d_refined, want_cand * sizeof(spk_edge), "refined"))) return r;
         if ((r = dev_alloc(c, c->d_refined_wo, want_cand * 8, "refined_wo"))) return r;
         c->cand_cap = c->refined_cap = want_cand;
     }
+    if (!c->d_audit) {                                        // audit sample of the filter: 1M pairs (16 MB) is plenty
+        const uint64_t cap = 1u << 20;
+        if (cudaMalloc(&c->d_audit, cap * sizeof(Candidate)) == cudaSuccess) c->audit_cap = cap; else { cudaGetLastError(); c->d_audit = nullptr; c->audit_cap = 0; }
+    }
     return SPK_OK;
+}
+
+// pinned result mirrors: D2H at full PCIe rate, no page-fault pass over a fresh std::vector
+static int grow_pinned(Ctx* c, spk_edge*& buf, uint64_t& cap, uint64_t want) {
+    if (want <= cap) return SPK_OK;
+    if (buf) { cudaFreeHost(buf); buf = nullptr; cap = 0; }
+    const uint64_t newcap = want + want / 4 + 1024;
+    if (cudaHostAlloc((void**)&buf, newcap * sizeof(spk_edge), cudaHostAllocDefault) != cudaSuccess) {
+        cudaGetLastError(); return fail(c, SPK_E_NOMEM, "pinned host allocation failed (%llu edges)", (unsigned long long)newcap);
+    }
+    cap = newcap; return SPK_OK;
 }
 
 int spk_mi_scan(spk_ctx* c, const spk_scan_params* pp, spk_scan_result* res) {
@@ -388,102 +582,170 @@ int spk_mi_scan(spk_ctx* c, const spk_scan_params* pp, spk_scan_result* res) {
     const bool use_i8 = (p.engine == 0 || p.engine == 3 || p.engine == 4);
     const int i8_wr = p.engine == 3 ? 2 : (p.engine == 4 ? 1 : i8_default_wr());
     // default band: measured filter errors are ~3e-6 (int8 engine 3), ~1e-5 (engine 4), 4e-5 (bf16 T=2), 4e-3 (T=1); when the band is left to
-    // the library and a run's measured error exceeds band/2 the scan is repeated with a wider band (never silently accepted).
+    // the library and a run's measured error (over the candidates AND over the audit sample of non-candidates) exceeds band/2, or
+    // the audit finds a pair the filter would have lost, the scan is repeated with a wider band (never silently accepted).
     double band = p.band > 0.0 ? p.band : (use_i8 ? (i8_wr == 2 ? 4e-5 : 2e-4) : (T == 1 ? 1e-2 : 2e-4));
     const bool band_auto = !(p.band > 0.0);
     const uint64_t circle = p.circle_size ? p.circle_size : c->L;
+    // n_parts == 0 on a context that belongs to a communicator: the collective scan (this rank's partition + the exchange)
+    const bool collective = (p.n_parts == 0 && c->world > 1);
+    if (collective) { p.part_index = (uint32_t)c->rank; p.n_parts = (uint32_t)c->world; }
     if (p.n_parts == 0) p.n_parts = 1;
     if (p.part_index >= p.n_parts) return fail(c, SPK_E_INVALID, "mi_scan: part_index >= n_parts");
     if (c->dl_pending) { SPK_CUDA(c, cudaEventSynchronize(c->ev_dl)); c->dl_pending = false; }
-    int r = ensure_scan_buffers(c, p.max_edges, p.engine == 1); if (r) return r;
+    const uint64_t possible = (uint64_t)c->L * (c->L - 1) / 2;
+    uint64_t want_edges = p.max_edges ? p.max_edges : 2 * std::min<uint64_t>(10000000ull, 100ull * c->L) + 65536;
+    if (p.n_parts > 1 && !p.max_edges) want_edges = want_edges / p.n_parts + want_edges / (4 * p.n_parts) + 65536;   // a partition holds ~1/G of the edges
+    uint64_t want_cand = want_edges + want_edges / 2 + (uint64_t)c->L * 64 / p.n_parts + (1u << 20);
+    int r = ensure_scan_buffers(c, want_edges, want_cand, p.engine == 1); if (r) return r;
 
-    unsigned long long h_counters[8] = {0};
+    unsigned long long h_counters[16] = {0};
     uint64_t ne = 0, nw = 0;
+    bool first = true;
     for (int attempt = 0;; ++attempt) {
-    SPK_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 8 * sizeof(unsigned long long), c->stream));
-    fill_u64_kernel<<<(c->L_pad + 255) / 256, 256, 0, c->stream>>>((unsigned long long*)c->d_colmax, f64_ordered(-DBL_MAX), c->L_pad);
-    c->tm.kernel_launches += 1;
-    c->tm.gemm_ms = c->tm.refine_ms = c->tm.compact_ms = c->tm.sort_ms = 0.f; c->tm.gemm_tiles = 0;
-
-    if (p.engine == 1) {
-        r = mi_scan_exact(c, p, circle); if (r) return r;
-    } else {
-        if (use_i8) {
-            // the refine's plane build only needs the weights: queued first, it runs on the GPU while the host prepares the filter
-            if (attempt == 0) { r = mi_refine_prepare(c, p.pseudocount); if (r) return r; }
-            r = mi_i8_filter(c, p, band, circle, i8_wr); if (r) return r;
+        if (attempt > 8) return fail(c, SPK_E_OVERFLOW, "mi_scan: result buffers still too small after %d rescans", attempt);
+        SPK_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 16 * sizeof(unsigned long long), c->stream));
+        fill_u64_kernel<<<(c->L_pad + 255) / 256, 256, 0, c->stream>>>((unsigned long long*)c->d_colmax, f64_ordered(-DBL_MAX), c->L_pad);
+        c->tm.kernel_launches += 1;
+        c->tm.gemm_ms = c->tm.refine_ms = c->tm.compact_ms = c->tm.sort_ms = c->tm.seed_ms = c->tm.audit_ms = c->tm.exchange_ms = 0.f; c->tm.gemm_tiles = 0;
+        bool audited = false;
+        if (p.engine == 1) {
+            r = mi_scan_exact(c, p, circle); if (r) return r;
         } else {
-            r = prep_column_stats(c, p.pseudocount); if (r) return r;
-            r = prep_operands(c, T); if (r) return r;
-            r = mi_gemm_filter(c, p, T, band, circle); if (r) return r;
+            if (use_i8) {
+                // the refine's plane build only needs the weights: queued first, it runs on the GPU while the host prepares the filter
+                if (first) { r = mi_refine_prepare(c, p.pseudocount); if (r) return r; }
+                r = mi_i8_filter(c, p, band, circle, i8_wr, !first); if (r) return r;
+                if (first && c->d_audit && c->audit_cap) {
+                    r = mi_audit(c, c->d_audit, c->d_counters + 11, c->audit_cap, p.pseudocount, p.threshold, (float)(p.threshold - band)); if (r) return r;
+                    audited = true;
+                }
+            } else {
+                r = prep_column_stats(c, p.pseudocount); if (r) return r;
+                r = prep_operands(c, T); if (r) return r;
+                r = mi_gemm_filter(c, p, T, band, circle); if (r) return r;
+            }
+            first = false;
+            SPK_CUDA(c, cudaMemcpyAsync(h_counters, c->d_counters, sizeof h_counters, cudaMemcpyDeviceToHost, c->stream));
+            SPK_CUDA(c, cudaStreamSynchronize(c->stream));
+            if (h_counters[4]) {
+                // candidate buffer too small: the reservation counter kept counting, so the needed size is known -- grow and rescan
+                // (the reference stores any number of edges; a low user threshold must not abort the run)
+                const uint64_t need = h_counters[0] + h_counters[0] / 8 + (1u << 16);
+                if (c->verbose) fprintf(stderr, "spydrpick_b200: %llu candidates > capacity %llu: rescanning with larger buffers\n", h_counters[0], (unsigned long long)c->cand_cap);
+                if (need > possible + (uint64_t)c->sm_count * 16 * 2 * 128 + (1u << 16) && c->cand_cap >= possible) return fail(c, SPK_E_OVERFLOW, "candidate buffer overflow");
+                r = ensure_scan_buffers(c, std::max<uint64_t>(c->edges_cap, need * 2 / 3), need, false); if (r) return r;
+                continue;
+            }
+            uint64_t ncand = h_counters[0];                  // int8 engine: reserved slots, a few of them invalid-marked holes
+            if (audited) {
+                res->audit_pairs = h_counters[10]; res->audit_violations = h_counters[9];
+                res->audit_max_error = h_counters[8] ? f64_from_ordered(h_counters[8]) : 0.0;
+            }
+            SPK_CUDA(c, cudaEventRecord(c->ev[EV_REF0], c->stream));
+            r = mi_refine_candidates(c, ncand, p.pseudocount, p.threshold, &ncand); if (r) return r;
+            res->n_candidates = ncand;
+            SPK_CUDA(c, cudaEventRecord(c->ev[EV_REF1], c->stream));
+            r = mi_compact(c, ncand, p, circle); if (r) return r;
+            SPK_CUDA(c, cudaEventRecord(c->ev[EV_CMP1], c->stream));
+            c->tm_pending |= TMP_REFINE | TMP_COMPACT;
         }
+        ordered_to_double_kernel<<<(c->L_pad + 255) / 256, 256, 0, c->stream>>>((unsigned long long*)c->d_colmax, c->L_pad);
+        c->tm.kernel_launches += 1;
         SPK_CUDA(c, cudaMemcpyAsync(h_counters, c->d_counters, sizeof h_counters, cudaMemcpyDeviceToHost, c->stream));
         SPK_CUDA(c, cudaStreamSynchronize(c->stream));
-        if (h_counters[4]) return fail(c, SPK_E_OVERFLOW, "candidate buffer overflow (%llu candidates > capacity %llu): raise max_edges or the threshold",
-                                       h_counters[0], (unsigned long long)c->cand_cap);
-        uint64_t ncand = h_counters[0];                  // int8 engine: reserved slots, a few of them invalid-marked holes
-        SPK_CUDA(c, cudaEventRecord(c->ev[4], c->stream));
-        r = mi_refine_candidates(c, ncand, p.pseudocount, p.threshold, &ncand); if (r) return r;
-        res->n_candidates = ncand;
-        SPK_CUDA(c, cudaEventRecord(c->ev[5], c->stream));
-        r = mi_compact(c, ncand, p, circle); if (r) return r;
-        SPK_CUDA(c, cudaEventRecord(c->ev[6], c->stream));
-        SPK_CUDA(c, cudaEventSynchronize(c->ev[6]));
-        SPK_CUDA(c, cudaEventElapsedTime(&c->tm.refine_ms, c->ev[4], c->ev[5]));
-        SPK_CUDA(c, cudaEventElapsedTime(&c->tm.compact_ms, c->ev[5], c->ev[6]));
-    }
-    ordered_to_double_kernel<<<(c->L_pad + 255) / 256, 256, 0, c->stream>>>((unsigned long long*)c->d_colmax, c->L_pad);
-    c->tm.kernel_launches += 1;
-    SPK_CUDA(c, cudaMemcpyAsync(h_counters, c->d_counters, sizeof h_counters, cudaMemcpyDeviceToHost, c->stream));
-    SPK_CUDA(c, cudaStreamSynchronize(c->stream));
-    if (h_counters[4]) return fail(c, SPK_E_OVERFLOW, "edge buffer overflow (%llu edges > capacity %llu): raise max_edges", h_counters[1],
-                                   (unsigned long long)c->edges_cap);
-    ne = h_counters[1]; nw = h_counters[2];
-    res->max_filter_error = h_counters[3] ? f64_from_ordered(h_counters[3]) : 0.0;
-    if (p.engine != 1 && res->max_filter_error > 0.5 * band) {
-        if (band_auto && attempt < 3) {
-            const double wider = std::max(4.0 * res->max_filter_error, 4.0 * band);
-            if (c->verbose) fprintf(stderr, "spydrpick_b200: filter error %.3g > band/2 (band %.3g): rescanning with band %.3g\n",
-                                    res->max_filter_error, band, wider);
-            band = wider;
+        resolve_timings(c);
+        if (h_counters[4]) {
+            const uint64_t need = std::max(h_counters[1], h_counters[2]) + h_counters[1] / 8 + (1u << 16);
+            if (c->verbose) fprintf(stderr, "spydrpick_b200: %llu edges > capacity %llu: rescanning with larger buffers\n", h_counters[1], (unsigned long long)c->edges_cap);
+            if (c->edges_cap > possible) return fail(c, SPK_E_OVERFLOW, "edge buffer overflow");
+            r = ensure_scan_buffers(c, need, std::max<uint64_t>(c->cand_cap, need + need / 2), p.engine == 1); if (r) return r;
             continue;
         }
-        return fail(c, SPK_E_PRECISION, "fp32 filter error %.3g exceeds half the safety band %.3g: raise band (or n_terms with engine 2)",
-                    res->max_filter_error, band);
-    }
-    break;
-    }
-    // pinned mirrors: D2H at full PCIe rate, no page-fault pass over a fresh std::vector
-    auto grow = [&](spk_edge*& buf, uint64_t& cap, uint64_t want) -> int {
-        if (want <= cap) return SPK_OK;
-        if (buf) { cudaFreeHost(buf); buf = nullptr; cap = 0; }
-        const uint64_t newcap = want + want / 4 + 1024;
-        if (cudaHostAlloc((void**)&buf, newcap * sizeof(spk_edge), cudaHostAllocDefault) != cudaSuccess) {
-            cudaGetLastError(); return fail(c, SPK_E_NOMEM, "pinned host allocation failed (%llu edges)", (unsigned long long)newcap);
+        ne = h_counters[1]; nw = h_counters[2];
+        res->max_filter_error = h_counters[3] ? f64_from_ordered(h_counters[3]) : 0.0;
+        double worst = std::max(res->max_filter_error, res->audit_max_error);
+        bool lost = res->audit_violations != 0;
+        if (collective && p.engine != 1) {
+            // the band decision is taken by all ranks together (a rescan with a wider band repeats the collective seed pass)
+            if (!c->d_xcnt && cudaMalloc(&c->d_xcnt, 2 * 64 * sizeof(unsigned long long)) != cudaSuccess) { cudaGetLastError(); return fail(c, SPK_E_NOMEM, "exchange counters"); }
+            double dec[2] = {worst, lost ? 1.0 : 0.0};
+            SPK_CUDA(c, cudaMemcpyAsync(c->d_xcnt, dec, 16, cudaMemcpyHostToDevice, c->stream));
+            r = comm_allreduce_max_f64(c, (double*)c->d_xcnt, 2); if (r) return r;
+            SPK_CUDA(c, cudaMemcpyAsync(dec, c->d_xcnt, 16, cudaMemcpyDeviceToHost, c->stream));
+            SPK_CUDA(c, cudaStreamSynchronize(c->stream));
+            worst = dec[0]; lost = dec[1] != 0.0;
         }
-        cap = newcap; return SPK_OK;
-    };
-    // colmax is final after compaction: read back BEFORE the bulk downloads are queued (one D2H copy engine, in issue order)
+        if (p.engine != 1 && (worst > 0.5 * band || lost)) {
+            if (band_auto && attempt < 6) {
+                const double wider = std::max(4.0 * worst, 4.0 * band);
+                if (c->verbose) fprintf(stderr, "spydrpick_b200: filter error %.3g (audit: %.3g over %llu pairs, %llu lost) vs band %.3g: rescanning with band %.3g\n",
+                                        res->max_filter_error, res->audit_max_error, (unsigned long long)res->audit_pairs, (unsigned long long)res->audit_violations, band, wider);
+                band = wider;
+                first = true;                                   // a wider band needs a new audit sample (its window moves with the band)
+                continue;
+            }
+            return fail(c, SPK_E_PRECISION, "filter error %.3g (audit %.3g, %llu pairs lost) exceeds half the safety band %.3g: raise band (or use engine 3)",
+                        res->max_filter_error, res->audit_max_error, (unsigned long long)res->audit_violations, band);
+        }
+        break;
+    }
+    res->band = band;
+    c->d_edges_sorted_n = 0; c->d_edges_view = c->d_edges;
+    if (p.sort_desc) { r = sort_edges_device(c, c->d_edges, ne); if (r) return r; }
+    spk_edge* d_list = c->d_edges; spk_edge* d_wolist = c->d_wo;
+    uint64_t ne_all = ne, nw_all = nw;
+    if (collective) {
+        // ---- the one exchange step before ARACNE (MI_solver::join, include/mi.hpp:355-361): edge lists concatenated, colmax max-reduced
+        const int G = c->world;
+        SPK_CUDA(c, cudaEventRecord(c->ev[EV_XCH0], c->stream));
+        if (!c->d_xcnt && cudaMalloc(&c->d_xcnt, 2 * 64 * sizeof(unsigned long long)) != cudaSuccess) { cudaGetLastError(); return fail(c, SPK_E_NOMEM, "exchange counters"); }
+        unsigned long long mine[2] = {ne, nw};
+        SPK_CUDA(c, cudaMemcpyAsync(c->d_xcnt + 2 * c->rank, mine, 16, cudaMemcpyHostToDevice, c->stream));
+        r = comm_allgather_inplace(c, c->d_xcnt, 16); if (r) return r;
+        std::vector<unsigned long long> cnt(2 * G);
+        SPK_CUDA(c, cudaMemcpyAsync(cnt.data(), c->d_xcnt, (size_t)G * 16, cudaMemcpyDeviceToHost, c->stream));
+        r = comm_allreduce_max_f64(c, c->d_colmax, c->L); if (r) return r;
+        SPK_CUDA(c, cudaStreamSynchronize(c->stream));
+        std::vector<size_t> eb(G), eo(G), wb(G), wo(G);
+        std::vector<uint64_t> runs(G);
+        ne_all = 0; nw_all = 0;
+        for (int q = 0; q < G; ++q) { eo[q] = ne_all * sizeof(spk_edge); eb[q] = cnt[2 * q] * sizeof(spk_edge); runs[q] = cnt[2 * q]; ne_all += cnt[2 * q];
+                                      wo[q] = nw_all * sizeof(spk_edge); wb[q] = cnt[2 * q + 1] * sizeof(spk_edge); nw_all += cnt[2 * q + 1]; }
+        if (ne_all > 0x7fffffffull) return fail(c, SPK_E_INVALID, "mi_scan: more than 2^31 edges in total");
+        if (c->merge_cap < ne_all) {
+            free_dev(c->d_merge); c->merge_cap = 0;
+            const uint64_t cap = ne_all + ne_all / 8 + 4096;
+            if (cudaMalloc(&c->d_merge, cap * sizeof(spk_edge)) != cudaSuccess) { cudaGetLastError(); return fail(c, SPK_E_NOMEM, "merged edge list (%llu edges)", (unsigned long long)cap); }
+            c->merge_cap = cap;
+        }
+        r = comm_allgatherv(c, c->d_edges, c->d_merge, eb.data(), eo.data()); if (r) return r;
+        if (c->rank == 0 && c->wo_all_cap < nw_all) {
+            free_dev(c->d_wo_all); c->wo_all_cap = 0;
+            const uint64_t cap = nw_all + nw_all / 8 + 4096;
+            if (cudaMalloc(&c->d_wo_all, cap * sizeof(spk_edge)) != cudaSuccess) { cudaGetLastError(); return fail(c, SPK_E_NOMEM, "gathered MI-without-gaps list"); }
+            c->wo_all_cap = cap;
+        }
+        r = comm_gatherv_root(c, c->d_wo, c->d_wo_all, wb.data(), wo.data()); if (r) return r;
+        // every rank sorted its own edges: the gathered list is G sorted runs -> G-1 merges give the list a full sort gives
+        if (p.sort_desc) { r = merge_sorted_runs_device(c, c->d_merge, runs.data(), (uint32_t)G); if (r) return r; }
+        SPK_CUDA(c, cudaEventRecord(c->ev[EV_XCH1], c->stream));
+        c->tm_pending |= TMP_XCH;
+        d_list = c->d_merge; d_wolist = (c->rank == 0) ? c->d_wo_all : nullptr;
+        if (c->rank != 0) nw_all = 0;
+        c->d_edges_view = c->d_merge;
+    }
+    if (p.sort_desc) c->d_edges_sorted_n = ne_all;
+    // colmax is final: read back BEFORE the bulk downloads are queued (one D2H copy engine, in issue order)
     c->h_colmax.resize(c->L);
     SPK_CUDA(c, cudaMemcpyAsync(c->h_colmax.data(), c->d_colmax, (size_t)c->L * 8, cudaMemcpyDeviceToHost, c->stream));
-    bool wo_in_flight = false;
-    if (p.keep_on_device == 2 && nw) {
-        // the MI-without-gaps list is final after compaction (the sort only touches the edge list): its download
-        // starts now on the side stream and runs under the edge sort
-        if ((r = grow(c->hp_wo, c->hp_wo_cap, nw))) return r;
-        SPK_CUDA(c, cudaEventRecord(c->ev_ready, c->stream));
-        SPK_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->ev_ready, 0));
-        SPK_CUDA(c, cudaMemcpyAsync(c->hp_wo, c->d_wo, nw * sizeof(spk_edge), cudaMemcpyDeviceToHost, c->copy_stream));
-        wo_in_flight = true;
-    }
-    c->d_edges_sorted_n = 0;
-    if (p.sort_desc) { r = sort_edges_device(c, c->d_edges, ne); if (r) return r; c->d_edges_sorted_n = ne; }
-    res->n_edges = ne; res->n_wo_gaps = nw;
-    res->d_edges = c->d_edges; res->d_edges_wo_gaps = c->d_wo; res->d_colmax = c->d_colmax;
+    res->n_edges = ne_all; res->n_wo_gaps = nw_all;
+    res->d_edges = d_list; res->d_edges_wo_gaps = d_wolist; res->d_colmax = c->d_colmax;
     c->host_edges_n = 0;
-    if (p.keep_on_device != 1) {
-        if ((r = grow(c->hp_edges, c->hp_edges_cap, ne))) return r;
-        if ((r = grow(c->hp_wo, c->hp_wo_cap, nw))) return r;
+    const bool want_host = p.keep_on_device != 1 && (!collective || c->rank == 0);
+    if (want_host) {
+        if ((r = grow_pinned(c, c->hp_edges, c->hp_edges_cap, ne_all))) return r;
+        if ((r = grow_pinned(c, c->hp_wo, c->hp_wo_cap, nw_all))) return r;
         // keep_on_device == 2: the copies run on a side stream and overlap whatever the caller launches next (ARACNE on the
         // device copy); the host pointers are returned now, their contents are valid after spk_wait_download().
         cudaStream_t cs = c->stream;
@@ -492,14 +754,15 @@ int spk_mi_scan(spk_ctx* c, const spk_scan_params* pp, spk_scan_result* res) {
             SPK_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->ev_ready, 0));
             cs = c->copy_stream;
         }
-        if (ne) SPK_CUDA(c, cudaMemcpyAsync(c->hp_edges, c->d_edges, ne * sizeof(spk_edge), cudaMemcpyDeviceToHost, cs));
-        if (nw && !wo_in_flight) SPK_CUDA(c, cudaMemcpyAsync(c->hp_wo, c->d_wo, nw * sizeof(spk_edge), cudaMemcpyDeviceToHost, cs));
+        if (nw_all) SPK_CUDA(c, cudaMemcpyAsync(c->hp_wo, d_wolist, nw_all * sizeof(spk_edge), cudaMemcpyDeviceToHost, cs));
+        if (ne_all) SPK_CUDA(c, cudaMemcpyAsync(c->hp_edges, d_list, ne_all * sizeof(spk_edge), cudaMemcpyDeviceToHost, cs));
         if (p.keep_on_device == 2) { SPK_CUDA(c, cudaEventRecord(c->ev_dl, cs)); c->dl_pending = true; }
-        if (p.sort_desc) c->host_edges_n = ne;
+        if (p.sort_desc) c->host_edges_n = ne_all;
     }
     SPK_CUDA(c, cudaStreamSynchronize(c->stream));
+    resolve_timings(c);
     res->colmax = c->h_colmax.data();
-    if (p.keep_on_device != 1) { res->edges = c->hp_edges; res->edges_wo_gaps = c->hp_wo; }
+    if (want_host) { res->edges = c->hp_edges; res->edges_wo_gaps = c->hp_wo; }
     return SPK_OK;
 }
 
@@ -508,6 +771,7 @@ int spk_sort_edges_device(spk_ctx* c, void* d_edges, uint64_t n) {
     SPK_CUDA(c, cudaSetDevice(c->device));
     int r = sort_edges_device(c, (spk_edge*)d_edges, n); if (r) return r;
     SPK_CUDA(c, cudaStreamSynchronize(c->stream));
+    resolve_timings(c);
     return SPK_OK;
 }
 
@@ -521,6 +785,7 @@ int spk_sort_edges(spk_ctx* c, spk_edge* edges, uint64_t n) {
     if (!r) r = sort_edges_device(c, d, n);
     if (!r) r = cuda_check(c, cudaMemcpyAsync(edges, d, n * sizeof(spk_edge), cudaMemcpyDeviceToHost, c->stream), "D2H edges");
     if (!r) r = cuda_check(c, cudaStreamSynchronize(c->stream), "sync");
+    if (!r) resolve_timings(c);
     cudaFree(d);
     return r;
 }
@@ -531,26 +796,49 @@ int spk_merge_sorted_runs_device(spk_ctx* c, void* d_edges, const uint64_t* run_
     for (uint32_t r = 0; r < n_runs; ++r) n += run_counts[r];
     if (n && !d_edges) return SPK_E_INVALID;
     SPK_CUDA(c, cudaSetDevice(c->device));
-    return merge_sorted_runs_device(c, (spk_edge*)d_edges, run_counts, n_runs);
-}
-
-int spk_aracne_device(spk_ctx* c, const void* d_edges, uint64_t n, double eps, uint32_t part, uint32_t nparts, void* d_flags) {
-    if (!c || (n && (!d_edges || !d_flags))) return SPK_E_INVALID;
-    if (nparts == 0) nparts = 1;
-    if (part >= nparts) return fail(c, SPK_E_INVALID, "aracne: part_index >= n_parts");
-    SPK_CUDA(c, cudaSetDevice(c->device));
-    int r = aracne_device(c, (const spk_edge*)d_edges, n, eps, part, nparts, (uint8_t*)d_flags); if (r) return r;
+    int r = merge_sorted_runs_device(c, (spk_edge*)d_edges, run_counts, n_runs); if (r) return r;
     SPK_CUDA(c, cudaStreamSynchronize(c->stream));
     return SPK_OK;
 }
 
+// ARACNE on a device list. Collective (context in a communicator, n_parts == 0): every rank evaluates its range of the edge
+// list, the flag shards are exchanged in place (grouped broadcast of each rank's range), every rank ends with all flags.
+static int aracne_collective(spk_ctx* c, const spk_edge* d_edges, uint64_t n, double eps, uint8_t* d_flags) {
+    int r = aracne_device(c, d_edges, n, eps, (uint32_t)c->rank, (uint32_t)c->world, d_flags); if (r) return r;
+    std::vector<size_t> fb(c->world), fo(c->world);
+    for (int q = 0; q < c->world; ++q) { const uint64_t e0 = n * (uint64_t)q / (uint64_t)c->world, e1 = n * (uint64_t)(q + 1) / (uint64_t)c->world; fo[q] = e0; fb[q] = e1 - e0; }
+    return comm_allgatherv(c, d_flags + fo[c->rank], d_flags, fb.data(), fo.data());
+}
+
+int spk_aracne_device(spk_ctx* c, const void* d_edges, uint64_t n, double eps, uint32_t part, uint32_t nparts, void* d_flags) {
+    if (!c || (n && (!d_edges || !d_flags))) return SPK_E_INVALID;
+    SPK_CUDA(c, cudaSetDevice(c->device));
+    int r;
+    if (nparts == 0 && c->world > 1) {
+        r = aracne_collective(c, (const spk_edge*)d_edges, n, eps, (uint8_t*)d_flags); if (r) return r;
+    } else {
+        if (nparts == 0) nparts = 1;
+        if (part >= nparts) return fail(c, SPK_E_INVALID, "aracne: part_index >= n_parts");
+        r = aracne_device(c, (const spk_edge*)d_edges, n, eps, part, nparts, (uint8_t*)d_flags); if (r) return r;
+    }
+    SPK_CUDA(c, cudaStreamSynchronize(c->stream));
+    resolve_timings(c);
+    return SPK_OK;
+}
+
 int spk_aracne(spk_ctx* c, const spk_edge* edges, uint64_t n, double eps, uint32_t part, uint32_t nparts, uint8_t* flags) {
-    if (!c || (n && (!edges || !flags))) return SPK_E_INVALID;
+    if (!c) return SPK_E_INVALID;
+    const bool collective = (nparts == 0 && c->world > 1);
+    // collective: every rank calls with the same n (the scan's n_edges); ranks other than 0 hold no host copy and may pass
+    // edges = flags = NULL -- the flags are delivered to rank 0's host buffer
+    if (!collective && n && (!edges || !flags)) return SPK_E_INVALID;
     if (n == 0) return SPK_OK;
     if (nparts == 0) nparts = 1;
-    if (part >= nparts) return fail(c, SPK_E_INVALID, "aracne: part_index >= n_parts");
+    if (!collective && part >= nparts) return fail(c, SPK_E_INVALID, "aracne: part_index >= n_parts");
     SPK_CUDA(c, cudaSetDevice(c->device));
-    if (edges == c->hp_edges && n == c->host_edges_n && c->d_edges) {
+    const bool own_list = c->d_edges_view && c->d_edges_sorted_n == n && (collective ? true : (edges == c->hp_edges && n == c->host_edges_n));
+    if (collective && !own_list) return fail(c, SPK_E_INVALID, "aracne: the collective form runs on the edge list of the last collective scan");
+    if (own_list) {
         // the caller hands back the sorted edge list of the last scan unchanged (the reference's
         // run_ARACNE(network) right after get_MI_network): the device copy is still valid, skip the upload.
         if (c->d_flags_cap < n) {                                // (aracne_device owns the context scratch buffer)
@@ -561,11 +849,12 @@ int spk_aracne(spk_ctx* c, const spk_edge* edges, uint64_t n, double eps, uint32
         }
         uint8_t* f0 = c->d_flags_buf;
         // whole list evaluated: every flag is written; a partition leaves the others as the caller passed them
-        int r0 = (nparts <= 1) ? cuda_check(c, cudaMemsetAsync(f0, 0, n, c->stream), "clear flags")
-                               : cuda_check(c, cudaMemcpyAsync(f0, flags, n, cudaMemcpyHostToDevice, c->stream), "H2D flags");
-        if (!r0) r0 = aracne_device(c, c->d_edges, n, eps, part, nparts, f0);
-        if (!r0) r0 = cuda_check(c, cudaMemcpyAsync(flags, f0, n, cudaMemcpyDeviceToHost, c->stream), "D2H flags");
+        int r0 = (nparts <= 1 || collective) ? cuda_check(c, cudaMemsetAsync(f0, 0, n, c->stream), "clear flags")
+                                             : cuda_check(c, cudaMemcpyAsync(f0, flags, n, cudaMemcpyHostToDevice, c->stream), "H2D flags");
+        if (!r0) r0 = collective ? aracne_collective(c, c->d_edges_view, n, eps, f0) : aracne_device(c, c->d_edges_view, n, eps, part, nparts, f0);
+        if (!r0 && flags) r0 = cuda_check(c, cudaMemcpyAsync(flags, f0, n, cudaMemcpyDeviceToHost, c->stream), "D2H flags");
         if (!r0) r0 = cuda_check(c, cudaStreamSynchronize(c->stream), "sync");
+        if (!r0) resolve_timings(c);
         return r0;
     }
     spk_edge* d = nullptr; uint8_t* f = nullptr;
@@ -578,6 +867,7 @@ int spk_aracne(spk_ctx* c, const spk_edge* edges, uint64_t n, double eps, uint32
     if (!r) r = aracne_device(c, d, n, eps, part, nparts, f);
     if (!r) r = cuda_check(c, cudaMemcpyAsync(flags, f, n, cudaMemcpyDeviceToHost, c->stream), "D2H flags");
     if (!r) r = cuda_check(c, cudaStreamSynchronize(c->stream), "sync");
+    if (!r) resolve_timings(c);
     cudaFree(d); cudaFree(f);
     return r;
 }
@@ -590,6 +880,7 @@ int spk_wait_download(spk_ctx* c) {
 
 int spk_get_timings(spk_ctx* c, spk_timings* out) {
     if (!c || !out) return SPK_E_INVALID;
+    if (c->tm_pending) { cudaSetDevice(c->device); cudaStreamSynchronize(c->stream); resolve_timings(c); }
     *out = c->tm;
     return SPK_OK;
 }

@@ -47,7 +47,7 @@ static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
 int sort_edges_device(Ctx* c, spk_edge* d_edges, uint64_t n) {
     if (n < 2) return SPK_OK;
-    if (n > 0xffffffffull) return fail(c, SPK_E_INVALID, "edge sort supports < 2^32 edges (reference limit, ARACNE.hpp:416)");
+    if (n > 0x7fffffffull) return fail(c, SPK_E_INVALID, "edge sort supports < 2^31 edges (CUB item counts are int; the reference's own limit is 2^32, ARACNE.hpp:416)");
     size_t tmp1 = 0, tmp2 = 0;
     cub::DeviceRadixSort::SortPairs(nullptr, tmp1, (unsigned long long*)nullptr, (unsigned long long*)nullptr,
                                     (uint32_t*)nullptr, (uint32_t*)nullptr, (int)n, 0, 64, c->stream);
@@ -62,10 +62,10 @@ int sort_edges_device(Ctx* c, spk_edge* d_edges, uint64_t n) {
     spk_edge* ebuf = (spk_edge*)(base + 2 * kb + 2 * ib);
     void* tmp = base + 2 * kb + 2 * ib + eb;
     const unsigned g = (unsigned)((n + 255) / 256);
-    SPK_CUDA(c, cudaEventRecord(c->ev[0], c->stream));
+    SPK_CUDA(c, cudaEventRecord(c->ev[EV_SORT0], c->stream));
     // node ids of a scan are < L: 2*ceil(log2 L) radix bits instead of 64; caller-supplied lists: largest id found first
     uint32_t nn = c->L;
-    if (!c->d_states || d_edges != c->d_edges) {
+    if (!c->d_states || (d_edges != c->d_edges && d_edges != c->d_edges_view)) {
         unsigned int* d_max = (unsigned int*)k1;
         SPK_CUDA(c, cudaMemsetAsync(d_max, 0, 4, c->stream));
         max_node_kernel<<<g, 256, 0, c->stream>>>(d_edges, n, d_max);
@@ -82,9 +82,8 @@ int sort_edges_device(Ctx* c, spk_edge* d_edges, uint64_t n) {
     gather_edges_kernel<<<g, 256, 0, c->stream>>>(d_edges, i0, n, ebuf);
     SPK_CUDA(c, cudaMemcpyAsync(d_edges, ebuf, n * sizeof(spk_edge), cudaMemcpyDeviceToDevice, c->stream));
     c->tm.kernel_launches += 3 + 2 * 8;     // 3 own kernels + radix passes (CUB library kernels)
-    SPK_CUDA(c, cudaEventRecord(c->ev[1], c->stream));
-    SPK_CUDA(c, cudaEventSynchronize(c->ev[1]));
-    SPK_CUDA(c, cudaEventElapsedTime(&c->tm.sort_ms, c->ev[0], c->ev[1]));
+    SPK_CUDA(c, cudaEventRecord(c->ev[EV_SORT1], c->stream));
+    c->tm_pending |= TMP_SORT;
     SPK_CUDA(c, cudaGetLastError());
     return SPK_OK;
 }
@@ -113,7 +112,6 @@ int merge_sorted_runs_device(Ctx* c, spk_edge* d_edges, const uint64_t* run_coun
     if (!base) return fail(c, SPK_E_NOMEM, "scratch allocation failed (run merge)");
     spk_edge* src = d_edges; spk_edge* dst = (spk_edge*)base;
     void* tmp = base + eb;
-    SPK_CUDA(c, cudaEventRecord(c->ev[0], c->stream));
     while (off.size() > 2) {
         std::vector<uint64_t> next(1, 0);
         for (size_t r = 0; r + 1 < off.size(); r += 2) {
@@ -134,9 +132,6 @@ int merge_sorted_runs_device(Ctx* c, spk_edge* d_edges, const uint64_t* run_coun
         std::swap(src, dst);
     }
     if (src != d_edges) SPK_CUDA(c, cudaMemcpyAsync(d_edges, src, n * sizeof(spk_edge), cudaMemcpyDeviceToDevice, c->stream));
-    SPK_CUDA(c, cudaEventRecord(c->ev[1], c->stream));
-    SPK_CUDA(c, cudaEventSynchronize(c->ev[1]));
-    SPK_CUDA(c, cudaEventElapsedTime(&c->tm.sort_ms, c->ev[0], c->ev[1]));
     SPK_CUDA(c, cudaGetLastError());
     return SPK_OK;
 }
@@ -347,13 +342,13 @@ int aracne_device(Ctx* c, const spk_edge* d_edges, uint64_t n, double eps, uint3
     void* tmp = hbase + 9 * hb;
     unsigned int* d_scan = (unsigned int*)(hbase + 9 * hb + align256(tmpb));   // [0] max node id, [1] node queue, [2] unsorted flag
     const unsigned ge = (unsigned)((n + 255) / 256), gm = (unsigned)((m + 255) / 256);
-    SPK_CUDA(c, cudaEventRecord(c->ev[0], c->stream));
+    SPK_CUDA(c, cudaEventRecord(c->ev[EV_AR0], c->stream));
     // node count is unknown for caller-supplied edge lists: found on the device first (one small sync). The last scan's own
     // sorted list needs neither (node ids < L, order known) -- and must not: the 16-byte read-back would queue on the D2H
     // copy engine behind the asynchronous download of that very list (measured: CSR build 3.0 -> 5.7 ms).
     SPK_CUDA(c, cudaMemsetAsync(d_scan, 0, 16, c->stream));
     unsigned int h_scan[4] = {0, 0, 0, 0};
-    if (d_edges == c->d_edges && c->d_edges_sorted_n == n && c->d_states) {
+    if ((d_edges == c->d_edges || d_edges == c->d_edges_view) && c->d_edges_sorted_n == n && c->d_states) {
         h_scan[0] = c->L - 1;
     } else {
         // caller-supplied list: the 16 bytes come back through a mapped page-locked mailbox written by a kernel, not through
@@ -394,7 +389,7 @@ int aracne_device(Ctx* c, const spk_edge* d_edges, uint64_t n, double eps, uint3
     }
     csr_finish_kernel<<<(unsigned)((m + 1 + 255) / 256), 256, 0, c->stream>>>(k1, e1buf, d_edges, m, bits, offsets, nn, idst, ival, ieid);
     weight_lists_kernel<<<gm, 256, 0, c->stream>>>(d_edges, we1, m, wdst, wval);
-    SPK_CUDA(c, cudaEventRecord(c->ev[1], c->stream));
+    SPK_CUDA(c, cudaEventRecord(c->ev[EV_AR1], c->stream));
     if (nparts == 0) nparts = 1;
     const unsigned long long e0 = (unsigned long long)n * part / nparts, e1 = (unsigned long long)n * (part + 1) / nparts;
     const size_t bm_bytes = (size_t)((nn + 31) / 32) * 4;
@@ -412,11 +407,9 @@ int aracne_device(Ctx* c, const spk_edge* d_edges, uint64_t n, double eps, uint3
         aracne_search_kernel<<<(unsigned)blocks, 256, 0, c->stream>>>(d_edges, e0, e1, idst, ival, offsets, eps, d_flags);
     }
     c->tm.kernel_launches += 5 + (2 * bits + 7) / 8 + (bits + 7) / 8;
-    SPK_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
-    SPK_CUDA(c, cudaEventSynchronize(c->ev[2]));
-    SPK_CUDA(c, cudaEventElapsedTime(&c->tm.aracne_build_ms, c->ev[0], c->ev[1]));
-    SPK_CUDA(c, cudaEventElapsedTime(&c->tm.aracne_ms, c->ev[1], c->ev[2]));
-    if (offsets_tmp) cudaFree(offsets_tmp);
+    SPK_CUDA(c, cudaEventRecord(c->ev[EV_AR2], c->stream));
+    c->tm_pending |= TMP_ARB | TMP_AR;
+    if (offsets_tmp) { SPK_CUDA(c, cudaStreamSynchronize(c->stream)); cudaFree(offsets_tmp); }
     SPK_CUDA(c, cudaGetLastError());
     return SPK_OK;
 }

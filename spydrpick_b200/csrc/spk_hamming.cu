@@ -302,7 +302,7 @@ __global__ void fill_ones_kernel(unsigned long long* counts, uint32_t n, unsigne
 int hamming_neighbour_counts(Ctx* c, uint64_t min_identical, int quirks, uint32_t part, uint32_t n_parts) {
     const uint32_t nt = (c->n + HT - 1) / HT;
     const int quirk = quirks & SPK_QUIRK_LASTBLOCK;
-    SPK_CUDA(c, cudaEventRecord(c->ev[0], c->stream));
+    SPK_CUDA(c, cudaEventRecord(c->ev[EV_K1_0], c->stream));
     fill_ones_kernel<<<(c->n + 255) / 256, 256, 0, c->stream>>>((unsigned long long*)c->d_counts, c->n, part == 0 ? 1ull : 0ull);
     static const bool v1 = [] { const char* e = getenv("SPYDRPICK_B200_K1"); return e && e[0] == '0'; }();
     if (n_parts == 0) n_parts = 1;
@@ -325,7 +325,8 @@ int hamming_neighbour_counts(Ctx* c, uint64_t min_identical, int quirks, uint32_
                                                                    quirk, (unsigned long long*)c->d_counts);
         c->tm.kernel_launches += 1;
     }
-    SPK_CUDA(c, cudaEventRecord(c->ev[1], c->stream));
+    SPK_CUDA(c, cudaEventRecord(c->ev[EV_K1_1], c->stream));
+    c->tm_pending |= TMP_K1;
     SPK_CUDA(c, cudaGetLastError());
     return SPK_OK;
 }

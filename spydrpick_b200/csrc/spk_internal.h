@@ -13,6 +13,28 @@ namespace spk {
 constexpr int NSTATES = 5;
 constexpr int GAP = 4;
 
+// stage timing events (Ctx::ev)
+enum {
+    EV_UP0 = 0, EV_UP1, EV_PREP1,            // set_alignment: upload, packing
+    EV_K1_0, EV_K1_1,                        // K1
+    EV_EXP0, EV_EXP1, EV_STAT1,              // int8 operand expansion, column records
+    EV_GEMM0, EV_SEED1, EV_GEMM1,            // K2 filter: start, end of the seed pass, end
+    EV_REF0, EV_REF1, EV_CMP1,               // fp64 refine, compaction
+    EV_SORT0, EV_SORT1,                      // edge sort
+    EV_XCH0, EV_XCH1,                        // multi-GPU exchange + run merge
+    EV_AR0, EV_AR1, EV_AR2,                  // ARACNE: CSR build, K3
+    EV_PAIRS0, EV_PAIRS1,                    // K2b
+    EV_AUD0, EV_AUD1,                        // filter audit
+    EV_THR0, EV_THR1,                        // threshold estimator (device part)
+    EV_TMP0, EV_TMP1,                        // short-lived local use (debug paths)
+    EV_COUNT
+};
+enum {                                       // Ctx::tm_pending bits
+    TMP_UPLOAD = 1u << 0, TMP_PREP = 1u << 1, TMP_K1 = 1u << 2, TMP_EXPAND = 1u << 3, TMP_STATS = 1u << 4, TMP_GEMM = 1u << 5,
+    TMP_SEED = 1u << 6, TMP_REFINE = 1u << 7, TMP_COMPACT = 1u << 8, TMP_SORT = 1u << 9, TMP_XCH = 1u << 10, TMP_ARB = 1u << 11,
+    TMP_AR = 1u << 12, TMP_PAIRS = 1u << 13, TMP_AUDIT = 1u << 14, TMP_THR = 1u << 15
+};
+
 // GEMM tile geometry (K2): A tile = 32 i-columns x 4 states = 128 rows (weighted, T terms),
 // B tile = 64 j-columns x 4 states = 256 rows (unweighted one-hot), K block = 64 samples.
 constexpr int TILE_I = 32;
@@ -140,13 +162,39 @@ struct Ctx {
     int       g_state = 0;                // 0 = not built, 1 = built, 2 = weights not groupable (byte kernel is used)
 
     spk_timings tm = {};
-    cudaEvent_t ev[8] = {};
+    // Stage timing events. Every stage owns its own pair so that no host synchronisation is needed between stages: the
+    // events are recorded as the work is queued, `tm_pending` remembers which intervals are outstanding and
+    // resolve_timings() turns them into spk_timings fields at the next point where the stream is known to be idle.
+    cudaEvent_t ev[EV_COUNT] = {};
+    uint32_t tm_pending = 0;
+    // multi-GPU (spk_comm.cu): NCCL communicator of this context's rank; world == 1: single device
+    void* comm = nullptr; int rank = 0, world = 1;
+    spk_edge* d_merge = nullptr; uint64_t merge_cap = 0;      // all-gathered edge list (world > 1)
+    spk_edge* d_wo_all = nullptr; uint64_t wo_all_cap = 0;    // gathered MI-without-gaps list (rank 0)
+    spk_edge* d_edges_view = nullptr;                         // the list the last scan returned (d_edges, or d_merge after an exchange)
+    unsigned long long* d_xcnt = nullptr;                     // [2 * world] per-rank (edges, wo) counts of the exchange
+    uint32_t* d_i8_colmax32_seed = nullptr;                   // seeded fp32 maxima kept for rescans (band / overflow retries)
+    bool i8_seed_valid = false;
+    Candidate* d_audit = nullptr; uint64_t audit_cap = 0;     // audit sample of the filter (pairs just below the candidate band)
     int i8_wr = 0;                         // weight rows the int8 operands / records were prepared for (2 = hi/lo, 1 = factorised)
     cudaStream_t copy_stream = nullptr;   // asynchronous result download (keep_on_device = 2)
     cudaEvent_t ev_ready = nullptr, ev_dl = nullptr;
     bool dl_pending = false;
     uint8_t* d_flags_buf = nullptr; uint64_t d_flags_cap = 0;     // spk_aracne's device flags (grow-only)
 };
+
+void resolve_timings(Ctx* c);               // call when the context's stream is idle
+
+// ---- multi-GPU (spk_comm.cu): no-ops when c->world == 1; all calls are queued on c->stream
+int comm_allreduce_sum_u64(Ctx* c, unsigned long long* d, size_t n);
+int comm_allreduce_max_u32(Ctx* c, uint32_t* d, size_t n);
+int comm_allreduce_max_f64(Ctx* c, double* d, size_t n);
+int comm_allreduce_sum_f64(Ctx* c, double* d, size_t n);
+int comm_allgather_inplace(Ctx* c, void* d_buf, size_t bytes_per_rank);
+int comm_allgatherv(Ctx* c, const void* d_mine, void* d_out, const size_t* bytes, const size_t* off);
+int comm_gatherv_root(Ctx* c, const void* d_mine, void* d_out, const size_t* bytes, const size_t* off);
+int comm_broadcast(Ctx* c, void* d_buf, size_t bytes, int root);
+void comm_free(Ctx* c);
 
 int fail(Ctx* c, int code, const char* fmt, ...);
 int cuda_check(Ctx* c, cudaError_t e, const char* what);
@@ -167,7 +215,10 @@ int hamming_neighbour_counts(Ctx* c, uint64_t min_identical, int quirk, uint32_t
 // ---- exact fp64 MI (spk_mi_exact.cu)
 int mi_pairs_exact(Ctx* c, const uint32_t* d_pi, const uint32_t* d_pj, uint64_t npairs, double pc, double* d_mi);
 // refine candidates -> d_refined (i,j,mi64), d_refined_wo (NaN when no gap column involved)
-int mi_refine_prepare(Ctx* c, double pc);     // weight-grouped bit planes + entropy tables of the fp64 refine (asynchronous; idempotent until the weights change)
+int mi_refine_prepare(Ctx* c, double pc);     // weight-grouped bit planes + entropy tables of the fp64 refine (asynchronous; idempotent until the weights change; world > 1: the plane build is sharded over the ranks and all-gathered)
+// audit of the tensor-core filter: fp64 MI of the sample of pairs the seed pass emitted (mi32 > audit_lo): counters[8] = max |mi32 - mi64|
+// (ordered bits), [9] = pairs with mi64 > thr that the main pass would NOT have refined (mi32 <= cand_lo), [10] = pairs audited
+int mi_audit(Ctx* c, const Candidate* d_audit, const unsigned long long* d_n, uint64_t cap, double pc, double threshold, float cand_lo);
 int mi_refine_candidates(Ctx* c, uint64_t ncand, double pc, double wo_threshold, uint64_t* n_valid = nullptr);   // MI-without-gaps only when mi > wo_threshold
 // exhaustive diagnostic engine: emits every pair of the partition as a candidate-free exact scan
 int mi_scan_exact(Ctx* c, const spk_scan_params& p, uint64_t circle);
@@ -182,7 +233,7 @@ int mi_gemm_debug_tile(Ctx* c, uint32_t ib, uint32_t jb, int n_terms, float* d_o
 // ---- K2, int8 compact engine (spk_mi_i8.cu)
 int i8_build_layout(Ctx* c);                                   // after prep_alignment: classes, permutation
 void i8_free(Ctx* c);
-int mi_i8_filter(Ctx* c, const spk_scan_params& p, double band, uint64_t circle, int wr);
+int mi_i8_filter(Ctx* c, const spk_scan_params& p, double band, uint64_t circle, int wr, bool reuse_seed);
 int i8_default_wr();
 int mi_i8_debug_tile(Ctx* c, uint32_t ti, uint32_t tj, double pc, uint32_t* d_out);
 
@@ -238,3 +289,5 @@ __host__ __device__ inline unsigned long long genome_distance(unsigned long long
 }
 
 } // namespace spk
+
+struct spk_ctx : public spk::Ctx {};

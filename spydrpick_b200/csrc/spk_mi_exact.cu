@@ -85,13 +85,13 @@ __device__ __forceinline__ double warp_mi_pass(double& v, uint32_t mask_i, uint3
 // =============================================================================================
 __global__ void __launch_bounds__(128)
 gbits_build_kernel(const uint8_t* __restrict__ colmajor, const int32_t* __restrict__ gslot, const double* __restrict__ gval,
-                   uint32_t* __restrict__ gbits, double* __restrict__ gmarg, uint32_t L, uint32_t n_pad, uint32_t NW) {
+                   uint32_t* __restrict__ gbits, double* __restrict__ gmarg, uint32_t L, uint32_t n_pad, uint32_t NW, uint32_t col0) {
     // one CTA per column; a warp builds one 32-sample word per iteration: lane b gathers the state of slot 32w+b
     // (the column's n_pad bytes are L1-resident) and five ballots give the five plane words, staged in shared
     // memory so that the column's 5 x NW words leave in one contiguous, coalesced burst.
     extern __shared__ uint32_t planes_sm[];                  // [NSTATES][NW]
     __shared__ double red[4][NSTATES];
-    const uint32_t c = blockIdx.x, lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+    const uint32_t c = col0 + blockIdx.x, lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
     const uint8_t* col = colmajor + (size_t)c * n_pad;
     for (uint32_t w = wid; w < NW; w += 4) {
         const int32_t sidx = gslot[w * 32 + lane];
@@ -735,6 +735,68 @@ mi_refine_kernel(const uint8_t* __restrict__ colmajor, const double* __restrict_
     if (lane == 0 && maxerr > 0.0) atomicMax(&counters[3], f64_ordered(maxerr));
 }
 
+// ---- filter audit ---------------------------------------------------------------------------------
+// The candidate rule of the tensor-core filter (mi32 > thr - band) can only lose an edge if the fp32 / quantised-weight MI
+// under-estimates the fp64 value by more than the band -- and such a pair is, by construction, never refined, so the error
+// measured over the candidates cannot see it. The audit closes that hole with an UNBIASED sample: the colmax seed pass (a
+// 1/32 sample of the tile chunks) emits every pair with mi32 > thr - 4*band; here each of them gets its fp64 MI, and
+//   counters[8]  = max |mi32 - mi64| over the audited pairs (ordered bits)
+//   counters[9]  = number of audited pairs with mi64 > thr whose mi32 was NOT above the candidate cut-off (false negatives)
+//   counters[10] = pairs audited
+// n is read on the device (no host round trip); one thread per pair on the grouped planes, one warp per pair on bytes.
+__global__ void __launch_bounds__(128)
+mi_audit_thread_kernel(const uint8_t* __restrict__ masks, const Candidate* __restrict__ cand, const unsigned long long* __restrict__ d_n,
+                       unsigned long long cap, double pc, double w_total, double threshold, float cand_lo,
+                       unsigned long long* __restrict__ counters,
+                       const uint32_t* __restrict__ gbits, const double* __restrict__ gval, const double* __restrict__ gmarg,
+                       const double* __restrict__ gH, uint32_t NW) {
+    const unsigned long long n = min(*d_n, cap);
+    double err = 0.0; unsigned int bad = 0, cnt = 0;
+    for (unsigned long long p = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += (unsigned long long)gridDim.x * blockDim.x) {
+        const Candidate cd = cand[p];
+        if (cd.i == I8_INVALID) continue;
+        double m = 0.0, m2 = 0.0;
+        pair_eval_dispatch(gbits, gval, gmarg, gH, NW, cd.i, cd.j, masks[cd.i], masks[cd.j], w_total, pc, INFINITY, &m, &m2);
+        err = fmax(err, fabs((double)cd.mi32 - m));
+        bad += (m > threshold && !(cd.mi32 > cand_lo)) ? 1u : 0u;
+        ++cnt;
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+        err = fmax(err, __shfl_xor_sync(0xffffffffu, err, o));
+        bad += __shfl_xor_sync(0xffffffffu, bad, o); cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        if (err > 0.0) atomicMax(&counters[8], f64_ordered(err));
+        if (bad) atomicAdd(&counters[9], (unsigned long long)bad);
+        if (cnt) atomicAdd(&counters[10], (unsigned long long)cnt);
+    }
+}
+__global__ void __launch_bounds__(EX_WARPS * 32)
+mi_audit_warp_kernel(const uint8_t* __restrict__ colmajor, const double* __restrict__ w, const uint8_t* __restrict__ masks,
+                     const Candidate* __restrict__ cand, const unsigned long long* __restrict__ d_n, unsigned long long cap,
+                     uint32_t n_pad, double pc, double threshold, float cand_lo, unsigned long long* __restrict__ counters) {
+    __shared__ double bins_all[EX_WARPS][25 * 32];
+    const uint32_t lane = threadIdx.x % 32, wid = threadIdx.x / 32;
+    double* bins = bins_all[wid];
+    const unsigned long long n = min(*d_n, cap);
+    double err = 0.0; unsigned long long bad = 0, cnt = 0;
+    for (unsigned long long p = (unsigned long long)blockIdx.x * EX_WARPS + wid; p < n; p += (unsigned long long)gridDim.x * EX_WARPS) {
+        const Candidate cd = cand[p];
+        if (cd.i == I8_INVALID) continue;
+        double v = warp_crosstab(colmajor + (size_t)cd.i * n_pad, colmajor + (size_t)cd.j * n_pad, w, n_pad, bins, lane);
+        const double m = warp_mi_pass(v, masks[cd.i], masks[cd.j], pc, lane);
+        err = fmax(err, fabs((double)cd.mi32 - m));
+        bad += (m > threshold && !(cd.mi32 > cand_lo)) ? 1ull : 0ull;
+        ++cnt;
+    }
+    if (lane == 0) {
+        if (err > 0.0) atomicMax(&counters[8], f64_ordered(err));
+        if (bad) atomicAdd(&counters[9], bad);
+        if (cnt) atomicAdd(&counters[10], cnt);
+    }
+}
+
 // ---- threshold / colmax / compaction over refined pairs (mi.hpp:414-461) ----------------------
 // counters[1] = n_edges, counters[2] = n_wo, counters[4] = overflow flag
 __global__ void mi_compact_kernel(const spk_edge* __restrict__ refined, const double* __restrict__ refined_wo,
@@ -868,7 +930,16 @@ static int ensure_grouped(Ctx* c, double pc) {
     const size_t gsm = (size_t)NSTATES * NW * 4;
     if (gsm > 200 * 1024) { c->g_state = 2; return SPK_OK; }        // one column's planes must fit shared memory
     if (gsm > 48 * 1024) SPK_CUDA(c, cudaFuncSetAttribute(gbits_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsm));
-    gbits_build_kernel<<<c->L_pad, 128, gsm, c->stream>>>(c->d_colmajor, c->d_gslot, c->d_gval, c->d_gbits, c->d_gmarg, c->L, c->n_pad, NW);
+    if (c->world > 1 && c->L_pad % (uint32_t)c->world == 0) {
+        // multi-GPU: every rank builds the planes of its L_pad / G columns, the slices are all-gathered over NVLink
+        // (the build depends on the weights only, so it is identical work on every rank otherwise)
+        const uint32_t per = c->L_pad / (uint32_t)c->world, col0 = per * (uint32_t)c->rank;
+        gbits_build_kernel<<<per, 128, gsm, c->stream>>>(c->d_colmajor, c->d_gslot, c->d_gval, c->d_gbits, c->d_gmarg, c->L, c->n_pad, NW, col0);
+        int rx = comm_allgather_inplace(c, c->d_gbits, (size_t)per * NSTATES * NW * 4); if (rx) return rx;
+        rx = comm_allgather_inplace(c, c->d_gmarg, (size_t)per * NSTATES * 8); if (rx) return rx;
+    } else {
+        gbits_build_kernel<<<c->L_pad, 128, gsm, c->stream>>>(c->d_colmajor, c->d_gslot, c->d_gval, c->d_gbits, c->d_gmarg, c->L, c->n_pad, NW, 0u);
+    }
     c->tm.kernel_launches += 1;
     SPK_CUDA(c, cudaGetLastError());
     c->g_NW = NW; c->g_state = 1; c->g_pc = -1.0;
@@ -883,10 +954,27 @@ static int refine_grid(Ctx* c, unsigned long long n) {
 
 int mi_refine_prepare(Ctx* c, double pc) { return ensure_grouped(c, pc); }
 
+int mi_audit(Ctx* c, const Candidate* d_audit, const unsigned long long* d_n, uint64_t cap, double pc, double threshold, float cand_lo) {
+    if (!d_audit || cap == 0) return SPK_OK;
+    { int rg = ensure_grouped(c, pc); if (rg) return rg; }
+    SPK_CUDA(c, cudaEventRecord(c->ev[EV_AUD0], c->stream));
+    if (c->g_state == 1)
+        mi_audit_thread_kernel<<<c->sm_count * 8, 128, 0, c->stream>>>(c->d_masks, d_audit, d_n, cap, pc, c->w_total, threshold, cand_lo, c->d_counters,
+                                                                      c->d_gbits, c->d_gval, c->d_gmarg, c->d_gH, c->g_NW);
+    else
+        mi_audit_warp_kernel<<<c->sm_count * 16, EX_WARPS * 32, 0, c->stream>>>(c->d_colmajor, c->d_w, c->d_masks, d_audit, d_n, cap, c->n_pad, pc,
+                                                                               threshold, cand_lo, c->d_counters);
+    c->tm.kernel_launches += 1;
+    SPK_CUDA(c, cudaEventRecord(c->ev[EV_AUD1], c->stream));
+    c->tm_pending |= TMP_AUDIT;
+    SPK_CUDA(c, cudaGetLastError());
+    return SPK_OK;
+}
+
 int mi_pairs_exact(Ctx* c, const uint32_t* d_pi, const uint32_t* d_pj, uint64_t npairs, double pc, double* d_mi) {
     if (npairs == 0) return SPK_OK;
-    SPK_CUDA(c, cudaEventRecord(c->ev[0], c->stream));
     { int rg = ensure_grouped(c, pc); if (rg) return rg; }
+    SPK_CUDA(c, cudaEventRecord(c->ev[EV_PAIRS0], c->stream));
     if (c->g_state == 1)
         mi_pairs_thread_kernel<<<(unsigned)((npairs + 127) / 128), 128, 0, c->stream>>>(c->d_masks, d_pi, d_pj, npairs, pc, c->w_total, d_mi,
                                                                                        c->d_gbits, c->d_gval, c->d_gmarg, c->d_gH, c->g_NW);
@@ -894,9 +982,8 @@ int mi_pairs_exact(Ctx* c, const uint32_t* d_pi, const uint32_t* d_pj, uint64_t 
         mi_pairs_kernel<<<refine_grid(c, npairs), EX_WARPS * 32, 0, c->stream>>>(c->d_colmajor, c->d_w, c->d_masks, d_pi, d_pj,
                                                                                 npairs, c->n_pad, pc, d_mi, nullptr, nullptr, nullptr, 0);
     c->tm.kernel_launches += 1;
-    SPK_CUDA(c, cudaEventRecord(c->ev[1], c->stream));
-    SPK_CUDA(c, cudaEventSynchronize(c->ev[1]));
-    SPK_CUDA(c, cudaEventElapsedTime(&c->tm.pairs_ms, c->ev[0], c->ev[1]));
+    SPK_CUDA(c, cudaEventRecord(c->ev[EV_PAIRS1], c->stream));
+    c->tm_pending |= TMP_PAIRS;
     SPK_CUDA(c, cudaGetLastError());
     return SPK_OK;
 }
@@ -983,15 +1070,15 @@ int mi_scan_exact(Ctx* c, const spk_scan_params& p, uint64_t circle) {
             if (b == a) return fail(c, SPK_E_OVERFLOW, "candidate buffer smaller than one row of pairs");
             enumerate_pairs_kernel<<<b - a, 256, 0, c->stream>>>(c->d_cand, a, b, L, cnt);
             c->tm.kernel_launches += 1;
-            SPK_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
+            SPK_CUDA(c, cudaEventRecord(c->ev[EV_REF0], c->stream));
             int r = mi_refine_candidates(c, cnt, p.pseudocount, p.threshold); if (r) return r;
-            SPK_CUDA(c, cudaEventRecord(c->ev[3], c->stream));
+            SPK_CUDA(c, cudaEventRecord(c->ev[EV_REF1], c->stream));
             r = mi_compact(c, cnt, p, circle); if (r) return r;
-            SPK_CUDA(c, cudaEventRecord(c->ev[4], c->stream));
-            SPK_CUDA(c, cudaEventSynchronize(c->ev[4]));
+            SPK_CUDA(c, cudaEventRecord(c->ev[EV_CMP1], c->stream));
+            SPK_CUDA(c, cudaEventSynchronize(c->ev[EV_CMP1]));
             float t1, t2;
-            SPK_CUDA(c, cudaEventElapsedTime(&t1, c->ev[2], c->ev[3]));
-            SPK_CUDA(c, cudaEventElapsedTime(&t2, c->ev[3], c->ev[4]));
+            SPK_CUDA(c, cudaEventElapsedTime(&t1, c->ev[EV_REF0], c->ev[EV_REF1]));
+            SPK_CUDA(c, cudaEventElapsedTime(&t2, c->ev[EV_REF1], c->ev[EV_CMP1]));
             ms_refine += t1; ms_compact += t2;
             a = b;
         }

@@ -440,11 +440,10 @@ int mi_gemm_filter(Ctx* c, const spk_scan_params& p, int T, double band, uint64_
     gp.band = (float)band; gp.thr_lo = (float)(p.threshold - band); gp.thr_hi = (float)(p.threshold + band);
     gp.ld_threshold = p.ld_threshold; gp.circle = circle; gp.linear = p.linear_genome;
     gp.debug_out = nullptr;
-    SPK_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
+    SPK_CUDA(c, cudaEventRecord(c->ev[EV_GEMM0], c->stream));
     int r = run_gemm(c, gp, T); if (r) return r;
-    SPK_CUDA(c, cudaEventRecord(c->ev[3], c->stream));
-    SPK_CUDA(c, cudaEventSynchronize(c->ev[3]));
-    SPK_CUDA(c, cudaEventElapsedTime(&c->tm.gemm_ms, c->ev[2], c->ev[3]));
+    SPK_CUDA(c, cudaEventRecord(c->ev[EV_GEMM1], c->stream));
+    c->tm_pending |= TMP_GEMM;
     // tiles actually computed by this partition (valid slots)
     unsigned long long tiles = 0;
     for (unsigned long long lq = 0; lq < local_chunks; ++lq) {

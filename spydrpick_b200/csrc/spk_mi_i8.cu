@@ -75,7 +75,9 @@ constexpr uint32_t I8_IDESC =                           // cute::UMMA::InstrDesc
 struct I8Params {
     const ColRec8* rec;
     Candidate* cand; unsigned long long cand_cap;
-    unsigned long long* counters;          // [0] n_cand, [4] overflow flag, [5] dynamic tile scheduler cursor
+    unsigned long long* counters;          // [5] dynamic tile scheduler cursor, [6] experiment sink
+    unsigned long long* cand_counter;      // slots reserved in `cand` (main pass: counters[0]; seed pass: the audit buffer's counter)
+    unsigned long long* cand_overflow;     // set to 1 when a reservation runs past cand_cap (main pass: counters[4])
     uint32_t* colmax32;                    // [Lperm] running fp32 maxima (ordered-uint), permuted index
     const unsigned long long* sr_prefix;   // [n_sr+1] chunk prefix per super-row
     uint32_t n_sr, NT;
@@ -176,7 +178,7 @@ constexpr uint32_t I8_CH = 128;
 struct I8Emit { uint32_t cur, used, next; };      // cur: chunk id (warp-uniform; I8_INVALID = none yet), next: reserved ahead (lane 0 only)
 
 __device__ __forceinline__ uint32_t i8_reserve_chunk(const I8Params& p) {
-    return (uint32_t)(atomicAdd(&p.counters[0], (unsigned long long)I8_CH) / I8_CH);
+    return (uint32_t)(atomicAdd(p.cand_counter, (unsigned long long)I8_CH) / I8_CH);
 }
 __device__ __forceinline__ void i8_fill_invalid(const I8Params& p, uint32_t chunk, uint32_t from, uint32_t lane) {
     Candidate cd; cd.i = I8_INVALID; cd.j = I8_INVALID; cd.mi32 = 0.f; cd.pad = 0;
@@ -191,7 +193,7 @@ __device__ __noinline__ void i8_emit_switch(const I8Params& p, I8Emit& em, uint3
     if (lane == 0 && nx == I8_INVALID) nx = i8_reserve_chunk(p);
     nx = __shfl_sync(0xffffffffu, nx, 0);
     em.cur = nx; em.used = 0; em.next = I8_INVALID;
-    if ((unsigned long long)(nx + 1u) * I8_CH > p.cand_cap && lane == 0) p.counters[4] = 1ull;
+    if ((unsigned long long)(nx + 1u) * I8_CH > p.cand_cap && lane == 0) *p.cand_overflow = 1ull;
 }
 __device__ __forceinline__ void i8_emit_flush(const I8Params& p, I8Emit& em, uint32_t lane) {
     if (em.cur != I8_INVALID) i8_fill_invalid(p, em.cur, em.used, lane);
@@ -365,8 +367,10 @@ __device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmemT<2
 #endif
             const uint32_t pj = cj0 + j_local;
             const float mi32 = mi_arr[s];
+            bool emit;
             if (p.seed_chunks) {
-                // seed pass: no candidates, only the running LD-admissible maxima of both columns
+                // seed pass: the running LD-admissible maxima of both columns; the only pairs it emits are the AUDIT sample of
+                // the filter (mi32 > thr - 4*band, into the audit buffer: see mi_audit_*_kernel, spk_mi_exact.cu)
                 const bool adm = (mi32 == mi32) && genome_distance(sm.ipos[i_local], sm.jpos[j_local], p.linear, p.circle) > p.ld_threshold;
                 const float m = adm ? mi32 : -INFINITY;
                 cm_i = fmaxf(cm_i, m);
@@ -376,14 +380,14 @@ __device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmemT<2
                 if (lane == g && gmax > sm.cmj[j_local]) {
                     if (atomicMax(&sm.cmj[j_local], gmax) < gmax) atomicMax(&p.colmax32[pj], gmax);
                 }
-                continue;
-            }
+                emit = mi32 > p.thr_lo;                                        // thr_lo of the seed launch = thr - 4*band (+inf: no audit)
+            } else {
             const float cm_lo_j = sm.jrec[j_local].cm_lo;
 #if defined(SPK_I8_EPI_LEVEL) && SPK_I8_EPI_LEVEL == 2          // experiment: MI arithmetic without tests / emission
             if (mi32 == 123.456f) p.counters[6] = 1ull;
             continue;
 #endif
-            bool emit = mi32 > p.thr_lo;                                   // false for NaN
+            emit = mi32 > p.thr_lo;                                        // false for NaN
 #if defined(SPK_I8_EPI_LEVEL) && SPK_I8_EPI_LEVEL == 3          // experiment: no open-column path
             if (mi32 == 123.456f) {
 #else
@@ -396,6 +400,7 @@ __device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmemT<2
             if (emit && mi32 == 123.456f) p.counters[6] = 1ull;
             continue;
 #endif
+            }
             const uint32_t bal = __ballot_sync(0xffffffffu, emit);
             if (bal) {
                 const uint32_t nb = __popc(bal);
@@ -821,7 +826,7 @@ template <class P> static void i8_free_dev(P*& p) { if (p) { cudaFree(p); p = nu
 
 void i8_free(Ctx* c) {
     i8_free_dev(c->d_i8_perm); i8_free_dev(c->d_i8_info); i8_free_dev(c->d_i8_rec); i8_free_dev(c->d_A8); i8_free_dev(c->d_B8);
-    i8_free_dev(c->d_q); i8_free_dev(c->d_i8_colmax32);
+    i8_free_dev(c->d_q); i8_free_dev(c->d_i8_colmax32); i8_free_dev(c->d_i8_colmax32_seed); c->i8_seed_valid = false;
     c->i8 = I8Layout();
     c->i8_weights_valid = c->i8_operands_valid = false; c->i8_rec_pc = -1.0;
     c->i8_cap_Lperm = c->i8_cap_NT = c->i8_cap_npad = 0;
@@ -871,7 +876,7 @@ int i8_build_layout(Ctx* c) {
     const uint32_t capL = c->i8_cap_Lperm;
     if (cudaMalloc(&c->d_i8_perm, (size_t)capL * 4) != cudaSuccess || cudaMalloc(&c->d_i8_info, (size_t)capL * 4) != cudaSuccess ||
         cudaMalloc(&c->d_i8_rec, (size_t)capL * sizeof(ColRec8)) != cudaSuccess ||
-        cudaMalloc(&c->d_i8_colmax32, (size_t)capL * 4) != cudaSuccess ||
+        cudaMalloc(&c->d_i8_colmax32, (size_t)capL * 4) != cudaSuccess || cudaMalloc(&c->d_i8_colmax32_seed, (size_t)capL * 4) != cudaSuccess ||
         cudaMalloc(&c->d_q, (size_t)c->n_pad * 6) != cudaSuccess) {
         cudaGetLastError();
         return fail(c, SPK_E_NOMEM, "int8 engine: layout allocation failed");
@@ -967,12 +972,12 @@ static int i8_prepare(Ctx* c, double pc, int wr) {
             c->i8_delta = wmax / best_M;
         }
         c->i8_wq_total = tot;
+        // (pageable sources: cudaMemcpyAsync stages them before it returns, so the vectors may go out of scope)
         SPK_CUDA(c, cudaMemcpyAsync(c->d_q, q.data(), (size_t)n_pad * 4, cudaMemcpyHostToDevice, c->stream));
         SPK_CUDA(c, cudaMemcpyAsync(d_qhi, qb.data(), (size_t)n_pad * 2, cudaMemcpyHostToDevice, c->stream));
-        SPK_CUDA(c, cudaStreamSynchronize(c->stream));
         c->i8_weights_valid = true; c->i8_operands_valid = false; c->i8_rec_pc = -1.0;
     }
-    SPK_CUDA(c, cudaEventRecord(c->ev[0], c->stream));
+    SPK_CUDA(c, cudaEventRecord(c->ev[EV_EXP0], c->stream));
     if (!c->i8_operands_valid) {
         const size_t rowsA = (size_t)128 * c->i8.NT;
         if (!c->d_A8) {
@@ -991,7 +996,7 @@ static int i8_prepare(Ctx* c, double pc, int wr) {
         SPK_CUDA(c, cudaGetLastError());
         c->i8_operands_valid = true;
     }
-    SPK_CUDA(c, cudaEventRecord(c->ev[1], c->stream));
+    SPK_CUDA(c, cudaEventRecord(c->ev[EV_EXP1], c->stream));
     if (c->i8_rec_pc != pc) {
         i8_colrec_kernel<<<(c->i8.Lperm + 7) / 8, 256, 0, c->stream>>>(c->d_colmajor, c->d_q, c->d_i8_perm, c->d_i8_info, c->d_pos, c->d_i8_rec,
                                                                       c->i8.Lperm, n, n_pad, (double)c->i8_wq_total, pc / c->i8_delta);
@@ -999,10 +1004,8 @@ static int i8_prepare(Ctx* c, double pc, int wr) {
         SPK_CUDA(c, cudaGetLastError());
         c->i8_rec_pc = pc;
     }
-    SPK_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
-    SPK_CUDA(c, cudaEventSynchronize(c->ev[2]));
-    SPK_CUDA(c, cudaEventElapsedTime(&c->tm.expand_ms, c->ev[0], c->ev[1]));
-    SPK_CUDA(c, cudaEventElapsedTime(&c->tm.stats_ms, c->ev[1], c->ev[2]));
+    SPK_CUDA(c, cudaEventRecord(c->ev[EV_STAT1], c->stream));
+    c->tm_pending |= TMP_EXPAND | TMP_STATS;
     return SPK_OK;
 }
 
@@ -1066,6 +1069,7 @@ template <int WR> static int i8_launch_wr(Ctx* c, I8Params& gp) {
     for (int g = 0; g < 3; ++g) { gp.tile_start[g] = c->i8.tile_start[g]; gp.col_start[g] = c->i8.col_start[g]; }
     gp.colmax32 = c->d_i8_colmax32;
     gp.counters = c->d_counters;
+    if (!gp.cand_counter) { gp.cand_counter = c->d_counters + 0; gp.cand_overflow = c->d_counters + 4; }
     const unsigned long long slots = gp.debug_out ? 1ull : gp.n_local_slots;
     if (!pair) {
         const unsigned grid = (unsigned)(slots < (unsigned long long)c->sm_count ? (slots ? slots : 1) : (unsigned long long)c->sm_count);
@@ -1105,7 +1109,7 @@ int i8_default_wr() {
     return v;
 }
 
-int mi_i8_filter(Ctx* c, const spk_scan_params& p, double band, uint64_t circle, int wr) {
+int mi_i8_filter(Ctx* c, const spk_scan_params& p, double band, uint64_t circle, int wr, bool reuse_seed) {
     int r = i8_prepare(c, p.pseudocount, wr); if (r) return r;
     I8Params gp; memset(&gp, 0, sizeof gp);
     const uint32_t NT = c->i8.NT;
@@ -1120,8 +1124,6 @@ int mi_i8_filter(Ctx* c, const spk_scan_params& p, double band, uint64_t circle,
     const unsigned long long local_chunks = total_chunks > p.part_index ? (total_chunks - p.part_index + nparts - 1) / nparts : 0;
     unsigned long long* d_prefix = (unsigned long long*)c->d_tilemap;
     SPK_CUDA(c, cudaMemcpyAsync(d_prefix, prefix.data(), (n_sr + 1) * 8, cudaMemcpyHostToDevice, c->stream));
-    i8_fill_u32_kernel<<<(c->i8.Lperm + 255) / 256, 256, 0, c->stream>>>(c->d_i8_colmax32, f32_ordered(-INFINITY), c->i8.Lperm);
-    c->tm.kernel_launches += 1;
     gp.cand = c->d_cand; gp.cand_cap = c->cand_cap;
     gp.sr_prefix = d_prefix; gp.n_sr = n_sr;
     gp.pair = i8_use_pair() ? 1u : 0u;
@@ -1130,34 +1132,63 @@ int mi_i8_filter(Ctx* c, const spk_scan_params& p, double band, uint64_t circle,
     gp.band = (float)band; gp.thr_lo = (float)(p.threshold - band); gp.thr_hi = (float)(p.threshold + band);
     gp.ld_threshold = p.ld_threshold; gp.circle = circle; gp.linear = p.linear_genome;
     gp.debug_out = nullptr;
-    SPK_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
-    // Seed pass: a 1/I8_SEED_STRIDE sample of the chunks (of ALL partitions), without candidates, to bring every column's
-    // running maximum close to its final value before the main pass. Without it the open-column rule (candidates within
-    // `band` of a column's running maximum while that maximum is below thr + band) fires on every record of a rising
-    // maximum: measured 6.6 M extra candidates and 5.5 ms of slow-path epilogue per launch at 3000 x 100000.
+    SPK_CUDA(c, cudaEventRecord(c->ev[EV_GEMM0], c->stream));
+    // Seed pass: a 1/I8_SEED_STRIDE sample of the chunks (of ALL partitions), to bring every column's running maximum close to
+    // its final value before the main pass. Without it the open-column rule (candidates within `band` of a column's running
+    // maximum while that maximum is below thr + band) fires on every record of a rising maximum: measured 6.6 M extra
+    // candidates and 5.5 ms of slow-path epilogue per launch at 3000 x 100000. The same launch emits the AUDIT sample of the
+    // filter (pairs with mi32 > thr - 4*band of the sampled chunks) into its own buffer.
+    // Multi-GPU (c->world > 1 and this scan is the collective one): the sampled chunks are dealt to the ranks and the maxima
+    // max-reduced over NVLink, instead of every rank repeating the whole seed pass.
+    // A rescan of the same scan (wider band, larger buffers) reuses the seeded maxima: it is local to the rank that needs it.
     bool seeded = false;
-    c->tm.seed_ms = 0.f;
-    if (i8_use_seed() && total_chunks >= 64ull * I8_SEED_STRIDE) {
-        std::vector<unsigned long long> seed;
-        for (uint32_t sr = 0; sr < n_sr; ++sr)
-            for (unsigned long long q = prefix[sr]; q < prefix[sr + 1]; ++q)
-                if ((uint32_t)(q - prefix[sr]) % I8_SEED_STRIDE == sr % I8_SEED_STRIDE) seed.push_back(q);
-        if (!seed.empty() && (size_t)(n_sr + 1 + seed.size()) * 8 <= (1u << 20)) {
-            SPK_CUDA(c, cudaMemcpyAsync(d_prefix + n_sr + 1, seed.data(), seed.size() * 8, cudaMemcpyHostToDevice, c->stream));
-            I8Params sp = gp;
-            sp.seed_chunks = d_prefix + n_sr + 1;
-            sp.n_local_slots = (unsigned long long)seed.size() * (gp.pair ? I8_SUPER / 2 : I8_SUPER);
-            r = i8_launch(c, sp, wr); if (r) return r;
-            seeded = true;
-            SPK_CUDA(c, cudaEventRecord(c->ev[7], c->stream));
-            SPK_CUDA(c, cudaMemsetAsync(c->d_counters + 5, 0, sizeof(unsigned long long), c->stream));   // rewind the tile cursor
+    const bool collective = c->world > 1 && nparts == (uint32_t)c->world && p.part_index == (uint32_t)c->rank;
+    if (reuse_seed && c->i8_seed_valid) {
+        SPK_CUDA(c, cudaMemcpyAsync(c->d_i8_colmax32, c->d_i8_colmax32_seed, (size_t)c->i8.Lperm * 4, cudaMemcpyDeviceToDevice, c->stream));
+        SPK_CUDA(c, cudaEventRecord(c->ev[EV_SEED1], c->stream));
+    } else {
+        i8_fill_u32_kernel<<<(c->i8.Lperm + 255) / 256, 256, 0, c->stream>>>(c->d_i8_colmax32, f32_ordered(-INFINITY), c->i8.Lperm);
+        c->tm.kernel_launches += 1;
+        c->i8_seed_valid = false;
+        if (i8_use_seed() && total_chunks >= 64ull * I8_SEED_STRIDE) {
+            std::vector<unsigned long long> seed;
+            unsigned long long k = 0;
+            for (uint32_t sr = 0; sr < n_sr; ++sr)
+                for (unsigned long long q = prefix[sr]; q < prefix[sr + 1]; ++q)
+                    if ((uint32_t)(q - prefix[sr]) % I8_SEED_STRIDE == sr % I8_SEED_STRIDE) {
+                        if (!collective || k % (unsigned long long)c->world == (unsigned long long)c->rank) seed.push_back(q);
+                        ++k;
+                    }
+            if ((size_t)(n_sr + 1 + seed.size()) * 8 <= (1u << 20)) {
+                if (!seed.empty()) {
+                    SPK_CUDA(c, cudaMemcpyAsync(d_prefix + n_sr + 1, seed.data(), seed.size() * 8, cudaMemcpyHostToDevice, c->stream));
+                    I8Params sp = gp;
+                    sp.seed_chunks = d_prefix + n_sr + 1;
+                    sp.n_local_slots = (unsigned long long)seed.size() * (gp.pair ? I8_SUPER / 2 : I8_SUPER);
+                    if (c->d_audit && c->audit_cap >= 4096) {
+                        sp.cand = c->d_audit; sp.cand_cap = c->audit_cap;
+                        sp.cand_counter = c->d_counters + 11; sp.cand_overflow = c->d_counters + 12;
+                        sp.thr_lo = (float)(p.threshold - 4.0 * band);
+                    } else {
+                        sp.thr_lo = INFINITY;
+                    }
+                    r = i8_launch(c, sp, wr); if (r) return r;
+                    SPK_CUDA(c, cudaMemsetAsync(c->d_counters + 5, 0, sizeof(unsigned long long), c->stream));   // rewind the tile cursor
+                }
+                if (collective) { r = comm_allreduce_max_u32(c, c->d_i8_colmax32, c->i8.Lperm); if (r) return r; }
+                seeded = true;
+                if (c->d_i8_colmax32_seed) {
+                    SPK_CUDA(c, cudaMemcpyAsync(c->d_i8_colmax32_seed, c->d_i8_colmax32, (size_t)c->i8.Lperm * 4, cudaMemcpyDeviceToDevice, c->stream));
+                    c->i8_seed_valid = true;
+                }
+            }
         }
+        SPK_CUDA(c, cudaEventRecord(c->ev[EV_SEED1], c->stream));
     }
+    (void)seeded;
     r = i8_launch(c, gp, wr); if (r) return r;
-    SPK_CUDA(c, cudaEventRecord(c->ev[3], c->stream));
-    SPK_CUDA(c, cudaEventSynchronize(c->ev[3]));
-    SPK_CUDA(c, cudaEventElapsedTime(&c->tm.gemm_ms, c->ev[2], c->ev[3]));
-    if (seeded) SPK_CUDA(c, cudaEventElapsedTime(&c->tm.seed_ms, c->ev[2], c->ev[7]));
+    SPK_CUDA(c, cudaEventRecord(c->ev[EV_GEMM1], c->stream));
+    c->tm_pending |= TMP_GEMM | TMP_SEED;
     // tiles = M128 x N256 MMA tiles of the main pass; pairs = column pairs they cover (incl. padding / below-diagonal halves)
     unsigned long long tiles = 0, pairs = 0;
     auto width = [&](uint32_t t) { return t >= c->i8.tile_start[2] ? 32u : (t >= c->i8.tile_start[1] ? 64u : 128u); };

@@ -153,14 +153,14 @@ int prep_alignment(Ctx* c) {
 
 int prep_column_stats(Ctx* c, double pc) {
     if (c->stats_valid && c->stats_pc == pc) return SPK_OK;
-    SPK_CUDA(c, cudaEventRecord(c->ev[0], c->stream));
+    SPK_CUDA(c, cudaEventRecord(c->ev[EV_TMP0], c->stream));
     column_stats_kernel<<<(c->L_pad + 7) / 8, 256, 0, c->stream>>>(c->d_colmajor, c->d_w, c->d_masks, c->d_pos,
                                                                    c->d_marg, c->d_colstat, c->n, c->L, c->L_pad,
                                                                    c->n_pad, c->w_total, pc);
     c->tm.kernel_launches += 1;
-    SPK_CUDA(c, cudaEventRecord(c->ev[1], c->stream));
-    SPK_CUDA(c, cudaEventSynchronize(c->ev[1]));
-    SPK_CUDA(c, cudaEventElapsedTime(&c->tm.stats_ms, c->ev[0], c->ev[1]));
+    SPK_CUDA(c, cudaEventRecord(c->ev[EV_TMP1], c->stream));
+    SPK_CUDA(c, cudaEventSynchronize(c->ev[EV_TMP1]));
+    SPK_CUDA(c, cudaEventElapsedTime(&c->tm.stats_ms, c->ev[EV_TMP0], c->ev[EV_TMP1]));
     SPK_CUDA(c, cudaGetLastError());
     c->stats_valid = true; c->stats_pc = pc;
     return SPK_OK;
@@ -181,14 +181,14 @@ int prep_operands(Ctx* c, int n_terms) {
     }
     __nv_bfloat16* wsplit = (__nv_bfloat16*)scratch(c, (size_t)3 * c->n_pad * sizeof(__nv_bfloat16));
     if (!wsplit) return fail(c, SPK_E_NOMEM, "scratch allocation failed");
-    SPK_CUDA(c, cudaEventRecord(c->ev[0], c->stream));
+    SPK_CUDA(c, cudaEventRecord(c->ev[EV_TMP0], c->stream));
     split_weights_kernel<<<(c->n_pad + 255) / 256, 256, 0, c->stream>>>(c->d_w, wsplit, c->n, c->n_pad, n_terms);
     expand_operands_kernel<<<(c->L_pad + 7) / 8, 256, 0, c->stream>>>(c->d_colmajor, wsplit, c->d_U, c->d_V,
                                                                       c->L_pad, c->n_pad, n_terms);
     c->tm.kernel_launches += 2;
-    SPK_CUDA(c, cudaEventRecord(c->ev[1], c->stream));
-    SPK_CUDA(c, cudaEventSynchronize(c->ev[1]));
-    SPK_CUDA(c, cudaEventElapsedTime(&c->tm.expand_ms, c->ev[0], c->ev[1]));
+    SPK_CUDA(c, cudaEventRecord(c->ev[EV_TMP1], c->stream));
+    SPK_CUDA(c, cudaEventSynchronize(c->ev[EV_TMP1]));
+    SPK_CUDA(c, cudaEventElapsedTime(&c->tm.expand_ms, c->ev[EV_TMP0], c->ev[EV_TMP1]));
     SPK_CUDA(c, cudaGetLastError());
     c->operands_terms = n_terms;
     return SPK_OK;

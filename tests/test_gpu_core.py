@@ -8,6 +8,7 @@ import numpy as np
 import pytest
 
 import oracle.oracle as orc
+from spydrpick_b200 import capi
 from spydrpick_b200 import Context, EDGE_DTYPE
 from spydrpick_b200.synth import generate_alignment
 
@@ -55,9 +56,10 @@ def _edges(lst):
 
 # ---------------------------------------------------------------- K1
 @pytest.mark.parametrize("n,L", [(50, 96), (130, 257), (64, 64), (200, 1000), (333, 1024), (7, 33)])
-@pytest.mark.parametrize("quirk", [True, False])
+@pytest.mark.parametrize("quirk", [True, False, orc.QUIRK_LASTBLOCK, orc.QUIRK_SAMPLE0])
 def test_neighbour_counts_bit_exact(ctx, n, L, quirk):
     s, _, _ = generate_alignment(n, L, seed=100 + n + L, n_planted=0)
+    s[n // 3] = s[0]                                           # a copy of sample 0: the sample-0 double count has neighbours to work on
     ctx.set_alignment(s)
     for frac in (0.9, 0.7, 0.99):
         thr = int(frac * float(L))
@@ -71,12 +73,28 @@ def test_neighbour_rule_pins(ctx):
     a = np.zeros(L, dtype=np.uint8); b = np.zeros(L, dtype=np.uint8); b[:10] = 1
     s = np.stack([a, b])
     ctx.set_alignment(s)
-    assert list(ctx.neighbour_counts(55, True)) == [2, 2]
+    assert list(ctx.neighbour_counts(55, orc.QUIRK_LASTBLOCK)) == [2, 2]
     assert list(ctx.neighbour_counts(55, False)) == [1, 1]
-    assert list(ctx.neighbour_counts(87, True)) == [1, 1]
+    assert list(ctx.neighbour_counts(87, orc.QUIRK_LASTBLOCK)) == [1, 1]
     g = np.full((2, 40), 4, dtype=np.uint8)
     ctx.set_alignment(g)
-    assert list(ctx.neighbour_counts(40, True)) == [2, 2]
+    assert list(ctx.neighbour_counts(40, False)) == [2, 2]
+    # the reference's sample-0 double count (pinned against the compiled reference, tests/test_ref_pins.py)
+    assert list(ctx.neighbour_counts(40, True)) == [5, 3]
+    three = np.zeros((3, 40), dtype=np.uint8); three[2] = 1
+    ctx.set_alignment(three)
+    assert list(ctx.neighbour_counts(36, True)) == [5, 3, 1]
+
+
+def test_reweight_matches_counts_and_oracle(ctx):
+    s, _, _ = generate_alignment(150, 640, seed=31)
+    s[5] = s[0]
+    ctx.set_alignment(s)
+    w, cnt = ctx.reweight(int(0.9 * 640), True)
+    exp = orc.neighbour_counts(s, int(0.9 * 640), True)
+    assert np.array_equal(cnt, exp) and np.array_equal(w, orc.weights_from_counts(exp))
+    w2, _ = ctx.reweight(int(0.9 * 640), True, rescale=True)
+    assert np.array_equal(w2, orc.weights_from_counts(exp, rescale=True))     # (w * n) / n_eff, bit for bit
 
 
 # ---------------------------------------------------------------- fp64 MI kernels
@@ -134,15 +152,37 @@ def test_exhaustive_scan_partition_union(ctx):
     assert np.array_equal(cm, whole["colmax"])
 
 
-def test_threshold_estimator_vs_oracle_logic(ctx):
+def test_threshold_estimator_equals_oracle(ctx):
+    """spk_determine_mi_threshold uses the reference's sampler (mt19937(seed + iteration), duplicates rejected) exactly as the
+    oracle restates it, so the two must agree to the last bits of the fp64 MI values."""
     s, _, _ = generate_alignment(150, 400, seed=8)
     w = orc.weights_from_counts(orc.neighbour_counts(s, int(0.9 * 400)))
     ctx.set_alignment(s); ctx.set_weights(w)
-    thr = ctx.determine_mi_threshold(4000, iterations=3, seed=5)
-    # the estimate is a quantile of the empirical MI distribution: check against the exact distribution
-    full = orc.mi_scan(s, w, threshold=-1.0)["edges"]["mi"]
-    frac_above = (full > thr).mean()
-    assert 0.5 * 4000 / len(full) < frac_above < 2.0 * 4000 / len(full)
+    for n_values, pairs, its, seed in ((4000, 0, 3, 5), (800, 5000, 10, 77), (20000, 0, 4, 1)):
+        thr = ctx.determine_mi_threshold(n_values, threshold_pairs=pairs, iterations=its, seed=seed)
+        exp = orc.determine_mi_threshold(s, w, n_values, threshold_pairs=pairs, iterations=its, seed=seed)
+        assert thr == pytest.approx(exp, rel=1e-12, abs=1e-15), (n_values, pairs, its, seed)
+    with pytest.raises(capi.SpkError):
+        ctx.determine_mi_threshold(400 * 399 // 2)               # every pair wanted: the reference indexes out of range here
+
+
+def test_threshold_estimator_device_sampler(ctx):
+    """the device sampler draws DISTINCT pairs from a keyed permutation of the pair index space: same quantile statistics"""
+    s, _, _ = generate_alignment(150, 400, seed=8)
+    w = orc.weights_from_counts(orc.neighbour_counts(s, int(0.9 * 400)))
+    ctx.set_alignment(s); ctx.set_weights(w)
+    full = np.sort(orc.mi_scan(s, w, threshold=-1.0)["edges"]["mi"])
+    exact = full[len(full) - 4000]                                # the exact threshold that saves 4000 pairs
+    thr = np.array([ctx.determine_mi_threshold(4000, iterations=10, seed=sd, sampler="device") for sd in range(6)])
+    ref = np.array([ctx.determine_mi_threshold(4000, iterations=10, seed=sd) for sd in range(6)])
+    assert abs(thr.mean() - exact) <= 3 * max(ref.std(), 1e-4) + abs(ref.mean() - exact)
+    assert len(set(thr.tolist())) > 1                             # the seed matters
+    # small alignment: pairs / 10 samples, all distinct by construction even when that is a large share of all pairs
+    s2, _, _ = generate_alignment(60, 40, seed=3)
+    ctx.set_alignment(s2)
+    t2 = ctx.determine_mi_threshold(100, iterations=5, seed=9, sampler="device")
+    f2 = np.sort(orc.mi_scan(s2, np.ones(60), threshold=-1.0)["edges"]["mi"])
+    assert f2[0] <= t2 <= f2[-1]
 
 
 # ---------------------------------------------------------------- sort + K3

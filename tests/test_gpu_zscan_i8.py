@@ -138,6 +138,71 @@ def test_scan_i8_vs_oracle(ctx, n, L, linear, ld, engine):
     assert_edges_match(e_got, e_exp, rtol=1e-10, atol=1e-13)       # what the fp64 refine actually gives
     assert np.allclose(got["colmax"], exp["colmax"], rtol=1e-10, atol=1e-13)
     assert got["max_filter_error"] < (5e-5 if engine == 3 else 2e-3)
+    # MI without gaps (K2c, the literal two-pass quirk of mi.hpp:108-135,465-489): same pairs, same values
+    wo_exp = {(int(a), int(b)): m for a, b, m in exp["edges_wo_gaps"]}
+    wo_got = {(int(a), int(b)): m for a, b, m in got["edges_wo_gaps"]}
+    assert wo_exp.keys() == wo_got.keys() and (len(wo_exp) > 0 or L == 64)
+    for k_ in wo_exp:
+        assert wo_got[k_] == pytest.approx(wo_exp[k_], rel=1e-10, abs=1e-13)
+    # the audit ran (when the alignment is large enough for a seed pass) and found nothing the filter would have lost
+    assert got["audit_violations"] == 0 and got["audit_max_error"] <= 0.5 * got["band"]
+
+
+def test_overflow_rescans_instead_of_failing(ctx):
+    """a capacity hint that is far too small: the scan grows its buffers and repeats itself (the reference stores any number
+    of edges), same result as with ample buffers."""
+    s, pos, _ = generate_alignment(150, 3000, seed=21)
+    ctx.set_alignment(s, pos)
+    ctx.set_weights(orc.weights_from_counts(orc.neighbour_counts(s, int(0.9 * 3000))))
+    big = ctx.mi_scan(0.01, max_edges=3000 * 3000 // 2)
+    c2 = Context()
+    try:
+        c2.set_alignment(s, pos)
+        c2.set_weights(orc.weights_from_counts(orc.neighbour_counts(s, int(0.9 * 3000))))
+        small = c2.mi_scan(0.01, max_edges=1000)
+    finally:
+        c2.close()
+    assert small["n_edges"] == big["n_edges"] > 100000
+    assert small["edges"].tobytes() == big["edges"].tobytes()
+    assert np.array_equal(np.sort(small["edges_wo_gaps"], order=("i", "j")), np.sort(big["edges_wo_gaps"], order=("i", "j")))
+
+
+@pytest.mark.parametrize("engine", [3, 4])
+def test_filter_audit_many_valued_weights(ctx, engine):
+    """--sample-weights style input: a wide, many-valued weight vector (no two samples share a weight, three decades of range)
+    through the tensor-core filter. The per-scan audit refines an unbiased sample of pairs on both sides of the candidate
+    cut-off; no pair above the threshold may have been invisible to the filter, and the result equals the exhaustive engine."""
+    n, L = 400, 9000
+    s, pos, _ = generate_alignment(n, L, seed=55)
+    rng = np.random.default_rng(8)
+    w = np.exp(rng.uniform(np.log(1e-3), np.log(3.0), size=n))
+    ctx.set_alignment(s, pos); ctx.set_weights(w)
+    thr = 0.08
+    got = ctx.mi_scan(thr, engine=engine, max_edges=L * L // 8)
+    assert got["audit_pairs"] >= 1000, got["audit_pairs"]
+    assert got["audit_violations"] == 0
+    assert got["audit_max_error"] <= 0.5 * got["band"]
+    exact = ctx.mi_scan(thr, engine=1, max_edges=L * L // 8)
+    assert got["n_edges"] == exact["n_edges"] > 1000
+    assert got["edges"].tobytes() == exact["edges"].tobytes()
+    assert np.array_equal(got["colmax"], exact["colmax"])
+
+
+def test_filter_audit_catches_a_band_that_is_too_narrow(ctx):
+    """a band far below the filter's actual error: the audit (or the candidate error check) must refuse the result instead of
+    silently dropping edges; with the band left to the library the same scan succeeds (widening until the audit is clean)."""
+    from spydrpick_b200.capi import SpkError, SPK_E_PRECISION
+    n, L = 300, 8000
+    s, pos, _ = generate_alignment(n, L, seed=56)
+    rng = np.random.default_rng(9)
+    w = np.exp(rng.uniform(np.log(1e-3), np.log(3.0), size=n))
+    ctx.set_alignment(s, pos); ctx.set_weights(w)
+    with pytest.raises(SpkError) as ei:
+        ctx.mi_scan(0.08, engine=4, band=1e-8, max_edges=L * L // 8)
+    assert ei.value.code == SPK_E_PRECISION
+    ok = ctx.mi_scan(0.08, engine=4, max_edges=L * L // 8)
+    exact = ctx.mi_scan(0.08, engine=1, max_edges=L * L // 8)
+    assert ok["edges"].tobytes() == exact["edges"].tobytes()
 
 
 @pytest.mark.parametrize("engine", [3, 4])
