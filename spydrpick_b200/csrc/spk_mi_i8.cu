@@ -1150,12 +1150,14 @@ int mi_i8_filter(Ctx* c, const spk_scan_params& p, double band, uint64_t circle,
         i8_fill_u32_kernel<<<(c->i8.Lperm + 255) / 256, 256, 0, c->stream>>>(c->d_i8_colmax32, f32_ordered(-INFINITY), c->i8.Lperm);
         c->tm.kernel_launches += 1;
         c->i8_seed_valid = false;
-        if (i8_use_seed() && total_chunks >= 64ull * I8_SEED_STRIDE) {
+        // small problems: a denser sample (down to every chunk) so that the audit still sees a meaningful number of pairs
+        const uint32_t stride = (uint32_t)std::max<unsigned long long>(1, std::min<unsigned long long>(I8_SEED_STRIDE, total_chunks / 64));
+        if (i8_use_seed() && total_chunks >= 1) {
             std::vector<unsigned long long> seed;
             unsigned long long k = 0;
             for (uint32_t sr = 0; sr < n_sr; ++sr)
                 for (unsigned long long q = prefix[sr]; q < prefix[sr + 1]; ++q)
-                    if ((uint32_t)(q - prefix[sr]) % I8_SEED_STRIDE == sr % I8_SEED_STRIDE) {
+                    if ((uint32_t)(q - prefix[sr]) % stride == sr % stride) {
                         if (!collective || k % (unsigned long long)c->world == (unsigned long long)c->rank) seed.push_back(q);
                         ++k;
                     }

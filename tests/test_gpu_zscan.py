@@ -81,7 +81,7 @@ def test_scan_tcgen05_vs_oracle(ctx, n, L, linear, ld, T):
     s, pos, _ = generate_alignment(n, L, seed=n + L)
     w = orc.weights_from_counts(orc.neighbour_counts(s, int(0.9 * L)))
     ctx.set_alignment(s, pos); ctx.set_weights(w)
-    thr = 0.05
+    thr = 0.05 if L > 64 else 0.01
     exp = orc.mi_scan(s, w, pos, threshold=thr, ld_threshold=ld, linear_genome=linear, circle_size=L)
     got = ctx.mi_scan(thr, ld_threshold=ld, linear_genome=linear, n_terms=T, engine=2, sort_desc=True)
     e_exp = orc.sort_edges(exp["edges"]); e_got = got["edges"]

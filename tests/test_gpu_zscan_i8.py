@@ -128,7 +128,7 @@ def test_scan_i8_vs_oracle(ctx, n, L, linear, ld, engine):
     s, pos, _ = generate_alignment(n, L, seed=n + L)
     w = orc.weights_from_counts(orc.neighbour_counts(s, int(0.9 * L)))
     ctx.set_alignment(s, pos); ctx.set_weights(w)
-    thr = 0.05
+    thr = 0.05 if L > 64 else 0.01
     exp = orc.mi_scan(s, w, pos, threshold=thr, ld_threshold=ld, linear_genome=linear, circle_size=L)
     got = ctx.mi_scan(thr, ld_threshold=ld, linear_genome=linear, engine=engine, sort_desc=True, max_edges=L * L // 2)
     e_exp = orc.sort_edges(exp["edges"]); e_got = got["edges"]
