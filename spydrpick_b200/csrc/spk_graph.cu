@@ -44,6 +44,10 @@ __global__ void gather_edges_kernel(const spk_edge* __restrict__ src, const uint
 }
 
 static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+__global__ void widen_u32_kernel(const unsigned int* __restrict__ in, unsigned long long* __restrict__ out, uint32_t n) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < n) out[k] = in[k];
+}
 
 int sort_edges_device(Ctx* c, spk_edge* d_edges, uint64_t n) {
     if (n < 2) return SPK_OK;
@@ -136,19 +140,22 @@ int merge_sorted_runs_device(Ctx* c, spk_edge* d_edges, const uint64_t* run_coun
     return SPK_OK;
 }
 
-// ---- CSR build --------------------------------------------------------------------------------
-// One adjacency structure over the 2E directed entries (entry 2r / 2r+1 = edge r seen from i / from j), per node
-// sorted by neighbour id: idst[] neighbour, ival[] weight, ieid[] edge index; offsets[] per node.
-__global__ void directed_entries_kernel(const spk_edge* __restrict__ e, unsigned long long n, uint32_t bits,
-                                        unsigned long long* __restrict__ keys, uint32_t* __restrict__ ents,
-                                        uint32_t* __restrict__ wkeys) {
+// ---- adjacency build --------------------------------------------------------------------------------
+// Over the 2E directed entries (entry 2r / 2r+1 = edge r seen from i / from j):
+//   offsets[]            per node, from a degree histogram + exclusive scan;
+//   wdst[], wval[], weid[]  per node its neighbours in WEIGHT-DESCENDING order (the input is Graph::sort order, so ONE stable
+//                        radix sort of the entries by source node -- ceil(log2 nodes) key bits -- keeps every list ordered);
+//   hkey[], hval[]       per node an open-addressing hash table neighbour -> weight in the slot range [2*offsets[u], 2*offsets[u+1])
+//                        (load factor 1/2), which replaces the id-ordered lists + binary searches of the first version (a second,
+//                        2*ceil(log2 nodes)-bit sort and deg*log(deg) divergent loads per edge).
+__global__ void directed_src_kernel(const spk_edge* __restrict__ e, unsigned long long n, uint32_t* __restrict__ wkeys, uint32_t* __restrict__ ents,
+                                    unsigned int* __restrict__ degree) {
     const unsigned long long k = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n) return;
     const spk_edge ed = e[k];
-    keys[2 * k] = ((unsigned long long)ed.i << bits) | ed.j;
-    keys[2 * k + 1] = ((unsigned long long)ed.j << bits) | ed.i;
-    ents[2 * k] = (uint32_t)(2 * k); ents[2 * k + 1] = (uint32_t)(2 * k + 1);
     wkeys[2 * k] = ed.i; wkeys[2 * k + 1] = ed.j;
+    ents[2 * k] = (uint32_t)(2 * k); ents[2 * k + 1] = (uint32_t)(2 * k + 1);
+    atomicAdd(&degree[ed.i], 1u); atomicAdd(&degree[ed.j], 1u);
 }
 // out[0] = max node id, out[2] = 1 if the list is not sorted by weight descending
 __global__ void edge_scan_kernel(const spk_edge* __restrict__ e, unsigned long long n, unsigned int* __restrict__ out) {
@@ -181,32 +188,23 @@ __global__ void entry_src_keys_kernel(const spk_edge* __restrict__ e, const uint
     const uint32_t en = ents[q];
     wkeys[q] = (en & 1u) ? e[en >> 1].j : e[en >> 1].i;
 }
-// weight-descending lists (same offsets as the id-ordered ones): neighbour and weight per entry
-__global__ void weight_lists_kernel(const spk_edge* __restrict__ e, const uint32_t* __restrict__ ents, unsigned long long m,
-                                    uint32_t* __restrict__ wdst, double* __restrict__ wval) {
+__device__ __forceinline__ uint32_t nbr_hash(uint32_t z) { z *= 0x9E3779B1u; z ^= z >> 15; return z; }
+// weight-descending lists + the per-node hash tables, from the entries sorted by source node
+__global__ void lists_and_hash_kernel(const spk_edge* __restrict__ e, const uint32_t* __restrict__ ents, const uint32_t* __restrict__ src_sorted,
+                                      unsigned long long m, const unsigned long long* __restrict__ offsets,
+                                      uint32_t* __restrict__ wdst, double* __restrict__ wval,
+                                      uint32_t* __restrict__ hkey, double* __restrict__ hval) {
     const unsigned long long q = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= m) return;
     const uint32_t en = ents[q];
     const spk_edge ed = e[en >> 1];
-    wdst[q] = (en & 1u) ? ed.i : ed.j;
-    wval[q] = ed.mi;
-}
-// offsets[v] = first sorted entry with src >= v, offsets[nn] = 2E; neighbour / weight / edge index per sorted entry
-__global__ void csr_finish_kernel(const unsigned long long* __restrict__ keys, const uint32_t* __restrict__ ents,
-                                  const spk_edge* __restrict__ e, unsigned long long m, uint32_t bits,
-                                  unsigned long long* __restrict__ offsets, uint32_t nn,
-                                  uint32_t* __restrict__ idst, double* __restrict__ ival, uint32_t* __restrict__ ieid) {
-    const unsigned long long k = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (k > m) return;
-    const long long prev = (k == 0) ? -1 : (long long)(keys[k - 1] >> bits);
-    const long long cur = (k == m) ? (long long)nn : (long long)(keys[k] >> bits);
-    for (long long v = prev + 1; v <= cur; ++v) offsets[v] = k;
-    if (k < m) {
-        const uint32_t en = ents[k];
-        idst[k] = (uint32_t)(keys[k] & ((1ull << bits) - 1ull));
-        ival[k] = e[en >> 1].mi;
-        ieid[k] = en >> 1;
-    }
+    const uint32_t dst = (en & 1u) ? ed.i : ed.j, src = src_sorted[q];
+    wdst[q] = dst; wval[q] = ed.mi;
+    const unsigned long long t0 = 2 * offsets[src];
+    const uint32_t cap = (uint32_t)(2 * (offsets[src + 1] - offsets[src]));
+    uint32_t slot = (uint32_t)(((unsigned long long)nbr_hash(dst) * cap) >> 32);
+    while (atomicCAS(&hkey[t0 + slot], 0xffffffffu, dst) != 0xffffffffu) { if (++slot == cap) slot = 0; }
+    hval[t0 + slot] = ed.mi;
 }
 
 // ---- K3 ------------------------------------------------------------------------------------------
@@ -215,24 +213,28 @@ __device__ __forceinline__ bool aracne_hit(double w, double w2, double w3, doubl
     const double minval = fmin(w, fmin(w2, w3));                        // ARACNE.hpp:310
     return (midval - minval >= threshold) && (w == minval);
 }
-// position of `node` in the id-ordered list [b0, b1), or b1
-__device__ __forceinline__ unsigned long long find_neighbour(const uint32_t* __restrict__ idst, unsigned long long b0, unsigned long long b1, uint32_t node) {
-    unsigned long long lo = b0, hi = b1;
-    while (lo < hi) { const unsigned long long mid = (lo + hi) >> 1; if (idst[mid] < node) lo = mid + 1; else hi = mid; }
-    return (lo < b1 && idst[lo] == node) ? lo : b1;
+// weight of edge (u, z) from u's hash table [t0, t0 + cap); z must be a neighbour of u (the caller checked the bitmap)
+__device__ __forceinline__ double nbr_weight(const uint32_t* __restrict__ hkey, const double* __restrict__ hval, unsigned long long t0, uint32_t cap, uint32_t z) {
+    uint32_t slot = (uint32_t)(((unsigned long long)nbr_hash(z) * cap) >> 32);
+    for (uint32_t probes = 0; probes < cap; ++probes) {
+        const uint32_t k = hkey[t0 + slot];
+        if (k == z) return hval[t0 + slot];
+        if (k == 0xffffffffu) break;
+        if (++slot == cap) slot = 0;
+    }
+    return __longlong_as_double(0x7ff8000000000000ll);               // not a neighbour (cannot happen after the bitmap test)
 }
 
-// Main kernel: one block per node u (dynamic queue). u's neighbourhood is a bitmap in shared memory; every edge (u,v)
-// OWNED by u (u = the endpoint with the larger degree) is given to a warp that streams v's list (coalesced) and looks
-// only the members that are also neighbours of u, with both triangle sides >= w, up in u's list. The generic
-// formulation (walk the shorter list, binary-search every member in the longer one: aracne_search_kernel below) does
-// deg x log(deg) divergent loads per edge.
+// One block per node u (dynamic queue). u's neighbourhood is a bitmap in shared memory; every edge (u,v) OWNED by u (the
+// endpoint with the larger degree) is given to a warp that streams v's weight-descending list (coalesced), stops at the first
+// weight < w (no triangle with w as its minimum beyond that) and looks the members that are also neighbours of u up in u's
+// hash table (hot in L1: a few KB per node).
 __global__ void __launch_bounds__(256)
-aracne_bitmap_kernel(unsigned long long e_begin, unsigned long long e_end,
-                     const uint32_t* __restrict__ idst, const double* __restrict__ ival, const uint32_t* __restrict__ ieid,
-                     const uint32_t* __restrict__ wdst, const double* __restrict__ wval,
-                     const unsigned long long* __restrict__ offsets, uint32_t nn, unsigned int* __restrict__ next_node,
-                     double threshold, uint8_t* __restrict__ flags) {
+aracne_hash_kernel(unsigned long long e_begin, unsigned long long e_end,
+                   const uint32_t* __restrict__ wdst, const double* __restrict__ wval, const uint32_t* __restrict__ weid,
+                   const uint32_t* __restrict__ hkey, const double* __restrict__ hval,
+                   const unsigned long long* __restrict__ offsets, uint32_t nn, unsigned int* __restrict__ next_node,
+                   double threshold, uint8_t* __restrict__ flags) {
     extern __shared__ uint32_t bm[];
     __shared__ uint32_t s_u;
     const uint32_t lane = threadIdx.x % 32, wid = threadIdx.x / 32, nw = blockDim.x / 32;
@@ -245,17 +247,16 @@ aracne_bitmap_kernel(unsigned long long e_begin, unsigned long long e_end,
         if (u >= nn) break;
         const unsigned long long a0 = offsets[u], a1 = offsets[u + 1], degu = a1 - a0;
         if (degu == 0) continue;
-        for (unsigned long long k = a0 + threadIdx.x; k < a1; k += blockDim.x) { const uint32_t z = idst[k]; atomicOr(&bm[z >> 5], 1u << (z & 31u)); }
+        for (unsigned long long k = a0 + threadIdx.x; k < a1; k += blockDim.x) { const uint32_t z = wdst[k]; atomicOr(&bm[z >> 5], 1u << (z & 31u)); }
         __syncthreads();
+        const unsigned long long t0 = 2 * a0; const uint32_t cap = (uint32_t)(2 * degu);
         for (unsigned long long k = a0 + wid; k < a1; k += nw) {
-            const uint32_t v = idst[k];
-            const unsigned long long e = ieid[k];
+            const uint32_t v = wdst[k];
+            const unsigned long long e = weid[k] >> 1;
             if (e < e_begin || e >= e_end) continue;
             const unsigned long long b0 = offsets[v], b1 = offsets[v + 1], degv = b1 - b0;
             if (degv > degu || (degv == degu && v > u)) continue;             // the other endpoint owns this edge
-            const double w = ival[k];
-            // v's neighbours by weight descending: only the prefix with w_vz >= w can close a triangle in which w is the
-            // minimum, and strong sides (the likely witnesses) come first
+            const double w = wval[k];
             bool indirect = false, done = false;
             for (unsigned long long base = b0; base < b1 && !done; base += 32) {
                 const unsigned long long q = base + lane;
@@ -265,10 +266,7 @@ aracne_bitmap_kernel(unsigned long long e_begin, unsigned long long e_end,
                     below = w2 < w;
                     if (!below) {
                         const uint32_t z = wdst[q];
-                        if ((bm[z >> 5] >> (z & 31u)) & 1u) {
-                            const unsigned long long pz = find_neighbour(idst, a0, a1, z);
-                            if (pz < a1) hit = aracne_hit(w, w2, ival[pz], threshold);
-                        }
+                        if ((bm[z >> 5] >> (z & 31u)) & 1u) hit = aracne_hit(w, w2, nbr_weight(hkey, hval, t0, cap, z), threshold);
                     }
                 }
                 indirect = __any_sync(0xffffffffu, hit);
@@ -277,14 +275,16 @@ aracne_bitmap_kernel(unsigned long long e_begin, unsigned long long e_end,
             if (lane == 0) flags[e] = indirect ? 0 : 1;    // 1 = direct ("Booleans swapped", ARACNE.hpp:399-405)
         }
         __syncthreads();
-        for (unsigned long long k = a0 + threadIdx.x; k < a1; k += blockDim.x) { const uint32_t z = idst[k]; bm[z >> 5] = 0u; }
+        for (unsigned long long k = a0 + threadIdx.x; k < a1; k += blockDim.x) { const uint32_t z = wdst[k]; bm[z >> 5] = 0u; }
     }
 }
 
-// Fallback for graphs on more nodes than a shared-memory bitmap holds: warp per edge, walk the shorter list.
+// Fallback for graphs on more nodes than a shared-memory bitmap holds: warp per edge, walk the list of the lower-degree
+// endpoint, look every member with weight >= w up in the other endpoint's hash table.
 __global__ void __launch_bounds__(256)
 aracne_search_kernel(const spk_edge* __restrict__ edges, unsigned long long e_begin, unsigned long long e_end,
-                     const uint32_t* __restrict__ idst, const double* __restrict__ ival,
+                     const uint32_t* __restrict__ wdst, const double* __restrict__ wval,
+                     const uint32_t* __restrict__ hkey, const double* __restrict__ hval,
                      const unsigned long long* __restrict__ offsets, double threshold, uint8_t* __restrict__ flags) {
     const uint32_t lane = threadIdx.x % 32;
     const unsigned long long warp = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) / 32;
@@ -292,21 +292,21 @@ aracne_search_kernel(const spk_edge* __restrict__ edges, unsigned long long e_be
     for (unsigned long long e = e_begin + warp; e < e_end; e += nwarps) {
         const spk_edge ed = edges[e];
         const double w = ed.mi;
-        unsigned long long a0 = offsets[ed.i], a1 = offsets[ed.i + 1];
-        unsigned long long b0 = offsets[ed.j], b1 = offsets[ed.j + 1];
-        if (a1 - a0 > b1 - b0) { unsigned long long t; t = a0; a0 = b0; b0 = t; t = a1; a1 = b1; b1 = t; }   // A = shorter list
-        bool indirect = false;
-        for (unsigned long long base = a0; base < a1 && !indirect; base += 32) {
-            const unsigned long long k = base + lane;
-            bool hit = false;
-            if (k < a1) {
-                const double w2 = ival[k];
-                if (w2 >= w) {
-                    const unsigned long long pz = find_neighbour(idst, b0, b1, idst[k]);
-                    if (pz < b1) hit = aracne_hit(w, w2, ival[pz], threshold);
-                }
+        uint32_t u = ed.i, v = ed.j;
+        if (offsets[u + 1] - offsets[u] < offsets[v + 1] - offsets[v]) { const uint32_t t = u; u = v; v = t; }      // v = shorter list
+        const unsigned long long b0 = offsets[v], b1 = offsets[v + 1];
+        const unsigned long long t0 = 2 * offsets[u]; const uint32_t cap = (uint32_t)(2 * (offsets[u + 1] - offsets[u]));
+        bool indirect = false, done = false;
+        for (unsigned long long base = b0; base < b1 && !done; base += 32) {
+            const unsigned long long q = base + lane;
+            bool hit = false, below = false;
+            if (q < b1) {
+                const double w2 = wval[q];
+                below = w2 < w;
+                if (!below) { const double w3 = nbr_weight(hkey, hval, t0, cap, wdst[q]); if (w3 == w3) hit = aracne_hit(w, w2, w3, threshold); }
             }
             indirect = __any_sync(0xffffffffu, hit);
+            done = indirect || __any_sync(0xffffffffu, below);
         }
         if (lane == 0) flags[e] = indirect ? 0 : 1;
     }
@@ -314,41 +314,22 @@ aracne_search_kernel(const spk_edge* __restrict__ edges, unsigned long long e_be
 
 int aracne_device(Ctx* c, const spk_edge* d_edges, uint64_t n, double eps, uint32_t part, uint32_t nparts, uint8_t* d_flags) {
     if (n == 0) return SPK_OK;
-    if (n > 0x7fffffffull) return fail(c, SPK_E_INVALID, "ARACNE supports < 2^31 edges");
+    if (n > 0x3fffffffull) return fail(c, SPK_E_INVALID, "ARACNE supports < 2^30 edges");
     const unsigned long long m = 2 * n;
-    size_t tmpb = 0, tmpb2 = 0;
+    size_t tmpb = 0, tmpb2 = 0, tmpb3 = 0;
     cub::DeviceRadixSort::SortPairs(nullptr, tmpb, (unsigned long long*)nullptr, (unsigned long long*)nullptr,
                                     (uint32_t*)nullptr, (uint32_t*)nullptr, (int)m, 0, 64, c->stream);
     cub::DeviceRadixSort::SortPairs(nullptr, tmpb2, (uint32_t*)nullptr, (uint32_t*)nullptr,
                                     (uint32_t*)nullptr, (uint32_t*)nullptr, (int)m, 0, 32, c->stream);
     if (tmpb2 > tmpb) tmpb = tmpb2;
-    const size_t kb = align256(m * 8), hb = align256(m * 4);
-    uint8_t* base = (uint8_t*)scratch(c, 4 * kb + 9 * hb + align256(tmpb) + 256);
-    if (!base) return fail(c, SPK_E_NOMEM, "scratch allocation failed (aracne)");
-    unsigned long long* k0 = (unsigned long long*)base;                 // sort keys in, later offsets
-    unsigned long long* k1 = (unsigned long long*)(base + kb);          // sort keys out
-    double* ival = (double*)(base + 2 * kb);
-    double* wval = (double*)(base + 3 * kb);
-    uint8_t* hbase = base + 4 * kb;
-    uint32_t* e0buf = (uint32_t*)(hbase);
-    uint32_t* e1buf = (uint32_t*)(hbase + hb);
-    uint32_t* idst = (uint32_t*)(hbase + 2 * hb);
-    uint32_t* ieid = (uint32_t*)(hbase + 3 * hb);
-    uint32_t* wk0 = (uint32_t*)(hbase + 4 * hb);
-    uint32_t* wk1 = (uint32_t*)(hbase + 5 * hb);
-    uint32_t* we0 = (uint32_t*)(hbase + 6 * hb);
-    uint32_t* we1 = (uint32_t*)(hbase + 7 * hb);
-    uint32_t* wdst = (uint32_t*)(hbase + 8 * hb);
-    void* tmp = hbase + 9 * hb;
-    unsigned int* d_scan = (unsigned int*)(hbase + 9 * hb + align256(tmpb));   // [0] max node id, [1] node queue, [2] unsorted flag
     const unsigned ge = (unsigned)((n + 255) / 256), gm = (unsigned)((m + 255) / 256);
     SPK_CUDA(c, cudaEventRecord(c->ev[EV_AR0], c->stream));
     // node count is unknown for caller-supplied edge lists: found on the device first (one small sync). The last scan's own
     // sorted list needs neither (node ids < L, order known) -- and must not: the 16-byte read-back would queue on the D2H
     // copy engine behind the asynchronous download of that very list (measured: CSR build 3.0 -> 5.7 ms).
-    SPK_CUDA(c, cudaMemsetAsync(d_scan, 0, 16, c->stream));
     unsigned int h_scan[4] = {0, 0, 0, 0};
-    if ((d_edges == c->d_edges || d_edges == c->d_edges_view) && c->d_edges_sorted_n == n && c->d_states) {
+    const bool own = (d_edges == c->d_edges || d_edges == c->d_edges_view) && c->d_edges_sorted_n == n && c->d_states;
+    if (own) {
         h_scan[0] = c->L - 1;
     } else {
         // caller-supplied list: the 16 bytes come back through a mapped page-locked mailbox written by a kernel, not through
@@ -360,56 +341,77 @@ int aracne_device(Ctx* c, const spk_edge* d_edges, uint64_t n, double eps, uint3
                 return fail(c, SPK_E_NOMEM, "mapped mailbox allocation failed");
             }
         }
-        edge_scan_kernel<<<ge, 256, 0, c->stream>>>(d_edges, n, d_scan);
-        publish_words_kernel<<<1, 32, 0, c->stream>>>(d_scan, c->d_mail, 4);
+        unsigned int* d_pre = (unsigned int*)scratch(c, 256);
+        if (!d_pre) return fail(c, SPK_E_NOMEM, "scratch allocation failed (aracne)");
+        SPK_CUDA(c, cudaMemsetAsync(d_pre, 0, 16, c->stream));
+        edge_scan_kernel<<<ge, 256, 0, c->stream>>>(d_edges, n, d_pre);
+        publish_words_kernel<<<1, 32, 0, c->stream>>>(d_pre, c->d_mail, 4);
         SPK_CUDA(c, cudaStreamSynchronize(c->stream));
         for (int k = 0; k < 4; ++k) h_scan[k] = ((volatile unsigned int*)c->h_mail)[k];
     }
     const uint32_t nn = h_scan[0] + 1;
     uint32_t bits = 1; while (bits < 32 && (1ull << bits) < (unsigned long long)nn) ++bits;
-    directed_entries_kernel<<<ge, 256, 0, c->stream>>>(d_edges, n, bits, k0, e0buf, wk0);
-    SPK_CUDA(c, cub::DeviceRadixSort::SortPairs(tmp, tmpb, k0, k1, e0buf, e1buf, (int)m, 0, (int)(2 * bits), c->stream));   // (src, dst) ascending
+    cub::DeviceScan::ExclusiveSum(nullptr, tmpb3, (unsigned long long*)nullptr, (unsigned long long*)nullptr, (int)(nn + 1), c->stream);
+    if (tmpb3 > tmpb) tmpb = tmpb3;
+    const size_t kb = align256(m * 8), hb = align256(m * 4), ob = align256((size_t)(nn + 2) * 8);
+    // layout: [wval kb][hval 2kb][k64 tmp keys 2kb, only for unsorted input][wk0 wk1 we0 we1 wdst : 5hb][hkey 2hb][deg64 ob][offsets ob][degree ob][tmp][scan words]
+    const size_t k64b = h_scan[2] ? 2 * kb : 0;
+    uint8_t* base = (uint8_t*)scratch(c, 3 * kb + k64b + 7 * hb + 3 * ob + align256(tmpb) + 256);
+    if (!base) return fail(c, SPK_E_NOMEM, "scratch allocation failed (aracne)");
+    double* wval = (double*)base;
+    double* hval = (double*)(base + kb);
+    unsigned long long* k64a = (unsigned long long*)(base + 3 * kb);
+    unsigned long long* k64b_ = (unsigned long long*)(base + 3 * kb + kb);
+    uint8_t* hbase = base + 3 * kb + k64b;
+    uint32_t* wk0 = (uint32_t*)(hbase);
+    uint32_t* wk1 = (uint32_t*)(hbase + hb);
+    uint32_t* we0 = (uint32_t*)(hbase + 2 * hb);
+    uint32_t* we1 = (uint32_t*)(hbase + 3 * hb);
+    uint32_t* wdst = (uint32_t*)(hbase + 4 * hb);
+    uint32_t* hkey = (uint32_t*)(hbase + 5 * hb);
+    unsigned long long* deg64 = (unsigned long long*)(hbase + 7 * hb);
+    unsigned long long* offsets = (unsigned long long*)(hbase + 7 * hb + ob);
+    unsigned int* degree = (unsigned int*)(hbase + 7 * hb + 2 * ob);     // u32 histogram (its own region: a sparse graph has more nodes than entries)
+    void* tmp = hbase + 7 * hb + 3 * ob;
+    unsigned int* d_scan = (unsigned int*)(hbase + 7 * hb + 3 * ob + align256(tmpb));   // [1] node queue
+    SPK_CUDA(c, cudaMemsetAsync(d_scan, 0, 16, c->stream));
+    SPK_CUDA(c, cudaMemsetAsync(degree, 0, (size_t)(nn + 1) * 4, c->stream));
+    SPK_CUDA(c, cudaMemsetAsync(hkey, 0xff, (size_t)m * 2 * 4, c->stream));
+    directed_src_kernel<<<ge, 256, 0, c->stream>>>(d_edges, n, wk0, we0, degree);
+    // degrees -> u64 -> exclusive scan (offsets[nn] = 2E)
+    widen_u32_kernel<<<(nn + 1 + 255) / 256, 256, 0, c->stream>>>(degree, deg64, nn + 1);
+    SPK_CUDA(c, cub::DeviceScan::ExclusiveSum(tmp, tmpb, deg64, offsets, (int)(nn + 1), c->stream));
     // weight-descending lists: the input is sorted by weight (Graph::sort), so a STABLE sort of the entries by source node
     // alone keeps them in weight order inside every list; an unsorted caller-supplied list is ordered by weight first
-    uint32_t* went_in = e0buf;                                           // identity entry order (still intact: sort input)
+    uint32_t* went_in = we0;
     if (h_scan[2]) {
-        entry_weight_keys_kernel<<<gm, 256, 0, c->stream>>>(d_edges, m, k0, we1);
-        SPK_CUDA(c, cub::DeviceRadixSort::SortPairs(tmp, tmpb, k0, (unsigned long long*)wval, we1, we0, (int)m, 0, 64, c->stream));
+        entry_weight_keys_kernel<<<gm, 256, 0, c->stream>>>(d_edges, m, k64a, we1);
+        SPK_CUDA(c, cub::DeviceRadixSort::SortPairs(tmp, tmpb, k64a, k64b_, we1, we0, (int)m, 0, 64, c->stream));
         entry_src_keys_kernel<<<gm, 256, 0, c->stream>>>(d_edges, we0, m, wk0);
-        went_in = we0;
         c->tm.kernel_launches += 2 + 8;
     }
     SPK_CUDA(c, cub::DeviceRadixSort::SortPairs(tmp, tmpb, wk0, wk1, went_in, we1, (int)m, 0, (int)bits, c->stream));    // stable by src
-    // offsets live in the (now free) k0 buffer when they fit
-    unsigned long long* offsets = k0;
-    unsigned long long* offsets_tmp = nullptr;
-    if ((size_t)(nn + 2) * 8 > kb) {          // sparse graph on many nodes: offsets do not fit the recycled key buffer
-        if (cudaMalloc(&offsets_tmp, (size_t)(nn + 2) * 8) != cudaSuccess) return fail(c, SPK_E_NOMEM, "offset table allocation failed");
-        offsets = offsets_tmp;
-    }
-    csr_finish_kernel<<<(unsigned)((m + 1 + 255) / 256), 256, 0, c->stream>>>(k1, e1buf, d_edges, m, bits, offsets, nn, idst, ival, ieid);
-    weight_lists_kernel<<<gm, 256, 0, c->stream>>>(d_edges, we1, m, wdst, wval);
+    lists_and_hash_kernel<<<gm, 256, 0, c->stream>>>(d_edges, we1, wk1, m, offsets, wdst, wval, hkey, hval);
     SPK_CUDA(c, cudaEventRecord(c->ev[EV_AR1], c->stream));
     if (nparts == 0) nparts = 1;
     const unsigned long long e0 = (unsigned long long)n * part / nparts, e1 = (unsigned long long)n * (part + 1) / nparts;
     const size_t bm_bytes = (size_t)((nn + 31) / 32) * 4;
     if (bm_bytes <= 160 * 1024) {
-        if (bm_bytes > 48 * 1024) SPK_CUDA(c, cudaFuncSetAttribute(aracne_bitmap_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bm_bytes));
+        if (bm_bytes > 48 * 1024) SPK_CUDA(c, cudaFuncSetAttribute(aracne_hash_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bm_bytes));
         const unsigned per_sm = (unsigned)std::max<size_t>(1, std::min<size_t>(8, (200 * 1024) / (bm_bytes + 1024)));
         unsigned long long blocks = (unsigned long long)c->sm_count * per_sm;
         if (blocks > nn) blocks = nn;
-        aracne_bitmap_kernel<<<(unsigned)blocks, 256, bm_bytes, c->stream>>>(e0, e1, idst, ival, ieid, wdst, wval, offsets, nn, d_scan + 1, eps, d_flags);
+        aracne_hash_kernel<<<(unsigned)blocks, 256, bm_bytes, c->stream>>>(e0, e1, wdst, wval, we1, hkey, hval, offsets, nn, d_scan + 1, eps, d_flags);
     } else {
         unsigned long long blocks = (e1 - e0 + 7) / 8;
         const unsigned long long cap = (unsigned long long)c->sm_count * 32;
         if (blocks > cap) blocks = cap;
         if (blocks == 0) blocks = 1;
-        aracne_search_kernel<<<(unsigned)blocks, 256, 0, c->stream>>>(d_edges, e0, e1, idst, ival, offsets, eps, d_flags);
+        aracne_search_kernel<<<(unsigned)blocks, 256, 0, c->stream>>>(d_edges, e0, e1, wdst, wval, hkey, hval, offsets, eps, d_flags);
     }
-    c->tm.kernel_launches += 5 + (2 * bits + 7) / 8 + (bits + 7) / 8;
+    c->tm.kernel_launches += 6 + (bits + 7) / 8;
     SPK_CUDA(c, cudaEventRecord(c->ev[EV_AR2], c->stream));
     c->tm_pending |= TMP_ARB | TMP_AR;
-    if (offsets_tmp) { SPK_CUDA(c, cudaStreamSynchronize(c->stream)); cudaFree(offsets_tmp); }
     SPK_CUDA(c, cudaGetLastError());
     return SPK_OK;
 }

@@ -584,8 +584,15 @@ mi_refine_class_kernel(const uint8_t* __restrict__ masks, const Candidate* __res
 // transposing butterfly (G-1 exchanges per cell instead of G log G) that leaves lane t of the group with the complete
 // table of ITS pair, and the entropy tail runs thread-per-pair as before. G = min(8, 32 / (KI*KJ)) bounds the
 // partial tables at 32 doubles per thread.
+#ifndef SPK_REFINE_UNROLL
+#define SPK_REFINE_UNROLL 1           // plane-walk iterations in flight per thread (A/B: tools/build_variant.sh)
+#endif
+constexpr int REFINE_UNROLL = SPK_REFINE_UNROLL;
+#ifndef SPK_REFINE_MINBLOCKS
+#define SPK_REFINE_MINBLOCKS 1
+#endif
 template <int KI, int KJ, int G>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, SPK_REFINE_MINBLOCKS)
 mi_refine_coop_kernel(const uint8_t* __restrict__ masks, const Candidate* __restrict__ cand, unsigned long long ncand,
                       double pc, double w_total, double wo_threshold,
                       spk_edge* __restrict__ refined, double* __restrict__ refined_wo, unsigned long long* __restrict__ counters,
@@ -623,6 +630,7 @@ mi_refine_coop_kernel(const uint8_t* __restrict__ masks, const Candidate* __rest
         double acc[C];
 #pragma unroll
         for (int q = 0; q < C; ++q) acc[q] = 0.0;
+#pragma unroll (REFINE_UNROLL)
         for (uint32_t w4 = sub; w4 < nchunk; w4 += G) {
             const double2 v01 = gv2[2 * w4], v23 = gv2[2 * w4 + 1];
             uint4 xi[KI], xj[KJ];
@@ -744,6 +752,8 @@ mi_refine_kernel(const uint8_t* __restrict__ colmajor, const double* __restrict_
 //   counters[9]  = number of audited pairs with mi64 > thr whose mi32 was NOT above the candidate cut-off (false negatives)
 //   counters[10] = pairs audited
 // n is read on the device (no host round trip); one thread per pair on the grouped planes, one warp per pair on bytes.
+constexpr unsigned long long AUDIT_TARGET = 300000;     // buffer entries visited per scan and rank (about half of them are unused slots of the
+                                                        // emission chunks: >= 1e5 pairs recomputed when the sample is that large)
 __global__ void __launch_bounds__(128)
 mi_audit_thread_kernel(const uint8_t* __restrict__ masks, const Candidate* __restrict__ cand, const unsigned long long* __restrict__ d_n,
                        unsigned long long cap, double pc, double w_total, double threshold, float cand_lo,
@@ -751,8 +761,12 @@ mi_audit_thread_kernel(const uint8_t* __restrict__ masks, const Candidate* __res
                        const uint32_t* __restrict__ gbits, const double* __restrict__ gval, const double* __restrict__ gmarg,
                        const double* __restrict__ gH, uint32_t NW) {
     const unsigned long long n = min(*d_n, cap);
+    // at most ~AUDIT_TARGET pairs are recomputed: every stride-th entry of the emission order (unbiased: entries land in the
+    // buffer in the order the tiles finish)
+    const unsigned long long stride = (n + AUDIT_TARGET - 1) / AUDIT_TARGET;
     double err = 0.0; unsigned int bad = 0, cnt = 0;
-    for (unsigned long long p = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += (unsigned long long)gridDim.x * blockDim.x) {
+    for (unsigned long long q = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; q * stride < n; q += (unsigned long long)gridDim.x * blockDim.x) {
+        const unsigned long long p = q * stride;
         const Candidate cd = cand[p];
         if (cd.i == I8_INVALID) continue;
         double m = 0.0, m2 = 0.0;
@@ -780,8 +794,10 @@ mi_audit_warp_kernel(const uint8_t* __restrict__ colmajor, const double* __restr
     const uint32_t lane = threadIdx.x % 32, wid = threadIdx.x / 32;
     double* bins = bins_all[wid];
     const unsigned long long n = min(*d_n, cap);
+    const unsigned long long stride = (n + AUDIT_TARGET - 1) / AUDIT_TARGET;
     double err = 0.0; unsigned long long bad = 0, cnt = 0;
-    for (unsigned long long p = (unsigned long long)blockIdx.x * EX_WARPS + wid; p < n; p += (unsigned long long)gridDim.x * EX_WARPS) {
+    for (unsigned long long q = (unsigned long long)blockIdx.x * EX_WARPS + wid; q * stride < n; q += (unsigned long long)gridDim.x * EX_WARPS) {
+        const unsigned long long p = q * stride;
         const Candidate cd = cand[p];
         if (cd.i == I8_INVALID) continue;
         double v = warp_crosstab(colmajor + (size_t)cd.i * n_pad, colmajor + (size_t)cd.j * n_pad, w, n_pad, bins, lane);
