@@ -265,6 +265,10 @@ int spk_debug_tile_counts(spk_ctx* ctx, uint32_t iblock32, uint32_t jblock64, in
  * weight per quantisation step. perm / info / q / delta may be NULL. */
 /* weight rows of the default int8 engine: 2 = engine 3 ({hi, lo} bytes), 1 = engine 4 (factorised weights) */
 int spk_debug_i8_mode(void);
+/* Measured peak of the tensor instruction the int8 filter issues (tcgen05.mma.cta_group::2.kind::i8 M256 N256 K32 on operands already in
+ * shared memory, one CTA pair per TPC, no loads, no epilogue): `reps` launches of `kblocks` 128-byte K blocks each, back to back.
+ * *tops = u8 tensor ops per second (1e12) over the interval, *ms = its device time. bench.py's roofline denominator. */
+int spk_debug_i8_peak(spk_ctx* ctx, uint32_t kblocks, uint32_t reps, double* tops, float* ms);
 int spk_debug_i8_layout(spk_ctx* ctx, uint32_t* ntiles3, uint32_t* col_start3, uint32_t* perm, uint32_t* info,
                         uint64_t perm_cap, uint32_t* q /* [n] */, double* delta);
 /* Raw s32 joint counts (quantised-weight units) of the tile pair (ti <= tj) as produced by the kind::i8

@@ -21,7 +21,7 @@ EXPORTS = ["spk_create", "spk_destroy", "spk_last_error", "spk_set_stream", "spk
            "spk_neighbour_counts", "spk_neighbour_counts_part", "spk_reweight", "spk_set_weights", "spk_mi_pairs", "spk_determine_mi_threshold",
            "spk_determine_mi_threshold_ex", "spk_comm_init_all", "spk_comm_unique_id", "spk_comm_init_rank", "spk_comm_rank",
            "spk_mi_scan", "spk_outlier_thresholds", "spk_sort_edges", "spk_aracne", "spk_sort_edges_device",
-           "spk_aracne_device", "spk_merge_sorted_runs_device", "spk_wait_download", "spk_get_timings", "spk_debug_tile_counts", "spk_debug_i8_mode", "spk_debug_i8_layout", "spk_debug_i8_tile",
+           "spk_aracne_device", "spk_merge_sorted_runs_device", "spk_wait_download", "spk_get_timings", "spk_debug_tile_counts", "spk_debug_i8_mode", "spk_debug_i8_peak", "spk_debug_i8_layout", "spk_debug_i8_tile",
            "spk_version"]
 
 
@@ -107,6 +107,7 @@ def load():
     L.spk_host_free.argtypes = [C.c_void_p]
     L.spk_debug_i8_layout.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p,
                                       C.POINTER(C.c_double)]
+    L.spk_debug_i8_peak.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(C.c_double), C.POINTER(C.c_float)]
     L.spk_debug_i8_tile.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p]
     _lib = L
     return L
@@ -359,6 +360,12 @@ class Context:
         out = np.zeros((32, 64, 4, 4), dtype=np.float32)
         self._check(self.lib.spk_debug_tile_counts(self.h, ib, jb, n_terms, _ptr(out)))
         return out
+
+    def debug_i8_peak(self, kblocks=100000, reps=1):
+        """(TOP/s, ms) of the MMA-only microbenchmark: the measured tensor-pipe peak for the filter's instruction."""
+        t = C.c_double(0); ms = C.c_float(0)
+        self._check(self.lib.spk_debug_i8_peak(self.h, int(kblocks), int(reps), C.byref(t), C.byref(ms)))
+        return t.value, ms.value
 
     def debug_i8_mode(self):
         """weight rows of the default int8 engine: 2 = engine 3 ({hi, lo} weight bytes), 1 = engine 4 (factorised weights)"""

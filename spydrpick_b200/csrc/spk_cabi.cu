@@ -601,6 +601,7 @@ int spk_mi_scan(spk_ctx* c, const spk_scan_params* pp, spk_scan_result* res) {
 
     unsigned long long h_counters[16] = {0};
     uint64_t ne = 0, nw = 0;
+    std::vector<double> xcnt;                                // collective: {edges, wo, worst error, lost} of every rank
     bool first = true;
     for (int attempt = 0;; ++attempt) {
         if (attempt > 8) return fail(c, SPK_E_OVERFLOW, "mi_scan: result buffers still too small after %d rescans", attempt);
@@ -666,15 +667,17 @@ int spk_mi_scan(spk_ctx* c, const spk_scan_params* pp, spk_scan_result* res) {
         res->max_filter_error = h_counters[3] ? f64_from_ordered(h_counters[3]) : 0.0;
         double worst = std::max(res->max_filter_error, res->audit_max_error);
         bool lost = res->audit_violations != 0;
-        if (collective && p.engine != 1) {
-            // the band decision is taken by all ranks together (a rescan with a wider band repeats the collective seed pass)
-            if (!c->d_xcnt && cudaMalloc(&c->d_xcnt, 2 * 64 * sizeof(unsigned long long)) != cudaSuccess) { cudaGetLastError(); return fail(c, SPK_E_NOMEM, "exchange counters"); }
-            double dec[2] = {worst, lost ? 1.0 : 0.0};
-            SPK_CUDA(c, cudaMemcpyAsync(c->d_xcnt, dec, 16, cudaMemcpyHostToDevice, c->stream));
-            r = comm_allreduce_max_f64(c, (double*)c->d_xcnt, 2); if (r) return r;
-            SPK_CUDA(c, cudaMemcpyAsync(dec, c->d_xcnt, 16, cudaMemcpyDeviceToHost, c->stream));
+        if (collective) {
+            // ONE 32-byte-per-rank all-gather carries the band decision (taken by all ranks together: a rescan with a wider band
+            // repeats the collective seed pass) and the list lengths the exchange below needs
+            if (!c->d_xcnt && cudaMalloc(&c->d_xcnt, 4 * 64 * sizeof(double)) != cudaSuccess) { cudaGetLastError(); return fail(c, SPK_E_NOMEM, "exchange counters"); }
+            xcnt.assign(4 * (size_t)c->world, 0.0);
+            const double mine[4] = {(double)ne, (double)nw, worst, lost ? 1.0 : 0.0};       // counts < 2^53: exact in a double
+            SPK_CUDA(c, cudaMemcpyAsync((double*)c->d_xcnt + 4 * c->rank, mine, 32, cudaMemcpyHostToDevice, c->stream));
+            r = comm_allgather_inplace(c, c->d_xcnt, 32); if (r) return r;
+            SPK_CUDA(c, cudaMemcpyAsync(xcnt.data(), c->d_xcnt, (size_t)c->world * 32, cudaMemcpyDeviceToHost, c->stream));
             SPK_CUDA(c, cudaStreamSynchronize(c->stream));
-            worst = dec[0]; lost = dec[1] != 0.0;
+            for (int q = 0; q < c->world; ++q) { worst = std::max(worst, xcnt[4 * q + 2]); lost = lost || xcnt[4 * q + 3] != 0.0; }
         }
         if (p.engine != 1 && (worst > 0.5 * band || lost)) {
             if (band_auto && attempt < 6) {
@@ -699,14 +702,9 @@ int spk_mi_scan(spk_ctx* c, const spk_scan_params* pp, spk_scan_result* res) {
         // ---- the one exchange step before ARACNE (MI_solver::join, include/mi.hpp:355-361): edge lists concatenated, colmax max-reduced
         const int G = c->world;
         SPK_CUDA(c, cudaEventRecord(c->ev[EV_XCH0], c->stream));
-        if (!c->d_xcnt && cudaMalloc(&c->d_xcnt, 2 * 64 * sizeof(unsigned long long)) != cudaSuccess) { cudaGetLastError(); return fail(c, SPK_E_NOMEM, "exchange counters"); }
-        unsigned long long mine[2] = {ne, nw};
-        SPK_CUDA(c, cudaMemcpyAsync(c->d_xcnt + 2 * c->rank, mine, 16, cudaMemcpyHostToDevice, c->stream));
-        r = comm_allgather_inplace(c, c->d_xcnt, 16); if (r) return r;
         std::vector<unsigned long long> cnt(2 * G);
-        SPK_CUDA(c, cudaMemcpyAsync(cnt.data(), c->d_xcnt, (size_t)G * 16, cudaMemcpyDeviceToHost, c->stream));
+        for (int q = 0; q < G; ++q) { cnt[2 * q] = (unsigned long long)xcnt[4 * q]; cnt[2 * q + 1] = (unsigned long long)xcnt[4 * q + 1]; }
         r = comm_allreduce_max_f64(c, c->d_colmax, c->L); if (r) return r;
-        SPK_CUDA(c, cudaStreamSynchronize(c->stream));
         std::vector<size_t> eb(G), eo(G), wb(G), wo(G);
         std::vector<uint64_t> runs(G);
         ne_all = 0; nw_all = 0;
@@ -905,6 +903,12 @@ int spk_debug_tile_counts(spk_ctx* c, uint32_t ib, uint32_t jb, int32_t n_terms,
 }
 
 int spk_debug_i8_mode(void) { return i8_default_wr(); }
+
+int spk_debug_i8_peak(spk_ctx* c, uint32_t kblocks, uint32_t reps, double* tops, float* ms) {
+    if (!c) return SPK_E_INVALID;
+    SPK_CUDA(c, cudaSetDevice(c->device));
+    return i8_tensor_peak(c, kblocks, reps, ms, tops);
+}
 
 int spk_debug_i8_layout(spk_ctx* c, uint32_t* ntiles3, uint32_t* col_start3, uint32_t* perm, uint32_t* info, uint64_t perm_cap,
                         uint32_t* q, double* delta) {

@@ -172,7 +172,7 @@ struct Ctx {
     spk_edge* d_merge = nullptr; uint64_t merge_cap = 0;      // all-gathered edge list (world > 1)
     spk_edge* d_wo_all = nullptr; uint64_t wo_all_cap = 0;    // gathered MI-without-gaps list (rank 0)
     spk_edge* d_edges_view = nullptr;                         // the list the last scan returned (d_edges, or d_merge after an exchange)
-    unsigned long long* d_xcnt = nullptr;                     // [2 * world] per-rank (edges, wo) counts of the exchange
+    unsigned long long* d_xcnt = nullptr;                     // [4 * world] doubles: per-rank {edges, wo, worst filter error, lost} (one all-gather)
     uint32_t* d_i8_colmax32_seed = nullptr;                   // seeded fp32 maxima kept for rescans (band / overflow retries)
     bool i8_seed_valid = false;
     Candidate* d_audit = nullptr; uint64_t audit_cap = 0;     // audit sample of the filter (pairs just below the candidate band)
@@ -235,6 +235,7 @@ int i8_build_layout(Ctx* c);                                   // after prep_ali
 void i8_free(Ctx* c);
 int mi_i8_filter(Ctx* c, const spk_scan_params& p, double band, uint64_t circle, int wr, bool reuse_seed);
 int i8_default_wr();
+int i8_tensor_peak(Ctx* c, uint32_t kblocks, uint32_t reps, float* ms, double* tops);   // MMA-only microbenchmark (roofline denominator)
 int mi_i8_debug_tile(Ctx* c, uint32_t ti, uint32_t tj, double pc, uint32_t* d_out);
 
 // ---- graph (spk_graph.cu)

@@ -1223,4 +1223,102 @@ int mi_i8_debug_tile(Ctx* c, uint32_t ti, uint32_t tj, double pc, uint32_t* d_ou
     return SPK_OK;
 }
 
+
+// =============================================================================================
+// Tensor-pipe peak of the instruction the filter issues (the roofline denominator bench.py reports against).
+// A CTA pair per TPC issues tcgen05.mma.cta_group::2.kind::i8 M256 N256 K32 back to back on operands that already sit in
+// shared memory (same 128B-swizzled K-major stages, same 4 MMAs per 128-byte K block, two alternating accumulators): no TMA,
+// no epilogue, no L2 traffic -- what the pipe sustains when nothing else limits it. cuBLASLt's s8 GEMM (torch._int_mm) reaches
+// only ~75 % of this figure, which is why the filter's issued rate exceeded that "peak".
+// =============================================================================================
+constexpr int I8_PEAK_STAGES = 5;
+constexpr uint32_t I8_PEAK_STAGE_BYTES = I8_A_BYTES + 128u * I8_BK;        // 16 KB A + this CTA's half of B
+constexpr uint32_t I8_PEAK_BATCH = 64;                                      // K blocks per commit
+
+__global__ void __launch_bounds__(128, 1)
+i8_peak_kernel(uint32_t kblocks) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    __shared__ __align__(8) uint64_t batch_bar[2];
+    __shared__ __align__(8) uint64_t fin_bar;
+    __shared__ uint32_t tmem_slot;
+    const uint32_t warp = threadIdx.x / 32, rank = cluster_ctarank();
+    // operand bytes: any pattern (the accumulators wrap, nothing is read back); small values as the one-hot operands have
+    for (uint32_t e = threadIdx.x; e < I8_PEAK_STAGES * I8_PEAK_STAGE_BYTES / 4; e += blockDim.x)
+        ((uint32_t*)smem_raw)[e] = ((e * 2654435761u) >> 7) & 0x01030107u;
+    if (threadIdx.x == 0) {
+        mbar_init(&batch_bar[0], 1); mbar_init(&batch_bar[1], 1); mbar_init(&fin_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");              // generic-proxy stores -> visible to the tensor core's async proxy
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)), "r"(512u) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    tcgen05_fence_before();
+    cluster_sync_all();
+    tcgen05_fence_after();
+    const uint32_t tmem_base = tmem_slot;
+    if (warp == 1 && rank == 0) {
+        constexpr uint32_t IDESC = (I8_IDESC & ~(31u << 24)) | ((256u >> 4) << 24);
+        const uint32_t nb = (kblocks + I8_PEAK_BATCH - 1) / I8_PEAK_BATCH;
+        uint32_t kb = 0;
+        for (uint32_t b = 0; b < nb; ++b) {
+            if (b >= 2) mbar_wait(&batch_bar[b & 1u], ((b - 2u) >> 1) & 1u);     // at most two batches in flight
+            tcgen05_fence_after();
+            if (elect_one()) {
+                for (uint32_t e = 0; e < I8_PEAK_BATCH && kb + e < kblocks; ++e) {
+                    const uint32_t stage = (kb + e) % I8_PEAK_STAGES;
+                    const uint32_t sb = smem_u32(smem_raw + (size_t)stage * I8_PEAK_STAGE_BYTES);
+                    const uint64_t db = umma_smem_desc(sb), da = umma_smem_desc(sb + 128u * I8_BK);
+                    const uint32_t d_tmem = tmem_base + (((kb + e) / 24u) & 1u) * 256u;      // 24 K blocks = one 3,000-sample tile
+#pragma unroll
+                    for (uint32_t k = 0; k < I8_BK / 32; ++k) umma_i8_pair(d_tmem, da + 2u * k, db + 2u * k, IDESC, 1u);
+                }
+                umma_commit_pair(&batch_bar[b & 1u]);
+            }
+            __syncwarp();
+            kb += I8_PEAK_BATCH;
+        }
+        if (elect_one()) umma_commit_pair(&fin_bar);
+        __syncwarp();
+    }
+    if (warp == 1) { mbar_wait_cluster(&fin_bar, 0u); tcgen05_fence_after(); }
+    tcgen05_fence_before();
+    cluster_sync_all();
+    if (warp == 1) {
+        tcgen05_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+    }
+}
+
+// launches the peak kernel `reps` times back to back; *ms = total device time, *tops = tensor ops per second over that interval
+int i8_tensor_peak(Ctx* c, uint32_t kblocks, uint32_t reps, float* ms, double* tops) {
+    if (kblocks == 0 || reps == 0) return fail(c, SPK_E_INVALID, "i8_tensor_peak: kblocks and reps must be > 0");
+    const size_t smem = (size_t)I8_PEAK_STAGES * I8_PEAK_STAGE_BYTES;
+    SPK_CUDA(c, cudaFuncSetAttribute(i8_peak_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cudaLaunchConfig_t cfg; memset(&cfg, 0, sizeof cfg);
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.blockDim = dim3(128); cfg.dynamicSmemBytes = smem; cfg.stream = c->stream; cfg.attrs = attr; cfg.numAttrs = 1;
+    cfg.gridDim = dim3(2u * (unsigned)(c->sm_count / 2));
+    int max_clusters = 0;
+    if (cudaOccupancyMaxActiveClusters(&max_clusters, i8_peak_kernel, &cfg) != cudaSuccess || max_clusters < 1) { cudaGetLastError(); max_clusters = c->sm_count / 2; }
+    const unsigned pairs = (unsigned)std::min(max_clusters, c->sm_count / 2);
+    cfg.gridDim = dim3(2u * pairs);
+    cudaEvent_t e0, e1;
+    SPK_CUDA(c, cudaEventCreate(&e0)); SPK_CUDA(c, cudaEventCreate(&e1));
+    SPK_CUDA(c, cudaEventRecord(e0, c->stream));
+    for (uint32_t r = 0; r < reps; ++r) SPK_CUDA(c, cudaLaunchKernelEx(&cfg, i8_peak_kernel, kblocks));
+    SPK_CUDA(c, cudaEventRecord(e1, c->stream));
+    SPK_CUDA(c, cudaEventSynchronize(e1));
+    float t = 0.f;
+    SPK_CUDA(c, cudaEventElapsedTime(&t, e0, e1));
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    c->tm.kernel_launches += reps;
+    if (ms) *ms = t;
+    if (tops) *tops = 2.0 * 256.0 * 256.0 * 32.0 * (I8_BK / 32) * (double)kblocks * pairs * reps / (t * 1e-3) / 1e12;
+    return SPK_OK;
+}
+
 } // namespace spk
