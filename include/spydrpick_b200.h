@@ -106,6 +106,20 @@ int spk_neighbour_counts(spk_ctx* ctx, uint64_t min_identical, int quirks,
 int spk_neighbour_counts_part(spk_ctx* ctx, uint64_t min_identical, int quirks,
                               uint32_t part_index, uint32_t n_parts, uint64_t* counts /* [n] host */);
 
+/* K1 without any allocation. NO COUNTERPART IN THE REFERENCE: added for callers that cannot
+ * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it). Same result as
+ * spk_set_alignment + spk_neighbour_counts (bit-exact; both quirks honoured), but context-free and on the CURRENT device:
+ *   d_states  device, row-major uint8[n][L], codes 0..4          d_counts  device, uint64[n], written by the call
+ *   cuda_stream  the cudaStream_t to launch on (NULL = default stream); the call only enqueues work and returns.
+ * The bit planes live in a fixed file-scope __device__ array of SPK_NOALLOC_MAX_SCRATCH_BYTES that every GPU loading the library
+ * holds until exit: 3 * n * ceil(L / 32) * 4 bytes must not exceed it, larger problems are rejected with SPK_E_INVALID (message
+ * via spk_last_error(NULL)). The call makes no cudaMalloc / cudaFree / allocating library call. All calls on a device share the
+ * array (each call overwrites the extent it uses): calls that overlap on the GPU race -- issue them on one stream or order them
+ * with events. The first call on a device resolves the array's address (cudaGetSymbolAddress); make it before a graph capture. */
+#define SPK_NOALLOC_MAX_SCRATCH_BYTES (16u << 20)
+int spk_neighbour_counts_noalloc(const void* d_states, uint32_t n, uint32_t L, uint64_t min_identical, int quirks,
+                                 uint64_t* d_counts, void* cuda_stream);
+
 /* K1 + the computed branch of cache_sample_weights in one call (Alignment_utility.hpp:219-251): neighbour counts -> w = 1 / count
  * -> optional rescale (w * n) / n_eff (:245) -> the context's weights. weights_out / counts_out ([n], host) may be NULL.
  * On a context that belongs to a communicator this is a collective call (tile pairs sharded, partial counts all-reduced). */

@@ -9,7 +9,7 @@ from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-SOURCES = ["spk_prep.cu", "spk_hamming.cu", "spk_mi_exact.cu", "spk_mi_gemm.cu", "spk_mi_i8.cu", "spk_graph.cu", "spk_comm.cu", "spk_cabi.cu"]
+SOURCES = ["spk_prep.cu", "spk_hamming.cu", "spk_mi_exact.cu", "spk_mi_gemm.cu", "spk_mi_i8.cu", "spk_graph.cu", "spk_comm.cu", "spk_noalloc.cu", "spk_cabi.cu"]
 LIB = os.path.join(HERE, "libspydrpick_b200.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

@@ -18,7 +18,7 @@ SPK_OK, SPK_E_INVALID, SPK_E_CUDA, SPK_E_NOMEM, SPK_E_OVERFLOW, SPK_E_PRECISION 
 
 EXPORTS = ["spk_create", "spk_destroy", "spk_last_error", "spk_set_stream", "spk_host_alloc", "spk_host_free",
            "spk_set_alignment", "spk_set_alignment_device", "spk_column_state_counts", "spk_set_alignment_filtered",
-           "spk_neighbour_counts", "spk_neighbour_counts_part", "spk_reweight", "spk_set_weights", "spk_mi_pairs", "spk_determine_mi_threshold",
+           "spk_neighbour_counts", "spk_neighbour_counts_part", "spk_neighbour_counts_noalloc", "spk_reweight", "spk_set_weights", "spk_mi_pairs", "spk_determine_mi_threshold",
            "spk_determine_mi_threshold_ex", "spk_comm_init_all", "spk_comm_unique_id", "spk_comm_init_rank", "spk_comm_rank",
            "spk_mi_scan", "spk_outlier_thresholds", "spk_sort_edges", "spk_aracne", "spk_sort_edges_device",
            "spk_aracne_device", "spk_merge_sorted_runs_device", "spk_wait_download", "spk_get_timings", "spk_debug_tile_counts", "spk_debug_i8_mode", "spk_debug_i8_peak", "spk_debug_i8_layout", "spk_debug_i8_tile",
@@ -78,6 +78,7 @@ def load():
     L.spk_set_alignment_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p]
     L.spk_neighbour_counts.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_void_p]
     L.spk_neighbour_counts_part.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_uint32, C.c_uint32, C.c_void_p]
+    L.spk_neighbour_counts_noalloc.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint64, C.c_int, C.c_void_p, C.c_void_p]
     L.spk_set_weights.argtypes = [C.c_void_p, C.c_void_p]
     L.spk_mi_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_double, C.c_void_p]
     L.spk_determine_mi_threshold.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_double, C.c_uint64,
@@ -111,6 +112,16 @@ def load():
     L.spk_debug_i8_tile.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p]
     _lib = L
     return L
+
+
+def neighbour_counts_noalloc(d_states_ptr, n, L, min_identical, d_counts_ptr, quirks=True, stream=None):
+    """spk_neighbour_counts_noalloc: device pointers in, nothing allocated; enqueues on `stream` (a cudaStream_t handle, None =
+    default stream) of the current device. quirks: True = the reference's behaviour, False = none, or a mask."""
+    lib = load()
+    q = QUIRKS_REFERENCE if quirks is True else int(quirks)
+    rc = lib.spk_neighbour_counts_noalloc(C.c_void_p(d_states_ptr), n, L, int(min_identical), q, C.c_void_p(d_counts_ptr), C.c_void_p(stream or 0))
+    if rc != 0:
+        raise SpkError(rc, (lib.spk_last_error(None) or b"").decode())
 
 
 def _ptr(a):

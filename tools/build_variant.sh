@@ -4,7 +4,7 @@ cd "$(dirname "$0")/.."
 name=$1; shift
 mkdir -p variants/obj_$name
 FLAGS="-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC --expt-relaxed-constexpr $*"
-for s in spk_prep spk_hamming spk_mi_exact spk_mi_gemm spk_mi_i8 spk_graph spk_comm spk_cabi; do
+for s in spk_prep spk_hamming spk_mi_exact spk_mi_gemm spk_mi_i8 spk_graph spk_comm spk_noalloc spk_cabi; do
   nvcc $FLAGS -c spydrpick_b200/csrc/$s.cu -o variants/obj_$name/$s.o &
 done
 wait
