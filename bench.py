@@ -490,6 +490,17 @@ def run_b200(args):
         "filter audit": {"ms": stages.get("audit_ms", 0.0), "pairs": r["audit_pairs"], "max_error": r["audit_max_error"]},
     }
 
+    # measured DRAM traffic per launch of the secondary kernels, from the same committed ncu --set full summary (null without one)
+    pk_k = (prof or {}).get("kernels", {})
+    def _traffic(*names):
+        hits = [v["dram_bytes_per_launch"] for k, v in pk_k.items() if any(k.startswith(nm) for nm in names)]
+        return sum(hits) if hits else None
+    kernels["K1 hamming_csa_kernel"]["traffic"] = _traffic("hamming_csa_kernel")
+    kernels["K2r mi_refine_coop_kernel x9"]["traffic"] = _traffic("mi_refine_coop_kernel")
+    kernels["K3 aracne_hash_kernel"]["traffic"] = _traffic("aracne_hash_kernel")
+    kernels["K3 adjacency build (degree histogram + scan + one stable radix sort + per-node hash tables)"]["traffic_lists_and_hash_kernel"] = _traffic("lists_and_hash_kernel")
+    kernels["filter audit"]["traffic"] = _traffic("mi_audit")
+
     e2e = None
     if not args.no_e2e:
         ems, (h2d, d2h, nd2), _, _, _ = timed(step_e2e, max(1, min(args.steps, 3)), 2)

@@ -48,9 +48,6 @@ namespace spk {
 #ifndef SPK_I8_EPI_WARPS
 #define SPK_I8_EPI_WARPS 16           // epilogue warps: 8 (two per TMEM lane quadrant) or 16 (four per quadrant)
 #endif
-#ifndef SPK_I8_TWO_PHASE
-#define SPK_I8_TWO_PHASE 2           // 0: test + emit pair by pair; 1: MI of all pairs of a (wider) load first, tests afterwards;
-#endif                               // 2: as 1 at the normal load width, and ONE warp vote skips the tests of a load nothing in which can pass
 constexpr int I8_EPI_WARPS = SPK_I8_EPI_WARPS;
 constexpr int I8_EPI_THREADS = I8_EPI_WARPS * 32;
 constexpr int I8_THREADS = 64 + I8_EPI_THREADS + 64;        // + TMA warp, MMA warp, record-staging warp, tile-scheduler warp
@@ -62,7 +59,7 @@ constexpr uint32_t I8_B_BYTES = 256 * I8_BK;            // 32 KB
 constexpr uint32_t I8_STAGE_BYTES = I8_A_BYTES + I8_B_BYTES;
 constexpr int I8_NSTAGES = 4;
 #ifndef SPK_I8_SUPER
-#define SPK_I8_SUPER 16
+#define SPK_I8_SUPER 96
 #endif
 constexpr uint32_t I8_SUPER = SPK_I8_SUPER;             // i-tiles per super-row: their A panels (SUPER x 128 rows x n_pad B) stay L2-resident while B panels stream
 constexpr uint32_t I8_IDESC =                           // cute::UMMA::InstrDescriptor
@@ -95,7 +92,9 @@ struct I8Params {
     uint32_t* debug_out; uint32_t debug_ti, debug_tj;
 };
 
-struct __align__(16) JRec { uint32_t mq[4]; uint32_t smq, k, orig; float cm_lo; };   // cm_lo: running max - band, +inf when closed
+// what a pair of a 1- or 2-row j class reads sits in the first 16 bytes (ONE LDS.128): mq[0..1], smq, cm_lo
+struct __align__(16) JRec { uint32_t mq01[2]; uint32_t smq; float cm_lo; uint32_t mq23[2]; uint32_t k, orig;     // cm_lo: running max - band, +inf when closed
+    __device__ __forceinline__ uint32_t mq(int b) const { return b < 2 ? mq01[b] : mq23[b - 2]; } };
 template <int JMAX>                // JMAX = j columns a B panel can hold: 128 (two weight rows per j row) or 256 (one)
 struct I8EpiSmemT {                // column records of one tile, staged by the stager warp one tile ahead
     JRec jrec[JMAX];
@@ -208,11 +207,7 @@ __device__ __forceinline__ void i8_emit_flush(const I8Params& p, I8Emit& em, uin
 template <int KI, int KJ, int WR>
 __device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmemT<256 / WR>& sm, I8Emit& em, uint32_t tmem_acc, uint32_t q, uint32_t half,
                                                  uint32_t lane, bool diag, uint32_t ci0, uint32_t cj0) {
-#if SPK_I8_TWO_PHASE == 1
-    constexpr int LOADW = ((KI == 1 && KJ == 1) ? 16 : 32) / (3 - WR);   // TMEM columns per load (>= 2 independent pairs per lane where possible)
-#else
-    constexpr int LOADW = ((KI == 4) ? 32 : 16) / (3 - WR);              // WR = 1: half the columns hold the same number of j rows
-#endif
+    constexpr int LOADW = ((KI == 4) ? 32 : 16) / (3 - WR);              // TMEM columns per load; WR = 1: half the columns hold the same number of j rows
     constexpr int NJ = LOADW / (WR * KJ);              // j columns per load
     constexpr int PPL = NJ / KI;                       // pairs per lane per load
     constexpr int JMAX = 256 / WR;
@@ -236,6 +231,7 @@ __device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmemT<2
     const float ih_lo = sm.ih2[i_local], ih_hi = sm.ih2[128 + i_local];
     const float* jh_row = sm.jh + ki * (uint32_t)(JMAX + 1);
     const float ln2 = 0.69314718055994530942f;
+    const float thr_lo = p.thr_lo;
 
 #pragma unroll 1
     for (uint32_t ld = 0; ld < I8_COLS_PER_WARP / LOADW; ++ld) {
@@ -290,15 +286,10 @@ __device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmemT<2
                     }
             }
         }
+        if (p.debug_out) {                                     // tests only: raw counts of the requested tile (one branch per load)
 #pragma unroll
-        // phase 1: branch-free MI of the PPL pairs of this load (independent chains -> MUFU / LDS latencies overlap)
-        float mi_arr[PPL];
-        bool need = false; (void)need;
-#pragma unroll
-        for (int s = 0; s < PPL; ++s) {
-            const uint32_t j_local = col0 / (WR * KJ) + s * KI + g;
-            mi_arr[s] = __int_as_float(0x7fc00000);
-            if (p.debug_out) {
+            for (int s = 0; s < PPL; ++s) {
+                const uint32_t j_local = col0 / (WR * KJ) + s * KI + g;
                 if (j_local / WJT == p.debug_tj % p.jt) {
 #pragma unroll
                     for (int a = 0; a < KI; ++a)
@@ -306,8 +297,18 @@ __device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmemT<2
                         for (int b = 0; b < KJ; ++b)
                             p.debug_out[(((size_t)i_local * WJT + j_local % WJT) * KI + a) * KJ + b] = v[(s * KI + a) * KJ + b];
                 }
-                continue;
             }
+            continue;
+        }
+        // phase 1: branch-free MI of the PPL pairs of this load (independent chains -> MUFU / LDS latencies overlap). No validity
+        // logic here: padding / below-diagonal pairs are dropped in phase 2, which only the rare load with a passing pair enters
+        // (the per-pair valid-select, NaN constant and debug branch had cost 10 of 52 instructions per pair).
+        float mi_arr[PPL];
+        bool need = false;
+        const float t_i = fminf(thr_lo, cm_i_lo);                  // cm_i_lo only moves in phase 2
+#pragma unroll
+        for (int s = 0; s < PPL; ++s) {
+            const uint32_t j_local = col0 / (WR * KJ) + s * KI + g;
             const JRec jr = sm.jrec[j_local];
             const uint32_t kj = jr.k;
             const bool khi = (KJ == 2) || (kj == KJ_HI);
@@ -320,53 +321,50 @@ __device__ __forceinline__ void i8_epilogue_tile(const I8Params& p, I8EpiSmemT<2
                 float l; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(l) : "f"(pr));
                 return pr * l;
             };
-            uint32_t colsum[KJ];
+            // integer pass: row sums, column sums, total of the kept cells
+            uint32_t colsum[KJ], rs[KI];
 #pragma unroll
             for (int b = 0; b < KJ; ++b) colsum[b] = 0;
             uint32_t tot = 0;
-            float S = 0.f;
 #pragma unroll
             for (int a = 0; a < KI; ++a) {
-                const bool rv = (KI == 2) ? true : (KI == 1 ? (ki >= 1u) : (a < 3 || ki == 4u));
-                uint32_t rs = 0;
-                float racc = 0.f;
+                rs[a] = 0;
 #pragma unroll
-                for (int b = 0; b < KJ; ++b) {
-                    const bool cv = (KJ == 2) ? true : (KJ == 1 ? (kj >= 1u) : (b < 3 || kj == 4u));
-                    const uint32_t nab = v[(s * KI + a) * KJ + b];
-                    rs += nab; colsum[b] += nab;
-                    const float t = xlg(nab);
-                    racc += cv ? t : 0.f;
-                }
-                racc += xlg(mi_[a] - rs);                                // cell (a, dropped_j)
-                S += rv ? racc : 0.f;
-                tot += rs;
+                for (int b = 0; b < KJ; ++b) { const uint32_t nab = v[(s * KI + a) * KJ + b]; rs[a] += nab; colsum[b] += nab; }
+                tot += rs[a];
             }
+            // S = sum of p log2 p over the cells of the (ki+1) x (kj+1) table: the dropped-i row starts the chain, every kept row
+            // continues it (one FFMA per cell; a row / column the column does not have is skipped with a select, never added as 0 + x)
+            float S = xlg(mi_d - jr.smq + tot);                          // cell (dropped_i, dropped_j)
 #pragma unroll
             for (int b = 0; b < KJ; ++b) {
                 const bool cv = (KJ == 2) ? true : (KJ == 1 ? (kj >= 1u) : (b < 3 || kj == 4u));
-                const float t = xlg(jr.mq[b] - colsum[b]);               // cell (dropped_i, b)
-                S += cv ? t : 0.f;
+                const float t = S + xlg(jr.mq(b) - colsum[b]);           // cell (dropped_i, b)
+                S = cv ? t : S;
             }
-            S += xlg(mi_d - jr.smq + tot);                               // cell (dropped_i, dropped_j)
-            const bool valid = vi && (jr.orig != I8_INVALID) && (!diag || pi < cj0 + j_local);
-            mi_arr[s] = valid ? fmaf(S, ln2, -hsum) : __int_as_float(0x7fc00000);
-#if SPK_I8_TWO_PHASE
-#if SPK_I8_TWO_PHASE == 2
-            need = need || (mi_arr[s] >= fminf(fminf(p.thr_lo, cm_i_lo), jr.cm_lo));   // superset of the exact tests below; false for NaN
-#endif
+#pragma unroll
+            for (int a = 0; a < KI; ++a) {
+                const bool rv = (KI == 2) ? true : (KI == 1 ? (ki >= 1u) : (a < 3 || ki == 4u));
+                float racc = S + xlg(mi_[a] - rs[a]);                    // cell (a, dropped_j)
+#pragma unroll
+                for (int b = 0; b < KJ; ++b) {
+                    const bool cv = (KJ == 2) ? true : (KJ == 1 ? (kj >= 1u) : (b < 3 || kj == 4u));
+                    const float t = racc + xlg(v[(s * KI + a) * KJ + b]);
+                    racc = cv ? t : racc;
+                }
+                S = rv ? racc : S;
+            }
+            mi_arr[s] = fmaf(S, ln2, -hsum);
+            need = need || (mi_arr[s] >= fminf(t_i, jr.cm_lo));          // superset of the exact tests below
         }
-        if (p.debug_out) continue;
-#if SPK_I8_TWO_PHASE == 2
         if (!__any_sync(0xffffffffu, need)) continue;             // nothing to test or emit in this load (the common case)
-#endif
-        // phase 2: threshold / open-column tests and candidate emission
+        // phase 2: validity, threshold / open-column tests and candidate emission
 #pragma unroll
         for (int s = 0; s < PPL; ++s) {
             const uint32_t j_local = col0 / (WR * KJ) + s * KI + g;
-#endif
             const uint32_t pj = cj0 + j_local;
-            const float mi32 = mi_arr[s];
+            const bool valid = vi && (sm.jrec[j_local].orig != I8_INVALID) && (!diag || pi < pj);
+            const float mi32 = valid ? mi_arr[s] : __int_as_float(0x7fc00000);     // NaN fails every test below
             bool emit;
             if (p.seed_chunks) {
                 // seed pass: the running LD-admissible maxima of both columns; the only pairs it emits are the AUDIT sample of
@@ -628,7 +626,7 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
             for (uint32_t e = lane; e < WJ; e += 32) {
                 const ColRec8 rc = p.rec[cj0 + e];
                 JRec jr;
-                jr.mq[0] = rc.mq[0]; jr.mq[1] = rc.mq[1]; jr.mq[2] = rc.mq[2]; jr.mq[3] = rc.mq[3];
+                jr.mq01[0] = rc.mq[0]; jr.mq01[1] = rc.mq[1]; jr.mq23[0] = rc.mq[2]; jr.mq23[1] = rc.mq[3];
                 jr.smq = rc.smq; jr.k = rc.k; jr.orig = rc.orig;
                 const uint32_t cm = p.colmax32[cj0 + e];
                 const float cmf = f32_from_ordered(cm);

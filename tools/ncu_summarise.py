@@ -3,6 +3,8 @@
 
   python tools/ncu_summarise.py launches gpurun_out/X_launches_raw.csv  > profiles/X_launches.csv
   python tools/ncu_summarise.py full gpurun_out/A.ncu-rep [B.ncu-rep..]  > profiles/X_ncu_full_summary.csv
+  python tools/ncu_summarise.py index profiles/X_ncu_full_summary.csv ENGINE N L NGPUS   (adds / replaces the entry in profiles/index.json
+                                                                                         that bench.py reads its `traffic` values from)
 """
 import csv
 import io
@@ -64,8 +66,45 @@ def full(paths):
             print(",".join(parts))
 
 
+def _bytes(txt):
+    v, u = txt.split()
+    return float(v) * {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}[u]
+
+
+def _ms(txt):
+    v, u = txt.split()
+    return float(v) * {"ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3}[u]
+
+
+def index(summary, engine, n, L, ngpus):
+    import json
+    import os
+    kernels = {}
+    for line in open(summary):
+        if line.startswith("#") or not line.strip():
+            continue
+        parts = line.strip().split(",")
+        d = dict(x.split("=", 1) for x in parts[1:])
+        name = parts[0].replace("void ", "").replace("; ", ",").strip()
+        kernels[name] = {"dram_bytes_per_launch": _bytes(d["dram__bytes_read.sum"]) + _bytes(d["dram__bytes_write.sum"]),
+                         "ncu_ms": _ms(d["gpu__time_duration.sum"]),
+                         "tensor_pipe_active_pct": float(d["sm__pipe_tensor_cycles_active_realtime.avg.pct_of_peak_sustained_elapsed"].split()[0]),
+                         "ipc": float(d["sm__inst_executed.avg.per_cycle_elapsed"].split()[0])}
+    main = next(k for k in kernels if k.startswith("mi_i8_kernel") or k.startswith("mi_gemm_kernel"))
+    ent = {"engine": engine, "n": n, "L": L, "n_gpus": ngpus, "file": os.path.relpath(summary, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..")),
+           "kernel": main, "dram_bytes_per_launch": kernels[main]["dram_bytes_per_launch"], "tensor_pipe_active_pct": kernels[main]["tensor_pipe_active_pct"],
+           "kernels": kernels}
+    path = os.path.join(os.path.dirname(os.path.abspath(summary)), "index.json")
+    idx = json.load(open(path)) if os.path.exists(path) else {"ncu_full": []}
+    idx["ncu_full"] = [e for e in idx["ncu_full"] if (e["engine"], e["n"], e["L"], e.get("n_gpus", 1)) != (engine, n, L, ngpus)] + [ent]
+    json.dump(idx, open(path, "w"), indent=1, sort_keys=True)
+    print("wrote", path, "(%d kernels)" % len(kernels))
+
+
 if __name__ == "__main__":
     if sys.argv[1] == "launches":
         launches(sys.argv[2])
+    elif sys.argv[1] == "index":
+        index(sys.argv[2], int(sys.argv[3]), int(sys.argv[4]), int(sys.argv[5]), int(sys.argv[6]))
     else:
         full(sys.argv[2:])
