@@ -37,8 +37,8 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--n", type=int, default=3000)
-    ap.add_argument("--L", type=int, default=100000)
+    ap.add_argument("--n", "--samples", dest="n", type=int, default=3000)        # (--samples / --columns: torchrun's own parser trips over "--n")
+    ap.add_argument("--L", "--columns", dest="L", type=int, default=100000)
     ap.add_argument("--seed", type=int, default=20260102)
     ap.add_argument("--n-terms", type=int, default=0)
     ap.add_argument("--engine", type=int, default=0, help="0 = default int8 engine (= 4), 3 = int8 compact one-hot GEMM with {hi, lo} 16-bit weight rows, 4 = factorised byte weights (half the tensor work), 2 = dense bf16 GEMM")

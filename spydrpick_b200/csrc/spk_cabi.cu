@@ -801,11 +801,12 @@ int spk_merge_sorted_runs_device(spk_ctx* c, void* d_edges, const uint64_t* run_
 
 // ARACNE on a device list. Collective (context in a communicator, n_parts == 0): every rank evaluates its range of the edge
 // list, the flag shards are exchanged in place (grouped broadcast of each rank's range), every rank ends with all flags.
+// collective ARACNE: every rank evaluates the edges owned by ITS nodes (u = rank mod world; an edge is owned by its larger-degree
+// endpoint) into zero-initialised flags, and one all-reduce(max) of E bytes gives every rank the whole vector
 static int aracne_collective(spk_ctx* c, const spk_edge* d_edges, uint64_t n, double eps, uint8_t* d_flags) {
-    int r = aracne_device(c, d_edges, n, eps, (uint32_t)c->rank, (uint32_t)c->world, d_flags); if (r) return r;
-    std::vector<size_t> fb(c->world), fo(c->world);
-    for (int q = 0; q < c->world; ++q) { const uint64_t e0 = n * (uint64_t)q / (uint64_t)c->world, e1 = n * (uint64_t)(q + 1) / (uint64_t)c->world; fo[q] = e0; fb[q] = e1 - e0; }
-    return comm_allgatherv(c, d_flags + fo[c->rank], d_flags, fb.data(), fo.data());
+    SPK_CUDA(c, cudaMemsetAsync(d_flags, 0, n, c->stream));
+    int r = aracne_device(c, d_edges, n, eps, (uint32_t)c->rank, (uint32_t)c->world, d_flags, true); if (r) return r;
+    return comm_allreduce_max_u8(c, d_flags, n);
 }
 
 int spk_aracne_device(spk_ctx* c, const void* d_edges, uint64_t n, double eps, uint32_t part, uint32_t nparts, void* d_flags) {

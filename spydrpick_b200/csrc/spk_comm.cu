@@ -9,7 +9,7 @@
 //                                             merge buffer at its prefix offset (no padding, no concatenation pass)
 //           MI-without-gaps lists             grouped ncclSend / ncclRecv to rank 0 (only the writer needs them)
 //           per-column maxima                 ncclAllReduce(max, f64[L])
-//   ARACNE  direct-edge flag shards           grouped in-place ncclBroadcast of each rank's edge range
+//   ARACNE  direct-edge flags (node shards)   ncclAllReduce(max, u8[E]) over zero-initialised flags
 //   upload  alignment rows                    each rank uploads n/G rows over its own PCIe link, ncclAllGather over NVLink
 //
 // NCCL is loaded with dlopen (libnccl.so.2): inside a Python process that is torch's bundled copy (already mapped), for the
@@ -96,6 +96,12 @@ int comm_allreduce_max_u32(Ctx* c, uint32_t* d, size_t n) {
     if (c->world <= 1) return SPK_OK;
     NcclApi* a = nccl_api(nullptr);
     SPK_NCCL(c, a->AllReduce(d, d, n, NCCL_UINT32, NCCL_MAX, (ncclComm_t)c->comm, c->stream), "allreduce(max,u32)");
+    return SPK_OK;
+}
+int comm_allreduce_max_u8(Ctx* c, uint8_t* d, size_t n) {
+    if (c->world <= 1 || n == 0) return SPK_OK;
+    NcclApi* a = nccl_api(nullptr);
+    SPK_NCCL(c, a->AllReduce(d, d, n, NCCL_UINT8, NCCL_MAX, (ncclComm_t)c->comm, c->stream), "allreduce(max,u8)");
     return SPK_OK;
 }
 int comm_allreduce_max_f64(Ctx* c, double* d, size_t n) {

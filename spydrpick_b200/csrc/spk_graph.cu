@@ -230,7 +230,7 @@ __device__ __forceinline__ double nbr_weight(const uint32_t* __restrict__ hkey, 
 // weight < w (no triangle with w as its minimum beyond that) and looks the members that are also neighbours of u up in u's
 // hash table (hot in L1: a few KB per node).
 __global__ void __launch_bounds__(256)
-aracne_hash_kernel(unsigned long long e_begin, unsigned long long e_end,
+aracne_hash_kernel(unsigned long long e_begin, unsigned long long e_end, uint32_t node_part, uint32_t node_nparts,
                    const uint32_t* __restrict__ wdst, const double* __restrict__ wval, const uint32_t* __restrict__ weid,
                    const uint32_t* __restrict__ hkey, const double* __restrict__ hval,
                    const unsigned long long* __restrict__ offsets, uint32_t nn, unsigned int* __restrict__ next_node,
@@ -243,8 +243,11 @@ aracne_hash_kernel(unsigned long long e_begin, unsigned long long e_end,
         __syncthreads();
         if (threadIdx.x == 0) s_u = atomicAdd(next_node, 1u);
         __syncthreads();
-        const uint32_t u = s_u;
-        if (u >= nn) break;
+        // node shard (collective form): this partition visits nodes node_part, node_part + node_nparts, ...; every edge is owned by
+        // exactly one of its endpoints, so the node shards partition the edge set and each rank pays the bitmap work of its nodes only
+        const unsigned long long u64 = (unsigned long long)s_u * node_nparts + node_part;
+        if (u64 >= nn) break;
+        const uint32_t u = (uint32_t)u64;
         const unsigned long long a0 = offsets[u], a1 = offsets[u + 1], degu = a1 - a0;
         if (degu == 0) continue;
         for (unsigned long long k = a0 + threadIdx.x; k < a1; k += blockDim.x) { const uint32_t z = wdst[k]; atomicOr(&bm[z >> 5], 1u << (z & 31u)); }
@@ -312,7 +315,10 @@ aracne_search_kernel(const spk_edge* __restrict__ edges, unsigned long long e_be
     }
 }
 
-int aracne_device(Ctx* c, const spk_edge* d_edges, uint64_t n, double eps, uint32_t part, uint32_t nparts, uint8_t* d_flags) {
+// by_node = false: the partition is the edge range [part*n/nparts, (part+1)*n/nparts) (the public part_index / n_parts contract);
+// by_node = true (collective form): the partition is the set of edges owned by nodes u = part (mod nparts) -- some disjoint
+// cover of the edge list, combined by the caller with an element-wise max over zero-initialised flags.
+int aracne_device(Ctx* c, const spk_edge* d_edges, uint64_t n, double eps, uint32_t part, uint32_t nparts, uint8_t* d_flags, bool by_node) {
     if (n == 0) return SPK_OK;
     if (n > 0x3fffffffull) return fail(c, SPK_E_INVALID, "ARACNE supports < 2^30 edges");
     const unsigned long long m = 2 * n;
@@ -394,14 +400,16 @@ int aracne_device(Ctx* c, const spk_edge* d_edges, uint64_t n, double eps, uint3
     lists_and_hash_kernel<<<gm, 256, 0, c->stream>>>(d_edges, we1, wk1, m, offsets, wdst, wval, hkey, hval);
     SPK_CUDA(c, cudaEventRecord(c->ev[EV_AR1], c->stream));
     if (nparts == 0) nparts = 1;
-    const unsigned long long e0 = (unsigned long long)n * part / nparts, e1 = (unsigned long long)n * (part + 1) / nparts;
+    unsigned long long e0 = (unsigned long long)n * part / nparts, e1 = (unsigned long long)n * (part + 1) / nparts;
     const size_t bm_bytes = (size_t)((nn + 31) / 32) * 4;
+    const bool node_shard = by_node && nparts > 1 && bm_bytes <= 160 * 1024;
+    if (node_shard) { e0 = 0; e1 = n; }
     if (bm_bytes <= 160 * 1024) {
         if (bm_bytes > 48 * 1024) SPK_CUDA(c, cudaFuncSetAttribute(aracne_hash_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bm_bytes));
         const unsigned per_sm = (unsigned)std::max<size_t>(1, std::min<size_t>(8, (200 * 1024) / (bm_bytes + 1024)));
         unsigned long long blocks = (unsigned long long)c->sm_count * per_sm;
         if (blocks > nn) blocks = nn;
-        aracne_hash_kernel<<<(unsigned)blocks, 256, bm_bytes, c->stream>>>(e0, e1, wdst, wval, we1, hkey, hval, offsets, nn, d_scan + 1, eps, d_flags);
+        aracne_hash_kernel<<<(unsigned)blocks, 256, bm_bytes, c->stream>>>(e0, e1, node_shard ? part : 0u, node_shard ? nparts : 1u, wdst, wval, we1, hkey, hval, offsets, nn, d_scan + 1, eps, d_flags);
     } else {
         unsigned long long blocks = (e1 - e0 + 7) / 8;
         const unsigned long long cap = (unsigned long long)c->sm_count * 32;

@@ -188,6 +188,7 @@ void resolve_timings(Ctx* c);               // call when the context's stream is
 // ---- multi-GPU (spk_comm.cu): no-ops when c->world == 1; all calls are queued on c->stream
 int comm_allreduce_sum_u64(Ctx* c, unsigned long long* d, size_t n);
 int comm_allreduce_max_u32(Ctx* c, uint32_t* d, size_t n);
+int comm_allreduce_max_u8(Ctx* c, uint8_t* d, size_t n);
 int comm_allreduce_max_f64(Ctx* c, double* d, size_t n);
 int comm_allreduce_sum_f64(Ctx* c, double* d, size_t n);
 int comm_allgather_inplace(Ctx* c, void* d_buf, size_t bytes_per_rank);
@@ -241,7 +242,7 @@ int mi_i8_debug_tile(Ctx* c, uint32_t ti, uint32_t tj, double pc, uint32_t* d_ou
 // ---- graph (spk_graph.cu)
 int sort_edges_device(Ctx* c, spk_edge* d_edges, uint64_t n);
 int merge_sorted_runs_device(Ctx* c, spk_edge* d_edges, const uint64_t* run_counts, uint32_t n_runs);
-int aracne_device(Ctx* c, const spk_edge* d_edges, uint64_t n, double eps, uint32_t part, uint32_t nparts, uint8_t* d_flags);
+int aracne_device(Ctx* c, const spk_edge* d_edges, uint64_t n, double eps, uint32_t part, uint32_t nparts, uint8_t* d_flags, bool by_node = false);
 
 // ordered-int encodings for atomic max on floating point
 __host__ __device__ inline uint32_t f32_ordered(float f) {

@@ -718,7 +718,35 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
 // =============================================================================================
 // preparation kernels: integer marginals + epilogue tables, operand expansion
 // =============================================================================================
-// one warp per permuted column
+// column record from the integer marginals m[5] (by state code) of permuted column pc: kept-order marginals, position, and the
+// entropy / normaliser tables by the partner column's number of present states
+__device__ __forceinline__ void i8_write_record(ColRec8* __restrict__ out, uint32_t orig, const uint32_t* m, const uint32_t* __restrict__ info,
+                                                const uint64_t* __restrict__ pos, uint32_t pc, double wq_total, double pcq) {
+    ColRec8 r; memset(&r, 0, sizeof r);
+    r.orig = orig;
+    uint32_t k = 0;
+    double pm[NSTATES]; int npres = 0;                       // marginals of the present states
+    if (orig != I8_INVALID) {
+        const uint32_t inf = info[pc];
+        k = inf & 15u;
+        for (uint32_t a = 0; a < k; ++a) { const uint32_t code = (inf >> (4 + 3 * a)) & 7u; r.mq[a] = m[code]; r.smq += m[code]; pm[npres++] = (double)m[code]; }
+        const uint32_t drop = (inf >> 16) & 7u;
+        r.mqd = m[drop]; pm[npres++] = (double)m[drop];
+        const uint64_t ps = pos[orig];
+        r.pos_lo = (uint32_t)ps; r.pos_hi = (uint32_t)(ps >> 32);
+    }
+    r.k = k;
+    for (int mm = 1; mm <= NSTATES; ++mm) {
+        const double Z = wq_total + pcq * (double)(k + 1) * (double)mm;
+        double h = 0.0;
+        for (int a = 0; a < npres; ++a) { const double pr = (pm[a] + pcq * (double)mm) / Z; h += pr * log(pr); }
+        r.h[mm - 1] = (float)h;
+        r.invz[mm - 1] = (float)(1.0 / Z);
+    }
+    *out = r;
+}
+
+// one warp per permuted column (records only: used when just the pseudocount changed; i8_prep_kernel is the normal path)
 __global__ void i8_colrec_kernel(const uint8_t* __restrict__ colmajor, const uint32_t* __restrict__ qw,
                                  const uint32_t* __restrict__ perm, const uint32_t* __restrict__ info,
                                  const uint64_t* __restrict__ pos, ColRec8* __restrict__ rec,
@@ -739,43 +767,22 @@ __global__ void i8_colrec_kernel(const uint8_t* __restrict__ colmajor, const uin
         for (int a = 0; a < NSTATES; ++a)
             for (int o = 16; o; o >>= 1) m[a] += __shfl_xor_sync(0xffffffffu, m[a], o);
     }
-    if (lane == 0) {
-        ColRec8 r; memset(&r, 0, sizeof r);
-        r.orig = orig;
-        uint32_t k = 0;
-        double pm[NSTATES]; int npres = 0;                       // marginals of the present states
-        if (orig != I8_INVALID) {
-            const uint32_t inf = info[pc];
-            k = inf & 15u;
-            for (uint32_t a = 0; a < k; ++a) { const uint32_t code = (inf >> (4 + 3 * a)) & 7u; r.mq[a] = m[code]; r.smq += m[code]; pm[npres++] = (double)m[code]; }
-            const uint32_t drop = (inf >> 16) & 7u;
-            r.mqd = m[drop]; pm[npres++] = (double)m[drop];
-            const uint64_t ps = pos[orig];
-            r.pos_lo = (uint32_t)ps; r.pos_hi = (uint32_t)(ps >> 32);
-        }
-        r.k = k;
-        for (int mm = 1; mm <= NSTATES; ++mm) {
-            const double Z = wq_total + pcq * (double)(k + 1) * (double)mm;
-            double h = 0.0;
-            for (int a = 0; a < npres; ++a) { const double pr = (pm[a] + pcq * (double)mm) / Z; h += pr * log(pr); }
-            r.h[mm - 1] = (float)h;
-            r.invz[mm - 1] = (float)(1.0 / Z);
-        }
-        rec[pc] = r;
-    }
+    if (lane == 0) i8_write_record(rec + pc, orig, m, info, pos, pc, wq_total, pcq);
 }
 
-// one warp per permuted column; each lane converts 16 consecutive samples per iteration.
-// wr = 2: A = one-hot, B = one-hot x {hi, lo} weight byte (two rows per kept state); wr = 1: A = one-hot x a_s
-// (byte array qhi), B = one-hot x b_s (byte array qlo), one row per kept state at the same row index as in A.
-__global__ void i8_expand_kernel(const uint8_t* __restrict__ colmajor, const uint8_t* __restrict__ qhi, const uint8_t* __restrict__ qlo,
-                                 const uint32_t* __restrict__ perm, const uint32_t* __restrict__ info,
-                                 uint8_t* __restrict__ A8, uint8_t* __restrict__ B8, uint32_t Lperm, uint32_t n, uint32_t n_pad,
-                                 uint32_t cs1, uint32_t cs2, uint32_t ts1, uint32_t ts2, uint32_t wr) {
+// Operands AND column records in one pass over the column-major alignment: one warp per permuted column, each lane converts 16
+// consecutive samples per iteration. wr = 2: A = one-hot, B = one-hot x {hi, lo} weight byte (two rows per kept state); wr = 1:
+// A = one-hot x a_s (byte array qhi), B = one-hot x b_s (byte array qlo), one row per kept state at the same row index as in A.
+// EVERY row of the column's class slot is written (zeros for rows the column does not use, for padding columns and for the padded
+// samples), so the operand arrays need no memset: 1.1 GB written once per step instead of twice, the 0.3 GB alignment read once.
+__global__ void __launch_bounds__(256)
+i8_prep_kernel(const uint8_t* __restrict__ colmajor, const uint8_t* __restrict__ qhi, const uint8_t* __restrict__ qlo,
+               const uint32_t* __restrict__ perm, const uint32_t* __restrict__ info, const uint64_t* __restrict__ pos,
+               uint8_t* __restrict__ A8, uint8_t* __restrict__ B8, ColRec8* __restrict__ rec, uint32_t Lperm, uint32_t n, uint32_t n_pad,
+               uint32_t cs1, uint32_t cs2, uint32_t ts1, uint32_t ts2, uint32_t wr, double wq_total, double pcq) {
     const uint32_t pc = blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32;
     if (pc >= Lperm) return;
     const uint32_t orig = perm[pc];
-    if (orig == I8_INVALID) return;                              // rows stay zero
     const uint32_t lane = threadIdx.x % 32;
     const uint32_t cls = (pc >= cs2) ? 2u : (pc >= cs1) ? 1u : 0u;
     const uint32_t kp = 1u << cls;
@@ -784,31 +791,59 @@ __global__ void i8_expand_kernel(const uint8_t* __restrict__ colmajor, const uin
     const uint32_t lc = pc - cstart;
     const size_t rowA = (size_t)128 * tstart + (size_t)lc * kp;
     const size_t rowB = (wr == 2) ? (size_t)256 * tstart + (size_t)lc * 2 * kp : rowA;
-    const uint32_t inf = info[pc];
+    const bool live = orig != I8_INVALID;
+    const uint32_t inf = live ? info[pc] : 0u;
     const uint32_t k = inf & 15u;
-    const uint8_t* col = colmajor + (size_t)orig * n_pad;
+    const uint8_t* col = colmajor + (size_t)(live ? orig : 0u) * n_pad;
+    // integer marginals of the kept states come from the operand bytes just built (a_s * b_s resp. hi * 256 + lo of the samples
+    // in that state, 0 elsewhere); the dropped state's is the total minus their sum
+    uint32_t mk[4] = {0, 0, 0, 0};
+    const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
     for (uint32_t s0 = lane * 16; s0 < n_pad; s0 += 512) {
-        const uint4 raw = *reinterpret_cast<const uint4*>(col + s0);
-        const uint4 rh = *reinterpret_cast<const uint4*>(qhi + s0);
-        const uint4 rl = *reinterpret_cast<const uint4*>(qlo + s0);
         uint8_t x[16], wh[16], wl[16];
-        memcpy(x, &raw, 16); memcpy(wh, &rh, 16); memcpy(wl, &rl, 16);
-        for (uint32_t a = 0; a < k; ++a) {
-            const uint32_t code = (inf >> (4 + 3 * a)) & 7u;
-            __align__(16) uint8_t oa[16], oh[16], ol[16];
+        if (live) {
+            const uint4 raw = *reinterpret_cast<const uint4*>(col + s0);
+            const uint4 rh = *reinterpret_cast<const uint4*>(qhi + s0);
+            const uint4 rl = *reinterpret_cast<const uint4*>(qlo + s0);
+            memcpy(x, &raw, 16); memcpy(wh, &rh, 16); memcpy(wl, &rl, 16);
+        }
 #pragma unroll
-            for (int t = 0; t < 16; ++t) {
-                const bool hit = (x[t] == code) && (s0 + t < n);
-                oa[t] = hit ? (wr == 2 ? (uint8_t)1 : wh[t]) : (uint8_t)0; oh[t] = hit ? wh[t] : 0; ol[t] = hit ? wl[t] : 0;
+        for (uint32_t a = 0; a < 4; ++a) {
+            if (a >= kp) break;
+            uint4 va = zero, vh = zero, vl = zero;
+            if (live && a < k) {
+                const uint32_t code = (inf >> (4 + 3 * a)) & 7u;
+                __align__(16) uint8_t oa[16], oh[16], ol[16];
+                uint32_t acc = 0;
+#pragma unroll
+                for (int t = 0; t < 16; ++t) {
+                    const bool hit = (x[t] == code) && (s0 + t < n);
+                    oa[t] = hit ? (wr == 2 ? (uint8_t)1 : wh[t]) : (uint8_t)0; oh[t] = hit ? wh[t] : 0; ol[t] = hit ? wl[t] : 0;
+                    acc += (wr == 2) ? ((uint32_t)oh[t] << 8) + ol[t] : (uint32_t)oh[t] * ol[t];
+                }
+                mk[a] += acc;
+                va = *reinterpret_cast<const uint4*>(oa); vh = *reinterpret_cast<const uint4*>(oh); vl = *reinterpret_cast<const uint4*>(ol);
             }
-            *reinterpret_cast<uint4*>(A8 + (rowA + a) * n_pad + s0) = *reinterpret_cast<const uint4*>(oa);
+            *reinterpret_cast<uint4*>(A8 + (rowA + a) * n_pad + s0) = va;
             if (wr == 2) {
-                *reinterpret_cast<uint4*>(B8 + (rowB + a) * n_pad + s0) = *reinterpret_cast<const uint4*>(oh);
-                *reinterpret_cast<uint4*>(B8 + (rowB + kp + a) * n_pad + s0) = *reinterpret_cast<const uint4*>(ol);
+                *reinterpret_cast<uint4*>(B8 + (rowB + a) * n_pad + s0) = vh;
+                *reinterpret_cast<uint4*>(B8 + (rowB + kp + a) * n_pad + s0) = vl;
             } else {
-                *reinterpret_cast<uint4*>(B8 + (rowB + a) * n_pad + s0) = *reinterpret_cast<const uint4*>(ol);
+                *reinterpret_cast<uint4*>(B8 + (rowB + a) * n_pad + s0) = vl;
             }
         }
+    }
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+        for (int o = 16; o; o >>= 1) mk[a] += __shfl_xor_sync(0xffffffffu, mk[a], o);
+    if (lane == 0) {
+        uint32_t m[NSTATES] = {0, 0, 0, 0, 0};
+        if (live) {
+            uint32_t sum = 0;
+            for (uint32_t a = 0; a < k; ++a) { m[(inf >> (4 + 3 * a)) & 7u] = mk[a]; sum += mk[a]; }
+            m[(inf >> 16) & 7u] = (uint32_t)((unsigned long long)wq_total - sum);
+        }
+        i8_write_record(rec + pc, orig, m, info, pos, pc, wq_total, pcq);
     }
 }
 
@@ -985,13 +1020,14 @@ static int i8_prepare(Ctx* c, double pc, int wr) {
                 return fail(c, SPK_E_NOMEM, "int8 engine: cannot allocate operands (%zu bytes)", 3 * rowsA * n_pad);
             }
         }
-        SPK_CUDA(c, cudaMemsetAsync(c->d_A8, 0, rowsA * n_pad, c->stream));
-        SPK_CUDA(c, cudaMemsetAsync(c->d_B8, 0, (size_t)wr * rowsA * n_pad, c->stream));
-        i8_expand_kernel<<<(c->i8.Lperm + 7) / 8, 256, 0, c->stream>>>(c->d_colmajor, d_qhi, d_qlo, c->d_i8_perm, c->d_i8_info, c->d_A8, c->d_B8,
-                                                                      c->i8.Lperm, n, n_pad, c->i8.col_start[1], c->i8.col_start[2],
-                                                                      c->i8.tile_start[1], c->i8.tile_start[2], (uint32_t)wr);
+        // (no memset: i8_prep_kernel writes every row of every class slot, padding included)
+        i8_prep_kernel<<<(c->i8.Lperm + 7) / 8, 256, 0, c->stream>>>(c->d_colmajor, d_qhi, d_qlo, c->d_i8_perm, c->d_i8_info, c->d_pos, c->d_A8, c->d_B8, c->d_i8_rec,
+                                                                    c->i8.Lperm, n, n_pad, c->i8.col_start[1], c->i8.col_start[2],
+                                                                    c->i8.tile_start[1], c->i8.tile_start[2], (uint32_t)wr,
+                                                                    (double)c->i8_wq_total, pc / c->i8_delta);
         c->tm.kernel_launches += 1;
         SPK_CUDA(c, cudaGetLastError());
+        c->i8_rec_pc = pc;
         c->i8_operands_valid = true;
     }
     SPK_CUDA(c, cudaEventRecord(c->ev[EV_EXP1], c->stream));
