@@ -85,7 +85,8 @@ struct Options {
 
 [[noreturn]] void die(const std::string& msg) {
     std::cerr << "SpydrPick error: " << msg << "\n\n";
-    std::exit(EXIT_FAILURE);
+    std::cout.flush(); std::cerr.flush();
+    std::_Exit(EXIT_FAILURE);               // (not exit(): the CUDA start-up thread may still be running; nothing to unwind here)
 }
 
 void print_help() {
@@ -247,13 +248,16 @@ struct HostAlignment {
     // the device-side column filter leaves the host matrix as it is: column k of the alignment is column col_src[k] of the
     // L_src-column host matrix (empty = identity); only the exports read it
     uint64_t L_src = 0; std::vector<uint64_t> col_src;
-    void adopt(uint8_t* s) { if (states) spk_host_free(states); states = s; }
+    void adopt(uint8_t* s) { if (states) std::free(states); states = s; }
     uint64_t src_col(uint64_t k) const { return col_src.empty() ? k : col_src[k]; }
 };
 
+// The alignment lives in ordinary (pageable) memory: the CUDA contexts are still being created on another thread while the
+// FASTA file is parsed (context creation takes far longer than the parse), and the one upload of a few hundred MB through the
+// driver's staging buffers costs less than page-locking them would.
 uint8_t* alloc_states(size_t bytes) {
     void* mem = nullptr;
-    if (spk_host_alloc(bytes ? bytes : 16, &mem) != SPK_OK) die("could not allocate " + std::to_string(bytes) + " bytes of page-locked host memory for the alignment");
+    if (posix_memalign(&mem, 4096, bytes ? bytes : 16) != 0) die("could not allocate " + std::to_string(bytes) + " bytes of host memory for the alignment");
     return (uint8_t*)mem;
 }
 
@@ -540,6 +544,22 @@ int main(int argc, char** argv) {
     const bool V = o.verbose;
     if (V) std::cout << "SpydrPick (" << spk_version() << ")\n";
 
+    // -- contexts: one per GPU (SPMD); rank 0 is the one whose results are written. Created on a side thread: CUDA start-up
+    //    (driver, primary contexts, NCCL communicator) takes seconds and overlaps the FASTA ingest below.
+    const int G = o.gpus;
+    std::vector<spk_ctx*> ctxs(G, nullptr);
+    std::string ctx_error; double ctx_seconds = 0.0;
+    std::thread ctx_thread([&]() {
+        Timer t;
+        for (int g = 0; g < G; ++g) {
+            const int dev = (G == 1) ? o.device : ((o.device < 0 ? 0 : o.device) + g);
+            if (spk_create(&ctxs[g], dev, (V && g == 0) ? 1 : 0) != SPK_OK) { ctx_error = std::string("cannot initialise the CUDA context: ") + spk_last_error(nullptr); return; }
+        }
+        if (G > 1 && spk_comm_init_all(ctxs.data(), G) != SPK_OK) ctx_error = std::string("NCCL communicator: ") + spk_last_error(ctxs[0]);
+        ctx_seconds = t.lap();
+    });
+    struct Joiner { std::thread& t; ~Joiner() { if (t.joinable()) t.join(); } } ctx_joiner{ctx_thread};
+
     // -- ingest (src/SpydrPick.cpp:163; apegrunt/Alignment_utility.hpp:69-160)
     HostAlignment A = read_fasta(o.alignment_files[0], o);
     if (o.genome_size) A.n_original_positions = o.genome_size;             // Alignment_parsers.hpp:133
@@ -570,14 +590,9 @@ int main(int argc, char** argv) {
         if (V) std::cout << "SpydrPick: exclude list leaves " << A.L << " loci\n";
     }
 
-    // -- contexts: one per GPU (SPMD); rank 0 is the one whose results are written
-    const int G = o.gpus;
-    std::vector<spk_ctx*> ctxs(G, nullptr);
-    for (int g = 0; g < G; ++g) {
-        const int dev = (G == 1) ? o.device : ((o.device < 0 ? 0 : o.device) + g);
-        if (spk_create(&ctxs[g], dev, (V && g == 0) ? 1 : 0) != SPK_OK) die(std::string("cannot initialise the CUDA context: ") + spk_last_error(nullptr));
-    }
-    if (G > 1) check(ctxs[0], spk_comm_init_all(ctxs.data(), G), "NCCL communicator");
+    ctx_thread.join();
+    if (!ctx_error.empty()) die(ctx_error);
+    if (V) std::cout << "SpydrPick: " << G << " CUDA context" << (G > 1 ? "s + NCCL communicator" : "") << " ready (" << ctx_seconds << " s of start-up, overlapped with the ingest; waited " << lap.lap() << " s)\n";
     spk_ctx* ctx = ctxs[0];
     auto on_all = [&](auto fn) {           // the same call on every rank's context, one host thread each (collective calls meet on the GPUs)
         if (G == 1) { fn(0); return; }
@@ -744,7 +759,7 @@ int main(int argc, char** argv) {
         std::cout << "SpydrPick: analysis completed\n      total " << total.lap() << " s\n";
     }
     for (auto* c : ctxs) spk_destroy(c);
-    if (A.states) spk_host_free(A.states);
+    if (A.states) std::free(A.states);
     spk_host_free(flag_mem);
     return EXIT_SUCCESS;
 }

@@ -718,32 +718,43 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
 // =============================================================================================
 // preparation kernels: integer marginals + epilogue tables, operand expansion
 // =============================================================================================
-// column record from the integer marginals m[5] (by state code) of permuted column pc: kept-order marginals, position, and the
-// entropy / normaliser tables by the partner column's number of present states
+// column record from the integer marginals m[5] (by state code; valid in every lane) of permuted column pc: kept-order marginals,
+// position, and the entropy / normaliser tables by the partner column's number of present states (lane t computes entry t of the
+// five, in fp64; lane 0 writes the record). Called by the whole warp.
 __device__ __forceinline__ void i8_write_record(ColRec8* __restrict__ out, uint32_t orig, const uint32_t* m, const uint32_t* __restrict__ info,
-                                                const uint64_t* __restrict__ pos, uint32_t pc, double wq_total, double pcq) {
+                                                const uint64_t* __restrict__ pos, uint32_t pc, double wq_total, double pcq, uint32_t lane) {
     ColRec8 r; memset(&r, 0, sizeof r);
     r.orig = orig;
     uint32_t k = 0;
-    double pm[NSTATES]; int npres = 0;                       // marginals of the present states
+    double pm[NSTATES] = {0.0, 0.0, 0.0, 0.0, 0.0}; int npres = 0;      // marginals of the present states
     if (orig != I8_INVALID) {
         const uint32_t inf = info[pc];
         k = inf & 15u;
-        for (uint32_t a = 0; a < k; ++a) { const uint32_t code = (inf >> (4 + 3 * a)) & 7u; r.mq[a] = m[code]; r.smq += m[code]; pm[npres++] = (double)m[code]; }
+#pragma unroll
+        for (uint32_t a = 0; a < 4; ++a)
+            if (a < k) {
+                const uint32_t code = (inf >> (4 + 3 * a)) & 7u;
+                const uint32_t v = code == 0 ? m[0] : code == 1 ? m[1] : code == 2 ? m[2] : code == 3 ? m[3] : m[4];
+                r.mq[a] = v; r.smq += v; pm[a] = (double)v;
+            }
         const uint32_t drop = (inf >> 16) & 7u;
-        r.mqd = m[drop]; pm[npres++] = (double)m[drop];
+        r.mqd = drop == 0 ? m[0] : drop == 1 ? m[1] : drop == 2 ? m[2] : drop == 3 ? m[3] : m[4];
+        npres = (int)k + 1;
         const uint64_t ps = pos[orig];
         r.pos_lo = (uint32_t)ps; r.pos_hi = (uint32_t)(ps >> 32);
     }
     r.k = k;
-    for (int mm = 1; mm <= NSTATES; ++mm) {
-        const double Z = wq_total + pcq * (double)(k + 1) * (double)mm;
-        double h = 0.0;
-        for (int a = 0; a < npres; ++a) { const double pr = (pm[a] + pcq * (double)mm) / Z; h += pr * log(pr); }
-        r.h[mm - 1] = (float)h;
-        r.invz[mm - 1] = (float)(1.0 / Z);
-    }
-    *out = r;
+    const int mm = (int)(lane % NSTATES) + 1;
+    const double Z = wq_total + pcq * (double)(k + 1) * (double)mm;
+    double h = 0.0;
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+        if (a < (int)k) { const double pr = (pm[a] + pcq * (double)mm) / Z; h += pr * log(pr); }
+    if (npres) { const double pr = ((double)r.mqd + pcq * (double)mm) / Z; h += pr * log(pr); }
+    const float hf = (float)h, izf = (float)(1.0 / Z);
+#pragma unroll
+    for (int t = 0; t < NSTATES; ++t) { r.h[t] = __shfl_sync(0xffffffffu, hf, t); r.invz[t] = __shfl_sync(0xffffffffu, izf, t); }
+    if (lane == 0) *out = r;
 }
 
 // one warp per permuted column (records only: used when just the pseudocount changed; i8_prep_kernel is the normal path)
@@ -767,7 +778,7 @@ __global__ void i8_colrec_kernel(const uint8_t* __restrict__ colmajor, const uin
         for (int a = 0; a < NSTATES; ++a)
             for (int o = 16; o; o >>= 1) m[a] += __shfl_xor_sync(0xffffffffu, m[a], o);
     }
-    if (lane == 0) i8_write_record(rec + pc, orig, m, info, pos, pc, wq_total, pcq);
+    i8_write_record(rec + pc, orig, m, info, pos, pc, wq_total, pcq, lane);
 }
 
 // Operands AND column records in one pass over the column-major alignment: one warp per permuted column, each lane converts 16
@@ -799,52 +810,61 @@ i8_prep_kernel(const uint8_t* __restrict__ colmajor, const uint8_t* __restrict__
     // in that state, 0 elsewhere); the dropped state's is the total minus their sum
     uint32_t mk[4] = {0, 0, 0, 0};
     const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
+    // byte-wise SIMD on 32-bit words (__vcmpeq4 / AND / __dp4a): samples beyond n carry weight bytes 0 (and the GAP code), so they
+    // contribute nothing and need no bound test
     for (uint32_t s0 = lane * 16; s0 < n_pad; s0 += 512) {
-        uint8_t x[16], wh[16], wl[16];
+        uint4 raw = zero, rh = zero, rl = zero;
         if (live) {
-            const uint4 raw = *reinterpret_cast<const uint4*>(col + s0);
-            const uint4 rh = *reinterpret_cast<const uint4*>(qhi + s0);
-            const uint4 rl = *reinterpret_cast<const uint4*>(qlo + s0);
-            memcpy(x, &raw, 16); memcpy(wh, &rh, 16); memcpy(wl, &rl, 16);
+            raw = *reinterpret_cast<const uint4*>(col + s0);
+            rh = *reinterpret_cast<const uint4*>(qhi + s0);
+            rl = *reinterpret_cast<const uint4*>(qlo + s0);
         }
+        const uint32_t xw[4] = {raw.x, raw.y, raw.z, raw.w}, hw[4] = {rh.x, rh.y, rh.z, rh.w}, lw[4] = {rl.x, rl.y, rl.z, rl.w};
 #pragma unroll
         for (uint32_t a = 0; a < 4; ++a) {
             if (a >= kp) break;
-            uint4 va = zero, vh = zero, vl = zero;
+            uint32_t oa[4] = {0, 0, 0, 0}, oh[4] = {0, 0, 0, 0}, ol[4] = {0, 0, 0, 0};
             if (live && a < k) {
-                const uint32_t code = (inf >> (4 + 3 * a)) & 7u;
-                __align__(16) uint8_t oa[16], oh[16], ol[16];
-                uint32_t acc = 0;
+                const uint32_t code4 = ((inf >> (4 + 3 * a)) & 7u) * 0x01010101u;
+                uint32_t acc = 0, acc_hi = 0;
 #pragma unroll
-                for (int t = 0; t < 16; ++t) {
-                    const bool hit = (x[t] == code) && (s0 + t < n);
-                    oa[t] = hit ? (wr == 2 ? (uint8_t)1 : wh[t]) : (uint8_t)0; oh[t] = hit ? wh[t] : 0; ol[t] = hit ? wl[t] : 0;
-                    acc += (wr == 2) ? ((uint32_t)oh[t] << 8) + ol[t] : (uint32_t)oh[t] * ol[t];
+                for (int w = 0; w < 4; ++w) {
+                    const uint32_t hit = __vcmpeq4(xw[w], code4);                 // 0xff in the bytes of samples in this state
+                    oh[w] = hit & hw[w]; ol[w] = hit & lw[w];
+                    oa[w] = (wr == 2) ? (hit & 0x01010101u) : oh[w];
+                    if (wr == 2) { acc_hi = __dp4a(oh[w], 0x01010101u, acc_hi); acc = __dp4a(ol[w], 0x01010101u, acc); }
+                    else acc = __dp4a(oh[w], ol[w], acc);
                 }
-                mk[a] += acc;
-                va = *reinterpret_cast<const uint4*>(oa); vh = *reinterpret_cast<const uint4*>(oh); vl = *reinterpret_cast<const uint4*>(ol);
+                mk[a] += acc + (acc_hi << 8);
             }
-            *reinterpret_cast<uint4*>(A8 + (rowA + a) * n_pad + s0) = va;
+            *reinterpret_cast<uint4*>(A8 + (rowA + a) * n_pad + s0) = make_uint4(oa[0], oa[1], oa[2], oa[3]);
             if (wr == 2) {
-                *reinterpret_cast<uint4*>(B8 + (rowB + a) * n_pad + s0) = vh;
-                *reinterpret_cast<uint4*>(B8 + (rowB + kp + a) * n_pad + s0) = vl;
+                *reinterpret_cast<uint4*>(B8 + (rowB + a) * n_pad + s0) = make_uint4(oh[0], oh[1], oh[2], oh[3]);
+                *reinterpret_cast<uint4*>(B8 + (rowB + kp + a) * n_pad + s0) = make_uint4(ol[0], ol[1], ol[2], ol[3]);
             } else {
-                *reinterpret_cast<uint4*>(B8 + (rowB + a) * n_pad + s0) = vl;
+                *reinterpret_cast<uint4*>(B8 + (rowB + a) * n_pad + s0) = make_uint4(ol[0], ol[1], ol[2], ol[3]);
             }
         }
     }
 #pragma unroll
     for (int a = 0; a < 4; ++a)
         for (int o = 16; o; o >>= 1) mk[a] += __shfl_xor_sync(0xffffffffu, mk[a], o);
-    if (lane == 0) {
-        uint32_t m[NSTATES] = {0, 0, 0, 0, 0};
-        if (live) {
-            uint32_t sum = 0;
-            for (uint32_t a = 0; a < k; ++a) { m[(inf >> (4 + 3 * a)) & 7u] = mk[a]; sum += mk[a]; }
-            m[(inf >> 16) & 7u] = (uint32_t)((unsigned long long)wq_total - sum);
-        }
-        i8_write_record(rec + pc, orig, m, info, pos, pc, wq_total, pcq);
+    uint32_t m[NSTATES] = {0, 0, 0, 0, 0};
+    if (live) {
+        uint32_t sum = 0;
+#pragma unroll
+        for (uint32_t a = 0; a < 4; ++a)
+            if (a < k) {
+                const uint32_t code = (inf >> (4 + 3 * a)) & 7u;
+#pragma unroll
+                for (int t = 0; t < NSTATES; ++t) if (code == (uint32_t)t) m[t] = mk[a];
+                sum += mk[a];
+            }
+        const uint32_t drop = (inf >> 16) & 7u, md = (uint32_t)((unsigned long long)wq_total - sum);
+#pragma unroll
+        for (int t = 0; t < NSTATES; ++t) if (drop == (uint32_t)t) m[t] = md;
     }
+    i8_write_record(rec + pc, orig, m, info, pos, pc, wq_total, pcq, lane);
 }
 
 __global__ void i8_fill_u32_kernel(uint32_t* p, uint32_t v, size_t n) {
