@@ -263,7 +263,7 @@ typedef struct {
     uint64_t gemm_pairs;                    /* column pairs covered by those tiles (incl. padding / masked diagonal halves) */
     float    seed_ms;                       /* int8 engine: the colmax seed launch, included in gemm_ms (main pass = gemm_ms - seed_ms) */
     float    exchange_ms;                   /* collective scan: counts + edge all-gather + colmax all-reduce + run merge */
-    float    audit_ms;                      /* filter audit kernel */
+    float    audit_ms;                      /* filter audit: appending the audit sample to the candidate list (its fp64 recomputation is part of refine_ms) */
     float    threshold_ms;                  /* threshold estimator: sampling + K2b + segmented sort (device part) */
 } spk_timings;
 int spk_get_timings(spk_ctx* ctx, spk_timings* out);

@@ -459,12 +459,14 @@ int spk_determine_mi_threshold_ex(spk_ctx* c, uint64_t n_values, uint64_t thresh
     for (uint32_t k = 0; k <= nit; ++k) h_off[k] = (int)(tp * k);
     if (nit) cub::DeviceSegmentedRadixSort::SortKeys(nullptr, tmpb, (const double*)nullptr, (double*)nullptr, (int)total, (int)nit, (const int*)nullptr, (const int*)nullptr, 0, 64, c->stream);
     const size_t offb = ((size_t)(nit + 1) * 4 + 255) & ~(size_t)255, thrb = ((size_t)iterations * 8 + 255) & ~(size_t)255;
-    uint8_t* base = (uint8_t*)scratch(c, 2 * ib + 2 * ob + offb + thrb + ((tmpb + 255) & ~(size_t)255) + 256);
+    const size_t workb = mi_pairs_segmented_scratch(total, nit);
+    uint8_t* base = (uint8_t*)scratch(c, 2 * ib + 2 * ob + offb + thrb + ((tmpb + 255) & ~(size_t)255) + 256 + workb);
     if (!base) return fail(c, SPK_E_NOMEM, "scratch allocation failed");
     uint32_t* d_pi = (uint32_t*)base; uint32_t* d_pj = (uint32_t*)(base + ib);
     double* d_mi = (double*)(base + 2 * ib); double* d_sorted = (double*)(base + 2 * ib + ob);
     int* d_off = (int*)(base + 2 * ib + 2 * ob); double* d_thr = (double*)(base + 2 * ib + 2 * ob + offb);
     void* d_tmp = base + 2 * ib + 2 * ob + offb + thrb;
+    void* d_work = base + 2 * ib + 2 * ob + offb + thrb + ((tmpb + 255) & ~(size_t)255) + 256;
     SPK_CUDA(c, cudaMemsetAsync(d_thr, 0, (size_t)iterations * 8, c->stream));
     if (nit) {
         if (sampler == SPK_SAMPLER_REFERENCE) {
@@ -494,7 +496,11 @@ int spk_determine_mi_threshold_ex(spk_ctx* c, uint64_t n_values, uint64_t thresh
             sample_pairs_kernel<<<(unsigned)((total + 255) / 256), 256, 0, c->stream>>>(d_pi, d_pj, tp, nit, rank, world, L, possible, half_bits, seed);
             c->tm.kernel_launches += 1;
         }
-        r = mi_pairs_exact(c, d_pi, d_pj, total, pc, d_mi); if (r) return r;
+        // all pairs through the class-bucketed cooperative refine kernels (the order inside an iteration's segment is free: it is
+        // sorted next); the thread-per-pair kernel only when the weights are not groupable
+        r = mi_pairs_segmented(c, d_pi, d_pj, total, tp, nit, pc, d_mi, d_work);
+        if (r == SPK_E_INVALID && c->g_state != 1) r = mi_pairs_exact(c, d_pi, d_pj, total, pc, d_mi);
+        if (r) return r;
         SPK_CUDA(c, cudaMemcpyAsync(d_off, h_off.data(), (size_t)(nit + 1) * 4, cudaMemcpyHostToDevice, c->stream));
         SPK_CUDA(c, cub::DeviceSegmentedRadixSort::SortKeys(d_tmp, tmpb, (const double*)d_mi, d_sorted, (int)total, (int)nit, d_off, d_off + 1, 0, 64, c->stream));
         // this rank's iterations sit at rank, rank + world, ...: write them to their global slots
@@ -605,7 +611,10 @@ int spk_mi_scan(spk_ctx* c, const spk_scan_params* pp, spk_scan_result* res) {
     bool first = true;
     for (int attempt = 0;; ++attempt) {
         if (attempt > 8) return fail(c, SPK_E_OVERFLOW, "mi_scan: result buffers still too small after %d rescans", attempt);
-        SPK_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 16 * sizeof(unsigned long long), c->stream));
+        // counters [11], [12] (size / overflow of the audit sample) belong to the seed pass: a rescan that reuses the seeds keeps them
+        if (first) SPK_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 16 * sizeof(unsigned long long), c->stream));
+        else { SPK_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 11 * sizeof(unsigned long long), c->stream));
+               SPK_CUDA(c, cudaMemsetAsync(c->d_counters + 13, 0, 3 * sizeof(unsigned long long), c->stream)); }
         fill_u64_kernel<<<(c->L_pad + 255) / 256, 256, 0, c->stream>>>((unsigned long long*)c->d_colmax, f64_ordered(-DBL_MAX), c->L_pad);
         c->tm.kernel_launches += 1;
         c->tm.gemm_ms = c->tm.refine_ms = c->tm.compact_ms = c->tm.sort_ms = c->tm.seed_ms = c->tm.audit_ms = c->tm.exchange_ms = 0.f; c->tm.gemm_tiles = 0;
@@ -617,8 +626,9 @@ int spk_mi_scan(spk_ctx* c, const spk_scan_params* pp, spk_scan_result* res) {
                 // the refine's plane build only needs the weights: queued first, it runs on the GPU while the host prepares the filter
                 if (first) { r = mi_refine_prepare(c, p.pseudocount); if (r) return r; }
                 r = mi_i8_filter(c, p, band, circle, i8_wr, !first); if (r) return r;
-                if (first && c->d_audit && c->audit_cap) {
-                    r = mi_audit(c, c->d_audit, c->d_counters + 11, c->audit_cap, p.pseudocount, p.threshold, (float)(p.threshold - band)); if (r) return r;
+                if (c->d_audit && c->audit_cap) {
+                    // the audit sample the seed pass left (this attempt's, or the one a rescan reuses) joins the candidate list as marked entries
+                    r = mi_audit_append(c, c->d_audit, c->d_counters + 11, c->audit_cap); if (r) return r;
                     audited = true;
                 }
             } else {
@@ -638,16 +648,12 @@ int spk_mi_scan(spk_ctx* c, const spk_scan_params* pp, spk_scan_result* res) {
                 r = ensure_scan_buffers(c, std::max<uint64_t>(c->edges_cap, need * 2 / 3), need, false); if (r) return r;
                 continue;
             }
-            uint64_t ncand = h_counters[0];                  // int8 engine: reserved slots, a few of them invalid-marked holes
-            if (audited) {
-                res->audit_pairs = h_counters[10]; res->audit_violations = h_counters[9];
-                res->audit_max_error = h_counters[8] ? f64_from_ordered(h_counters[8]) : 0.0;
-            }
+            uint64_t ncand = h_counters[0];                  // int8 engine: reserved slots, a few of them invalid-marked holes; + the audit entries
             SPK_CUDA(c, cudaEventRecord(c->ev[EV_REF0], c->stream));
             r = mi_refine_candidates(c, ncand, p.pseudocount, p.threshold, &ncand); if (r) return r;
             res->n_candidates = ncand;
             SPK_CUDA(c, cudaEventRecord(c->ev[EV_REF1], c->stream));
-            r = mi_compact(c, ncand, p, circle); if (r) return r;
+            r = mi_compact(c, ncand, p, circle, audited ? (float)(p.threshold - band) : __builtin_nanf("")); if (r) return r;
             SPK_CUDA(c, cudaEventRecord(c->ev[EV_CMP1], c->stream));
             c->tm_pending |= TMP_REFINE | TMP_COMPACT;
         }
@@ -665,6 +671,11 @@ int spk_mi_scan(spk_ctx* c, const spk_scan_params* pp, spk_scan_result* res) {
         }
         ne = h_counters[1]; nw = h_counters[2];
         res->max_filter_error = h_counters[3] ? f64_from_ordered(h_counters[3]) : 0.0;
+        if (audited) {                                       // written by the compaction from the marked entries
+            res->audit_pairs = h_counters[10]; res->audit_violations = h_counters[9];
+            res->audit_max_error = h_counters[8] ? f64_from_ordered(h_counters[8]) : 0.0;
+            res->n_candidates -= std::min<uint64_t>(res->n_candidates, h_counters[10]);
+        }
         double worst = std::max(res->max_filter_error, res->audit_max_error);
         bool lost = res->audit_violations != 0;
         if (collective) {

@@ -219,12 +219,14 @@ int mi_pairs_exact(Ctx* c, const uint32_t* d_pi, const uint32_t* d_pj, uint64_t 
 int mi_refine_prepare(Ctx* c, double pc);     // weight-grouped bit planes + entropy tables of the fp64 refine (asynchronous; idempotent until the weights change; world > 1: the plane build is sharded over the ranks and all-gathered)
 // audit of the tensor-core filter: fp64 MI of the sample of pairs the seed pass emitted (mi32 > audit_lo): counters[8] = max |mi32 - mi64|
 // (ordered bits), [9] = pairs with mi64 > thr that the main pass would NOT have refined (mi32 <= cand_lo), [10] = pairs audited
-int mi_audit(Ctx* c, const Candidate* d_audit, const unsigned long long* d_n, uint64_t cap, double pc, double threshold, float cand_lo);
+int mi_audit_append(Ctx* c, const Candidate* d_audit, const unsigned long long* d_n, uint64_t cap);      // audit sample -> marked entries of the candidate list
+size_t mi_pairs_segmented_scratch(uint64_t total, uint32_t nseg);
+int mi_pairs_segmented(Ctx* c, const uint32_t* d_pi, const uint32_t* d_pj, uint64_t total, uint64_t per, uint32_t nseg, double pc, double* d_mi, void* work);
 int mi_refine_candidates(Ctx* c, uint64_t ncand, double pc, double wo_threshold, uint64_t* n_valid = nullptr);   // MI-without-gaps only when mi > wo_threshold
 // exhaustive diagnostic engine: emits every pair of the partition as a candidate-free exact scan
 int mi_scan_exact(Ctx* c, const spk_scan_params& p, uint64_t circle);
 // threshold + colmax + compaction over refined candidates
-int mi_compact(Ctx* c, uint64_t ncand, const spk_scan_params& p, uint64_t circle);
+int mi_compact(Ctx* c, uint64_t ncand, const spk_scan_params& p, uint64_t circle, float audit_cand_lo);
 void mi_exact_free(Ctx* c);                                   // releases the weight-grouped bit planes
 
 // ---- K2 (spk_mi_gemm.cu)

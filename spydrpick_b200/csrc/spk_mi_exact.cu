@@ -100,9 +100,10 @@ gbits_build_kernel(const uint8_t* __restrict__ colmajor, const int32_t* __restri
         const uint32_t p0 = __ballot_sync(0xffffffffu, x == 0u), p1 = __ballot_sync(0xffffffffu, x == 1u);
         const uint32_t p2 = __ballot_sync(0xffffffffu, x == 2u), p3 = __ballot_sync(0xffffffffu, x == 3u);
         const uint32_t occ = __ballot_sync(0xffffffffu, x < (uint32_t)NSTATES);
-        if (lane < (uint32_t)NSTATES) {
-            const uint32_t pl = lane == 0 ? p0 : lane == 1 ? p1 : lane == 2 ? p2 : lane == 3 ? p3 : (occ & ~(p0 | p1 | p2 | p3));
-            planes_sm[lane * NW + w] = pl;
+        if (lane == 0) {                                     // five predicated stores by one lane: the per-lane select of the five
+            planes_sm[w] = p0; planes_sm[NW + w] = p1;        // ballots compiled into a branch ladder twice as long as the votes
+            planes_sm[2 * NW + w] = p2; planes_sm[3 * NW + w] = p3;
+            planes_sm[4 * NW + w] = occ & ~(p0 | p1 | p2 | p3);
         }
     }
     __syncthreads();
@@ -743,90 +744,60 @@ mi_refine_kernel(const uint8_t* __restrict__ colmajor, const double* __restrict_
     if (lane == 0 && maxerr > 0.0) atomicMax(&counters[3], f64_ordered(maxerr));
 }
 
-// ---- filter audit ---------------------------------------------------------------------------------
-// The candidate rule of the tensor-core filter (mi32 > thr - band) can only lose an edge if the fp32 / quantised-weight MI
-// under-estimates the fp64 value by more than the band -- and such a pair is, by construction, never refined, so the error
-// measured over the candidates cannot see it. The audit closes that hole with an UNBIASED sample: the colmax seed pass (a
-// 1/32 sample of the tile chunks) emits every pair with mi32 > thr - 4*band; here each of them gets its fp64 MI, and
-//   counters[8]  = max |mi32 - mi64| over the audited pairs (ordered bits)
-//   counters[9]  = number of audited pairs with mi64 > thr whose mi32 was NOT above the candidate cut-off (false negatives)
-//   counters[10] = pairs audited
-// n is read on the device (no host round trip); one thread per pair on the grouped planes, one warp per pair on bytes.
+// ---- filter audit ------------------------------------------------------------------------------
+// The seed launch of the filter leaves an unbiased sample of pairs with mi32 > thr - 4*band in the audit buffer. A strided
+// subsample of it (>= 1e5 pairs when the sample is that large) is APPENDED to the candidate list, marked pad = 1, so that the
+// regular refine launches recompute it in fp64 (no kernel of its own: one thread per pair over 1e5 pairs had cost 0.84 ms, the
+// cooperative refine does them in ~0.06); mi_compact_kernel turns the marked entries into the audit statistics
+// (counters[8] max |mi32 - mi64|, [9] pairs with mi64 > thr that the filter would have dropped, [10] pairs audited)
+// instead of edges. n is read on the device (no host round trip).
 constexpr unsigned long long AUDIT_TARGET = 300000;     // buffer entries visited per scan and rank (about half of them are unused slots of the
                                                         // emission chunks: >= 1e5 pairs recomputed when the sample is that large)
-__global__ void __launch_bounds__(128)
-mi_audit_thread_kernel(const uint8_t* __restrict__ masks, const Candidate* __restrict__ cand, const unsigned long long* __restrict__ d_n,
-                       unsigned long long cap, double pc, double w_total, double threshold, float cand_lo,
-                       unsigned long long* __restrict__ counters,
-                       const uint32_t* __restrict__ gbits, const double* __restrict__ gval, const double* __restrict__ gmarg,
-                       const double* __restrict__ gH, uint32_t NW) {
+__global__ void __launch_bounds__(256)
+audit_append_kernel(const Candidate* __restrict__ audit, const unsigned long long* __restrict__ d_n, unsigned long long cap,
+                    Candidate* __restrict__ cand, unsigned long long cand_cap, unsigned long long* __restrict__ counters) {
     const unsigned long long n = min(*d_n, cap);
-    // at most ~AUDIT_TARGET pairs are recomputed: every stride-th entry of the emission order (unbiased: entries land in the
-    // buffer in the order the tiles finish)
-    const unsigned long long stride = (n + AUDIT_TARGET - 1) / AUDIT_TARGET;
-    double err = 0.0; unsigned int bad = 0, cnt = 0;
+    const unsigned long long stride = (n + AUDIT_TARGET - 1) / AUDIT_TARGET;     // every stride-th entry of the emission order
     for (unsigned long long q = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; q * stride < n; q += (unsigned long long)gridDim.x * blockDim.x) {
-        const unsigned long long p = q * stride;
-        const Candidate cd = cand[p];
+        Candidate cd = audit[q * stride];
         if (cd.i == I8_INVALID) continue;
-        double m = 0.0, m2 = 0.0;
-        pair_eval_dispatch(gbits, gval, gmarg, gH, NW, cd.i, cd.j, masks[cd.i], masks[cd.j], w_total, pc, INFINITY, &m, &m2);
-        err = fmax(err, fabs((double)cd.mi32 - m));
-        bad += (m > threshold && !(cd.mi32 > cand_lo)) ? 1u : 0u;
-        ++cnt;
-    }
-#pragma unroll
-    for (int o = 16; o; o >>= 1) {
-        err = fmax(err, __shfl_xor_sync(0xffffffffu, err, o));
-        bad += __shfl_xor_sync(0xffffffffu, bad, o); cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
-    }
-    if ((threadIdx.x & 31) == 0) {
-        if (err > 0.0) atomicMax(&counters[8], f64_ordered(err));
-        if (bad) atomicAdd(&counters[9], (unsigned long long)bad);
-        if (cnt) atomicAdd(&counters[10], (unsigned long long)cnt);
-    }
-}
-__global__ void __launch_bounds__(EX_WARPS * 32)
-mi_audit_warp_kernel(const uint8_t* __restrict__ colmajor, const double* __restrict__ w, const uint8_t* __restrict__ masks,
-                     const Candidate* __restrict__ cand, const unsigned long long* __restrict__ d_n, unsigned long long cap,
-                     uint32_t n_pad, double pc, double threshold, float cand_lo, unsigned long long* __restrict__ counters) {
-    __shared__ double bins_all[EX_WARPS][25 * 32];
-    const uint32_t lane = threadIdx.x % 32, wid = threadIdx.x / 32;
-    double* bins = bins_all[wid];
-    const unsigned long long n = min(*d_n, cap);
-    const unsigned long long stride = (n + AUDIT_TARGET - 1) / AUDIT_TARGET;
-    double err = 0.0; unsigned long long bad = 0, cnt = 0;
-    for (unsigned long long q = (unsigned long long)blockIdx.x * EX_WARPS + wid; q * stride < n; q += (unsigned long long)gridDim.x * EX_WARPS) {
-        const unsigned long long p = q * stride;
-        const Candidate cd = cand[p];
-        if (cd.i == I8_INVALID) continue;
-        double v = warp_crosstab(colmajor + (size_t)cd.i * n_pad, colmajor + (size_t)cd.j * n_pad, w, n_pad, bins, lane);
-        const double m = warp_mi_pass(v, masks[cd.i], masks[cd.j], pc, lane);
-        err = fmax(err, fabs((double)cd.mi32 - m));
-        bad += (m > threshold && !(cd.mi32 > cand_lo)) ? 1ull : 0ull;
-        ++cnt;
-    }
-    if (lane == 0) {
-        if (err > 0.0) atomicMax(&counters[8], f64_ordered(err));
-        if (bad) atomicAdd(&counters[9], bad);
-        if (cnt) atomicAdd(&counters[10], cnt);
+        const unsigned long long slot = atomicAdd(&counters[0], 1ull);            // the main pass is complete: single slots after its chunks
+        if (slot < cand_cap) { cd.pad = 1u; cand[slot] = cd; } else counters[4] = 1ull;
     }
 }
 
-// ---- threshold / colmax / compaction over refined pairs (mi.hpp:414-461) ----------------------
-// counters[1] = n_edges, counters[2] = n_wo, counters[4] = overflow flag
 __global__ void mi_compact_kernel(const spk_edge* __restrict__ refined, const double* __restrict__ refined_wo,
                                   unsigned long long ncand, const uint64_t* __restrict__ pos,
                                   double threshold, unsigned long long ld_threshold, int linear, unsigned long long circle,
                                   unsigned long long* __restrict__ colmax_ord,
                                   spk_edge* __restrict__ edges, unsigned long long edges_cap,
                                   spk_edge* __restrict__ wo, unsigned long long wo_cap,
-                                  unsigned long long* __restrict__ counters) {
+                                  unsigned long long* __restrict__ counters,
+                                  const Candidate* __restrict__ meta, float cand_lo) {
     const unsigned long long p = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t lane = threadIdx.x % 32;
     bool keep = false, keep_wo = false;
     spk_edge e; e.i = 0; e.j = 0; e.mi = 0.0; double m2 = 0.0;
-    if (p < ncand) {
+    // audit entries (meta[p].pad == 1; `meta` is the candidate array `refined` runs parallel to): statistics, never edges
+    double aerr = 0.0; unsigned int abad = 0, acnt = 0;
+    const bool is_audit = meta && p < ncand && meta[p].pad == 1u;
+    if (is_audit) {
+        const double m = refined[p].mi; const float mi32 = meta[p].mi32;
+        aerr = fabs((double)mi32 - m); abad = (m > threshold && !(mi32 > cand_lo)) ? 1u : 0u; acnt = 1u;
+    }
+    if (meta && __any_sync(0xffffffffu, is_audit)) {
+#pragma unroll
+        for (int o = 16; o; o >>= 1) {
+            aerr = fmax(aerr, __shfl_xor_sync(0xffffffffu, aerr, o));
+            abad += __shfl_xor_sync(0xffffffffu, abad, o); acnt += __shfl_xor_sync(0xffffffffu, acnt, o);
+        }
+        if (lane == 0) {
+            if (aerr > 0.0) atomicMax(&counters[8], f64_ordered(aerr));
+            if (abad) atomicAdd(&counters[9], (unsigned long long)abad);
+            atomicAdd(&counters[10], (unsigned long long)acnt);
+        }
+    }
+    if (p < ncand && !is_audit) {
         e = refined[p]; m2 = refined_wo[p];
         if (genome_distance(pos[e.i], pos[e.j], linear, circle) > ld_threshold) {
             const unsigned long long o = f64_ordered(e.mi);
@@ -970,16 +941,10 @@ static int refine_grid(Ctx* c, unsigned long long n) {
 
 int mi_refine_prepare(Ctx* c, double pc) { return ensure_grouped(c, pc); }
 
-int mi_audit(Ctx* c, const Candidate* d_audit, const unsigned long long* d_n, uint64_t cap, double pc, double threshold, float cand_lo) {
+int mi_audit_append(Ctx* c, const Candidate* d_audit, const unsigned long long* d_n, uint64_t cap) {
     if (!d_audit || cap == 0) return SPK_OK;
-    { int rg = ensure_grouped(c, pc); if (rg) return rg; }
     SPK_CUDA(c, cudaEventRecord(c->ev[EV_AUD0], c->stream));
-    if (c->g_state == 1)
-        mi_audit_thread_kernel<<<c->sm_count * 8, 128, 0, c->stream>>>(c->d_masks, d_audit, d_n, cap, pc, c->w_total, threshold, cand_lo, c->d_counters,
-                                                                      c->d_gbits, c->d_gval, c->d_gmarg, c->d_gH, c->g_NW);
-    else
-        mi_audit_warp_kernel<<<c->sm_count * 16, EX_WARPS * 32, 0, c->stream>>>(c->d_colmajor, c->d_w, c->d_masks, d_audit, d_n, cap, c->n_pad, pc,
-                                                                               threshold, cand_lo, c->d_counters);
+    audit_append_kernel<<<c->sm_count * 4, 256, 0, c->stream>>>(d_audit, d_n, cap, c->d_cand, c->cand_cap, c->d_counters);
     c->tm.kernel_launches += 1;
     SPK_CUDA(c, cudaEventRecord(c->ev[EV_AUD1], c->stream));
     c->tm_pending |= TMP_AUDIT;
@@ -1004,13 +969,51 @@ int mi_pairs_exact(Ctx* c, const uint32_t* d_pi, const uint32_t* d_pj, uint64_t 
     return SPK_OK;
 }
 
-// *n_valid: entries written to d_refined (the int8 engine leaves invalid-marked holes in the candidate list, dropped here)
+// Refines the candidate list d_in[0, n): class buckets (counting sort into d_bucket), one converged cooperative launch per class
+// pair; d_refined / d_refined_wo run parallel to d_bucket. *n_valid: entries written (the int8 engine leaves invalid-marked
+// holes in its list, dropped here). d_cnt: 32 u64 of scratch. Needs the grouped planes (g_state == 1).
+int mi_refine_list(Ctx* c, const Candidate* d_in, uint64_t n, double pc, double wo_threshold, Candidate* d_bucket,
+                   spk_edge* d_refined, double* d_refined_wo, unsigned long long* d_cnt, uint64_t* n_valid) {
+    SPK_CUDA(c, cudaMemsetAsync(d_cnt, 0, 32 * sizeof(unsigned long long), c->stream));
+    const unsigned cgrid = (unsigned)std::min<unsigned long long>((n + 2047) / 2048, (unsigned long long)c->sm_count * 8);
+    classify_count_kernel<<<cgrid, 256, 0, c->stream>>>(d_in, n, c->d_masks, d_cnt);
+    unsigned long long h_cnt[9], h_off[10];
+    SPK_CUDA(c, cudaMemcpyAsync(h_cnt, d_cnt, sizeof h_cnt, cudaMemcpyDeviceToHost, c->stream));
+    SPK_CUDA(c, cudaStreamSynchronize(c->stream));
+    h_off[0] = 0; for (int q = 0; q < 9; ++q) h_off[q + 1] = h_off[q] + h_cnt[q];
+    if (n_valid) *n_valid = h_off[9];
+    SPK_CUDA(c, cudaMemcpyAsync(d_cnt + 16, h_off, 9 * sizeof(unsigned long long), cudaMemcpyHostToDevice, c->stream));
+    classify_scatter_kernel<<<cgrid, 256, 0, c->stream>>>(d_in, n, c->d_masks, d_cnt + 16, d_bucket);
+    c->tm.kernel_launches += 2;
+    for (int q = 0; q < 9; ++q) {
+        const unsigned long long n_q = h_cnt[q], o_q = h_off[q];
+        if (!n_q) continue;
+        const unsigned g = (unsigned)((n_q + 127) / 128);
+        static const bool coop = [] { const char* e = getenv("SPYDRPICK_B200_REFINE_COOP"); return !(e && e[0] == '0'); }();
+#define SPK_RCASE(Q, A, B) case Q: \
+            if (coop) mi_refine_coop_kernel<A, B, ((A) * (B) <= 4 ? 8 : ((A) * (B) == 8 ? 4 : 2))><<<g, 128, 0, c->stream>>>(c->d_masks, d_bucket + o_q, n_q, pc, c->w_total, wo_threshold, \
+                d_refined + o_q, d_refined_wo + o_q, c->d_counters, c->d_gbits, c->d_gval, c->d_gmarg, c->d_gH, c->g_NW); \
+            else mi_refine_class_kernel<A, B><<<g, 128, 0, c->stream>>>(c->d_masks, d_bucket + o_q, n_q, pc, c->w_total, wo_threshold, \
+                d_refined + o_q, d_refined_wo + o_q, c->d_counters, c->d_gbits, c->d_gval, c->d_gmarg, c->d_gH, c->g_NW); \
+            break;
+        switch (q) {
+            SPK_RCASE(0, 1, 1) SPK_RCASE(1, 1, 2) SPK_RCASE(2, 1, 4)
+            SPK_RCASE(3, 2, 1) SPK_RCASE(4, 2, 2) SPK_RCASE(5, 2, 4)
+            SPK_RCASE(6, 4, 1) SPK_RCASE(7, 4, 2) SPK_RCASE(8, 4, 4)
+        }
+#undef SPK_RCASE
+        c->tm.kernel_launches += 1;
+    }
+    SPK_CUDA(c, cudaGetLastError());
+    return SPK_OK;
+}
+
+// the scan's own candidate list (c->d_cand -> c->d_refined, bucketed copy in c->d_cand2)
 int mi_refine_candidates(Ctx* c, uint64_t ncand, double pc, double wo_threshold, uint64_t* n_valid) {
     if (n_valid) *n_valid = ncand;
     if (ncand == 0) return SPK_OK;
     { int rg = ensure_grouped(c, pc); if (rg) return rg; }
     if (c->g_state == 1) {
-        // bucket by class pair (counting sort), then one converged launch per class
         unsigned long long* d_cnt = (unsigned long long*)scratch(c, 32 * sizeof(unsigned long long));
         if (!d_cnt) return fail(c, SPK_E_NOMEM, "scratch allocation failed");
         if (c->cand2_cap < c->cand_cap) {
@@ -1018,51 +1021,70 @@ int mi_refine_candidates(Ctx* c, uint64_t ncand, double pc, double wo_threshold,
             if (cudaMalloc(&c->d_cand2, c->cand_cap * sizeof(Candidate)) != cudaSuccess) { cudaGetLastError(); return fail(c, SPK_E_NOMEM, "candidate sort buffer"); }
             c->cand2_cap = c->cand_cap;
         }
-        SPK_CUDA(c, cudaMemsetAsync(d_cnt, 0, 32 * sizeof(unsigned long long), c->stream));
-        const unsigned cgrid = (unsigned)std::min<unsigned long long>((ncand + 2047) / 2048, (unsigned long long)c->sm_count * 8);
-        classify_count_kernel<<<cgrid, 256, 0, c->stream>>>(c->d_cand, ncand, c->d_masks, d_cnt);
-        unsigned long long h_cnt[9], h_off[10];
-        SPK_CUDA(c, cudaMemcpyAsync(h_cnt, d_cnt, sizeof h_cnt, cudaMemcpyDeviceToHost, c->stream));
-        SPK_CUDA(c, cudaStreamSynchronize(c->stream));
-        h_off[0] = 0; for (int q = 0; q < 9; ++q) h_off[q + 1] = h_off[q] + h_cnt[q];
-        if (n_valid) *n_valid = h_off[9];
-        SPK_CUDA(c, cudaMemcpyAsync(d_cnt + 16, h_off, 9 * sizeof(unsigned long long), cudaMemcpyHostToDevice, c->stream));
-        classify_scatter_kernel<<<cgrid, 256, 0, c->stream>>>(c->d_cand, ncand, c->d_masks, d_cnt + 16, c->d_cand2);
-        c->tm.kernel_launches += 2;
-        for (int q = 0; q < 9; ++q) {
-            const unsigned long long n_q = h_cnt[q], o_q = h_off[q];
-            if (!n_q) continue;
-            const unsigned g = (unsigned)((n_q + 127) / 128);
-            static const bool coop = [] { const char* e = getenv("SPYDRPICK_B200_REFINE_COOP"); return !(e && e[0] == '0'); }();
-#define SPK_RCASE(Q, A, B) case Q: \
-                if (coop) mi_refine_coop_kernel<A, B, ((A) * (B) <= 4 ? 8 : ((A) * (B) == 8 ? 4 : 2))><<<g, 128, 0, c->stream>>>(c->d_masks, c->d_cand2 + o_q, n_q, pc, c->w_total, wo_threshold, \
-                    c->d_refined + o_q, c->d_refined_wo + o_q, c->d_counters, c->d_gbits, c->d_gval, c->d_gmarg, c->d_gH, c->g_NW); \
-                else mi_refine_class_kernel<A, B><<<g, 128, 0, c->stream>>>(c->d_masks, c->d_cand2 + o_q, n_q, pc, c->w_total, wo_threshold, \
-                    c->d_refined + o_q, c->d_refined_wo + o_q, c->d_counters, c->d_gbits, c->d_gval, c->d_gmarg, c->d_gH, c->g_NW); \
-                break;
-            switch (q) {
-                SPK_RCASE(0, 1, 1) SPK_RCASE(1, 1, 2) SPK_RCASE(2, 1, 4)
-                SPK_RCASE(3, 2, 1) SPK_RCASE(4, 2, 2) SPK_RCASE(5, 2, 4)
-                SPK_RCASE(6, 4, 1) SPK_RCASE(7, 4, 2) SPK_RCASE(8, 4, 4)
-            }
-#undef SPK_RCASE
-            c->tm.kernel_launches += 1;
-        }
+        return mi_refine_list(c, c->d_cand, ncand, pc, wo_threshold, c->d_cand2, c->d_refined, c->d_refined_wo, d_cnt, n_valid);
     }
-    else
-        mi_refine_kernel<<<refine_grid(c, ncand), EX_WARPS * 32, 0, c->stream>>>(c->d_colmajor, c->d_w, c->d_masks, c->d_cand, ncand,
-                                                                                c->n_pad, pc, c->d_refined, c->d_refined_wo,
-                                                                                c->d_counters, nullptr, nullptr, nullptr, 0);
+    mi_refine_kernel<<<refine_grid(c, ncand), EX_WARPS * 32, 0, c->stream>>>(c->d_colmajor, c->d_w, c->d_masks, c->d_cand, ncand,
+                                                                            c->n_pad, pc, c->d_refined, c->d_refined_wo,
+                                                                            c->d_counters, nullptr, nullptr, nullptr, 0);
     c->tm.kernel_launches += 1;
     SPK_CUDA(c, cudaGetLastError());
     return SPK_OK;
 }
 
-int mi_compact(Ctx* c, uint64_t ncand, const spk_scan_params& p, uint64_t circle) {
+// MI of `total` pairs in `nseg` equal segments through the cooperative refine kernels: out[seg * per + k] = the MI values of
+// segment seg in arbitrary order (the threshold estimator sorts every segment anyway). work = caller's scratch:
+// 2 * total Candidates + total spk_edge + total doubles + 32 + nseg u64. Returns SPK_E_INVALID when the planes are not grouped.
+__global__ void pairs_to_candidates_kernel(const uint32_t* __restrict__ pi, const uint32_t* __restrict__ pj, unsigned long long total,
+                                           unsigned long long per, Candidate* __restrict__ out) {
+    const unsigned long long p = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= total) return;
+    Candidate cd; cd.i = pi[p]; cd.j = pj[p]; cd.mi32 = __int_as_float(0x7fc00000); cd.pad = (uint32_t)(p / per);
+    out[p] = cd;
+}
+__global__ void scatter_segment_mi_kernel(const Candidate* __restrict__ bucket, const spk_edge* __restrict__ refined, unsigned long long n,
+                                          unsigned long long per, unsigned long long* __restrict__ seg_fill, double* __restrict__ out) {
+    const unsigned long long p = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    const unsigned long long seg = bucket[p].pad;
+    const unsigned long long k = atomicAdd(&seg_fill[seg], 1ull);
+    if (k < per) out[seg * per + k] = refined[p].mi;
+}
+size_t mi_pairs_segmented_scratch(uint64_t total, uint32_t nseg) {
+    return (size_t)total * (2 * sizeof(Candidate) + sizeof(spk_edge) + 8) + (32 + (size_t)nseg) * 8 + 1024;
+}
+int mi_pairs_segmented(Ctx* c, const uint32_t* d_pi, const uint32_t* d_pj, uint64_t total, uint64_t per, uint32_t nseg, double pc,
+                       double* d_mi, void* work) {
+    if (total == 0) return SPK_OK;
+    { int rg = ensure_grouped(c, pc); if (rg) return rg; }
+    if (c->g_state != 1) return SPK_E_INVALID;
+    uint8_t* w = (uint8_t*)work;
+    Candidate* d_in = (Candidate*)w; w += (size_t)total * sizeof(Candidate);
+    Candidate* d_bucket = (Candidate*)w; w += (size_t)total * sizeof(Candidate);
+    spk_edge* d_ref = (spk_edge*)w; w += (size_t)total * sizeof(spk_edge);
+    double* d_wo = (double*)w; w += (size_t)total * 8;
+    w = (uint8_t*)(((uintptr_t)w + 255) & ~(uintptr_t)255);
+    unsigned long long* d_cnt = (unsigned long long*)w; unsigned long long* d_fill = d_cnt + 32;
+    SPK_CUDA(c, cudaEventRecord(c->ev[EV_PAIRS0], c->stream));
+    pairs_to_candidates_kernel<<<(unsigned)((total + 255) / 256), 256, 0, c->stream>>>(d_pi, d_pj, total, per, d_in);
+    SPK_CUDA(c, cudaMemsetAsync(d_fill, 0, (size_t)nseg * 8, c->stream));
+    uint64_t nv = 0;
+    int r = mi_refine_list(c, d_in, total, pc, INFINITY, d_bucket, d_ref, d_wo, d_cnt, &nv); if (r) return r;
+    if (nv != total) return fail(c, SPK_E_INVALID, "mi_pairs_segmented: %llu of %llu pairs classified", (unsigned long long)nv, (unsigned long long)total);
+    scatter_segment_mi_kernel<<<(unsigned)((total + 255) / 256), 256, 0, c->stream>>>(d_bucket, d_ref, total, per, d_fill, d_mi);
+    c->tm.kernel_launches += 2;
+    SPK_CUDA(c, cudaEventRecord(c->ev[EV_PAIRS1], c->stream));
+    c->tm_pending |= TMP_PAIRS;
+    SPK_CUDA(c, cudaGetLastError());
+    return SPK_OK;
+}
+
+// audit_cand_lo: NaN = the list holds no audit entries; else thr - band of the filter (entries marked pad = 1 are judged, not saved)
+int mi_compact(Ctx* c, uint64_t ncand, const spk_scan_params& p, uint64_t circle, float audit_cand_lo) {
     if (ncand == 0) return SPK_OK;
+    const Candidate* meta = (audit_cand_lo == audit_cand_lo) ? (c->g_state == 1 ? c->d_cand2 : c->d_cand) : nullptr;
     mi_compact_kernel<<<(unsigned)((ncand + 255) / 256), 256, 0, c->stream>>>(
         c->d_refined, c->d_refined_wo, ncand, c->d_pos, p.threshold, p.ld_threshold, p.linear_genome, circle,
-        (unsigned long long*)c->d_colmax, c->d_edges, c->edges_cap, c->d_wo, c->wo_cap, c->d_counters);
+        (unsigned long long*)c->d_colmax, c->d_edges, c->edges_cap, c->d_wo, c->wo_cap, c->d_counters, meta, audit_cand_lo);
     c->tm.kernel_launches += 1;
     SPK_CUDA(c, cudaGetLastError());
     return SPK_OK;
@@ -1089,7 +1111,7 @@ int mi_scan_exact(Ctx* c, const spk_scan_params& p, uint64_t circle) {
             SPK_CUDA(c, cudaEventRecord(c->ev[EV_REF0], c->stream));
             int r = mi_refine_candidates(c, cnt, p.pseudocount, p.threshold); if (r) return r;
             SPK_CUDA(c, cudaEventRecord(c->ev[EV_REF1], c->stream));
-            r = mi_compact(c, cnt, p, circle); if (r) return r;
+            r = mi_compact(c, cnt, p, circle, __builtin_nanf("")); if (r) return r;
             SPK_CUDA(c, cudaEventRecord(c->ev[EV_CMP1], c->stream));
             SPK_CUDA(c, cudaEventSynchronize(c->ev[EV_CMP1]));
             float t1, t2;

@@ -294,3 +294,14 @@ def test_candidate_chunks_have_no_effect_on_results(ctx):
     assert np.array_equal(a["colmax"], b["colmax"])
     assert a["n_candidates"] >= a["n_edges"]
     assert a["n_candidates"] <= 6000 * 5999 // 2                   # valid candidates only: holes of the reserved chunks are not counted
+
+
+def test_mma_peak_probe_is_a_plausible_denominator(ctx):
+    """spk_debug_i8_peak (the MMA-only kernel bench.py's roofline divides by): a rate between the cuBLASLt int8 GEMM class and a
+    generous bound above the nominal 4.5 POP/s of a B200, reproducible to a few per cent."""
+    ctx.debug_i8_peak(20000, 1)                                   # warm-up (module load, clocks)
+    a, ms_a = ctx.debug_i8_peak(60000, 1)
+    b, ms_b = ctx.debug_i8_peak(60000, 2)
+    assert 2500.0 < a < 6000.0 and 2500.0 < b < 6000.0, (a, b)
+    assert abs(a / b - 1.0) < 0.1
+    assert ms_b == pytest.approx(2 * ms_a, rel=0.15)
