@@ -27,7 +27,7 @@ python tools/ncu_summarise.py launches gpurun_out/${TAG}_launches_raw.csv > gpur
 head -30 gpurun_out/${TAG}_launches.csv
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:mi_i8_kernel -s 3 -c 1 -o gpurun_out/${TAG}_mi_i8_full -f \
   python bench.py --steps 1 --warmup 1 --no-e2e --no-cpu-baseline --no-peaks > gpurun_out/${TAG}_ncu_f.log 2>&1
-timeout 1200 ncu --set full --clock-control none --import-source on -k regex:'hamming_csa|mi_refine_coop|aracne_hash|lists_and_hash|gbits_build|mi_compact|mi_audit|i8_expand|i8_colrec|mi_pairs_grouped' -s 10 -c 14 -o gpurun_out/${TAG}_others_full -f \
+timeout 1200 ncu --set full --clock-control none --import-source on -k regex:'hamming_csa|mi_refine_coop|aracne_hash|lists_and_hash|gbits_build|mi_compact|i8_prep|audit_append|scatter_segment|sample_pairs' -s 24 -c 18 -o gpurun_out/${TAG}_others_full -f \
   python bench.py --steps 1 --warmup 1 --no-e2e --no-cpu-baseline --no-peaks > gpurun_out/${TAG}_ncu_o.log 2>&1
 python tools/ncu_summarise.py full gpurun_out/${TAG}_mi_i8_full.ncu-rep gpurun_out/${TAG}_others_full.ncu-rep > gpurun_out/${TAG}_ncu_full_summary.csv
 ls -la gpurun_out | tail -14
