@@ -505,7 +505,7 @@ mi_refine_thread_kernel(const uint8_t* __restrict__ masks, const Candidate* __re
     }
 #pragma unroll
     for (int o = 16; o; o >>= 1) err = fmax(err, __shfl_xor_sync(0xffffffffu, err, o));
-    if ((threadIdx.x & 31) == 0 && err > 0.0) atomicMax(&counters[3], f64_ordered(err));
+    if ((threadIdx.x & 31) == 0 && err > 0.0 && f64_ordered(err) > *(volatile unsigned long long*)&counters[3]) atomicMax(&counters[3], f64_ordered(err));
 }
 
 // ---- class-sorted refine: candidates are bucketed by the (rows_i, rows_j) class pair so that every launch runs
@@ -575,7 +575,7 @@ mi_refine_class_kernel(const uint8_t* __restrict__ masks, const Candidate* __res
     }
 #pragma unroll
     for (int o = 16; o; o >>= 1) err = fmax(err, __shfl_xor_sync(0xffffffffu, err, o));
-    if ((threadIdx.x & 31) == 0 && err > 0.0) atomicMax(&counters[3], f64_ordered(err));
+    if ((threadIdx.x & 31) == 0 && err > 0.0 && f64_ordered(err) > *(volatile unsigned long long*)&counters[3]) atomicMax(&counters[3], f64_ordered(err));
 }
 
 // Cooperative version of mi_refine_class_kernel. Thread-per-pair plane loads are 32 scattered 16-byte requests per
@@ -686,7 +686,7 @@ mi_refine_coop_kernel(const uint8_t* __restrict__ masks, const Candidate* __rest
     }
 #pragma unroll
     for (int o = 16; o; o >>= 1) err = fmax(err, __shfl_xor_sync(0xffffffffu, err, o));
-    if (lane == 0 && err > 0.0) atomicMax(&counters[3], f64_ordered(err));
+    if (lane == 0 && err > 0.0 && f64_ordered(err) > *(volatile unsigned long long*)&counters[3]) atomicMax(&counters[3], f64_ordered(err));   // (read first: the maximum settles early, 4 x 10^5 same-address atomics otherwise)
 }
 
 // ---- K2b: explicit pair list ---------------------------------------------------------------
@@ -766,7 +766,7 @@ audit_append_kernel(const Candidate* __restrict__ audit, const unsigned long lon
     }
 }
 
-__global__ void mi_compact_kernel(const spk_edge* __restrict__ refined, const double* __restrict__ refined_wo,
+__global__ void __launch_bounds__(256) mi_compact_kernel(const spk_edge* __restrict__ refined, const double* __restrict__ refined_wo,
                                   unsigned long long ncand, const uint64_t* __restrict__ pos,
                                   double threshold, unsigned long long ld_threshold, int linear, unsigned long long circle,
                                   unsigned long long* __restrict__ colmax_ord,
@@ -807,26 +807,29 @@ __global__ void mi_compact_kernel(const spk_edge* __restrict__ refined, const do
         keep = threshold < e.mi;                 // strict (mi.hpp:430,454); NaN never kept
         keep_wo = keep && (m2 == m2);
     }
-    const uint32_t bal = __ballot_sync(0xffffffffu, keep);
-    if (bal) {
-        unsigned long long base = 0;
-        if (lane == 0) base = atomicAdd(&counters[1], (unsigned long long)__popc(bal));
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (keep) {
-            const unsigned long long idx = base + __popc(bal & ((1u << lane) - 1u));
-            if (idx < edges_cap) edges[idx] = e; else counters[4] = 1ull;
-        }
+    // slots: ONE atomicAdd per block and list (per-warp reservations were 8 x 10^5 atomics on two addresses, which serialise in
+    // the L2 slice that owns them: most of the kernel's 0.76 ms). blockDim.x == 256.
+    __shared__ unsigned int s_cnt[2][8];
+    __shared__ unsigned long long s_base[2];
+    const uint32_t wid = threadIdx.x / 32;
+    const uint32_t bal = __ballot_sync(0xffffffffu, keep), bal2 = __ballot_sync(0xffffffffu, keep_wo);
+    if (lane == 0) { s_cnt[0][wid] = __popc(bal); s_cnt[1][wid] = __popc(bal2); }
+    __syncthreads();
+    if (threadIdx.x < 2) {
+        unsigned int tot = 0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) { const unsigned int v = s_cnt[threadIdx.x][w]; s_cnt[threadIdx.x][w] = tot; tot += v; }    // exclusive prefix
+        s_base[threadIdx.x] = tot ? atomicAdd(&counters[1 + threadIdx.x], (unsigned long long)tot) : 0ull;
     }
-    const uint32_t bal2 = __ballot_sync(0xffffffffu, keep_wo);
-    if (bal2) {
-        unsigned long long base = 0;
-        if (lane == 0) base = atomicAdd(&counters[2], (unsigned long long)__popc(bal2));
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (keep_wo) {
-            const unsigned long long idx = base + __popc(bal2 & ((1u << lane) - 1u));
-            spk_edge e2 = e; e2.mi = m2;
-            if (idx < wo_cap) wo[idx] = e2; else counters[4] = 1ull;
-        }
+    __syncthreads();
+    if (keep) {
+        const unsigned long long idx = s_base[0] + s_cnt[0][wid] + __popc(bal & ((1u << lane) - 1u));
+        if (idx < edges_cap) edges[idx] = e; else counters[4] = 1ull;
+    }
+    if (keep_wo) {
+        const unsigned long long idx = s_base[1] + s_cnt[1][wid] + __popc(bal2 & ((1u << lane) - 1u));
+        spk_edge e2 = e; e2.mi = m2;
+        if (idx < wo_cap) wo[idx] = e2; else counters[4] = 1ull;
     }
 }
 
