@@ -414,6 +414,10 @@ __global__ void sample_pairs_kernel(uint32_t* __restrict__ pi, uint32_t* __restr
     while (row_start(i + 1) <= x) ++i;
     pi[t] = (uint32_t)i; pj[t] = (uint32_t)(i + 1 + (x - row_start(i)));
 }
+__global__ void segment_ids_kernel(uint32_t* __restrict__ seg, unsigned long long total, unsigned long long per) {
+    const unsigned long long p = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < total) seg[p] = (uint32_t)(p / per);
+}
 __global__ void pick_kth_kernel(const double* __restrict__ sorted, uint64_t count, uint64_t idx, uint32_t iterations, double* __restrict__ out) {
     const uint32_t it = blockIdx.x * blockDim.x + threadIdx.x;
     if (it < iterations) out[it] = sorted[(uint64_t)it * count + idx];
@@ -457,16 +461,26 @@ int spk_determine_mi_threshold_ex(spk_ctx* c, uint64_t n_values, uint64_t thresh
     size_t tmpb = 0;
     std::vector<int> h_off(nit + 1);
     for (uint32_t k = 0; k <= nit; ++k) h_off[k] = (int)(tp * k);
-    if (nit) cub::DeviceSegmentedRadixSort::SortKeys(nullptr, tmpb, (const double*)nullptr, (double*)nullptr, (int)total, (int)nit, (const int*)nullptr, (const int*)nullptr, 0, 64, c->stream);
+    // per-iteration ascending order from two GLOBAL stable radix sorts (by value, then by iteration): a segmented sort runs one
+    // block per segment -- 1.1 ms for 10 x 100,000 values against 0.2 ms this way
+    uint32_t seg_bits = 1; while ((1u << seg_bits) < std::max(nit, 2u)) ++seg_bits;
+    if (nit) {
+        size_t t1 = 0, t2 = 0;
+        cub::DeviceRadixSort::SortPairs(nullptr, t1, (const double*)nullptr, (double*)nullptr, (const uint32_t*)nullptr, (uint32_t*)nullptr, (int)total, 0, 64, c->stream);
+        cub::DeviceRadixSort::SortPairs(nullptr, t2, (const uint32_t*)nullptr, (uint32_t*)nullptr, (const double*)nullptr, (double*)nullptr, (int)total, 0, (int)seg_bits, c->stream);
+        tmpb = std::max(t1, t2);
+    }
     const size_t offb = ((size_t)(nit + 1) * 4 + 255) & ~(size_t)255, thrb = ((size_t)iterations * 8 + 255) & ~(size_t)255;
-    const size_t workb = mi_pairs_segmented_scratch(total, nit);
-    uint8_t* base = (uint8_t*)scratch(c, 2 * ib + 2 * ob + offb + thrb + ((tmpb + 255) & ~(size_t)255) + 256 + workb);
+    const size_t workb = (mi_pairs_segmented_scratch(total, nit) + 255) & ~(size_t)255;
+    uint8_t* base = (uint8_t*)scratch(c, 2 * ib + 2 * ob + offb + thrb + ((tmpb + 255) & ~(size_t)255) + 256 + workb + 2 * ib + ob);
     if (!base) return fail(c, SPK_E_NOMEM, "scratch allocation failed");
     uint32_t* d_pi = (uint32_t*)base; uint32_t* d_pj = (uint32_t*)(base + ib);
     double* d_mi = (double*)(base + 2 * ib); double* d_sorted = (double*)(base + 2 * ib + ob);
     int* d_off = (int*)(base + 2 * ib + 2 * ob); double* d_thr = (double*)(base + 2 * ib + 2 * ob + offb);
     void* d_tmp = base + 2 * ib + 2 * ob + offb + thrb;
-    void* d_work = base + 2 * ib + 2 * ob + offb + thrb + ((tmpb + 255) & ~(size_t)255) + 256;
+    uint8_t* d_work = base + 2 * ib + 2 * ob + offb + thrb + ((tmpb + 255) & ~(size_t)255) + 256;
+    uint32_t* d_seg = (uint32_t*)(d_work + workb); uint32_t* d_seg2 = (uint32_t*)(d_work + workb + ib);
+    double* d_byval = (double*)(d_work + workb + 2 * ib);
     SPK_CUDA(c, cudaMemsetAsync(d_thr, 0, (size_t)iterations * 8, c->stream));
     if (nit) {
         if (sampler == SPK_SAMPLER_REFERENCE) {
@@ -502,7 +516,9 @@ int spk_determine_mi_threshold_ex(spk_ctx* c, uint64_t n_values, uint64_t thresh
         if (r == SPK_E_INVALID && c->g_state != 1) r = mi_pairs_exact(c, d_pi, d_pj, total, pc, d_mi);
         if (r) return r;
         SPK_CUDA(c, cudaMemcpyAsync(d_off, h_off.data(), (size_t)(nit + 1) * 4, cudaMemcpyHostToDevice, c->stream));
-        SPK_CUDA(c, cub::DeviceSegmentedRadixSort::SortKeys(d_tmp, tmpb, (const double*)d_mi, d_sorted, (int)total, (int)nit, d_off, d_off + 1, 0, 64, c->stream));
+        segment_ids_kernel<<<(unsigned)((total + 255) / 256), 256, 0, c->stream>>>(d_seg, total, tp);
+        SPK_CUDA(c, cub::DeviceRadixSort::SortPairs(d_tmp, tmpb, (const double*)d_mi, d_byval, (const uint32_t*)d_seg, d_seg2, (int)total, 0, 64, c->stream));
+        SPK_CUDA(c, cub::DeviceRadixSort::SortPairs(d_tmp, tmpb, (const uint32_t*)d_seg2, d_seg, (const double*)d_byval, d_sorted, (int)total, 0, (int)seg_bits, c->stream));
         // this rank's iterations sit at rank, rank + world, ...: write them to their global slots
         std::vector<double*> dummy;
         for (uint32_t k = 0; k < nit; ++k)
