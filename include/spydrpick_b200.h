@@ -139,8 +139,8 @@ int spk_mi_pairs(spk_ctx* ctx, const uint32_t* pi, const uint32_t* pj, uint64_t 
  * seeds std::mt19937 from the clock (:178); here the seed is explicit (seed+iteration). */
 int spk_determine_mi_threshold(spk_ctx* ctx, uint64_t n_values, uint64_t threshold_pairs /*0=auto*/,
                                uint32_t iterations, double pseudocount, uint64_t seed, double* threshold);
-/* The same estimator with a choice of pair sampler. Either way all iterations go through one K2b launch and one segmented sort on
- * the device; only `iterations` doubles come back. n_values >= L(L-1)/2 is SPK_E_INVALID (the reference indexes out of range).
+/* The same estimator with a choice of pair sampler. Either way all iterations go through the device together (class-bucketed fp64
+ * kernels + two global radix sorts); only `iterations` doubles come back. n_values >= L(L-1)/2 is SPK_E_INVALID (the reference indexes out of range).
  *   SPK_SAMPLER_REFERENCE  the reference's sample_pairs() (std::mt19937(seed + iteration), duplicates rejected; SpydrPick.hpp:171-207),
  *                          one host thread per iteration -- what spk_determine_mi_threshold uses; reproducible against the oracle
  *   SPK_SAMPLER_DEVICE     distinct pairs from a keyed Feistel permutation of the pair index space, generated on the device */
@@ -264,7 +264,7 @@ typedef struct {
     float    seed_ms;                       /* int8 engine: the colmax seed launch, included in gemm_ms (main pass = gemm_ms - seed_ms) */
     float    exchange_ms;                   /* collective scan: counts + edge all-gather + colmax all-reduce + run merge */
     float    audit_ms;                      /* filter audit: appending the audit sample to the candidate list (its fp64 recomputation is part of refine_ms) */
-    float    threshold_ms;                  /* threshold estimator: sampling + K2b + segmented sort (device part) */
+    float    threshold_ms;                  /* threshold estimator: sampling + K2b + sorts (device part) */
 } spk_timings;
 int spk_get_timings(spk_ctx* ctx, spk_timings* out);
 

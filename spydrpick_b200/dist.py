@@ -1,4 +1,7 @@
-"""Multi-GPU plumbing for the sharded hot path (torch.distributed; NCCL on GPUs, gloo in CPU tests).
+"""The CALLER-DRIVEN multi-GPU recipe over torch.distributed (NCCL on GPUs, gloo in CPU tests). The product path no longer
+needs it: the exchange lives inside the library (csrc/spk_comm.cu; `spk_comm_init_rank` + collective `spk_mi_scan` /
+`spk_aracne`, what bench.py and the CLI's --gpus use). Kept for hosts that own their communication and for the gloo tests of
+its CPU-side logic (tests/test_dist_gloo.py).
 
 The scan shards the upper-triangle tile space (`part_index = rank`); the one exchange step before ARACNE
 is an all-gather of the per-rank edge lists plus a max-reduction of colmax. ARACNE shards
