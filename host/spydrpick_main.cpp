@@ -122,7 +122,8 @@ void print_help() {
         "  --output-state-frequencies            Write column-wise state frequencies to file.\n"
         "  --output-sample-weights               Output sample weights.\n"
         "  --output-sample-groups                Output sample groups (accepted; unused by SpydrPick).\n"
-        "  --output-sample-distance-matrix       Output triangular sample-sample Hamming distance matrix (not available in this build).\n"
+        "  --output-sample-distance-matrix       Output triangular sample-sample Hamming distance matrix (not available: the reference\n"
+        "                                        itself recurses without end in Alignment::distance_matrix() and crashes).\n"
         "  --output-indexing-base arg (=1)       Base index for output.\n"
         "  --output-alignment                    Write alignment to file.\n"
         "  --output-filtered-alignment           Write filtered alignment to file.\n"
@@ -673,11 +674,32 @@ int main(int argc, char** argv) {
         std::vector<uint64_t> all(A.L); for (uint64_t c = 0; c < A.L; ++c) all[c] = c;
         write_alignment(A, all, o, V);
     }
-    if (o.output_state_frequencies) {                                                                         // Alignment_utility.hpp:471-500 (the un-weighted table)
-        std::ofstream out(unique_name(prefix + ".frequencies.txt"));
+    if (o.output_state_frequencies) {
+        // apegrunt::output_state_frequencies (Alignment_utility.hpp:431-449, 470-580): per column the fraction of samples in each of
+        // the five states, "f f f f f \n" at the stream's default precision; with reweighting also the weight-normalised table.
+        // The two *_distribution.txt summaries (apegrunt's Boost.Accumulators extension) are not written.
         std::vector<uint32_t> cnt(A.L * 5, 0);
-        for (uint32_t s = 0; s < n; ++s) { const uint8_t* row = A.states + (size_t)s * A.L_src; for (uint64_t c = 0; c < A.L; ++c) cnt[c * 5 + row[A.src_col(c)]]++; }
-        for (uint64_t c = 0; c < A.L; ++c) { for (int a = 0; a < 5; ++a) out << double(cnt[c * 5 + a]) / double(n) << " "; out << "\n"; }
+        std::vector<double> wcnt(o.no_sample_reweighting ? 0 : A.L * 5, 0.0);
+        parallel_chunks(host_threads(o), A.L, [&](size_t b, size_t e, unsigned) {
+            for (uint32_t s = 0; s < n; ++s) {
+                const uint8_t* row = A.states + (size_t)s * A.L_src; const double ws = w[s];
+                for (size_t c = b; c < e; ++c) { const uint8_t x = row[A.src_col(c)]; cnt[c * 5 + x]++; if (!wcnt.empty()) wcnt[c * 5 + x] += ws; }
+            }
+        });
+        auto write_table = [&](const std::string& path, auto value) {
+            const std::string fn = unique_name(path);
+            if (V) std::cout << "apegrunt: write " << (path.find("weighted") != std::string::npos ? "weighted " : "") << "columnwise state frequencies to file \"" << fn << "\"\n";
+            std::ofstream out(fn);
+            char t[32]; std::string line;
+            for (uint64_t c = 0; c < A.L; ++c) {
+                line.clear();
+                for (int a = 0; a < 5; ++a) { std::snprintf(t, sizeof t, "%g ", value(c, a)); line += t; }     // operator<<(double): %g, 6 digits
+                line += "\n"; out << line;
+            }
+        };
+        write_table(prefix + ".frequencies.txt", [&](uint64_t c, int a) { return double(cnt[c * 5 + a]) / double(n); });
+        if (!o.no_sample_reweighting) write_table(prefix + ".weighted_frequencies.txt", [&](uint64_t c, int a) { return wcnt[c * 5 + a] / neff; });
+        if (V) std::cout << "SpydrPick: the frequency_distribution.txt summaries are not written by this build\n";
     }
 
     // -- saving threshold (src/SpydrPick.cpp:336-356; SpydrPick.hpp:285-343)

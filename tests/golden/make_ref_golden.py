@@ -145,6 +145,10 @@ def main():
                                          "--aracne-block-size", "500"], note="non-default pseudocount, ARACNE tolerance and block size")
     run_case("filter_thresholds", raw, ["--mi-threshold", "0.2", "--maf-threshold", "0.05", "--gap-threshold", "0.05", "--output-filtered-alignment"],
              note="non-default filter thresholds + filtered alignment export")
+    run_case("state_frequencies", raw, ["--mi-threshold", "0.2", "--output-state-frequencies"],
+             note="--output-state-frequencies on the filtered, reweighted alignment (the two *_distribution.txt files come from the Boost.Accumulators stand-in of oracle/ref_shims and are not pins)")
+    # (--output-sample-distance-matrix has no fixture: Alignment::distance_matrix() is not implemented by the reference's storage class
+    #  and the CRTP forwarder calls itself until the stack overflows)
     # automatic threshold: the estimator is clock-seeded, so several runs give the spread the parity test accepts
     run_case("auto_threshold", raw, ["--mi-values", "20000"], repeat=7, note="--mi-threshold -1 (automatic), 7 runs: mi_save_thresholds_printed")
     size = sum(os.path.getsize(os.path.join(dp, f)) for dp, _, fs in os.walk(OUT) for f in fs)

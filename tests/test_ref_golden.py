@@ -70,3 +70,23 @@ def test_oracle_threshold_estimator_vs_reference_runs():
     for seed in (1, 2, 3):
         t = orc.determine_mi_threshold(f, w, 20000, seed=seed)
         assert -0.005 <= t / ref_thr.mean() - 1.0 <= 0.015, (t, ref_thr)
+
+
+def test_state_frequency_tables_of_the_reference():
+    """--output-state-frequencies (apegrunt::output_state_frequencies, Alignment_utility.hpp:431-449): per filtered column the
+    fraction of samples in each state, un-weighted and weight-normalised, as the reference's stream prints doubles ("%g")."""
+    case = refcmp.load_case("state_frequencies")
+    states, _ = refcmp.fasta_states(refcmp.read_gz(case, case["name"] + ".fasta"))
+    keep = orc.filter_columns(states)
+    f = np.ascontiguousarray(states[:, keep])
+    n, L = f.shape
+    w = orc.weights_from_counts(orc.neighbour_counts(f, int(0.9 * float(L)), True))
+    onehot = (f[:, :, None] == np.arange(5)[None, None, :])
+    unw = onehot.sum(axis=0) / float(n)
+    wtd = (onehot * w[:, None, None]).sum(axis=0) / w.sum()
+    fmt = lambda t: "".join("".join("%g " % x for x in row) + "\n" for row in t)
+    assert fmt(unw) == refcmp.read_gz(case, refcmp.output_named(case, ".frequencies.txt").replace("weighted_", ""))
+    got = fmt(wtd).split(); exp = refcmp.read_gz(case, refcmp.output_named(case, ".weighted_frequencies.txt")).split()
+    assert len(got) == len(exp)
+    # the weighted sums are accumulated in a different order: equal to the printed 6 digits up to one unit of the last one
+    assert all(a == b or abs(float(a) - float(b)) <= 1.5e-6 * max(abs(float(b)), 1e-6) + 1e-12 for a, b in zip(got, exp))
