@@ -499,7 +499,10 @@ def run_b200(args):
     kernels["K2r mi_refine_coop_kernel x9"]["traffic"] = _traffic("mi_refine_coop_kernel")
     kernels["K3 aracne_hash_kernel"]["traffic"] = _traffic("aracne_hash_kernel")
     kernels["K3 adjacency build (degree histogram + scan + one stable radix sort + per-node hash tables)"]["traffic_lists_and_hash_kernel"] = _traffic("lists_and_hash_kernel")
-    kernels["filter audit"]["traffic"] = _traffic("mi_audit")
+    kernels["filter audit"]["traffic"] = _traffic("audit_append_kernel")
+    kernels["operand prep i8_prep_kernel"] = {"ms": stages.get("expand_ms", 0.0), "bound": "hbm (write)", "algorithmic_GBps": (n * L + 2.0 * 1.7 * L * ((n + 127) // 128 * 128)) / (stages["expand_ms"] * 1e-3) / 1e9 if stages.get("expand_ms") else None,
+                                              "hbm_peak_GBps": hbm, "traffic": _traffic("i8_prep_kernel")}
+    kernels["compaction mi_compact_kernel"] = {"ms": stages.get("compact_ms", 0.0), "bound": "hbm", "traffic": _traffic("mi_compact_kernel")}
 
     e2e = None
     if not args.no_e2e:
