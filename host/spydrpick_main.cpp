@@ -552,10 +552,16 @@ int main(int argc, char** argv) {
     std::string ctx_error; double ctx_seconds = 0.0;
     std::thread ctx_thread([&]() {
         Timer t;
-        for (int g = 0; g < G; ++g) {
-            const int dev = (G == 1) ? o.device : ((o.device < 0 ? 0 : o.device) + g);
-            if (spk_create(&ctxs[g], dev, (V && g == 0) ? 1 : 0) != SPK_OK) { ctx_error = std::string("cannot initialise the CUDA context: ") + spk_last_error(nullptr); return; }
-        }
+        // one thread per device: primary-context creation is per device and takes most of a second each
+        std::vector<std::string> errs(G);
+        std::vector<std::thread> th;
+        for (int g = 0; g < G; ++g)
+            th.emplace_back([&, g]() {
+                const int dev = (G == 1) ? o.device : ((o.device < 0 ? 0 : o.device) + g);
+                if (spk_create(&ctxs[g], dev, (V && g == 0) ? 1 : 0) != SPK_OK) errs[g] = std::string("cannot initialise the CUDA context: ") + spk_last_error(nullptr);
+            });
+        for (auto& x : th) x.join();
+        for (int g = 0; g < G; ++g) if (!errs[g].empty()) { ctx_error = errs[g]; return; }
         if (G > 1 && spk_comm_init_all(ctxs.data(), G) != SPK_OK) ctx_error = std::string("NCCL communicator: ") + spk_last_error(ctxs[0]);
         ctx_seconds = t.lap();
     });
