@@ -571,6 +571,13 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
         if (leader) {
             constexpr uint32_t IDESC = PAIR ? ((I8_IDESC & ~(31u << 24)) | ((256u >> 4) << 24)) : I8_IDESC;
             uint32_t stage = 0, phase = 0, it = 0, r = 0, rph = 0;
+            // shared-memory matrix descriptors: the high word is a constant and the 14-bit address field of the low word never
+            // carries (shared memory < 256 KB), so a stage's descriptors are one 32-bit add away from the previous stage's and the
+            // four K steps of a stage are compile-time offsets (the 64-bit descriptor arithmetic per K block was ~25 of the ~70
+            // dependent uniform instructions the issuing thread spends per 128 samples)
+            constexpr uint32_t DESC_HI = 64u | (1u << 14) | (2u << 29);          // SBO = 1024 B >> 4, version 1, SWIZZLE_128B
+            const uint32_t desc_lo0 = ((smem_u32(tiles) >> 4) & 0x3FFFu) | (1u << 16);
+            uint32_t desc_lo = desc_lo0;                                         // B operand of the current stage; A = + B_BYTES >> 4
             while (true) {
                 q_wait(r, rph);
                 const uint32_t ti = __shfl_sync(0xffffffffu, q_tile[r].x, 0);
@@ -584,18 +591,19 @@ mi_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
                 for (uint32_t kb = 0; kb < p.num_kb; ++kb) {
                     mbar_wait(&full_bar[stage], phase);
                     tcgen05_fence_after();
-                    const uint32_t sb = smem_u32(tiles + (size_t)stage * Cfg::STAGE);
-                    const uint64_t db = umma_smem_desc(sb), da = umma_smem_desc(sb + Cfg::B_BYTES);
+                    const uint32_t lb = desc_lo, la = desc_lo + (Cfg::B_BYTES >> 4);
                     if (elect_one()) {
 #pragma unroll
                         for (uint32_t k = 0; k < I8_BK / 32; ++k) {      // +32 B along K = +2 in the descriptor's 16-byte address field
-                            if constexpr (PAIR) umma_i8_pair(d_tmem, da + 2u * k, db + 2u * k, IDESC, (kb | k) ? 1u : 0u);
-                            else umma_i8(d_tmem, da + 2u * k, db + 2u * k, IDESC, (kb | k) ? 1u : 0u);
+                            const uint64_t da = ((uint64_t)DESC_HI << 32) | (la + 2u * k), db = ((uint64_t)DESC_HI << 32) | (lb + 2u * k);
+                            if constexpr (PAIR) umma_i8_pair(d_tmem, da, db, IDESC, (kb | k) ? 1u : 0u);
+                            else umma_i8(d_tmem, da, db, IDESC, (kb | k) ? 1u : 0u);
                         }
                         if constexpr (PAIR) umma_commit_pair(&empty_bar[stage]); else umma_commit(&empty_bar[stage]);
                     }
                     __syncwarp();
-                    if (++stage == NST) { stage = 0; phase ^= 1u; }
+                    desc_lo += Cfg::STAGE >> 4;
+                    if (++stage == NST) { stage = 0; phase ^= 1u; desc_lo = desc_lo0; }
                 }
                 if (elect_one()) { if constexpr (PAIR) umma_commit_pair(&tfull_bar[buf]); else umma_commit(&tfull_bar[buf]); }
                 __syncwarp();
